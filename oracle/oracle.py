@@ -1,0 +1,166 @@
+"""ctypes front for the CPU oracle (oracle/liboracle.so).
+
+ORACLE = test infrastructure.  Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+--impl reference legs may import this module; the product package gtsfm_b200 never does.
+
+Each function cites the reference code it restates in oracle_match.c / oracle_verify.c.
+"""
+import ctypes
+import os
+import subprocess
+from typing import Optional, Tuple
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_HERE, "liboracle.so")
+_lib = None
+
+_dp = ctypes.POINTER(ctypes.c_double)
+_fp = ctypes.POINTER(ctypes.c_float)
+_ip = ctypes.POINTER(ctypes.c_int32)
+_up = ctypes.POINTER(ctypes.c_uint32)
+_bp = ctypes.POINTER(ctypes.c_uint8)
+
+
+def build(force: bool = False) -> str:
+    """Compile liboracle.so with the committed Makefile (gcc, a second or two)."""
+    srcs = [os.path.join(_HERE, f) for f in ("oracle_match.c", "oracle_verify.c", "Makefile")]
+    stale = (not os.path.exists(_LIB_PATH)) or any(os.path.getmtime(s) > os.path.getmtime(_LIB_PATH) for s in srcs)
+    if force or stale:
+        subprocess.check_call(["make", "-C", _HERE, "-B", "liboracle.so"], stdout=subprocess.DEVNULL)
+    return _LIB_PATH
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        build()
+        _lib = ctypes.CDLL(_LIB_PATH)
+        _lib.oracle_cv_l2sqr.restype = ctypes.c_float
+        _lib.oracle_sampson_sq.restype = ctypes.c_double
+        _lib.oracle_lo_refine.restype = ctypes.c_double
+    return _lib
+
+
+def _d(a):
+    return a.ctypes.data_as(_dp)
+
+
+def l2sqr(a: np.ndarray, b: np.ndarray) -> np.float32:
+    a = np.ascontiguousarray(a, np.float32)
+    b = np.ascontiguousarray(b, np.float32)
+    return np.float32(lib().oracle_cv_l2sqr(a.ctypes.data_as(_fp), b.ctypes.data_as(_fp), int(a.size)))
+
+
+def knn2(q: np.ndarray, t: np.ndarray) -> Tuple[np.ndarray, np.ndarray, np.ndarray]:
+    """cv2.BFMatcher(NORM_L2).knnMatch(q, t, k=2) as (best idx, best dist, second dist)."""
+    q = np.ascontiguousarray(q, np.float32)
+    t = np.ascontiguousarray(t, np.float32)
+    nq, dim = q.shape
+    idx = np.empty(nq, np.int32)
+    d1 = np.empty(nq, np.float32)
+    d2 = np.empty(nq, np.float32)
+    lib().oracle_knn2(q.ctypes.data_as(_fp), nq, t.ctypes.data_as(_fp), int(t.shape[0]), dim,
+                      idx.ctypes.data_as(_ip), d1.ctypes.data_as(_fp), d2.ctypes.data_as(_fp))
+    return idx, d1, d2
+
+
+def twoway_match(desc1: np.ndarray, desc2: np.ndarray, ratio: Optional[float] = None) -> np.ndarray:
+    """TwoWayMatcher(EUCLIDEAN, ratio).match (twoway_matcher.py:42-144). Empty -> np.array([])."""
+    if desc1.size == 0 or desc2.size == 0:
+        return np.array([])
+    a = np.ascontiguousarray(desc1, np.float32)
+    b = np.ascontiguousarray(desc2, np.float32)
+    n1, dim = a.shape
+    n2 = b.shape[0]
+    out = np.empty((min(n1, n2), 2), np.uint32)
+    k = lib().oracle_twoway_match(a.ctypes.data_as(_fp), n1, b.ctypes.data_as(_fp), n2, dim,
+                                  int(ratio is not None), ctypes.c_double(0.0 if ratio is None else ratio),
+                                  out.ctypes.data_as(_up))
+    if k < 0:
+        raise ValueError("not enough values to unpack (expected 2, got 1)")
+    if k == 0:
+        return np.array([])
+    return out[:k].copy()
+
+
+def sampson_sq(F: np.ndarray, c1: np.ndarray, c2: np.ndarray) -> np.ndarray:
+    """gtsfm/utils/verification.py:170-214."""
+    F = np.ascontiguousarray(F, np.float64)
+    c1 = np.asarray(c1, np.float64)
+    c2 = np.asarray(c2, np.float64)
+    n = c1.shape[0]
+    x1, y1, x2, y2 = (np.ascontiguousarray(v) for v in (c1[:, 0], c1[:, 1], c2[:, 0], c2[:, 1]))
+    out = np.empty(n)
+    lib().oracle_sampson_sq_batch(_d(F), _d(x1), _d(y1), _d(x2), _d(y2), n, _d(out))
+    return out
+
+
+def fivept(p1: np.ndarray, p2: np.ndarray) -> np.ndarray:
+    """Nister 5-point on five normalised correspondences -> (k,3,3) unit-norm essential matrices."""
+    p1 = np.asarray(p1, np.float64)
+    p2 = np.asarray(p2, np.float64)
+    x1, y1, x2, y2 = (np.ascontiguousarray(v) for v in (p1[:, 0], p1[:, 1], p2[:, 0], p2[:, 1]))
+    out = np.zeros(90)
+    n = lib().oracle_fivept(_d(x1), _d(y1), _d(x2), _d(y2), _d(out))
+    return out[: 9 * n].reshape(n, 3, 3).copy()
+
+
+def recover_pose(E: np.ndarray, n1: np.ndarray, n2: np.ndarray):
+    """cv2.recoverPose(E, n1, n2) on normalised coordinates (verification.py:81) -> R, t, good[4]."""
+    E = np.ascontiguousarray(E, np.float64)
+    n1 = np.asarray(n1, np.float64)
+    n2 = np.asarray(n2, np.float64)
+    x1, y1, x2, y2 = (np.ascontiguousarray(v) for v in (n1[:, 0], n1[:, 1], n2[:, 0], n2[:, 1]))
+    R = np.empty(9)
+    t = np.empty(3)
+    good = np.zeros(4, np.int32)
+    lib().oracle_recover_pose(_d(E), _d(x1), _d(y1), _d(x2), _d(y2), int(n1.shape[0]), _d(R), _d(t),
+                              good.ctypes.data_as(_ip))
+    return R.reshape(3, 3), t, good
+
+
+def calibrate(coords: np.ndarray, cal) -> np.ndarray:
+    """normalize_coordinates (features.py:40-50); cal = (f, k1, k2, u0, v0)."""
+    coords = np.asarray(coords, np.float64)
+    out = np.empty((coords.shape[0], 2))
+    x = ctypes.c_double()
+    y = ctypes.c_double()
+    f = lib().oracle_calibrate
+    f.argtypes = [ctypes.c_double] * 7 + [_dp, _dp]
+    for i in range(coords.shape[0]):
+        f(coords[i, 0], coords[i, 1], cal[0], cal[1], cal[2], cal[3], cal[4], ctypes.byref(x), ctypes.byref(y))
+        out[i] = (x.value, y.value)
+    return out
+
+
+def verify_pair(kp1: np.ndarray, kp2: np.ndarray, match_indices: np.ndarray, cal1, cal2, thr_px: float,
+                samples: np.ndarray, lo_iters: int = 20) -> dict:
+    """OpencvVerifierBase.verify + Ransac.estimate_E with an explicit (H,5) sample array.
+
+    Returns a dict: status, E_min, E, mask (M,) uint8, R, t, ninl, best_id, ncand, cost_min, cost.
+    """
+    kp1 = np.ascontiguousarray(kp1, np.float64).reshape(-1, 2)
+    kp2 = np.ascontiguousarray(kp2, np.float64).reshape(-1, 2)
+    mi = np.asarray(match_indices).reshape(-1, 2)
+    M = mi.shape[0]
+    m1 = np.ascontiguousarray(mi[:, 0], np.int32)
+    m2 = np.ascontiguousarray(mi[:, 1], np.int32)
+    c1 = np.asarray(cal1, np.float64)
+    c2 = np.asarray(cal2, np.float64)
+    samples = np.ascontiguousarray(samples, np.int32).reshape(-1, 5)
+    E_min = np.zeros(9)
+    E = np.zeros(9)
+    mask = np.zeros(max(M, 1), np.uint8)
+    R = np.zeros(9)
+    t = np.zeros(3)
+    info = np.zeros(3, np.int32)
+    cost = np.zeros(2)
+    st = lib().oracle_verify_pair(_d(kp1), _d(kp2), m1.ctypes.data_as(_ip), m2.ctypes.data_as(_ip), M,
+                                  _d(c1), _d(c2), ctypes.c_double(thr_px), samples.ctypes.data_as(_ip),
+                                  int(samples.shape[0]), int(lo_iters), _d(E_min), _d(E),
+                                  mask.ctypes.data_as(_bp), _d(R), _d(t), info.ctypes.data_as(_ip), _d(cost))
+    return dict(status=int(st), E_min=E_min.reshape(3, 3), E=E.reshape(3, 3), mask=mask[:M], R=R.reshape(3, 3),
+                t=t, ninl=int(info[0]), best_id=int(info[1]), ncand=int(info[2]), cost_min=float(cost[0]),
+                cost=float(cost[1]))

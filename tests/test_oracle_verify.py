@@ -1,0 +1,141 @@
+"""The CPU oracle for the Ransac verifier: pinned piecewise against cv2 (the library the reference calls),
+against the reference's numpy Sampson code (golden), and against the reference tests' known answers."""
+import os
+
+import cv2
+import numpy as np
+
+from oracle import oracle as O
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def rot_angle_deg(R1, R2):
+    return np.degrees(np.arccos(np.clip((np.trace(R1.T @ R2) - 1) / 2, -1, 1)))
+
+
+def dir_angle_deg(a, b):
+    return np.degrees(np.arccos(np.clip(a @ b / np.linalg.norm(a) / np.linalg.norm(b), -1, 1)))
+
+
+def make_scene(rng, n, noise=0.0, out_frac=0.0):
+    X = rng.uniform(-2, 2, (n, 3)) + [0, 0, 6]
+    R, _ = cv2.Rodrigues(rng.normal(0, 0.2, 3))
+    t = rng.normal(0, 1, 3)
+    t /= np.linalg.norm(t)
+    x1 = X[:, :2] / X[:, 2:]
+    Xc = X @ R.T + t
+    x2 = Xc[:, :2] / Xc[:, 2:]
+    x1 = x1 + rng.normal(0, noise, x1.shape)
+    x2 = x2 + rng.normal(0, noise, x2.shape)
+    no = int(out_frac * n)
+    x2[:no] = rng.uniform(-0.5, 0.5, (no, 2))
+    tx = np.array([[0, -t[2], t[1]], [t[2], 0, -t[0]], [-t[1], t[0], 0]])
+    E = tx @ R
+    return x1, x2, E / np.linalg.norm(E), R, t
+
+
+def test_sampson_known_answers():
+    # tests/utils/test_verification_utils.py:81-111
+    F = np.array([[0, 1, 1], [1, 0, 0], [1, 0, 0]], float)
+    got = O.sampson_sq(F, np.array([[1.0, 3.5], [-2.0, 2.0]]), np.array([[2.0, -1.0], [1.0, 0.0]]))
+    np.testing.assert_allclose(got, [81 / (21.25 + 4.0), 1 / (13.0 + 2.0)], rtol=1e-12)
+    F = np.array([[7.41572822e-09, 4.26005557e-07, -2.61114657e-04], [-4.92270651e-07, 4.29568438e-09, 6.95083578e-04],
+                  [2.89444929e-04, -1.49345006e-05, -4.01395060e-01]])
+    got = O.sampson_sq(F, np.array([[1553, 622], [1553, 622]]), np.array([[357, 662], [818, 517]]))
+    np.testing.assert_allclose(got, [6.744895e-01, 2.397196e03], rtol=1e-3)
+
+
+def test_sampson_vs_reference_numpy_golden():
+    g = np.load(os.path.join(GOLDEN, "sampson.npz"))
+    np.testing.assert_allclose(O.sampson_sq(g["F"], g["c1"], g["c2"]), g["ref"], rtol=1e-12)
+
+
+def test_fivept_vs_cv2_minimal_solver():
+    """cv2.findEssentialMat(RANSAC, maxIters=1) on exactly 5 points returns every real solution stacked."""
+    rng = np.random.default_rng(7)
+    n_total = n_missing = n_gt = 0
+    for _ in range(300):
+        x1, x2, Egt, _, _ = make_scene(rng, 5)
+        Es = O.fivept(x1, x2)
+        h1, h2 = np.c_[x1, np.ones(5)], np.c_[x2, np.ones(5)]
+        for E in Es:
+            assert np.abs(np.einsum("ni,ij,nj->n", h2, E, h1)).max() < 1e-12
+        n_gt += min([min(np.abs(E - Egt).max(), np.abs(E + Egt).max()) for E in Es] + [9.0]) < 1e-6
+        Ecv, _ = cv2.findEssentialMat(x1, x2, np.eye(3), method=cv2.RANSAC, maxIters=1, threshold=1e-3)
+        if Ecv is None:
+            continue
+        for k in range(Ecv.shape[0] // 3):
+            Ec = Ecv[3 * k:3 * k + 3] / np.linalg.norm(Ecv[3 * k:3 * k + 3])
+            n_total += 1
+            n_missing += min([min(np.abs(E - Ec).max(), np.abs(E + Ec).max()) for E in Es] + [9.0]) > 1e-6
+    assert n_gt >= 297
+    assert n_missing <= 0.01 * n_total
+
+
+def test_recover_pose_vs_cv2():
+    rng = np.random.default_rng(11)
+    for _ in range(25):
+        x1, x2, E, _, _ = make_scene(rng, 150, noise=0.002)
+        _, Rc, tc, _ = cv2.recoverPose(E, x1, x2)
+        Ro, to, _ = O.recover_pose(E, x1, x2)
+        np.testing.assert_allclose(Ro, Rc, atol=1e-9)
+        np.testing.assert_allclose(to, tc.ravel(), atol=1e-9)
+
+
+def test_recover_pose_reference_scene():
+    # tests/utils/test_verification_utils.py:17-29 (two-plane scene, tolerance 1e-3)
+    g = np.load(os.path.join(GOLDEN, "verifier_recover_pose.npz"))
+    R, t, _ = O.recover_pose(g["E"], g["kp1"], g["kp2"])
+    np.testing.assert_allclose(R, g["R_gt"], atol=1e-3)
+    np.testing.assert_allclose(t, g["t_gt"], atol=1e-3)
+    np.testing.assert_allclose(R, g["ref_R"], atol=1e-9)
+
+
+def _samples(rng, M, H):
+    return np.stack([rng.choice(M, 5, replace=False) for _ in range(H)]).astype(np.int32)
+
+
+def test_verify_two_plane_scene():
+    # tests/frontend/verifier/test_verifier_base.py:81-100: all 8 matches verified, R/t within 2 deg
+    g = np.load(os.path.join(GOLDEN, "verifier_two_planes.npz"))
+    mi = np.c_[np.arange(8), np.arange(8)]
+    r = O.verify_pair(g["kp1"], g["kp2"], mi, (1, 0, 0, 0, 0), (1, 0, 0, 0, 0), 0.5, _samples(np.random.default_rng(0), 8, 200))
+    assert r["status"] == 0 and r["mask"].all()
+    assert rot_angle_deg(r["R"], g["R_gt"]) < 2 and dir_angle_deg(r["t"], g["t_gt"]) < 2
+
+
+def test_verify_argoverse_pair():
+    # tests/frontend/verifier/test_verifier_argoverse.py:73-119: euler within 1 deg, i1ti2 within 0.01
+    from scipy.spatial.transform import Rotation
+    g = np.load(os.path.join(GOLDEN, "verifier_argoverse.npz"))
+    n = g["kp1"].shape[0]
+    mi = np.c_[np.arange(n), np.arange(n)]
+    r = O.verify_pair(g["kp1"], g["kp2"], mi, g["cal"], g["cal"], 0.5, _samples(np.random.default_rng(0), n, 1024))
+    assert r["status"] == 0
+    i1Ri2 = r["R"].T
+    i1ti2 = -r["R"].T @ r["t"]
+    eul = Rotation.from_matrix(i1Ri2).as_euler("zyx", degrees=True)
+    assert np.allclose(eul, g["gt_euler_zyx_deg"], atol=1.0), eul
+    assert np.allclose(i1ti2, g["gt_i1ti2"], atol=0.01), i1ti2
+
+
+def test_verify_gates():
+    kp = np.random.default_rng(0).uniform(0, 100, (10, 2))
+    for M in (0, 4, 5):
+        mi = np.c_[np.arange(M), np.arange(M)].reshape(-1, 2)
+        r = O.verify_pair(kp, kp, mi, (1, 0, 0, 0, 0), (1, 0, 0, 0, 0), 0.5, np.zeros((1, 5), np.int32))
+        assert r["status"] == 1
+
+
+def test_verify_agrees_with_reference_usac_statistically():
+    """Recorded reference output (black-box USAC_ACCURATE): inlier-set IoU and pose agreement, not bit parity."""
+    g = np.load(os.path.join(GOLDEN, "verifier_synth2000.npz"))
+    M = g["mi"].shape[0]
+    r = O.verify_pair(g["kp1"], g["kp2"], g["mi"], g["cal"], g["cal"], 4.0, _samples(np.random.default_rng(1), M, 1024))
+    assert r["status"] == 0
+    got = set(map(tuple, g["mi"][r["mask"] == 1]))
+    ref = set(map(tuple, g["ref_idx"]))
+    assert len(got & ref) / len(got | ref) > 0.97
+    assert rot_angle_deg(r["R"], g["R_gt"]) < 0.5 and dir_angle_deg(r["t"], g["t_gt"]) < 1.5
+    assert rot_angle_deg(r["R"], g["ref_R"]) < 0.5 and dir_angle_deg(r["t"], g["ref_t"]) < 2.0
