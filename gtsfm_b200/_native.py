@@ -1,0 +1,240 @@
+"""ctypes binding of libgtsfm_b200.so (the C ABI declared in include/gtsfm_b200.h).
+
+The library is the product: there is no Python or CPU fallback.  Importing this module never touches the GPU; creating
+a Context does, and raises GtsfmB200Error when the shared library or a B200 is missing.
+"""
+import ctypes
+import os
+import threading
+from typing import Optional
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libgtsfm_b200.so")
+
+# every symbol include/gtsfm_b200.h declares
+EXPORTS = (
+    "gtsfm_ctx_create", "gtsfm_ctx_destroy", "gtsfm_last_error", "gtsfm_ctx_set_workspace", "gtsfm_kernel_launches",
+    "gtsfm_store_clear", "gtsfm_image_upload", "gtsfm_match_batch", "gtsfm_match_fetch", "gtsfm_ransac_samples",
+    "gtsfm_verify_batch", "gtsfm_match_pair", "gtsfm_verify_pair", "gtsfm_debug_fetch",
+)
+
+OK, E_CUDA, E_ARG, E_NO_DEVICE, E_KNN_UNPACK, E_UNSUPPORTED = range(6)
+V_OK, V_TOO_FEW, V_NO_MODEL = range(3)
+
+
+class GtsfmB200Error(RuntimeError):
+    pass
+
+
+class VerifyParams(ctypes.Structure):
+    _fields_ = [
+        ("threshold_px", ctypes.c_double),
+        ("n_hypotheses", ctypes.c_int),
+        ("lo_iters", ctypes.c_int),
+        ("seed", ctypes.c_uint64),
+        ("pair_keys", ctypes.c_void_p),
+        ("samples", ctypes.c_void_p),
+    ]
+
+
+_lib = None
+_lib_lock = threading.Lock()
+
+
+def lib() -> ctypes.CDLL:
+    """Load the shared library (built by `make -C gtsfm_b200/csrc` or __graft_entry__.build())."""
+    global _lib
+    with _lib_lock:
+        if _lib is None:
+            if not os.path.exists(LIB_PATH):
+                raise GtsfmB200Error(
+                    f"{LIB_PATH} is missing: build it with `make -C gtsfm_b200/csrc` (nvcc, sm_100a). "
+                    "gtsfm_b200 has no CPU fallback."
+                )
+            L = ctypes.CDLL(LIB_PATH)
+            L.gtsfm_last_error.restype = ctypes.c_char_p
+            L.gtsfm_last_error.argtypes = [ctypes.c_void_p]
+            L.gtsfm_kernel_launches.restype = ctypes.c_int64
+            L.gtsfm_kernel_launches.argtypes = [ctypes.c_void_p]
+            L.gtsfm_ctx_create.argtypes = [ctypes.c_int, ctypes.POINTER(ctypes.c_void_p)]
+            L.gtsfm_ctx_destroy.argtypes = [ctypes.c_void_p]
+            L.gtsfm_ctx_destroy.restype = None
+            L.gtsfm_ctx_set_workspace.argtypes = [ctypes.c_void_p, ctypes.c_int64]
+            L.gtsfm_store_clear.argtypes = [ctypes.c_void_p]
+            L.gtsfm_image_upload.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_int,
+                                             ctypes.c_void_p, ctypes.c_void_p]
+            L.gtsfm_match_batch.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_double, ctypes.c_void_p,
+                                            ctypes.POINTER(ctypes.c_int64)]
+            L.gtsfm_match_fetch.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+            L.gtsfm_ransac_samples.argtypes = [ctypes.c_uint64, ctypes.c_uint64, ctypes.c_int, ctypes.c_int, ctypes.c_void_p]
+            L.gtsfm_verify_batch.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p,
+                                             ctypes.POINTER(VerifyParams)] + [ctypes.c_void_p] * 6
+            L.gtsfm_match_pair.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int,
+                                           ctypes.c_int, ctypes.c_double, ctypes.c_void_p, ctypes.POINTER(ctypes.c_int32)]
+            L.gtsfm_verify_pair.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int,
+                                            ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p,
+                                            ctypes.POINTER(VerifyParams)] + [ctypes.c_void_p] * 6
+            L.gtsfm_debug_fetch.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int64]
+            _lib = L
+    return _lib
+
+
+def _ptr(a: Optional[np.ndarray]):
+    return None if a is None else a.ctypes.data_as(ctypes.c_void_p)
+
+
+class Context:
+    """One CUDA device context of the library (not thread-safe; create one per thread / process)."""
+
+    def __init__(self, device: int = 0):
+        self._L = lib()
+        h = ctypes.c_void_p()
+        rc = self._L.gtsfm_ctx_create(int(device), ctypes.byref(h))
+        if rc != OK:
+            raise GtsfmB200Error(f"gtsfm_ctx_create failed ({rc}): {self._L.gtsfm_last_error(None).decode()}")
+        self._h = h
+        self._keep = []   # host arrays whose asynchronous upload may still be in flight
+        self.device = int(device)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.gtsfm_ctx_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc: int):
+        if rc == OK:
+            return
+        msg = self._L.gtsfm_last_error(self._h).decode()
+        if rc == E_KNN_UNPACK:
+            # the reference's own exception type and text (twoway_matcher.py:137)
+            raise ValueError("not enough values to unpack (expected 2, got 1)")
+        if rc == E_UNSUPPORTED:
+            raise NotImplementedError(msg)
+        raise GtsfmB200Error(f"libgtsfm_b200 error {rc}: {msg}")
+
+    @property
+    def kernel_launches(self) -> int:
+        return int(self._L.gtsfm_kernel_launches(self._h))
+
+    def set_workspace(self, nbytes: int):
+        self._check(self._L.gtsfm_ctx_set_workspace(self._h, int(nbytes)))
+
+    # ---- store
+    def clear(self):
+        self._check(self._L.gtsfm_store_clear(self._h))
+        self._keep.clear()
+        self._n_images = 0
+
+    def upload_image(self, image_id: int, desc: Optional[np.ndarray], kps: Optional[np.ndarray] = None, cal=None):
+        """desc (n, dim) float32 or None; kps (n, 2) float64 pixel coordinates or None; cal = (f, k1, k2, u0, v0)."""
+        n = dim = 0
+        if desc is not None and desc.size:
+            desc = np.ascontiguousarray(desc, np.float32)
+            if desc.ndim != 2:
+                raise ValueError("descriptors must be (n, dim)")
+            n, dim = desc.shape
+        else:
+            desc = None
+        if kps is not None:
+            kps = np.ascontiguousarray(kps, np.float64).reshape(-1, 2)
+            if desc is not None and kps.shape[0] != n:
+                raise ValueError("keypoints and descriptors disagree on n")
+            n = kps.shape[0]
+        calv = None if cal is None else np.ascontiguousarray(cal, np.float64)
+        self._keep += [desc, kps, calv]
+        self._check(self._L.gtsfm_image_upload(self._h, int(image_id), _ptr(desc), int(n), int(dim), _ptr(kps), _ptr(calv)))
+
+    # ---- matcher
+    def match_batch(self, pairs: np.ndarray, ratio: Optional[float]):
+        """Returns (matches (total, 2) uint32, offsets (P + 1) int64)."""
+        pairs = np.ascontiguousarray(pairs, np.int32).reshape(-1, 2)
+        P = pairs.shape[0]
+        counts = np.zeros(P, np.int32)
+        total = ctypes.c_int64(0)
+        r = float("nan") if ratio is None else float(ratio)
+        self._check(self._L.gtsfm_match_batch(self._h, _ptr(pairs), P, r, _ptr(counts), ctypes.byref(total)))
+        self._keep.clear()
+        out = np.empty((total.value, 2), np.uint32)
+        self._check(self._L.gtsfm_match_fetch(self._h, _ptr(out)))
+        offsets = np.zeros(P + 1, np.int64)
+        np.cumsum(counts, out=offsets[1:])
+        return out, offsets
+
+    def match_pair(self, d1: np.ndarray, d2: np.ndarray, ratio: Optional[float]) -> np.ndarray:
+        d1 = np.ascontiguousarray(d1, np.float32)
+        d2 = np.ascontiguousarray(d2, np.float32)
+        if d1.size == 0 or d2.size == 0:
+            return np.empty((0, 2), np.uint32)
+        n1, dim = d1.shape
+        n2 = d2.shape[0]
+        out = np.empty((min(n1, n2), 2), np.uint32)
+        cnt = ctypes.c_int32(0)
+        r = float("nan") if ratio is None else float(ratio)
+        self._check(self._L.gtsfm_match_pair(self._h, _ptr(d1), n1, _ptr(d2), n2, dim, r, _ptr(out), ctypes.byref(cnt)))
+        return out[: cnt.value].copy()
+
+    def debug_fetch(self, what: int, count: int, dtype) -> np.ndarray:
+        out = np.zeros(count, dtype)
+        self._check(self._L.gtsfm_debug_fetch(self._h, int(what), _ptr(out), out.nbytes))
+        return out
+
+    # ---- verifier
+    def verify_batch(self, pairs: np.ndarray, params: "VerifyParams", match_idx: Optional[np.ndarray] = None,
+                     match_offsets: Optional[np.ndarray] = None, total: Optional[int] = None):
+        """Verify the last match batch (match_idx None) or caller-supplied matches.  Returns a dict of arrays."""
+        pairs = np.ascontiguousarray(pairs, np.int32).reshape(-1, 2)
+        P = pairs.shape[0]
+        if match_idx is not None:
+            match_idx = np.ascontiguousarray(match_idx, np.uint32).reshape(-1, 2)
+            match_offsets = np.ascontiguousarray(match_offsets, np.int64)
+            total = int(match_offsets[-1])
+        R = np.zeros((P, 9)); t = np.zeros((P, 3)); E = np.zeros((P, 9))
+        ninl = np.zeros(P, np.int32); status = np.zeros(P, np.int32)
+        mask = np.zeros(max(int(total or 0), 1), np.uint8)
+        self._check(self._L.gtsfm_verify_batch(self._h, _ptr(pairs), P, _ptr(match_idx), _ptr(match_offsets), ctypes.byref(params),
+                                               _ptr(R), _ptr(t), _ptr(ninl), _ptr(status), _ptr(mask), _ptr(E)))
+        return dict(R=R.reshape(P, 3, 3), t=t, n_inliers=ninl, status=status, mask=mask[: int(total or 0)], E=E.reshape(P, 3, 3))
+
+    def verify_pair(self, kps1, kps2, match_idx, cal1, cal2, params: "VerifyParams"):
+        kps1 = np.ascontiguousarray(kps1, np.float64).reshape(-1, 2)
+        kps2 = np.ascontiguousarray(kps2, np.float64).reshape(-1, 2)
+        mi = np.ascontiguousarray(match_idx, np.uint32).reshape(-1, 2)
+        c1 = np.ascontiguousarray(cal1, np.float64); c2 = np.ascontiguousarray(cal2, np.float64)
+        M = mi.shape[0]
+        R = np.zeros(9); t = np.zeros(3); E = np.zeros(9)
+        ninl = ctypes.c_int32(0); status = ctypes.c_int32(0)
+        mask = np.zeros(max(M, 1), np.uint8)
+        self._check(self._L.gtsfm_verify_pair(self._h, _ptr(kps1), kps1.shape[0], _ptr(kps2), kps2.shape[0], _ptr(mi), M, _ptr(c1),
+                                              _ptr(c2), ctypes.byref(params), _ptr(R), _ptr(t), ctypes.addressof(ninl),
+                                              ctypes.addressof(status), _ptr(mask), _ptr(E)))
+        return dict(R=R.reshape(3, 3), t=t, n_inliers=ninl.value, status=status.value, mask=mask[:M], E=E.reshape(3, 3))
+
+
+def ransac_samples(seed: int, pair_key: int, n_matches: int, n_hyp: int) -> np.ndarray:
+    """The (n_hyp, 5) sample-index set the device draws for (seed, pair_key): feed it to the CPU oracle."""
+    out = np.zeros((n_hyp, 5), np.int32)
+    rc = lib().gtsfm_ransac_samples(int(seed), int(pair_key), int(n_matches), int(n_hyp), _ptr(out))
+    if rc != OK:
+        raise GtsfmB200Error(f"gtsfm_ransac_samples failed ({rc})")
+    return out
+
+
+_default_ctx = {}
+_default_lock = threading.Lock()
+
+
+def default_context(device: int = 0) -> Context:
+    """Lazily created per-process, per-device context (plugin objects stay picklable: they never hold one)."""
+    key = (os.getpid(), int(device))
+    with _default_lock:
+        if key not in _default_ctx:
+            _default_ctx[key] = Context(device)
+        return _default_ctx[key]

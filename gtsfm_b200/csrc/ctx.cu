@@ -1,0 +1,272 @@
+// Context, descriptor store and image upload (C ABI: gtsfm_ctx_*, gtsfm_store_clear, gtsfm_image_upload).
+#include "ctx.h"
+
+#include <cstring>
+
+namespace g2v {
+
+struct PrepareArgs {
+    const float* src; __nv_bfloat16* bf; uint8_t* u8; __nv_bfloat16* augq; __nv_bfloat16* augt; int* norm_i; uint8_t* valid;
+    int* img_flags; int n, n_pad, dim, kpad;
+};
+cudaError_t launch_prepare(const PrepareArgs& a, cudaStream_t s);
+
+static std::string g_create_error;
+
+cudaError_t DevBuf::reserve(size_t bytes, bool keep, cudaStream_t s)
+{
+    if (bytes <= cap) return cudaSuccess;
+    size_t ncap = cap ? cap : 256;
+    while (ncap < bytes) ncap = ncap + ncap / 2 + 4096;
+    void* np = nullptr;
+    cudaError_t e = cudaMalloc(&np, ncap);
+    if (e != cudaSuccess) return e;
+    if (p) {
+        if (keep) { e = cudaMemcpyAsync(np, p, cap, cudaMemcpyDeviceToDevice, s); if (e != cudaSuccess) return e; }
+        e = cudaStreamSynchronize(s);
+        if (e != cudaSuccess) return e;
+        cudaFree(p);
+    }
+    p = np;
+    cap = ncap;
+    return cudaSuccess;
+}
+void DevBuf::release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+cudaError_t PinnedBuf::reserve(size_t bytes)
+{
+    if (bytes <= cap) return cudaSuccess;
+    if (p) cudaFreeHost(p);
+    p = nullptr; cap = 0;
+    size_t ncap = bytes + bytes / 2 + 4096;
+    cudaError_t e = cudaMallocHost(&p, ncap);
+    if (e == cudaSuccess) cap = ncap;
+    return e;
+}
+void PinnedBuf::release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+
+int fail(gtsfm_ctx* c, int code, const std::string& msg)
+{
+    if (c) c->err = msg; else g_create_error = msg;
+    return code;
+}
+int cuda_fail(gtsfm_ctx* c, cudaError_t e, const char* what)
+{
+    return fail(c, GTSFM_E_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+}
+
+// ---- TMA tensor maps (driver entry point fetched through the runtime: no link-time dependency on libcuda)
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_tiled()
+{
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    return fn;
+}
+static int make_map(gtsfm_ctx* c, CUtensorMap* m, void* base, int inner, long long rows, int box_inner, int box_rows, CUtensorMapSwizzle sw)
+{
+    EncodeTiledFn fn = encode_tiled();
+    if (!fn) return fail(c, GTSFM_E_CUDA, "cuTensorMapEncodeTiled entry point not found");
+    cuuint64_t gdim[2] = {static_cast<cuuint64_t>(inner), static_cast<cuuint64_t>(rows)};
+    cuuint64_t gstr[1] = {static_cast<cuuint64_t>(inner) * 2};
+    cuuint32_t box[2] = {static_cast<cuuint32_t>(box_inner), static_cast<cuuint32_t>(box_rows)};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
+                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(c, GTSFM_E_CUDA, "cuTensorMapEncodeTiled failed with code " + std::to_string(static_cast<int>(r)));
+    return GTSFM_OK;
+}
+
+int store_reserve_rows(gtsfm_ctx* c, long long rows)
+{
+    if (rows <= c->rows_cap) return GTSFM_OK;
+    long long ncap = c->rows_cap ? c->rows_cap : 4096;
+    while (ncap < rows) ncap *= 2;
+    cudaStream_t s = c->stream;
+    G2V_CUDA(c, c->desc_bf16.reserve(static_cast<size_t>(ncap) * c->kpad * 2, true, s));
+    G2V_CUDA(c, c->desc_u8.reserve(static_cast<size_t>(ncap) * c->kpad, true, s));
+    G2V_CUDA(c, c->desc_f32.reserve(static_cast<size_t>(ncap) * c->dim * 4, true, s));
+    G2V_CUDA(c, c->augq.reserve(static_cast<size_t>(ncap) * kAugK * 2, true, s));
+    G2V_CUDA(c, c->augt.reserve(static_cast<size_t>(ncap) * kAugK * 2, true, s));
+    G2V_CUDA(c, c->norm_i.reserve(static_cast<size_t>(ncap) * 4, true, s));
+    G2V_CUDA(c, c->valid.reserve(static_cast<size_t>(ncap), true, s));
+    G2V_CUDA(c, c->kps.reserve(static_cast<size_t>(ncap) * 16, true, s));
+    c->rows_cap = ncap;
+    c->maps_valid = false;
+    return GTSFM_OK;
+}
+
+static int ensure_maps(gtsfm_ctx* c)
+{
+    if (c->maps_valid) return GTSFM_OK;
+    int r;
+    if ((r = make_map(c, &c->tm_desc, c->desc_bf16.p, c->kpad, c->rows_cap, 64, kTileQ, CU_TENSOR_MAP_SWIZZLE_128B))) return r;
+    if ((r = make_map(c, &c->tm_augq, c->augq.p, kAugK, c->rows_cap, kAugK, kTileQ, CU_TENSOR_MAP_SWIZZLE_32B))) return r;
+    if ((r = make_map(c, &c->tm_augt, c->augt.p, kAugK, c->rows_cap, kAugK, kTileQ, CU_TENSOR_MAP_SWIZZLE_32B))) return r;
+    c->maps_valid = true;
+    return GTSFM_OK;
+}
+int store_ensure_maps(gtsfm_ctx* c) { return ensure_maps(c); }
+
+// Read back the per-image flags written by the prepare kernel (integer-valued? number of valid rows).
+int store_sync_flags(gtsfm_ctx* c)
+{
+    if (!c->flags_dirty) return GTSFM_OK;
+    const size_t n = c->images.size();
+    std::vector<int> h(2 * n);
+    G2V_CUDA(c, cudaMemcpyAsync(h.data(), c->img_flags.p, 2 * n * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    G2V_CUDA(c, cudaStreamSynchronize(c->stream));
+    for (size_t i = 0; i < n; ++i) {
+        c->images[i].path = (h[2 * i] & 1) ? 1 : 0;
+        c->images[i].n_valid = h[2 * i + 1];
+    }
+    c->flags_dirty = false;
+    return GTSFM_OK;
+}
+
+}  // namespace g2v
+
+using namespace g2v;
+
+g2v::StoreView gtsfm_ctx::view() const
+{
+    StoreView v;
+    v.desc_bf16 = desc_bf16.as<__nv_bfloat16>();
+    v.desc_u8 = desc_u8.as<uint8_t>();
+    v.desc_f32 = desc_f32.as<float>();
+    v.norm_i = norm_i.as<int>();
+    v.valid = valid.as<uint8_t>();
+    v.kps = kps.as<double2>();
+    v.dim = dim;
+    v.kpad = kpad;
+    return v;
+}
+
+extern "C" {
+
+int gtsfm_ctx_create(int device, gtsfm_ctx** out)
+{
+    if (!out) return fail(nullptr, GTSFM_E_ARG, "out is NULL");
+    *out = nullptr;
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0) return fail(nullptr, GTSFM_E_NO_DEVICE, "no CUDA device (the B200 path has no CPU fallback)");
+    if (device < 0 || device >= n) return fail(nullptr, GTSFM_E_ARG, "device index out of range");
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return fail(nullptr, GTSFM_E_CUDA, "cudaGetDeviceProperties failed");
+    if (prop.major != 10) return fail(nullptr, GTSFM_E_NO_DEVICE, std::string("device is sm_") + std::to_string(prop.major * 10 + prop.minor) + ", the kernels are built for sm_100a only");
+    if (cudaSetDevice(device) != cudaSuccess) return fail(nullptr, GTSFM_E_CUDA, "cudaSetDevice failed");
+    gtsfm_ctx* c = new gtsfm_ctx();
+    c->device = device;
+    c->n_sm = prop.multiProcessorCount;
+    if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return fail(nullptr, GTSFM_E_CUDA, "cudaStreamCreate failed"); }
+    *out = c;
+    return GTSFM_OK;
+}
+
+void gtsfm_ctx_destroy(gtsfm_ctx* c)
+{
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    DevBuf* bufs[] = {&c->desc_bf16, &c->desc_u8, &c->desc_f32, &c->augq, &c->augt, &c->norm_i, &c->valid, &c->kps, &c->img_flags, &c->stage,
+                      &c->d_pairs, &c->rp_v1, &c->rp_v2, &c->rp_g, &c->colraw, &c->row_best, &c->row_d1, &c->row_d2, &c->col_best, &c->col_d1,
+                      &c->col_d2, &c->flag_list, &c->n_flag, &c->keys_scratch, &c->match_slot, &c->match_count, &c->match_offsets,
+                      &c->match_out, &c->d_total};
+    for (DevBuf* b : bufs) b->release();
+    for (DevBuf& b : c->v_bufs) b.release();
+    c->h_pairs.release();
+    c->h_small.release();
+    cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+const char* gtsfm_last_error(const gtsfm_ctx* c) { return c ? c->err.c_str() : g_create_error.c_str(); }
+
+int gtsfm_ctx_set_workspace(gtsfm_ctx* c, int64_t bytes)
+{
+    if (!c || bytes < (64ll << 20)) return fail(c, GTSFM_E_ARG, "workspace must be at least 64 MiB");
+    c->workspace_bytes = bytes;
+    return GTSFM_OK;
+}
+
+int64_t gtsfm_kernel_launches(const gtsfm_ctx* c) { return c ? c->launches : 0; }
+
+int gtsfm_store_clear(gtsfm_ctx* c)
+{
+    if (!c) return GTSFM_E_ARG;
+    cudaSetDevice(c->device);
+    c->images.clear();
+    c->rows_used = 0;
+    c->dim = 0;
+    c->kpad = 0;
+    c->flags_dirty = false;
+    c->maps_valid = false;
+    c->batch_n = 0;
+    c->batch_total = 0;
+    return GTSFM_OK;
+}
+
+int gtsfm_image_upload(gtsfm_ctx* c, int image_id, const float* desc, int n, int dim, const double* kps, const double* cal)
+{
+    if (!c) return GTSFM_E_ARG;
+    cudaSetDevice(c->device);
+    if (image_id != static_cast<int>(c->images.size())) return fail(c, GTSFM_E_ARG, "image ids must be dense and uploaded in order");
+    if (n < 0 || dim < 0 || (n > 0 && dim > 0 && !desc)) return fail(c, GTSFM_E_ARG, "bad descriptor array");
+    if (dim > 4096) return fail(c, GTSFM_E_UNSUPPORTED, "descriptor dimension above 4096");
+    if (c->dim == 0 && dim > 0) {
+        if (c->rows_used != 0) return fail(c, GTSFM_E_ARG, "descriptor dimension changed inside one store");
+        c->dim = dim;
+        c->kpad = (dim + 63) / 64 * 64;
+        c->rows_cap = 0;   // row sizes changed: buffers are re-laid out (no image uploaded yet)
+    }
+    if (dim > 0 && n > 0 && dim != c->dim) return fail(c, GTSFM_E_ARG, "all images of a store must share the descriptor dimension");
+    ImageRec rec{};
+    rec.row0 = static_cast<int>(c->rows_used);
+    rec.n = (dim > 0) ? n : 0;
+    rec.n_kps = kps ? n : 0;
+    rec.dim = dim;
+    rec.path = 1;
+    rec.n_valid = 0;
+    rec.has_kps = kps != nullptr;
+    if (cal) std::memcpy(rec.cal, cal, sizeof(rec.cal)); else { rec.cal[0] = 1; rec.cal[1] = rec.cal[2] = rec.cal[3] = rec.cal[4] = 0; }
+    // keypoint-only images (verification of caller-supplied matches) still need store rows for their coordinates
+    if (c->dim == 0 && kps && n > 0) { c->dim = 1; c->kpad = 64; c->rows_cap = 0; }
+    const int n_rows = ((rec.n > rec.n_kps ? rec.n : rec.n_kps) + kRowPad - 1) / kRowPad * kRowPad;
+    rec.n_pad = n_rows;
+    G2V_CUDA(c, c->img_flags.reserve((c->images.size() + 1) * 2 * sizeof(int), true, c->stream));
+    G2V_CUDA(c, cudaMemsetAsync(c->img_flags.as<int>() + 2 * c->images.size(), 0, 2 * sizeof(int), c->stream));
+    if (n_rows > 0) {
+        int r = store_reserve_rows(c, c->rows_used + n_rows);
+        if (r) return r;
+    }
+    if (rec.n > 0) {
+        float* dst = c->desc_f32.as<float>() + static_cast<long long>(rec.row0) * c->dim;
+        G2V_CUDA(c, cudaMemcpyAsync(dst, desc, static_cast<size_t>(rec.n) * c->dim * 4, cudaMemcpyHostToDevice, c->stream));
+        PrepareArgs a;
+        a.src = dst;
+        a.bf = c->desc_bf16.as<__nv_bfloat16>() + static_cast<long long>(rec.row0) * c->kpad;
+        a.u8 = c->desc_u8.as<uint8_t>() + static_cast<long long>(rec.row0) * c->kpad;
+        a.augq = c->augq.as<__nv_bfloat16>() + static_cast<long long>(rec.row0) * kAugK;
+        a.augt = c->augt.as<__nv_bfloat16>() + static_cast<long long>(rec.row0) * kAugK;
+        a.norm_i = c->norm_i.as<int>() + rec.row0;
+        a.valid = c->valid.as<uint8_t>() + rec.row0;
+        a.img_flags = c->img_flags.as<int>() + 2 * c->images.size();
+        a.n = rec.n; a.n_pad = rec.n_pad; a.dim = c->dim; a.kpad = c->kpad;
+        G2V_CUDA(c, launch_prepare(a, c->stream));
+        ++c->launches;
+        c->flags_dirty = true;
+    }
+    if (kps && n > 0)
+        G2V_CUDA(c, cudaMemcpyAsync(c->kps.as<double2>() + rec.row0, kps, static_cast<size_t>(n) * 16, cudaMemcpyHostToDevice, c->stream));
+    c->images.push_back(rec);
+    c->rows_used += n_rows;
+    return GTSFM_OK;
+}
+
+}  // extern "C"

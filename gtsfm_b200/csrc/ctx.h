@@ -1,0 +1,77 @@
+// Host-side context: descriptor / keypoint store, work buffers, TMA tensor maps.  Internal to the library.
+#pragma once
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/gtsfm_b200.h"
+#include "store.h"
+
+namespace g2v {
+
+// A device buffer that only ever grows (contents are NOT preserved on growth unless keep = true).
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    cudaError_t reserve(size_t bytes, bool keep = false, cudaStream_t s = nullptr);
+    void release();
+    template <typename T> T* as() const { return static_cast<T*>(p); }
+};
+
+struct PinnedBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    cudaError_t reserve(size_t bytes);
+    void release();
+    template <typename T> T* as() const { return static_cast<T*>(p); }
+};
+
+}  // namespace g2v
+
+struct gtsfm_ctx {
+    int device = 0;
+    int n_sm = 0;
+    cudaStream_t stream = nullptr;
+    std::string err;
+    int64_t launches = 0;
+    int64_t workspace_bytes = 4ll << 30;
+
+    // ---- store
+    int dim = 0, kpad = 0;
+    long long rows_used = 0, rows_cap = 0;
+    std::vector<g2v::ImageRec> images;
+    bool flags_dirty = false;
+    g2v::DevBuf desc_bf16, desc_u8, desc_f32, augq, augt, norm_i, valid, kps, img_flags, stage;
+    CUtensorMap tm_desc{}, tm_augq{}, tm_augt{};
+    bool maps_valid = false;
+
+    // ---- matcher work buffers (one chunk of pairs) and batch outputs
+    g2v::DevBuf d_pairs, rp_v1, rp_v2, rp_g, colraw, row_best, row_d1, row_d2, col_best, col_d1, col_d2, flag_list, n_flag;
+    g2v::DevBuf keys_scratch, match_slot, match_count, match_offsets, match_out, d_total;
+    g2v::PinnedBuf h_pairs, h_small;
+    std::vector<g2v::PairDesc> batch_pairs;     // PairDescs of the last match batch (chunk-relative bases)
+    std::vector<int> batch_img;                 // (P, 2) image ids of the last match batch
+    int64_t batch_total = 0;
+    int batch_n = 0;
+
+    // ---- verifier buffers
+    g2v::DevBuf v_bufs[24];
+
+    g2v::StoreView view() const;
+};
+
+namespace g2v {
+int fail(gtsfm_ctx* c, int code, const std::string& msg);
+int cuda_fail(gtsfm_ctx* c, cudaError_t e, const char* what);
+#define G2V_CUDA(ctx, call)                                                 \
+    do {                                                                    \
+        cudaError_t e__ = (call);                                           \
+        if (e__ != cudaSuccess) return g2v::cuda_fail((ctx), e__, #call);   \
+    } while (0)
+
+int store_reserve_rows(gtsfm_ctx* c, long long rows);
+int store_sync_flags(gtsfm_ctx* c);
+}  // namespace g2v

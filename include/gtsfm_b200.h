@@ -1,0 +1,118 @@
+/*
+ * gtsfm_b200 -- C ABI of the B200-native two-view front-end (descriptor matching + essential-matrix RANSAC).
+ *
+ * Drop-in boundary for the reference's plugin API.  Each entry point names the reference interface it replaces
+ * (paths relative to the GTSfM tree):
+ *   MatcherBase.match(...)            gtsfm/frontend/matcher/matcher_base.py:31-63
+ *   TwoWayMatcher.match(...)          gtsfm/frontend/matcher/twoway_matcher.py:42-144
+ *   VerifierBase.verify(...)          gtsfm/frontend/verifier/verifier_base.py:58-82
+ *   OpencvVerifierBase.verify(...)    gtsfm/frontend/verifier/opencv_verifier_base.py:45-109
+ *   Ransac.estimate_E(...)            gtsfm/frontend/verifier/ransac.py:52-82
+ *   recover_relative_pose_from_essential_matrix   gtsfm/utils/verification.py:52-94
+ *   per-pair submission loops         gtsfm/frontend/correspondence_generator/det_desc_correspondence_generator.py:66-85,
+ *                                     gtsfm/two_view_estimator.py:567-587   (one call here per BATCH of pairs)
+ *
+ * Conventions: plain pointers and sizes, host memory unless a name says otherwise, no exceptions; every function
+ * returns 0 on success or a GTSFM_E_* code, and gtsfm_last_error() gives the text.  All buffers are borrowed for the
+ * duration of the call.  A context is bound to one CUDA device and is not thread-safe: use one per thread / process
+ * (the reference runs one matcher per Dask worker process, gtsfm/runner/gtsfm_runner_base.py:288-296).
+ * There is no CPU fallback: without a CUDA device gtsfm_ctx_create fails.
+ */
+#ifndef GTSFM_B200_H
+#define GTSFM_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct gtsfm_ctx gtsfm_ctx;
+
+enum {
+    GTSFM_OK = 0,
+    GTSFM_E_CUDA = 1,        /* a CUDA call failed (text in gtsfm_last_error) */
+    GTSFM_E_ARG = 2,         /* bad argument */
+    GTSFM_E_NO_DEVICE = 3,   /* no usable sm_100 device */
+    GTSFM_E_KNN_UNPACK = 4,  /* ratio test requested with < 2 valid train descriptors: the reference raises
+                                ValueError at twoway_matcher.py:137 ("not enough values to unpack") */
+    GTSFM_E_UNSUPPORTED = 5
+};
+
+/* per-pair verifier status (matches the oracle's VSTAT_* codes) */
+enum {
+    GTSFM_V_OK = 0,
+    GTSFM_V_TOO_FEW = 1,     /* fewer than 6 putative matches -> failure tuple (opencv_verifier_base.py:69-78) */
+    GTSFM_V_NO_MODEL = 2     /* no essential matrix / no inliers */
+};
+
+/* ---- context ------------------------------------------------------------------------------------------------ */
+int gtsfm_ctx_create(int device, gtsfm_ctx** out);
+void gtsfm_ctx_destroy(gtsfm_ctx* ctx);
+const char* gtsfm_last_error(const gtsfm_ctx* ctx);   /* ctx may be NULL: error of the last failed create */
+/* Work-buffer budget in bytes for one chunk of pairs (default 4 GiB). */
+int gtsfm_ctx_set_workspace(gtsfm_ctx* ctx, int64_t bytes);
+/* Number of hand-written kernels launched by this context since creation (bench.py's gpu_launches). */
+int64_t gtsfm_kernel_launches(const gtsfm_ctx* ctx);
+
+/* ---- descriptor / keypoint store (replaces pickling Keypoints + descriptors to every Dask task) ---------------- */
+/* Drop all images. */
+int gtsfm_store_clear(gtsfm_ctx* ctx);
+/* Upload image `image_id` (ids are dense, 0..n-1, in upload order).
+ *   desc  (n, dim) float32 row-major  -- the array MatcherBase.match receives as descriptors_i*
+ *   kps   (n, 2) float64 pixel coordinates (Keypoints.coordinates) or NULL when only matching is wanted
+ *   cal   {f, k1, k2, u0, v0} of the image's Cal3Bundler or NULL */
+int gtsfm_image_upload(gtsfm_ctx* ctx, int image_id, const float* desc, int n, int dim, const double* kps, const double* cal);
+
+/* ---- TwoWayMatcher over a batch of pairs ---------------------------------------------------------------------- */
+/* pairs: (P, 2) int32 image ids (i1, i2).  ratio: Lowe ratio threshold, NaN = ratio test off
+ * (TwoWayMatcher(ratio_test_threshold=None)).  On return counts[p] = number of matches of pair p and *total their
+ * sum; the matches stay on the device until gtsfm_match_fetch / gtsfm_verify_batch. */
+int gtsfm_match_batch(gtsfm_ctx* ctx, const int32_t* pairs, int n_pairs, double ratio, int32_t* counts, int64_t* total);
+/* Copy the matches of the last gtsfm_match_batch to the host: out is (total, 2) uint32, pair after pair in input
+ * order, rows of a pair ordered exactly like TwoWayMatcher.match's return value. */
+int gtsfm_match_fetch(gtsfm_ctx* ctx, uint32_t* out);
+
+/* ---- Ransac verifier (essential-matrix mode) over a batch of pairs --------------------------------------------- */
+/* Hypothesis h of pair-key k draws 5 distinct match rows in [0, M): the counter-based sampler used on the device,
+ * exported so that a CPU oracle can consume the identical (H, 5) index set.  out: (n_hyp, 5) int32. */
+int gtsfm_ransac_samples(uint64_t seed, uint64_t pair_key, int n_matches, int n_hyp, int32_t* out);
+
+typedef struct gtsfm_verify_params {
+    double threshold_px;    /* Ransac(estimation_threshold_px) */
+    int n_hypotheses;       /* 5-point samples per pair (the reference's cv2 default is maxIters = 1000) */
+    int lo_iters;           /* Levenberg-Marquardt local-optimisation iterations on the best model (0 = off) */
+    uint64_t seed;          /* sampler seed; pair key = index of the pair in the call unless pair_keys is given */
+    const uint64_t* pair_keys;   /* optional (P) sampler keys */
+    const int32_t* samples;      /* optional explicit samples (P, n_hypotheses, 5) int32, overrides the sampler */
+} gtsfm_verify_params;
+
+/* Verify the matches produced by the last gtsfm_match_batch (same pairs, same order; nothing is copied back to the
+ * host in between), or, when match_idx != NULL, caller-supplied putative matches:
+ *   match_idx (total, 2) uint32, match_offsets (P + 1) int64 row offsets.
+ * Outputs (any may be NULL): R (P, 9) row-major i2Ri1, t (P, 3) unit i2Ui1, n_inliers (P), status (P) GTSFM_V_*,
+ * inlier_mask (total) uint8 aligned with the match rows (v_corr_idxs = match rows with mask 1,
+ * inlier_ratio = n_inliers / M, opencv_verifier_base.py:98-101), E (P, 9) the final essential matrix. */
+int gtsfm_verify_batch(gtsfm_ctx* ctx, const int32_t* pairs, int n_pairs, const uint32_t* match_idx,
+                       const int64_t* match_offsets, const gtsfm_verify_params* params, double* R, double* t,
+                       int32_t* n_inliers, int32_t* status, uint8_t* inlier_mask, double* E);
+
+/* ---- single-pair conveniences used by the MatcherBase / VerifierBase plugin classes ---------------------------- */
+/* TwoWayMatcher.match for one pair from host arrays.  out capacity: min(n1, n2) rows of 2 uint32. */
+int gtsfm_match_pair(gtsfm_ctx* ctx, const float* desc1, int n1, const float* desc2, int n2, int dim, double ratio,
+                     uint32_t* out, int32_t* count);
+/* OpencvVerifierBase.verify for one pair from host arrays (kps in pixels, cal = {f,k1,k2,u0,v0}). */
+int gtsfm_verify_pair(gtsfm_ctx* ctx, const double* kps1, int n1, const double* kps2, int n2, const uint32_t* match_idx,
+                      int n_matches, const double* cal1, const double* cal2, const gtsfm_verify_params* params, double* R,
+                      double* t, int32_t* n_inliers, int32_t* status, uint8_t* inlier_mask, double* E);
+
+/* ---- diagnostics (tests and tools only) --------------------------------------------------------------------------- */
+/* Copy an internal device buffer of the last chunk to the host.  what: 0 rp_v1 (f32), 1 rp_v2 (f32), 2 rp_g (u8),
+ * 3 colraw (f32), 4 row_best (i32), 5 row_d1 (f32), 6 row_d2 (f32), 7 col_best (i32), 8 col_d1 (f32), 9 col_d2 (f32),
+ * 10 number of rows / columns flagged for the exact re-scan (i32). */
+int gtsfm_debug_fetch(gtsfm_ctx* ctx, int what, void* dst, int64_t bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GTSFM_B200_H */

@@ -1,0 +1,135 @@
+"""GPU parity of the batched TwoWayMatcher against the CPU oracle and the reference's golden vectors (bit-exact)."""
+import glob
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+TAGS = (("none", None), ("r08", 0.8), ("r095", 0.95))
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    import gtsfm_b200
+    c = gtsfm_b200.Context(0)
+    yield c
+    c.close()
+
+
+def sift_like(rng, n, dim=128, protos=None, noise=0.03):
+    """integer-valued float32 descriptors in [0,255] with L2 norm ~512."""
+    p = np.abs(rng.standard_normal((n, dim))) if protos is None else protos
+    p = p / np.linalg.norm(p, axis=1, keepdims=True)
+    p = np.minimum(p, 0.2)
+    p = p / np.linalg.norm(p, axis=1, keepdims=True)
+    p = p + rng.normal(0, noise, p.shape)
+    p = np.abs(p) / np.linalg.norm(p, axis=1, keepdims=True)
+    return np.clip(np.rint(p * 512), 0, 255).astype(np.float32)
+
+
+def check(got, want):
+    if want.shape[0] == 0:
+        assert got.shape[0] == 0
+    else:
+        assert got.dtype == np.uint32
+        np.testing.assert_array_equal(got, want)
+
+
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLDEN, "matcher_*.npz"))), ids=os.path.basename)
+def test_golden_vectors(ctx, path):
+    g = np.load(path)
+    for tag, ratio in TAGS:
+        if "raises_" + tag in g:
+            with pytest.raises(ValueError):
+                ctx.match_pair(g["d1"], g["d2"], ratio)
+            continue
+        check(ctx.match_pair(g["d1"], g["d2"], ratio), g["m_" + tag])
+
+
+def test_lund_door_pair(ctx):
+    g = np.load(os.path.join(GOLDEN, "lund_door_pair.npz"))
+    d0, d1 = g["d0_u8"].astype(np.float32), g["d1_u8"].astype(np.float32)
+    check(ctx.match_pair(d0, d1, 0.8), g["m_r08"])
+    check(ctx.match_pair(d0, d1, None), g["m_none"])
+
+
+@pytest.mark.parametrize("n1,n2", [(1000, 900), (256, 256), (300, 2049), (2500, 130), (5, 3)])
+def test_integer_path_vs_oracle(ctx, n1, n2):
+    from oracle import oracle as O
+    rng = np.random.default_rng(n1 * 7 + n2)
+    shared = min(n1, n2) // 2
+    protos = np.abs(rng.standard_normal((shared, 128)))
+    d1 = np.concatenate([sift_like(rng, shared, protos=protos), sift_like(rng, n1 - shared)])[rng.permutation(n1)]
+    d2 = np.concatenate([sift_like(rng, shared, protos=protos), sift_like(rng, n2 - shared)])[rng.permutation(n2)]
+    for ratio in (None, 0.8):
+        want = O.twoway_match(d1, d2, ratio)
+        check(ctx.match_pair(d1, d2, ratio), want.reshape(-1, 2))
+
+
+def test_integer_ties_and_duplicates(ctx):
+    """Duplicate descriptors force equal distances: lowest-index tie-breaks and the stable output order must hold."""
+    from oracle import oracle as O
+    rng = np.random.default_rng(5)
+    base = sift_like(rng, 200)
+    d1 = np.concatenate([base, base[:50], sift_like(rng, 100)])
+    d2 = np.concatenate([base[::-1], base[:30], sift_like(rng, 77)])
+    for ratio in (None, 0.8, 1.0):
+        check(ctx.match_pair(d1, d2, ratio), O.twoway_match(d1, d2, ratio).reshape(-1, 2))
+
+
+def test_integer_small_values_dim64(ctx):
+    from oracle import oracle as O
+    rng = np.random.default_rng(9)
+    d1 = rng.integers(0, 4, (700, 64)).astype(np.float32)
+    d2 = rng.integers(0, 4, (650, 64)).astype(np.float32)
+    for ratio in (None, 0.9):
+        check(ctx.match_pair(d1, d2, ratio), O.twoway_match(d1, d2, ratio).reshape(-1, 2))
+
+
+def test_float_path_vs_oracle(ctx):
+    from oracle import oracle as O
+    rng = np.random.default_rng(3)
+    for dim in (1, 37, 128, 256):
+        d1 = rng.standard_normal((400, dim)).astype(np.float32)
+        d2 = (d1[rng.permutation(400)[:350]] + 0.1 * rng.standard_normal((350, dim))).astype(np.float32)
+        for ratio in (None, 0.8):
+            check(ctx.match_pair(d1, d2, ratio), O.twoway_match(d1, d2, ratio).reshape(-1, 2))
+
+
+def test_nan_rows_integer_path(ctx):
+    from oracle import oracle as O
+    rng = np.random.default_rng(4)
+    d1, d2 = sift_like(rng, 600), sift_like(rng, 500)
+    d2[:200] = d1[100:300]
+    d1[[3, 150, 599]] = np.nan
+    d2[[0, 120]] = np.nan
+    for ratio in (None, 0.8):
+        check(ctx.match_pair(d1, d2, ratio), O.twoway_match(d1, d2, ratio).reshape(-1, 2))
+
+
+def test_empty_inputs(ctx):
+    e = np.zeros((0, 128), np.float32)
+    d = np.ones((4, 128), np.float32)
+    for a, b in ((e, d), (d, e), (e, e)):
+        assert ctx.match_pair(a, b, None).shape[0] == 0
+
+
+def test_batch_of_pairs_matches_single_pair_calls(ctx):
+    """Ragged batch, tiny workspace so several chunks are used; results must equal one-pair-at-a-time results."""
+    from oracle import oracle as O
+    rng = np.random.default_rng(11)
+    sizes = [700, 1300, 256, 90, 2100, 513]
+    protos = np.abs(rng.standard_normal((2100, 128)))
+    imgs = [sift_like(rng, n, protos=protos[rng.permutation(2100)[:n]]) for n in sizes]
+    pairs = np.array([(i, j) for i in range(len(sizes)) for j in range(i + 1, len(sizes))], np.int32)
+    ctx.set_workspace(64 << 20)
+    ctx.clear()
+    for k, d in enumerate(imgs):
+        ctx.upload_image(k, d)
+    m, off = ctx.match_batch(pairs, 0.8)
+    ctx.set_workspace(4 << 30)
+    for p, (i, j) in enumerate(pairs):
+        check(m[off[p]:off[p + 1]], O.twoway_match(imgs[i], imgs[j], 0.8).reshape(-1, 2))
