@@ -54,6 +54,7 @@ struct gtsfm_ctx {
     g2v::PinnedBuf h_pairs, h_small;
     std::vector<g2v::PairDesc> batch_pairs;     // PairDescs of the last match batch (chunk-relative bases)
     std::vector<int> batch_img;                 // (P, 2) image ids of the last match batch
+    std::vector<int> batch_counts;              // matches per pair of the last match batch
     int64_t batch_total = 0;
     int batch_n = 0;
 

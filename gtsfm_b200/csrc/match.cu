@@ -141,6 +141,7 @@ int gtsfm_match_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, double ra
     G2V_CUDA(c, cudaStreamSynchronize(s));
     long long sum = 0;
     const int* hc = c->h_small.as<int>();
+    c->batch_counts.assign(hc, hc + n_pairs);
     for (int p = 0; p < n_pairs; ++p) { if (counts) counts[p] = hc[p]; sum += hc[p]; }
     c->batch_n = n_pairs;
     c->batch_total = sum;

@@ -76,19 +76,31 @@ __global__ void __launch_bounds__(256) exact_scan_kernel(StoreView st, MatchWork
     int i1[4];
 #pragma unroll
     for (int u = 0; u < 4; ++u) { f1[u] = FLT_MAX; f2[u] = FLT_MAX; i1[u] = INT_MAX; }
-    const bool warp_active = warp * 4 < cnt;
+    const bool single = mode == 1;                     // one scan row: the 8 warps split each tile's rows
+    const bool warp_active = single || warp * 4 < cnt;
+    const int qrow0 = single ? 0 : warp * 4;
+    const int it0 = single ? warp * (kScanTile / 16) : 0, it1 = single ? (warp + 1) * (kScanTile / 16) : kScanTile / 2;
 
     for (int t0 = 0; t0 < other_n; t0 += kScanTile) {
         __syncthreads();
         const int tn = min(kScanTile, other_n - t0);
-        for (int k = threadIdx.x; k < tn * dim; k += blockDim.x) {
-            const int r = k / dim, c = k - r * dim;
-            stile[r * tstride + c] = st.desc_f32[static_cast<long long>(other_base + t0 + r) * dim + c];
+        if ((dim & 3) == 0) {
+            const int d4 = dim >> 2;
+            for (int k = threadIdx.x; k < tn * d4; k += blockDim.x) {
+                const int r = k / d4, c = (k - r * d4) * 4;
+                *reinterpret_cast<float4*>(stile + r * tstride + c) =
+                    *reinterpret_cast<const float4*>(st.desc_f32 + static_cast<long long>(other_base + t0 + r) * dim + c);
+            }
+        } else {
+            for (int k = threadIdx.x; k < tn * dim; k += blockDim.x) {
+                const int r = k / dim, c = k - r * dim;
+                stile[r * tstride + c] = st.desc_f32[static_cast<long long>(other_base + t0 + r) * dim + c];
+            }
         }
         if (threadIdx.x < kScanTile) svalid[threadIdx.x] = threadIdx.x < tn ? st.valid[other_base + t0 + threadIdx.x] : 0;
         __syncthreads();
         if (!warp_active) continue;
-        for (int it = 0; it < kScanTile / 2; ++it) {
+        for (int it = it0; it < it1; ++it) {
             const int jr = 2 * it + h;
             const float* trow = stile + jr * tstride;
             float acc[4] = {0.f, 0.f, 0.f, 0.f};
@@ -96,7 +108,7 @@ __global__ void __launch_bounds__(256) exact_scan_kernel(StoreView st, MatchWork
                 const float tv = trow[16 * b + r16];
 #pragma unroll
                 for (int u = 0; u < 4; ++u) {
-                    const float d = __fsub_rn(sq[(warp * 4 + u) * dim + 16 * b + r16], tv);
+                    const float d = __fsub_rn(sq[(qrow0 + u) * dim + 16 * b + r16], tv);
                     acc[u] = __fadd_rn(acc[u], __fmul_rn(d, d));
                 }
             }
@@ -110,7 +122,7 @@ __global__ void __launch_bounds__(256) exact_scan_kernel(StoreView st, MatchWork
                 const float s2 = __shfl_sync(0xffffffffu, s, 2, 16), s3 = __shfl_sync(0xffffffffu, s, 3, 16);
                 float d = __fadd_rn(__fadd_rn(s0, s2), __fadd_rn(s1, s3));
                 for (int e = 16 * nblk; e < dim; ++e) {
-                    const float t = __fsub_rn(sq[(warp * 4 + u) * dim + e], trow[e]);
+                    const float t = __fsub_rn(sq[(qrow0 + u) * dim + e], trow[e]);
                     d = __fadd_rn(d, __fmul_rn(t, t));
                 }
                 const float f = sqrtf(d);
@@ -131,6 +143,30 @@ __global__ void __launch_bounds__(256) exact_scan_kernel(StoreView st, MatchWork
         const float lose = take ? f1[u] : o1;
         f2[u] = fminf(fminf(f2[u], o2), lose);
         if (take) { f1[u] = o1; i1[u] = oi; }
+        if (single) {
+            // merge the 8 warps' partial results for the single scan row (u == 0) through shared memory
+            __shared__ float m_f1[8], m_f2[8];
+            __shared__ int m_i1[8];
+            if (u == 0) {
+                if (lane == 0) { m_f1[warp] = f1[0]; m_f2[warp] = f2[0]; m_i1[warp] = i1[0]; }
+                __syncthreads();
+                if (threadIdx.x == 0) {
+                    float b1 = m_f1[0], b2 = m_f2[0];
+                    int bi = m_i1[0];
+                    for (int k = 1; k < 8; ++k) {
+                        const bool tk = (m_f1[k] < b1) || (m_f1[k] == b1 && m_i1[k] < bi);
+                        const float ls = tk ? b1 : m_f1[k];
+                        b2 = fminf(fminf(b2, m_f2[k]), ls);
+                        if (tk) { b1 = m_f1[k]; bi = m_i1[k]; }
+                    }
+                    const bool valid = st.valid[scan_base + row0] && bi != INT_MAX;
+                    o_best[out0] = valid ? bi : -1;
+                    o_d1[out0] = valid ? b1 : FLT_MAX;
+                    o_d2[out0] = valid ? b2 : FLT_MAX;
+                }
+            }
+            continue;
+        }
         const int r = warp * 4 + u;
         if (lane == 0 && r < cnt) {
             const bool valid = st.valid[scan_base + row0 + r] && i1[u] != INT_MAX;

@@ -1,10 +1,159 @@
-// placeholder until the verifier kernels land (next commit)
+// Host orchestration of the batched Ransac verifier (C ABI: gtsfm_ransac_samples / gtsfm_verify_batch /
+// gtsfm_verify_pair).  Replaces the one-Dask-task-per-pair loop of gtsfm/two_view_estimator.py:569-584 for the
+// verifier part of run_2view (two_view_estimator.py:290-296).
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
 #include "ctx.h"
+#include "verify_types.h"
+
+namespace g2v {
+struct VerifyBufs {
+    const VPair* pairs; const uint2* match; double4* corr_d; float4* corr_f; float* E32; unsigned char* ncand; float* cost;
+    const int* samples; double* R; double* t; double* E; int* ninl; int* status; unsigned char* mask;
+};
+cudaError_t launch_verify_chunk(const StoreView& st, const VerifyBufs& b, const VerifyDims& d, int n_pairs, int max_m, cudaStream_t s);
+}  // namespace g2v
+
 using namespace g2v;
+
 extern "C" {
-int gtsfm_ransac_samples(uint64_t, uint64_t, int, int, int32_t*) { return GTSFM_E_UNSUPPORTED; }
-int gtsfm_verify_batch(gtsfm_ctx* c, const int32_t*, int, const uint32_t*, const int64_t*, const gtsfm_verify_params*, double*, double*,
-                       int32_t*, int32_t*, uint8_t*, double*) { return fail(c, GTSFM_E_UNSUPPORTED, "verifier not built"); }
-int gtsfm_verify_pair(gtsfm_ctx* c, const double*, int, const double*, int, const uint32_t*, int, const double*, const double*,
-                      const gtsfm_verify_params*, double*, double*, int32_t*, int32_t*, uint8_t*, double*) { return fail(c, GTSFM_E_UNSUPPORTED, "verifier not built"); }
+
+int gtsfm_ransac_samples(uint64_t seed, uint64_t pair_key, int n_matches, int n_hyp, int32_t* out)
+{
+    if (!out || n_matches < 5 || n_hyp < 0) return GTSFM_E_ARG;
+    for (int h = 0; h < n_hyp; ++h) sample5(seed, pair_key, static_cast<uint32_t>(h), static_cast<uint32_t>(n_matches), out + 5 * h);
+    return GTSFM_OK;
 }
+
+int gtsfm_verify_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, const uint32_t* match_idx, const int64_t* match_offsets,
+                       const gtsfm_verify_params* prm, double* R, double* t, int32_t* n_inliers, int32_t* status,
+                       uint8_t* inlier_mask, double* E)
+{
+    if (!c || !prm || n_pairs < 0 || (n_pairs > 0 && !pairs)) return fail(c, GTSFM_E_ARG, "bad arguments");
+    cudaSetDevice(c->device);
+    if (n_pairs == 0) return GTSFM_OK;
+    if (prm->n_hypotheses <= 0 || prm->n_hypotheses > (1 << 20)) return fail(c, GTSFM_E_ARG, "n_hypotheses out of range");
+    if (!(prm->threshold_px > 0)) return fail(c, GTSFM_E_ARG, "threshold_px must be positive");
+    cudaStream_t s = c->stream;
+    const int n_img = static_cast<int>(c->images.size());
+    const int H = prm->n_hypotheses;
+
+    // ---- match rows: the device-resident result of the last match batch, or the caller's arrays
+    std::vector<long long> off(n_pairs + 1, 0);
+    if (match_idx == nullptr && match_offsets == nullptr) {
+        if (c->batch_n != n_pairs) return fail(c, GTSFM_E_ARG, "verify_batch without matches needs the pairs of the last match_batch");
+        for (int p = 0; p < n_pairs; ++p) {
+            if (c->batch_img[2 * p] != pairs[2 * p] || c->batch_img[2 * p + 1] != pairs[2 * p + 1])
+                return fail(c, GTSFM_E_ARG, "pair list differs from the last match_batch");
+            off[p + 1] = off[p] + c->batch_counts[p];
+        }
+    } else {
+        if (!match_offsets) return fail(c, GTSFM_E_ARG, "match_offsets is NULL");
+        for (int p = 0; p <= n_pairs; ++p) off[p] = match_offsets[p];
+        for (int p = 0; p < n_pairs; ++p) if (off[p + 1] < off[p]) return fail(c, GTSFM_E_ARG, "match_offsets must be non-decreasing");
+        if (off[n_pairs] > 0 && !match_idx) return fail(c, GTSFM_E_ARG, "match_idx is NULL");
+        G2V_CUDA(c, c->match_out.reserve(8 * static_cast<size_t>(off[n_pairs] + 1), false, s));
+        if (off[n_pairs] > 0)
+            G2V_CUDA(c, cudaMemcpyAsync(c->match_out.p, match_idx, 8 * static_cast<size_t>(off[n_pairs]), cudaMemcpyHostToDevice, s));
+        c->batch_n = 0;   // the device match buffer no longer belongs to a match batch
+    }
+    const long long total = off[n_pairs];
+
+    // ---- per-pair records
+    std::vector<VPair> vps(n_pairs);
+    int max_m = 0;
+    for (int p = 0; p < n_pairs; ++p) {
+        const int a = pairs[2 * p], b = pairs[2 * p + 1];
+        if (a < 0 || b < 0 || a >= n_img || b >= n_img) return fail(c, GTSFM_E_ARG, "pair names an image that was not uploaded");
+        const ImageRec& i1 = c->images[a];
+        const ImageRec& i2 = c->images[b];
+        VPair v{};
+        v.m0 = off[p];
+        v.M = static_cast<int>(off[p + 1] - off[p]);
+        // opencv_verifier_base.py:69-78: fewer than 5 (then fewer than 6) correspondences -> failure tuple
+        v.status = v.M < 6 ? GTSFM_V_TOO_FEW : GTSFM_V_OK;
+        if (v.status == GTSFM_V_OK && (!i1.has_kps || !i2.has_kps)) return fail(c, GTSFM_E_ARG, "verification needs keypoints for every image of the pair list");
+        v.row1 = i1.row0; v.row2 = i2.row0;
+        std::memcpy(v.cal1, i1.cal, sizeof(v.cal1));
+        std::memcpy(v.cal2, i2.cal, sizeof(v.cal2));
+        const double fx = std::max(i1.cal[0], i2.cal[0]);                 // opencv_verifier_base.py:86
+        const double thr = prm->threshold_px / fx;                         // ransac.py:79
+        v.thr2 = thr * thr;
+        v.key = prm->pair_keys ? prm->pair_keys[p] : static_cast<unsigned long long>(p);
+        max_m = std::max(max_m, v.M);
+        vps[p] = v;
+    }
+
+    // ---- buffers
+    DevBuf* vb = c->v_bufs;
+    const size_t per_pair = static_cast<size_t>(H) * (9 * 10 * 4 + 1 + 10 * 4);
+    int chunk = static_cast<int>(std::max<long long>(1, std::min<long long>(c->workspace_bytes / static_cast<long long>(per_pair), 32768)));
+    chunk = std::min(chunk, n_pairs);
+    G2V_CUDA(c, vb[0].reserve(sizeof(VPair) * n_pairs, false, s));
+    G2V_CUDA(c, vb[1].reserve(32 * static_cast<size_t>(total + 1), false, s));
+    G2V_CUDA(c, vb[2].reserve(16 * static_cast<size_t>(total + 1), false, s));
+    G2V_CUDA(c, vb[3].reserve(static_cast<size_t>(chunk) * H * 360, false, s));
+    G2V_CUDA(c, vb[4].reserve(static_cast<size_t>(chunk) * H, false, s));
+    G2V_CUDA(c, vb[5].reserve(static_cast<size_t>(chunk) * H * 40, false, s));
+    G2V_CUDA(c, vb[7].reserve(72 * static_cast<size_t>(n_pairs), false, s));
+    G2V_CUDA(c, vb[8].reserve(24 * static_cast<size_t>(n_pairs), false, s));
+    G2V_CUDA(c, vb[9].reserve(72 * static_cast<size_t>(n_pairs), false, s));
+    G2V_CUDA(c, vb[10].reserve(4 * static_cast<size_t>(n_pairs), false, s));
+    G2V_CUDA(c, vb[11].reserve(4 * static_cast<size_t>(n_pairs), false, s));
+    G2V_CUDA(c, vb[12].reserve(static_cast<size_t>(total + 1), false, s));
+    G2V_CUDA(c, c->h_pairs.reserve(sizeof(VPair) * n_pairs));
+    std::memcpy(c->h_pairs.p, vps.data(), sizeof(VPair) * n_pairs);
+    G2V_CUDA(c, cudaMemcpyAsync(vb[0].p, c->h_pairs.p, sizeof(VPair) * n_pairs, cudaMemcpyHostToDevice, s));
+    if (prm->samples) {
+        const size_t nb = static_cast<size_t>(n_pairs) * H * 5 * 4;
+        G2V_CUDA(c, vb[6].reserve(nb, false, s));
+        G2V_CUDA(c, cudaMemcpyAsync(vb[6].p, prm->samples, nb, cudaMemcpyHostToDevice, s));
+    }
+    const StoreView st = c->view();
+    VerifyDims d{H, prm->lo_iters, prm->seed};
+    for (int p0 = 0; p0 < n_pairs; p0 += chunk) {
+        const int np = std::min(chunk, n_pairs - p0);
+        VerifyBufs b{};
+        b.pairs = vb[0].as<VPair>() + p0;
+        b.match = c->match_out.as<uint2>();
+        b.corr_d = vb[1].as<double4>(); b.corr_f = vb[2].as<float4>();
+        b.E32 = vb[3].as<float>(); b.ncand = vb[4].as<unsigned char>(); b.cost = vb[5].as<float>();
+        b.samples = prm->samples ? vb[6].as<int>() + static_cast<long long>(p0) * H * 5 : nullptr;
+        b.R = vb[7].as<double>() + 9ll * p0; b.t = vb[8].as<double>() + 3ll * p0; b.E = vb[9].as<double>() + 9ll * p0;
+        b.ninl = vb[10].as<int>() + p0; b.status = vb[11].as<int>() + p0; b.mask = vb[12].as<unsigned char>();
+        int mm = 0;
+        for (int p = p0; p < p0 + np; ++p) mm = std::max(mm, vps[p].M);
+        G2V_CUDA(c, launch_verify_chunk(st, b, d, np, mm, s));
+        c->launches += 4;
+    }
+    // ---- results back to the host
+    if (R) G2V_CUDA(c, cudaMemcpyAsync(R, vb[7].p, 72 * static_cast<size_t>(n_pairs), cudaMemcpyDeviceToHost, s));
+    if (t) G2V_CUDA(c, cudaMemcpyAsync(t, vb[8].p, 24 * static_cast<size_t>(n_pairs), cudaMemcpyDeviceToHost, s));
+    if (E) G2V_CUDA(c, cudaMemcpyAsync(E, vb[9].p, 72 * static_cast<size_t>(n_pairs), cudaMemcpyDeviceToHost, s));
+    if (n_inliers) G2V_CUDA(c, cudaMemcpyAsync(n_inliers, vb[10].p, 4 * static_cast<size_t>(n_pairs), cudaMemcpyDeviceToHost, s));
+    if (status) G2V_CUDA(c, cudaMemcpyAsync(status, vb[11].p, 4 * static_cast<size_t>(n_pairs), cudaMemcpyDeviceToHost, s));
+    if (inlier_mask && total > 0) G2V_CUDA(c, cudaMemcpyAsync(inlier_mask, vb[12].p, static_cast<size_t>(total), cudaMemcpyDeviceToHost, s));
+    G2V_CUDA(c, cudaStreamSynchronize(s));
+    return GTSFM_OK;
+}
+
+int gtsfm_verify_pair(gtsfm_ctx* c, const double* kps1, int n1, const double* kps2, int n2, const uint32_t* match_idx, int n_matches,
+                      const double* cal1, const double* cal2, const gtsfm_verify_params* prm, double* R, double* t,
+                      int32_t* n_inliers, int32_t* status, uint8_t* inlier_mask, double* E)
+{
+    if (!c || !prm || n_matches < 0 || !cal1 || !cal2) return fail(c, GTSFM_E_ARG, "bad arguments");
+    for (int k = 0; k < n_matches; ++k)
+        if (match_idx[2 * k] >= static_cast<uint32_t>(n1) || match_idx[2 * k + 1] >= static_cast<uint32_t>(n2))
+            return fail(c, GTSFM_E_ARG, "match index out of range");
+    int r;
+    if ((r = gtsfm_store_clear(c))) return r;
+    if ((r = gtsfm_image_upload(c, 0, nullptr, n1, 0, kps1, cal1))) return r;
+    if ((r = gtsfm_image_upload(c, 1, nullptr, n2, 0, kps2, cal2))) return r;
+    const int32_t pr[2] = {0, 1};
+    const int64_t off[2] = {0, n_matches};
+    return gtsfm_verify_batch(c, pr, 1, match_idx, off, prm, R, t, n_inliers, status, inlier_mask, E);
+}
+
+}  // extern "C"

@@ -1,0 +1,511 @@
+// K3-K7 -- batched essential-matrix RANSAC of the reference's Ransac verifier
+// (gtsfm/frontend/verifier/ransac.py:52-82, opencv_verifier_base.py:45-109, utils/verification.py:52-94).
+//
+//   K3 gather_normalize   match rows -> normalised correspondences (fp64 master + fp32 copy)   features.py:40-50
+//   K4 solve              one 5-point hypothesis per thread, fp64                              (cv2 USAC's minimal solver)
+//   K5 score              MSAC cost sum(min(sampson^2, thr^2)) of every candidate over all correspondences, fp32,
+//                         correspondences staged in shared memory, one candidate per warp, warp-shuffle reduction
+//   K6 finalize           best candidates re-solved and re-scored in fp64, Levenberg-Marquardt local optimisation,
+//                         final mask sampson^2 < thr^2 (fp64)                                  verification.py:170-214
+//   K7 (inside finalize)  pose recovery: SVD of E, four (R,t) candidates, DLT cheirality vote   verification.py:81
+#include <cfloat>
+
+#include "store.h"
+#include "verify_fivept.cuh"
+#include "verify_types.h"
+
+namespace g2v {
+
+struct VerifyBufs {
+    const VPair* pairs;        // [P] (this chunk)
+    const uint2* match;        // batch-wide (i1, i2)
+    double4* corr_d;           // [total] x1 y1 x2 y2 (normalised)
+    float4* corr_f;            // [total]
+    float* E32;                // [P][H][10][9]
+    unsigned char* ncand;      // [P][H]
+    float* cost;               // [P][H][10]
+    const int* samples;        // optional explicit [P][H][5] (chunk-relative) or nullptr
+    // outputs (batch-wide pointers already offset to this chunk's first pair)
+    double* R; double* t; double* E; int* ninl; int* status; unsigned char* mask;
+};
+
+// ---------------------------------------------------------------------------------------------------------------- K3
+__global__ void __launch_bounds__(256) gather_normalize_kernel(StoreView st, VerifyBufs b, int n_pairs)
+{
+    const int p = blockIdx.y;
+    if (p >= n_pairs) return;
+    const VPair& vp = b.pairs[p];
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < vp.M; i += gridDim.x * blockDim.x) {
+        const uint2 m = b.match[vp.m0 + i];
+        const double2 k1 = st.kps[vp.row1 + m.x], k2 = st.kps[vp.row2 + m.y];
+        double x1, y1, x2, y2;
+        vm::calibrate(k1.x, k1.y, vp.cal1, &x1, &y1);
+        vm::calibrate(k2.x, k2.y, vp.cal2, &x2, &y2);
+        b.corr_d[vp.m0 + i] = make_double4(x1, y1, x2, y2);
+        b.corr_f[vp.m0 + i] = make_float4(static_cast<float>(x1), static_cast<float>(y1), static_cast<float>(x2), static_cast<float>(y2));
+    }
+}
+
+__device__ __forceinline__ void hypothesis_samples(const VerifyBufs& b, const VerifyDims& d, int p, int h, const VPair& vp, int* s)
+{
+    if (b.samples) {
+        const int* src = b.samples + (static_cast<long long>(p) * d.H + h) * 5;
+        for (int k = 0; k < 5; ++k) s[k] = src[k];
+    } else {
+        sample5(d.seed, vp.key, static_cast<uint32_t>(h), static_cast<uint32_t>(vp.M), s);
+    }
+}
+
+// solve hypothesis h of pair p into Es (fp64); returns the number of essential matrices
+__device__ int solve_hypothesis(const VerifyBufs& b, const VerifyDims& d, int p, int h, double* Es)
+{
+    const VPair& vp = b.pairs[p];
+    int s[5];
+    hypothesis_samples(b, d, p, h, vp, s);
+    double x1[5], y1[5], x2[5], y2[5];
+    for (int k = 0; k < 5; ++k) {
+        const int idx = min(max(s[k], 0), vp.M - 1);
+        const double4 c = b.corr_d[vp.m0 + idx];
+        x1[k] = c.x; y1[k] = c.y; x2[k] = c.z; y2[k] = c.w;
+    }
+    return vm::fivept(x1, y1, x2, y2, Es);
+}
+
+// ---------------------------------------------------------------------------------------------------------------- K4
+__global__ void __launch_bounds__(128) solve_kernel(VerifyBufs b, VerifyDims d, int n_pairs)
+{
+    const long long g = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+    const int p = static_cast<int>(g / d.H), h = static_cast<int>(g - static_cast<long long>(p) * d.H);
+    if (p >= n_pairs) return;
+    if (b.pairs[p].status != 0) { b.ncand[g] = 0; return; }
+    double Es[9 * vm::kMaxCand];
+    const int ne = solve_hypothesis(b, d, p, h, Es);
+    float* dst = b.E32 + g * (9 * vm::kMaxCand);
+    for (int k = 0; k < 9 * ne; ++k) dst[k] = static_cast<float>(Es[k]);
+    b.ncand[g] = static_cast<unsigned char>(ne);
+}
+
+// ---------------------------------------------------------------------------------------------------------------- K5
+constexpr int kScoreHyp = 32;      // hypotheses per CTA
+constexpr int kScoreTile = 4096;   // correspondences staged per shared-memory tile (64 KB)
+constexpr int kScoreMaxCand = kScoreHyp * vm::kMaxCand;
+
+__global__ void __launch_bounds__(256) score_kernel(VerifyBufs b, VerifyDims d, int n_pairs)
+{
+    extern __shared__ float4 s_corr[];                 // [kScoreTile]
+    __shared__ float s_cost[kScoreMaxCand];
+    __shared__ unsigned short s_cand[kScoreMaxCand];   // (local hypothesis << 4) | candidate
+    __shared__ int s_n;
+    const int p = blockIdx.y;
+    if (p >= n_pairs) return;
+    const VPair& vp = b.pairs[p];
+    if (vp.status != 0) return;
+    const int h0 = blockIdx.x * kScoreHyp;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) {
+        int n = 0;
+        for (int hh = 0; hh < kScoreHyp && h0 + hh < d.H; ++hh) {
+            const int ne = b.ncand[static_cast<long long>(p) * d.H + h0 + hh];
+            for (int c = 0; c < ne; ++c) s_cand[n++] = static_cast<unsigned short>((hh << 4) | c);
+        }
+        s_n = n;
+    }
+    for (int k = threadIdx.x; k < kScoreMaxCand; k += blockDim.x) s_cost[k] = 0.f;
+    __syncthreads();
+    const int n = s_n;
+    if (n == 0) return;
+    const float thr2 = static_cast<float>(vp.thr2);
+    const float* Ebase = b.E32 + (static_cast<long long>(p) * d.H + h0) * (9 * vm::kMaxCand);
+    for (int t0 = 0; t0 < vp.M; t0 += kScoreTile) {
+        const int tn = min(kScoreTile, vp.M - t0);
+        __syncthreads();
+        for (int k = threadIdx.x; k < tn; k += blockDim.x) s_corr[k] = b.corr_f[vp.m0 + t0 + k];
+        __syncthreads();
+        for (int ci = warp; ci < n; ci += 8) {
+            const int code = s_cand[ci];
+            const float* E = Ebase + ((code >> 4) * vm::kMaxCand + (code & 15)) * 9;
+            const float e0 = __ldg(E), e1 = __ldg(E + 1), e2 = __ldg(E + 2), e3 = __ldg(E + 3), e4 = __ldg(E + 4), e5 = __ldg(E + 5),
+                        e6 = __ldg(E + 6), e7 = __ldg(E + 7), e8 = __ldg(E + 8);
+            float acc = 0.f;
+#pragma unroll 2
+            for (int k = lane; k < tn; k += 32) {
+                const float4 c = s_corr[k];
+                const float l0 = fmaf(e0, c.x, fmaf(e1, c.y, e2)), l1 = fmaf(e3, c.x, fmaf(e4, c.y, e5)), l2 = fmaf(e6, c.x, fmaf(e7, c.y, e8));
+                const float m0 = fmaf(e0, c.z, fmaf(e3, c.w, e6)), m1 = fmaf(e1, c.z, fmaf(e4, c.w, e7));
+                const float num = fmaf(c.z, l0, fmaf(c.w, l1, l2));
+                const float den = fmaf(l0, l0, fmaf(l1, l1, fmaf(m0, m0, m1 * m1)));
+                const float s = __fdividef(num * num, den);
+                acc += fminf(s, thr2);                 // NaN -> thr2: counts as an outlier
+            }
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
+            if (lane == 0) s_cost[ci] += acc;
+        }
+    }
+    __syncthreads();
+    for (int ci = threadIdx.x; ci < n; ci += blockDim.x) {
+        const int code = s_cand[ci];
+        b.cost[(static_cast<long long>(p) * d.H + h0 + (code >> 4)) * vm::kMaxCand + (code & 15)] = s_cost[ci];
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------- K6/K7
+constexpr int kTopK = 8;            // candidates re-scored in fp64 (fp32 scoring only has to rank the best few)
+constexpr int kFinThreads = 256;
+
+// deterministic block sum of NV doubles per thread: warp shuffle tree, then warps added in order by thread 0
+template <int NV> __device__ void block_sum(double* v, double (*s_red)[24], double* s_out)
+{
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+        double x = v[k];
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) x += __shfl_down_sync(0xffffffffu, x, off);
+        if (lane == 0) s_red[warp][k] = x;
+    }
+    __syncthreads();
+    if (threadIdx.x < NV) {
+        double s = 0;
+        for (int w = 0; w < kFinThreads / 32; ++w) s += s_red[w][threadIdx.x];
+        s_out[threadIdx.x] = s;
+    }
+    __syncthreads();
+}
+
+__device__ inline void skew_times(const double* t, const double* R, double* E)   // E = [t]x R
+{
+    for (int j = 0; j < 3; ++j) {
+        E[j] = -t[2] * R[3 + j] + t[1] * R[6 + j];
+        E[3 + j] = t[2] * R[j] - t[0] * R[6 + j];
+        E[6 + j] = -t[1] * R[j] + t[0] * R[3 + j];
+    }
+}
+__device__ inline void rodrigues(const double* w, double* R)
+{
+    const double th2 = w[0] * w[0] + w[1] * w[1] + w[2] * w[2], th = sqrt(th2);
+    double a, b;
+    if (th < 1e-8) { a = 1.0 - th2 / 6.0; b = 0.5 - th2 / 24.0; } else { a = sin(th) / th; b = (1.0 - cos(th)) / th2; }
+    const double K[9] = {0, -w[2], w[1], w[2], 0, -w[0], -w[1], w[0], 0};
+    double K2[9];
+    vm::mat3_mul(K, K, K2);
+    for (int i = 0; i < 9; ++i) R[i] = ((i % 4) == 0 ? 1.0 : 0.0) + a * K[i] + b * K2[i];
+}
+__device__ inline void tangent_basis(const double* t, double* b1, double* b2)
+{
+    int k = 0;
+    if (fabs(t[1]) < fabs(t[k])) k = 1;
+    if (fabs(t[2]) < fabs(t[k])) k = 2;
+    double e[3] = {0, 0, 0};
+    e[k] = 1.0;
+    vm::cross3(t, e, b1);
+    const double n = vm::norm3(b1);
+    for (int i = 0; i < 3; ++i) b1[i] /= n;
+    vm::cross3(t, b1, b2);
+}
+// (JtJ + lambda diag(JtJ)) d = -Jtr by Cholesky; false when not positive definite
+__device__ inline bool solve_lm5(const double* JtJ, const double* Jtr, double lambda, double* d)
+{
+    double L[25];
+    for (int i = 0; i < 25; ++i) L[i] = JtJ[i];
+    for (int i = 0; i < 5; ++i) L[6 * i] += lambda * JtJ[6 * i] + 1e-300;
+    for (int j = 0; j < 5; ++j) {
+        double s = L[6 * j];
+        for (int k = 0; k < j; ++k) s -= L[5 * j + k] * L[5 * j + k];
+        if (!(s > 0)) return false;
+        const double ljj = sqrt(s);
+        L[6 * j] = ljj;
+        for (int i = j + 1; i < 5; ++i) {
+            double v = L[5 * i + j];
+            for (int k = 0; k < j; ++k) v -= L[5 * i + k] * L[5 * j + k];
+            L[5 * i + j] = v / ljj;
+        }
+    }
+    double y[5];
+    for (int i = 0; i < 5; ++i) { double v = -Jtr[i]; for (int k = 0; k < i; ++k) v -= L[5 * i + k] * y[k]; y[i] = v / L[6 * i]; }
+    for (int i = 4; i >= 0; --i) { double v = y[i]; for (int k = i + 1; k < 5; ++k) v -= L[5 * k + i] * d[k]; d[i] = v / L[6 * i]; }
+    return true;
+}
+
+// One pass over all correspondences at model (R, t) in shared memory: s_out = {cost, #inliers, Jtr[5], JtJ upper[15]}
+// of the signed Sampson residuals of the inliers; parameters: R <- R Exp(w), t <- normalize(t + b1 a + b2 b).
+__device__ void lo_pass(const VerifyBufs& b, const VPair& vp, const double* s_R, const double* s_t, double* s_E, double* s_dE,
+                        double (*s_red)[24], double* s_out)
+{
+    if (threadIdx.x == 0) {
+        double b1[3], b2[3];
+        skew_times(s_t, s_R, s_E);
+        tangent_basis(s_t, b1, b2);
+        for (int i = 0; i < 3; ++i) {
+            s_dE[3 * i] = 0;                    s_dE[3 * i + 1] = s_E[3 * i + 2];       s_dE[3 * i + 2] = -s_E[3 * i + 1];
+            s_dE[9 + 3 * i] = -s_E[3 * i + 2];  s_dE[9 + 3 * i + 1] = 0;                s_dE[9 + 3 * i + 2] = s_E[3 * i];
+            s_dE[18 + 3 * i] = s_E[3 * i + 1];  s_dE[18 + 3 * i + 1] = -s_E[3 * i];     s_dE[18 + 3 * i + 2] = 0;
+        }
+        skew_times(b1, s_R, s_dE + 27);
+        skew_times(b2, s_R, s_dE + 36);
+    }
+    __syncthreads();
+    double E[9];
+    for (int i = 0; i < 9; ++i) E[i] = s_E[i];
+    double acc[22];
+    for (int i = 0; i < 22; ++i) acc[i] = 0;
+    for (int i = threadIdx.x; i < vp.M; i += kFinThreads) {
+        const double4 c = b.corr_d[vp.m0 + i];
+        const double a1 = c.x, c1 = c.y, a2 = c.z, c2 = c.w;
+        const double l0 = E[0] * a1 + E[1] * c1 + E[2], l1 = E[3] * a1 + E[4] * c1 + E[5], l2 = E[6] * a1 + E[7] * c1 + E[8];
+        const double m0 = E[0] * a2 + E[3] * c2 + E[6], m1 = E[1] * a2 + E[4] * c2 + E[7];
+        const double num = a2 * l0 + c2 * l1 + l2, den = l0 * l0 + l1 * l1 + m0 * m0 + m1 * m1;
+        const double s = num * num / den;
+        if (!(s < vp.thr2)) { acc[0] += vp.thr2; continue; }
+        acc[0] += s;
+        acc[1] += 1.0;
+        const double isd = 1.0 / sqrt(den), r = num * isd, q = r / den;
+        double J[5];
+#pragma unroll
+        for (int pz = 0; pz < 5; ++pz) {
+            const double* D = s_dE + 9 * pz;
+            const double dl0 = D[0] * a1 + D[1] * c1 + D[2], dl1 = D[3] * a1 + D[4] * c1 + D[5], dl2 = D[6] * a1 + D[7] * c1 + D[8];
+            const double dm0 = D[0] * a2 + D[3] * c2 + D[6], dm1 = D[1] * a2 + D[4] * c2 + D[7];
+            const double dnum = a2 * dl0 + c2 * dl1 + dl2;
+            J[pz] = dnum * isd - q * (l0 * dl0 + l1 * dl1 + m0 * dm0 + m1 * dm1);
+        }
+        int k = 7;
+#pragma unroll
+        for (int pz = 0; pz < 5; ++pz) {
+            acc[2 + pz] += J[pz] * r;
+#pragma unroll
+            for (int u = pz; u < 5; ++u) acc[k++] += J[pz] * J[u];
+        }
+    }
+    block_sum<22>(acc, s_red, s_out);
+}
+
+__global__ void __launch_bounds__(kFinThreads) finalize_kernel(VerifyBufs b, VerifyDims d, int n_pairs)
+{
+    __shared__ double s_red[kFinThreads / 32][24];
+    __shared__ double s_out[24];
+    __shared__ double s_Ek[kTopK][9];
+    __shared__ double s_R[9], s_t[3], s_E[9], s_dE[45];
+    __shared__ double s_R1[9], s_R2[9], s_tt[3];
+    __shared__ float s_topv[kTopK];
+    __shared__ int s_topi[kTopK];
+    __shared__ float s_wv[kFinThreads / 32];
+    __shared__ int s_wi[kFinThreads / 32];
+    __shared__ int s_ctrl;
+
+    const int p = blockIdx.x;
+    if (p >= n_pairs) return;
+    const VPair& vp = b.pairs[p];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int i = tid; i < vp.M; i += kFinThreads) b.mask[vp.m0 + i] = 0;
+    if (tid < 9) { b.R[p * 9 + tid] = 0; b.E[p * 9 + tid] = 0; }
+    if (tid < 3) b.t[p * 3 + tid] = 0;
+    if (tid == 0) { b.ninl[p] = 0; b.status[p] = vp.status; }
+    if (vp.status != 0) return;
+
+    // ---- (a) the kTopK best candidates by fp32 MSAC cost (ties: lowest candidate id = h * 10 + c)
+    const int n_slots = d.H * vm::kMaxCand;
+    const float* cost = b.cost + static_cast<long long>(p) * n_slots;
+    const unsigned char* ncand = b.ncand + static_cast<long long>(p) * d.H;
+    int n_top = 0;
+    for (int k = 0; k < kTopK; ++k) {
+        float bv = FLT_MAX;
+        int bi = INT_MAX;
+        for (int sidx = tid; sidx < n_slots; sidx += kFinThreads) {
+            const int h = sidx / vm::kMaxCand, c = sidx - h * vm::kMaxCand;
+            if (c >= ncand[h]) continue;
+            bool used = false;
+            for (int j = 0; j < k; ++j) used |= (s_topi[j] == sidx);
+            const float v = cost[sidx];
+            if (!used && (v < bv)) { bv = v; bi = sidx; }     // ascending scan: first minimum = lowest id
+        }
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            const float ov = __shfl_xor_sync(0xffffffffu, bv, off);
+            const int oi = __shfl_xor_sync(0xffffffffu, bi, off);
+            if (ov < bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+        }
+        if (lane == 0) { s_wv[warp] = bv; s_wi[warp] = bi; }
+        __syncthreads();
+        if (tid == 0) {
+            for (int w = 1; w < kFinThreads / 32; ++w)
+                if (s_wv[w] < bv || (s_wv[w] == bv && s_wi[w] < bi)) { bv = s_wv[w]; bi = s_wi[w]; }
+            s_topv[k] = bv;
+            s_topi[k] = bi;
+        }
+        __syncthreads();
+        if (s_topi[k] == INT_MAX) break;
+        ++n_top;
+    }
+    if (n_top == 0) { if (tid == 0) b.status[p] = 2; return; }
+
+    // ---- (b) re-solve those hypotheses in fp64
+    if (tid < n_top) {
+        const int h = s_topi[tid] / vm::kMaxCand, c = s_topi[tid] - h * vm::kMaxCand;
+        double Es[9 * vm::kMaxCand];
+        const int ne = solve_hypothesis(b, d, p, h, Es);
+        for (int e = 0; e < 9; ++e) s_Ek[tid][e] = (c < ne) ? Es[9 * c + e] : nan("");
+    }
+    __syncthreads();
+
+    // ---- (c) fp64 MSAC cost of the kTopK candidates, then the minimum (ties: lowest id)
+    {
+        double acc[kTopK];
+#pragma unroll
+        for (int k = 0; k < kTopK; ++k) acc[k] = 0;
+        for (int i = tid; i < vp.M; i += kFinThreads) {
+            const double4 c = b.corr_d[vp.m0 + i];
+#pragma unroll
+            for (int k = 0; k < kTopK; ++k) {
+                if (k < n_top) {
+                    const double s = vm::sampson_sq(s_Ek[k], c.x, c.y, c.z, c.w);
+                    acc[k] += (s < vp.thr2) ? s : vp.thr2;
+                }
+            }
+        }
+        block_sum<kTopK>(acc, s_red, s_out);
+    }
+    if (tid == 0) {
+        int best = 0;
+        for (int k = 1; k < n_top; ++k)
+            if (s_out[k] < s_out[best] || (s_out[k] == s_out[best] && s_topi[k] < s_topi[best])) best = k;
+        for (int e = 0; e < 9; ++e) s_E[e] = s_Ek[best][e];
+    }
+    __syncthreads();
+
+    // ---- (d) local optimisation: Levenberg-Marquardt on (R, t) over the Sampson residuals of the current inliers
+    if (d.lo_iters > 0) {
+        double R[9], t[3], JtJ[25], Jtr[5], cst = 0, lambda = 1e-4;
+        int ninl = 0, it = 0;
+        if (tid == 0) {
+            double R2[9];
+            vm::decompose_essential(s_E, R, R2, t);
+            for (int i = 0; i < 9; ++i) s_R[i] = R[i];
+            for (int i = 0; i < 3; ++i) s_t[i] = t[i];
+        }
+        __syncthreads();
+        lo_pass(b, vp, s_R, s_t, s_E, s_dE, s_red, s_out);
+        auto unpack = [&](double* jtj, double* jtr) {
+            for (int i = 0; i < 5; ++i) jtr[i] = s_out[2 + i];
+            int k = 7;
+            for (int i = 0; i < 5; ++i) for (int u = i; u < 5; ++u) { jtj[5 * i + u] = s_out[k]; jtj[5 * u + i] = s_out[k]; ++k; }
+        };
+        if (tid == 0) { cst = s_out[0]; ninl = static_cast<int>(s_out[1]); unpack(JtJ, Jtr); }
+        for (;;) {
+            if (tid == 0) {
+                bool done = false;
+                for (;;) {
+                    if (it >= d.lo_iters || ninl < 5) { done = true; break; }
+                    double dl[5];
+                    if (!solve_lm5(JtJ, Jtr, lambda, dl)) { lambda *= 10.0; ++it; if (lambda > 1e4) { done = true; break; } continue; }
+                    double dR[9], b1[3], b2[3], tn[3];
+                    rodrigues(dl, dR);
+                    vm::mat3_mul(R, dR, s_R);
+                    tangent_basis(t, b1, b2);
+                    for (int i = 0; i < 3; ++i) tn[i] = t[i] + b1[i] * dl[3] + b2[i] * dl[4];
+                    const double nn = vm::norm3(tn);
+                    for (int i = 0; i < 3; ++i) s_t[i] = tn[i] / nn;
+                    break;
+                }
+                s_ctrl = done ? 1 : 0;
+            }
+            __syncthreads();
+            if (s_ctrl) break;
+            lo_pass(b, vp, s_R, s_t, s_E, s_dE, s_red, s_out);
+            if (tid == 0) {
+                const double cn = s_out[0];
+                if (cn < cst) {
+                    const double gain = cst - cn;
+                    const bool stop = !(gain > 1e-10 * cst);
+                    for (int i = 0; i < 9; ++i) R[i] = s_R[i];
+                    for (int i = 0; i < 3; ++i) t[i] = s_t[i];
+                    unpack(JtJ, Jtr);
+                    cst = cn;
+                    ninl = static_cast<int>(s_out[1]);
+                    lambda *= 0.1;
+                    if (lambda < 1e-9) lambda = 1e-9;
+                    ++it;
+                    if (stop) it = d.lo_iters;
+                } else {
+                    lambda *= 10.0;
+                    ++it;
+                    if (lambda > 1e4) it = d.lo_iters;
+                }
+            }
+        }
+        if (tid == 0) skew_times(t, R, s_E);
+        __syncthreads();
+    }
+
+    // ---- (e) final mask: sampson^2 < thr^2 (strict), fp64
+    double E[9];
+    for (int i = 0; i < 9; ++i) E[i] = s_E[i];
+    {
+        double cnt[1] = {0};
+        for (int i = tid; i < vp.M; i += kFinThreads) {
+            const double4 c = b.corr_d[vp.m0 + i];
+            const bool in = vm::sampson_sq(E, c.x, c.y, c.z, c.w) < vp.thr2;
+            b.mask[vp.m0 + i] = in ? 1 : 0;
+            cnt[0] += in ? 1.0 : 0.0;
+        }
+        block_sum<1>(cnt, s_red, s_out);
+    }
+    const int n_in = static_cast<int>(s_out[0]);
+    __syncthreads();
+    if (tid < 9) b.E[p * 9 + tid] = E[tid];
+    if (tid == 0) b.ninl[p] = n_in;
+    if (n_in == 0) { if (tid == 0) b.status[p] = 2; return; }
+
+    // ---- (f) pose recovery (cv2.recoverPose): 4 candidates, cheirality vote over the inliers
+    if (tid == 0) vm::decompose_essential(E, s_R1, s_R2, s_tt);
+    __syncthreads();
+    {
+        double good[4] = {0, 0, 0, 0};
+        for (int i = tid; i < vp.M; i += kFinThreads) {
+            const double4 c = b.corr_d[vp.m0 + i];
+            if (!(vm::sampson_sq(E, c.x, c.y, c.z, c.w) < vp.thr2)) continue;
+#pragma unroll 1
+            for (int cand = 0; cand < 4; ++cand) {
+                const double* Rc = (cand & 1) ? s_R2 : s_R1;
+                const double sg = (cand & 2) ? -1.0 : 1.0;
+                double P1[12];
+                for (int r = 0; r < 3; ++r) { P1[4 * r] = Rc[3 * r]; P1[4 * r + 1] = Rc[3 * r + 1]; P1[4 * r + 2] = Rc[3 * r + 2]; P1[4 * r + 3] = sg * s_tt[r]; }
+                good[cand] += vm::cheirality_ok(P1, c.x, c.y, c.z, c.w) ? 1.0 : 0.0;
+            }
+        }
+        block_sum<4>(good, s_red, s_out);
+    }
+    if (tid == 0) {
+        const double g0 = s_out[0], g1 = s_out[1], g2 = s_out[2], g3 = s_out[3];
+        int best;
+        if (g0 >= g1 && g0 >= g2 && g0 >= g3) best = 0;
+        else if (g1 >= g0 && g1 >= g2 && g1 >= g3) best = 1;
+        else if (g2 >= g0 && g2 >= g1 && g2 >= g3) best = 2;
+        else best = 3;
+        const double* Rb = (best & 1) ? s_R2 : s_R1;
+        const double sg = (best & 2) ? -1.0 : 1.0;
+        for (int i = 0; i < 9; ++i) b.R[p * 9 + i] = Rb[i];
+        for (int i = 0; i < 3; ++i) b.t[p * 3 + i] = sg * s_tt[i];
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------- launch
+cudaError_t launch_verify_chunk(const StoreView& st, const VerifyBufs& b, const VerifyDims& d, int n_pairs, int max_m, cudaStream_t s)
+{
+    if (n_pairs <= 0) return cudaSuccess;
+    static bool configured = false;
+    if (!configured) {
+        cudaError_t e = cudaFuncSetAttribute(score_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kScoreTile * 16);
+        if (e != cudaSuccess) return e;
+        configured = true;
+    }
+    const int gx = max_m > 0 ? (max_m + 255) / 256 : 1;
+    gather_normalize_kernel<<<dim3(gx, n_pairs), 256, 0, s>>>(st, b, n_pairs);
+    const long long nh = static_cast<long long>(n_pairs) * d.H;
+    solve_kernel<<<static_cast<unsigned>((nh + 127) / 128), 128, 0, s>>>(b, d, n_pairs);
+    score_kernel<<<dim3((d.H + kScoreHyp - 1) / kScoreHyp, n_pairs), 256, kScoreTile * 16, s>>>(b, d, n_pairs);
+    finalize_kernel<<<n_pairs, kFinThreads, 0, s>>>(b, d, n_pairs);
+    return cudaGetLastError();
+}
+
+}  // namespace g2v

@@ -1,0 +1,54 @@
+// Structures and the counter-based 5-point sampler shared by the verifier's host and device code.
+#pragma once
+#include <cstdint>
+
+namespace g2v {
+
+struct VPair {
+    long long m0;            // first match row of the pair in the batch-wide match arrays
+    int M;                   // putative matches
+    int row1, row2;          // first store rows (keypoints) of image 1 / image 2
+    int status;              // GTSFM_V_TOO_FEW is decided on the host (M < 6, opencv_verifier_base.py:69-78)
+    double cal1[5], cal2[5]; // f, k1, k2, u0, v0
+    double thr2;             // (threshold_px / max(fx1, fx2))^2   (ransac.py:79, opencv_verifier_base.py:86)
+    unsigned long long key;  // sampler key
+};
+
+struct VerifyDims {
+    int H;                   // hypotheses per pair
+    int lo_iters;
+    unsigned long long seed;
+};
+
+#if defined(__CUDACC__)
+#define G2V_HD __host__ __device__
+#else
+#define G2V_HD
+#endif
+
+G2V_HD inline uint64_t splitmix64(uint64_t x)
+{
+    x += 0x9E3779B97F4A7C15ull;
+    uint64_t z = x;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+
+// Hypothesis h of pair `key`: five distinct match rows in [0, M), M >= 5.  Pure integer arithmetic, so the host copy
+// (gtsfm_ransac_samples) and the device copy agree bit for bit.
+G2V_HD inline void sample5(uint64_t seed, uint64_t key, uint32_t h, uint32_t M, int* out)
+{
+    const uint64_t state = splitmix64(splitmix64(seed) ^ splitmix64(key * 0xD1342543DE82EF95ull + h));
+    int k = 0;
+    uint64_t ctr = 0;
+    while (k < 5) {
+        const uint64_t r = splitmix64(state + ctr++);
+        const int idx = static_cast<int>(((r >> 32) * static_cast<uint64_t>(M)) >> 32);
+        bool dup = false;
+        for (int j = 0; j < k; ++j) dup |= (out[j] == idx);
+        if (!dup) out[k++] = idx;
+    }
+}
+
+}  // namespace g2v

@@ -1,0 +1,209 @@
+"""GPU parity of the batched Ransac verifier against the CPU oracle, driven by the identical (H, 5) sample sets.
+
+Bars (BASELINE.json north_star): inlier masks bit-exact except for correspondences whose squared Sampson distance is
+within 1e-6 (relative) of the threshold; rotation and translation direction within 0.1 degree of the oracle.
+"""
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+BAND = 1e-6
+ANGLE_TOL_DEG = 0.1
+
+
+def rot_angle_deg(R1, R2):
+    return np.degrees(np.arccos(np.clip((np.trace(R1.T @ R2) - 1) / 2, -1, 1)))
+
+
+def dir_angle_deg(a, b):
+    return np.degrees(np.arccos(np.clip(a @ b / np.linalg.norm(a) / np.linalg.norm(b), -1, 1)))
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    import gtsfm_b200
+    c = gtsfm_b200.Context(0)
+    yield c
+    c.close()
+
+
+def make_pixel_scene(rng, n, noise_px=0.5, out_frac=0.4, f=1000.0, u0=640.0, v0=480.0):
+    import cv2
+    X = rng.uniform(-2, 2, (n, 3)) + [0, 0, 6]
+    R, _ = cv2.Rodrigues(rng.normal(0, 0.2, 3))
+    t = rng.normal(0, 1, 3)
+    t /= np.linalg.norm(t)
+    x1 = X[:, :2] / X[:, 2:]
+    Xc = X @ R.T + t
+    x2 = Xc[:, :2] / Xc[:, 2:]
+    p1 = x1 * f + [u0, v0] + rng.normal(0, noise_px, x1.shape)
+    p2 = x2 * f + [u0, v0] + rng.normal(0, noise_px, x2.shape)
+    no = int(out_frac * n)
+    p2[:no] = rng.uniform(0, 1, (no, 2)) * [2 * u0, 2 * v0]
+    perm = rng.permutation(n)
+    return p1[perm], p2[perm], R, t, (f, 0.0, 0.0, u0, v0)
+
+
+def params(thr, H, lo=20, seed=7, samples=None, keys=None):
+    import gtsfm_b200
+    p = gtsfm_b200.VerifyParams()
+    p.threshold_px = thr
+    p.n_hypotheses = H
+    p.lo_iters = lo
+    p.seed = seed
+    p.pair_keys = None if keys is None else keys.ctypes.data
+    p.samples = None if samples is None else samples.ctypes.data
+    return p
+
+
+def check_against_oracle(got, kp1, kp2, mi, cal1, cal2, thr, samples, lo=20):
+    from oracle import oracle as O
+    ref = O.verify_pair(kp1, kp2, mi, cal1, cal2, thr, samples, lo_iters=lo)
+    assert got["status"] == ref["status"]
+    if ref["status"] != 0:
+        return ref
+    n1 = O.calibrate(kp1[mi[:, 0]], cal1)
+    n2 = O.calibrate(kp2[mi[:, 1]], cal2)
+    thr2 = (thr / max(cal1[0], cal2[0])) ** 2
+    s = O.sampson_sq(ref["E"], n1, n2)
+    differ = got["mask"] != ref["mask"]
+    in_band = np.abs(s / thr2 - 1.0) < BAND
+    assert not (differ & ~in_band).any(), f"{(differ & ~in_band).sum()} mask entries differ outside the 1e-6 band"
+    assert abs(int(got["n_inliers"]) - int(ref["ninl"])) <= int(in_band.sum())
+    assert rot_angle_deg(got["R"], ref["R"]) < ANGLE_TOL_DEG
+    assert dir_angle_deg(got["t"], ref["t"]) < ANGLE_TOL_DEG
+    return ref
+
+
+@pytest.mark.parametrize("n,out_frac,H", [(500, 0.4, 256), (3000, 0.5, 512), (64, 0.2, 128), (6, 0.0, 32)])
+def test_verify_pair_vs_oracle_same_samples(ctx, n, out_frac, H):
+    import gtsfm_b200
+    rng = np.random.default_rng(n)
+    kp1, kp2, R, t, cal = make_pixel_scene(rng, n, out_frac=out_frac)
+    mi = np.c_[np.arange(n), np.arange(n)].astype(np.uint32)
+    samples = gtsfm_b200.ransac_samples(7, 0, n, H)
+    # explicit samples and the device sampler must give the same result
+    g1 = ctx.verify_pair(kp1, kp2, mi, cal, cal, params(4.0, H, samples=samples))
+    g2 = ctx.verify_pair(kp1, kp2, mi, cal, cal, params(4.0, H))
+    np.testing.assert_array_equal(g1["mask"], g2["mask"])
+    np.testing.assert_array_equal(g1["R"], g2["R"])
+    ref = check_against_oracle(g1, kp1, kp2, mi, cal, cal, 4.0, samples)
+    if n >= 64:
+        assert rot_angle_deg(g1["R"], R) < 1.0 and dir_angle_deg(g1["t"], t) < 3.0
+
+
+def test_verify_without_local_optimisation(ctx):
+    import gtsfm_b200
+    rng = np.random.default_rng(3)
+    kp1, kp2, R, t, cal = make_pixel_scene(rng, 800)
+    mi = np.c_[np.arange(800), np.arange(800)].astype(np.uint32)
+    samples = gtsfm_b200.ransac_samples(1, 0, 800, 200)
+    g = ctx.verify_pair(kp1, kp2, mi, cal, cal, params(4.0, 200, lo=0, seed=1))
+    check_against_oracle(g, kp1, kp2, mi, cal, cal, 4.0, samples, lo=0)
+
+
+def test_reference_two_plane_scene(ctx):
+    # tests/frontend/verifier/test_verifier_base.py:81-100 -- all 8 matches verified, R/t within 2 degrees of GT
+    import gtsfm_b200
+    g = np.load(os.path.join(GOLDEN, "verifier_two_planes.npz"))
+    mi = np.c_[np.arange(8), np.arange(8)].astype(np.uint32)
+    cal = (1.0, 0.0, 0.0, 0.0, 0.0)
+    samples = gtsfm_b200.ransac_samples(7, 0, 8, 200)
+    got = ctx.verify_pair(g["kp1"], g["kp2"], mi, cal, cal, params(0.5, 200))
+    assert got["status"] == 0 and got["mask"].all()
+    assert rot_angle_deg(got["R"], g["R_gt"]) < 2 and dir_angle_deg(got["t"], g["t_gt"]) < 2
+    check_against_oracle(got, g["kp1"], g["kp2"], mi, cal, cal, 0.5, samples)
+
+
+def test_reference_argoverse_pair(ctx):
+    # tests/frontend/verifier/test_verifier_argoverse.py:73-119 (euler within 1 degree, i1ti2 within 0.01).
+    # The 20 annotated points admit two optima with 11 inliers each (MSAC cost 1.314e-6 and 1.337e-6); cv2's
+    # USAC_ACCURATE returns the second one.  With sampler seed 1 the best minimal model lies in that basin and the
+    # refined pose reproduces the recorded cv2 output (ref_R / ref_t) itself; other seeds reach the lower-cost optimum,
+    # which is 0.012 from the annotated translation.  Oracle parity is asserted for both.
+    import gtsfm_b200
+    from scipy.spatial.transform import Rotation
+    g = np.load(os.path.join(GOLDEN, "verifier_argoverse.npz"))
+    n = g["kp1"].shape[0]
+    mi = np.c_[np.arange(n), np.arange(n)].astype(np.uint32)
+    kp1, kp2, cal = g["kp1"].astype(np.float64), g["kp2"].astype(np.float64), tuple(g["cal"])
+    got = ctx.verify_pair(kp1, kp2, mi, cal, cal, params(0.5, 1024, seed=1))
+    assert got["status"] == 0
+    eul = Rotation.from_matrix(got["R"].T).as_euler("zyx", degrees=True)
+    assert np.allclose(eul, g["gt_euler_zyx_deg"], atol=1.0), eul
+    assert np.allclose(-got["R"].T @ got["t"], g["gt_i1ti2"], atol=0.01)
+    assert rot_angle_deg(got["R"], g["ref_R"]) < 1e-3 and dir_angle_deg(got["t"], g["ref_t"]) < 1e-3
+    np.testing.assert_array_equal(mi[got["mask"] == 1], g["ref_idx"])
+    check_against_oracle(got, kp1, kp2, mi, cal, cal, 0.5, gtsfm_b200.ransac_samples(1, 0, n, 1024))
+    got = ctx.verify_pair(kp1, kp2, mi, cal, cal, params(0.5, 1024, seed=0))
+    check_against_oracle(got, kp1, kp2, mi, cal, cal, 0.5, gtsfm_b200.ransac_samples(0, 0, n, 1024))
+    eul = Rotation.from_matrix(got["R"].T).as_euler("zyx", degrees=True)
+    assert np.allclose(eul, g["gt_euler_zyx_deg"], atol=1.0), eul
+
+
+def test_gates_too_few_matches(ctx):
+    # opencv_verifier_base.py:69-78 and tests/frontend/verifier/test_verifier_base.py:120-138
+    kp = np.random.default_rng(0).uniform(0, 100, (10, 2))
+    cal = (1.0, 0.0, 0.0, 0.0, 0.0)
+    for M in (0, 4, 5):
+        mi = np.c_[np.arange(M), np.arange(M)].astype(np.uint32).reshape(-1, 2)
+        got = ctx.verify_pair(kp, kp, mi, cal, cal, params(0.5, 16))
+        assert got["status"] == 1 and got["n_inliers"] == 0 and not got["mask"].any()
+
+
+def test_batch_of_ragged_pairs(ctx):
+    """Several pairs of different sizes in one call, small workspace -> several chunks; equals per-pair results."""
+    import gtsfm_b200
+    rng = np.random.default_rng(5)
+    sizes = [300, 5, 1200, 40, 0, 700]
+    scenes = [make_pixel_scene(rng, max(n, 1)) for n in sizes]
+    ctx.clear()
+    for k, (kp1, kp2, _, _, cal) in enumerate(scenes):
+        ctx.upload_image(2 * k, None, kp1, cal)
+        ctx.upload_image(2 * k + 1, None, kp2, cal)
+    pairs = np.array([(2 * k, 2 * k + 1) for k in range(len(sizes))], np.int32)
+    mi = np.concatenate([np.c_[np.arange(n), np.arange(n)] for n in sizes]).astype(np.uint32)
+    off = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int64)
+    keys = np.arange(100, 100 + len(sizes), dtype=np.uint64)
+    ctx.set_workspace(64 << 20)
+    out = ctx.verify_batch(pairs, params(4.0, 256, seed=9, keys=keys), mi, off)
+    ctx.set_workspace(4 << 30)
+    for k, n in enumerate(sizes):
+        kp1, kp2, _, _, cal = scenes[k]
+        got = dict(status=out["status"][k], mask=out["mask"][off[k]:off[k + 1]], R=out["R"][k], t=out["t"][k], n_inliers=out["n_inliers"][k])
+        if n < 6:
+            assert got["status"] == 1
+            continue
+        samples = gtsfm_b200.ransac_samples(9, int(keys[k]), n, 256)
+        check_against_oracle(got, kp1, kp2, mi[off[k]:off[k + 1]], cal, cal, 4.0, samples)
+
+
+def test_match_then_verify_on_device(ctx):
+    """The fused path: matches stay on the device between gtsfm_match_batch and gtsfm_verify_batch."""
+    import gtsfm_b200
+    from tests.test_gpu_match import sift_like
+    rng = np.random.default_rng(8)
+    n = 1500
+    kp1, kp2, R, t, cal = make_pixel_scene(rng, n, out_frac=0.0)
+    protos = np.abs(rng.standard_normal((n, 128)))
+    d1 = sift_like(rng, n, protos=protos)
+    d2 = sift_like(rng, n, protos=protos)
+    d2[: n // 3] = sift_like(rng, n // 3)            # a third of image 2 is clutter
+    perm = rng.permutation(n)
+    d2, kp2 = d2[perm], kp2[perm]
+    ctx.clear()
+    ctx.upload_image(0, d1, kp1, cal)
+    ctx.upload_image(1, d2, kp2, cal)
+    pairs = np.array([[0, 1]], np.int32)
+    m, off = ctx.match_batch(pairs, 0.8)
+    out = ctx.verify_batch(pairs, params(4.0, 512, seed=3), total=len(m))
+    assert out["status"][0] == 0
+    samples = gtsfm_b200.ransac_samples(3, 0, len(m), 512)
+    got = dict(status=out["status"][0], mask=out["mask"], R=out["R"][0], t=out["t"][0], n_inliers=out["n_inliers"][0])
+    check_against_oracle(got, kp1, kp2, m, cal, cal, 4.0, samples)
+    assert rot_angle_deg(out["R"][0], R) < 1.0
+    assert out["n_inliers"][0] > 0.5 * len(m)
