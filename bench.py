@@ -1,0 +1,302 @@
+#!/usr/bin/env python
+"""bench.py -- image pairs/s of the two-view front-end hot path (TwoWayMatcher + Ransac verifier) on B200.
+
+  python bench.py --gpus N --steps K --warmup W            the B200 path (one rank per GPU under torchrun for N > 1)
+  python bench.py --impl reference --gpus N --steps K ...  the reference's CPU path (cv2, one task per pair, all cores)
+
+Workload (BASELINE.json): config C2 = synthetic 100 images x 8192 SIFT-128 keypoints, exhaustive 4,950 pairs, ratio test
+0.8, 1,024 five-point hypotheses per pair, 4 px threshold.  A "step" is one pass over all pairs: match + verify.
+`value` times the pass with descriptors / keypoints already resident in HBM; `e2e` times it through the public batched
+API from pinned host buffers, uploads and result downloads included.  N > 1: every rank runs its own C2-sized shard
+(weak scaling, pairs are independent units) and the per-pair result records are gathered with one NCCL all_gather.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "image_pairs_per_sec_match_plus_ransac_verify"
+UNIT = "pairs/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--config", default="C2")
+    ap.add_argument("--images", type=int, default=0, help="shrink the config (debugging only; the line then says so)")
+    ap.add_argument("--kps", type=int, default=0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--ref-pairs", type=int, default=0, help="pairs per reference step (default: 2 per host core)")
+    return ap.parse_args()
+
+
+def load_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return dict(bf16_burst=p["bf16_tflops"], bf16_sustained=p.get("bf16_tflops_sustained", p["bf16_tflops"]), hbm=p["hbm_gbs"], source="measured")
+    except Exception:  # noqa: BLE001
+        return dict(bf16_burst=1590.0, bf16_sustained=1400.0, hbm=6650.0, source="fallback")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:  # noqa: BLE001
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+            except Exception:  # noqa: BLE001
+                continue
+            for n, v in zip(names, r[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def make_scene(args, rank: int):
+    from gtsfm_b200 import synthetic
+    cfg = dict(synthetic.CONFIGS[args.config])
+    if args.images:
+        cfg["n_images"] = args.images
+    if args.kps:
+        cfg["n_kps"] = args.kps
+    cfg["seed"] = cfg["seed"] + 1000 * rank          # every rank its own shard of the same shape (weak scaling)
+    return synthetic.make_scene(**cfg), cfg
+
+
+def workload_name(args, cfg, n_pairs):
+    s = f"{args.config}: synthetic {cfg['n_images']} images x {cfg['n_kps']} {cfg['kind']}-{cfg['dim']} keypoints, {n_pairs} pairs ({cfg['pairs']})"
+    if args.images or args.kps:
+        s += " [SHRUNK - not the BASELINE configuration]"
+    return s
+
+
+# ------------------------------------------------------------------------------------------------ reference arm (CPU)
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import ref_cv2
+    scene, cfg = make_scene(args, 0)
+    cores = len(os.sched_getaffinity(0))
+    per_step = args.ref_pairs or 2 * cores
+    pool = ref_cv2.PairPool(scene, cores)
+    rng = np.random.default_rng(0)
+    n_pairs = len(scene.pairs)
+
+    def step():
+        ids = rng.choice(n_pairs, min(per_step, n_pairs), replace=False)
+        t0 = time.perf_counter()
+        pool.run(ids)
+        return len(ids), time.perf_counter() - t0
+
+    for _ in range(args.warmup):
+        step()
+    done, secs = 0, 0.0
+    for _ in range(args.steps):
+        n, dt = step()
+        done += n; secs += dt
+    pool.close()
+    value = done / secs
+    sample = f"{per_step} random pairs per step, one task per pair on {cores} single-threaded cv2 workers"
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * secs / max(args.steps, 1), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "config": {"workload": workload_name(args, cfg, n_pairs), "n_hypotheses": "cv2 USAC_ACCURATE default (maxIters 1000)"},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------ B200 arm
+def cpu_baseline_sample(scene, cfg):
+    """The reference's CPU path (oracle/ref_cv2.py) on a bounded sample: 2 pairs per host core, all cores."""
+    from oracle import ref_cv2
+    cores = len(os.sched_getaffinity(0))
+    n = min(len(scene.pairs), 2 * cores)
+    pool = ref_cv2.PairPool(scene, cores)
+    ids = np.random.default_rng(1).choice(len(scene.pairs), n, replace=False)
+    pool.run(ids[:cores])                      # warm the workers (fork, cv2 import)
+    t0 = time.perf_counter()
+    pool.run(ids)
+    dt = time.perf_counter() - t0
+    pool.close()
+    return {"value": n / dt, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"{n} random pairs of the same workload, one task per pair on {cores} single-threaded cv2 workers ({dt:.1f} s)"}
+
+
+def run_b200(args):
+    import torch
+    import gtsfm_b200
+    from gtsfm_b200 import _native
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    scene, cfg = make_scene(args, rank)
+    pairs = scene.pairs
+    P = len(pairs)
+    n_img = len(scene.descriptors)
+    # CPU baseline first: the worker pool is forked before this process creates its CUDA context
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cpu = cpu_baseline_sample(scene, cfg)
+    ctx = gtsfm_b200.Context(local)
+
+    # pinned host copies of the step's inputs (the e2e leg uploads from these every step)
+    desc_pin = [torch.from_numpy(d).pin_memory() for d in scene.descriptors]
+    kps_pin = [torch.from_numpy(k).pin_memory() for k in scene.keypoints]
+    h2d_bytes = sum(t.numel() * t.element_size() for t in desc_pin + kps_pin)
+
+    prm = _native.VerifyParams()
+    prm.threshold_px, prm.n_hypotheses, prm.lo_iters, prm.seed = scene.threshold_px, scene.n_hyp, 20, 20260002
+    keys = (pairs[:, 0].astype(np.uint64) << np.uint64(32)) | pairs[:, 1].astype(np.uint64)
+    prm.pair_keys, prm.samples = keys.ctypes.data, None
+
+    def upload():
+        ctx.clear()
+        for i in range(n_img):
+            ctx.upload_image(i, desc_pin[i].numpy(), kps_pin[i].numpy(), scene.cal)
+
+    rec = torch.zeros((P, 16), dtype=torch.float64, device="cuda")       # per-pair result record gathered over NVLink
+    gathered = [torch.zeros_like(rec) for _ in range(world)] if world > 1 else None
+
+    def compute(fetch: bool):
+        m, off = ctx.match_batch(pairs, scene.ratio, fetch=fetch)
+        out = ctx.verify_batch(pairs, prm, total=int(off[-1]))
+        d2h = m.nbytes + out["mask"].nbytes + out["R"].nbytes + out["t"].nbytes + out["E"].nbytes + out["n_inliers"].nbytes + out["status"].nbytes + 4 * P
+        if world > 1:                                                      # results gathered via NCCL (north_star)
+            h = np.concatenate([out["R"].reshape(P, 9), out["t"], out["n_inliers"][:, None], out["status"][:, None],
+                                np.diff(off)[:, None], np.zeros((P, 1))], axis=1)
+            rec.copy_(torch.from_numpy(h), non_blocking=True)
+            dist.all_gather(gathered, rec)
+        return off, out, d2h
+
+    def sync_all():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        """K steps bracketed by barrier + synchronize; device time from CUDA events on the library's stream, max over ranks."""
+        sync_all()
+        ctx.event_record(0)
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            last = fn()
+        ctx.event_record(1)
+        sync_all()
+        wall = time.perf_counter() - t0
+        ms = ctx.event_elapsed_ms(0, 1)
+        ms = max(ms, 0.0)
+        if world > 1:
+            t = torch.tensor([ms, wall * 1e3], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms, wall = float(t[0]), float(t[1]) / 1e3
+        return ms, wall, last
+
+    # ---- resident leg: inputs already in HBM
+    upload()
+    for _ in range(args.warmup):
+        compute(False)
+    ctx.profile_enable(True)
+    launches0 = ctx.kernel_launches
+    clocks = ClockSampler(local)
+    clocks.start()
+    ms, wall, (off, out, _) = timed(lambda: compute(False), args.steps)
+    clk = clocks.stop()
+    launches = ctx.kernel_launches - launches0
+    prof = ctx.profile_get()
+    ctx.profile_enable(False)
+    # the device-event time excludes nothing but host gaps after the last kernel; use the larger of the two clocks
+    step_ms = max(ms, wall * 1e3) / args.steps
+    value = world * P / (step_ms / 1e3)
+
+    # ---- end-to-end leg: pinned host buffers -> device -> results on the host, every step
+    def e2e_step():
+        upload()
+        return compute(True)
+    for _ in range(min(args.warmup, 1)):
+        e2e_step()
+    ems, ewall, (_, _, d2h_bytes) = timed(e2e_step, args.steps)
+    e2e_ms = max(ems, ewall * 1e3) / args.steps
+    e2e_value = world * P / (e2e_ms / 1e3)
+
+    if rank == 0:
+        peaks = load_peaks()
+        n_kps, dim = cfg["n_kps"], cfg["dim"]
+        scr_ms, scr_calls = prof["screen"]
+        flops_per_launch = 2.0 * n_kps * n_kps * dim * P * args.steps / max(scr_calls, 1)
+        achieved = flops_per_launch / (scr_ms / max(scr_calls, 1) * 1e-3) / 1e12 if scr_ms > 0 else 0.0
+        total_kernel_ms = sum(v[0] for v in prof.values())
+        roofline = {"bound": "tensor", "kernel": "match_screen_kernel (tcgen05 distance GEMM + fused row/column minima)",
+                    "achieved": achieved, "peak": peaks["bf16_sustained"], "unit": "TFLOP/s", "frac": achieved / peaks["bf16_sustained"],
+                    "peak_source": peaks["source"] + " (sustained bf16; burst %.1f)" % peaks["bf16_burst"], "traffic": None,
+                    "algorithmic_flops_per_launch": flops_per_launch, "launch_ms": scr_ms / max(scr_calls, 1),
+                    "share_of_step": scr_ms / total_kernel_ms if total_kernel_ms else None,
+                    "kernel_ms_per_step": {k: v[0] / args.steps for k, v in prof.items()}}
+        n_match = int(off[-1])
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16 GEMM / f32 scoring / f64 finalize",
+                "data": "synthetic",
+                "config": {"workload": workload_name(args, cfg, P), "pairs_per_gpu": P, "ratio_test": scene.ratio, "n_hypotheses": scene.n_hyp,
+                           "threshold_px": scene.threshold_px, "lo_iters": 20, "matches_per_pair": n_match / P,
+                           "inliers_per_pair": float(out["n_inliers"].mean()), "verified_ok": int((out["status"] == 0).sum()),
+                           "l2": "inputs exceed L2 (descriptor store %.0f MB per GPU)" % (n_img * n_kps * (dim * 7 + 96) / 1e6),
+                           "parallelism": f"pairs sharded over {world} GPU(s), NCCL all_gather of result records" if world > 1 else "1 GPU"},
+                "roofline": roofline, "cpu_baseline": cpu,
+                "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": int(d2h_bytes)},
+                "gpu_launches": int(launches), "clocks": clk, "device_event_ms_per_step": ms / args.steps}
+        print(json.dumps(line), flush=True)
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200(a)

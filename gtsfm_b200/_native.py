@@ -18,6 +18,7 @@ EXPORTS = (
     "gtsfm_ctx_create", "gtsfm_ctx_destroy", "gtsfm_last_error", "gtsfm_ctx_set_workspace", "gtsfm_kernel_launches",
     "gtsfm_store_clear", "gtsfm_image_upload", "gtsfm_match_batch", "gtsfm_match_fetch", "gtsfm_ransac_samples",
     "gtsfm_verify_batch", "gtsfm_match_pair", "gtsfm_verify_pair", "gtsfm_debug_fetch",
+    "gtsfm_profile_enable", "gtsfm_profile_get", "gtsfm_event_record", "gtsfm_event_elapsed_ms",
 )
 
 OK, E_CUDA, E_ARG, E_NO_DEVICE, E_KNN_UNPACK, E_UNSUPPORTED = range(6)
@@ -77,6 +78,10 @@ def lib() -> ctypes.CDLL:
                                             ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p,
                                             ctypes.POINTER(VerifyParams)] + [ctypes.c_void_p] * 6
             L.gtsfm_debug_fetch.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int64]
+            L.gtsfm_profile_enable.argtypes = [ctypes.c_void_p, ctypes.c_int]
+            L.gtsfm_profile_get.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
+            L.gtsfm_event_record.argtypes = [ctypes.c_void_p, ctypes.c_int]
+            L.gtsfm_event_elapsed_ms.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_double)]
             _lib = L
     return _lib
 
@@ -153,8 +158,8 @@ class Context:
         self._check(self._L.gtsfm_image_upload(self._h, int(image_id), _ptr(desc), int(n), int(dim), _ptr(kps), _ptr(calv)))
 
     # ---- matcher
-    def match_batch(self, pairs: np.ndarray, ratio: Optional[float]):
-        """Returns (matches (total, 2) uint32, offsets (P + 1) int64)."""
+    def match_batch(self, pairs: np.ndarray, ratio: Optional[float], fetch: bool = True):
+        """Returns (matches (total, 2) uint32, offsets (P + 1) int64); fetch=False leaves the matches on the device."""
         pairs = np.ascontiguousarray(pairs, np.int32).reshape(-1, 2)
         P = pairs.shape[0]
         counts = np.zeros(P, np.int32)
@@ -162,8 +167,9 @@ class Context:
         r = float("nan") if ratio is None else float(ratio)
         self._check(self._L.gtsfm_match_batch(self._h, _ptr(pairs), P, r, _ptr(counts), ctypes.byref(total)))
         self._keep.clear()
-        out = np.empty((total.value, 2), np.uint32)
-        self._check(self._L.gtsfm_match_fetch(self._h, _ptr(out)))
+        out = np.empty((total.value if fetch else 0, 2), np.uint32)
+        if fetch:
+            self._check(self._L.gtsfm_match_fetch(self._h, _ptr(out)))
         offsets = np.zeros(P + 1, np.int64)
         np.cumsum(counts, out=offsets[1:])
         return out, offsets
@@ -180,6 +186,28 @@ class Context:
         r = float("nan") if ratio is None else float(ratio)
         self._check(self._L.gtsfm_match_pair(self._h, _ptr(d1), n1, _ptr(d2), n2, dim, r, _ptr(out), ctypes.byref(cnt)))
         return out[: cnt.value].copy()
+
+    PROFILE_SLOTS = ("prepare", "screen", "resolve_rows", "resolve_cols", "exact_scan", "match_finalize", "gather",
+                     "solve", "score", "verify_finalize")
+
+    def profile_enable(self, on: bool = True):
+        self._check(self._L.gtsfm_profile_enable(self._h, int(bool(on))))
+
+    def profile_get(self) -> dict:
+        """{kernel: (milliseconds, launches)} accumulated since profile_enable(True); CUDA-event timed on the device."""
+        n = len(self.PROFILE_SLOTS)
+        ms = np.zeros(n, np.float64)
+        calls = np.zeros(n, np.int64)
+        self._check(self._L.gtsfm_profile_get(self._h, _ptr(ms), _ptr(calls), n))
+        return {k: (float(ms[i]), int(calls[i])) for i, k in enumerate(self.PROFILE_SLOTS)}
+
+    def event_record(self, which: int):
+        self._check(self._L.gtsfm_event_record(self._h, int(which)))
+
+    def event_elapsed_ms(self, a: int, b: int) -> float:
+        ms = ctypes.c_double(0)
+        self._check(self._L.gtsfm_event_elapsed_ms(self._h, int(a), int(b), ctypes.byref(ms)))
+        return ms.value
 
     def debug_fetch(self, what: int, count: int, dtype) -> np.ndarray:
         out = np.zeros(count, dtype)

@@ -134,6 +134,36 @@ int store_sync_flags(gtsfm_ctx* c)
 
 using namespace g2v;
 
+cudaEvent_t gtsfm_ctx::prof_event()
+{
+    if (prof_used == prof_pool.size()) { cudaEvent_t e; cudaEventCreate(&e); prof_pool.push_back(e); }
+    return prof_pool[prof_used++];
+}
+void gtsfm_ctx::prof_begin(int slot)
+{
+    if (!prof_on) return;
+    ProfSpan sp{slot, prof_event(), prof_event()};
+    cudaEventRecord(sp.a, stream);
+    prof_spans.push_back(sp);
+}
+void gtsfm_ctx::prof_end()
+{
+    if (!prof_on || prof_spans.empty()) return;
+    cudaEventRecord(prof_spans.back().b, stream);
+}
+int gtsfm_ctx::prof_collect()
+{
+    if (prof_spans.empty()) return 0;
+    cudaStreamSynchronize(stream);
+    for (const ProfSpan& sp : prof_spans) {
+        float ms = 0;
+        if (cudaEventElapsedTime(&ms, sp.a, sp.b) == cudaSuccess) { prof_ms[sp.slot] += ms; prof_calls[sp.slot] += 1; }
+    }
+    prof_spans.clear();
+    prof_used = 0;
+    return 0;
+}
+
 g2v::StoreView gtsfm_ctx::view() const
 {
     StoreView v;
@@ -182,6 +212,8 @@ void gtsfm_ctx_destroy(gtsfm_ctx* c)
     for (DevBuf& b : c->v_bufs) b.release();
     c->h_pairs.release();
     c->h_small.release();
+    for (cudaEvent_t e : c->prof_pool) cudaEventDestroy(e);
+    for (cudaEvent_t e : c->user_ev) if (e) cudaEventDestroy(e);
     cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -196,6 +228,45 @@ int gtsfm_ctx_set_workspace(gtsfm_ctx* c, int64_t bytes)
 }
 
 int64_t gtsfm_kernel_launches(const gtsfm_ctx* c) { return c ? c->launches : 0; }
+
+int gtsfm_profile_enable(gtsfm_ctx* c, int on)
+{
+    if (!c) return GTSFM_E_ARG;
+    cudaSetDevice(c->device);
+    c->prof_collect();
+    c->prof_on = on != 0;
+    for (int k = 0; k < 16; ++k) { c->prof_ms[k] = 0; c->prof_calls[k] = 0; }
+    return GTSFM_OK;
+}
+
+int gtsfm_profile_get(gtsfm_ctx* c, double* ms, int64_t* calls, int n_slots)
+{
+    if (!c || n_slots < 0 || n_slots > 16) return GTSFM_E_ARG;
+    cudaSetDevice(c->device);
+    c->prof_collect();
+    for (int k = 0; k < n_slots; ++k) { if (ms) ms[k] = c->prof_ms[k]; if (calls) calls[k] = c->prof_calls[k]; }
+    return GTSFM_OK;
+}
+
+int gtsfm_event_record(gtsfm_ctx* c, int which)
+{
+    if (!c || which < 0 || which >= 8) return GTSFM_E_ARG;
+    cudaSetDevice(c->device);
+    if (!c->user_ev[which]) G2V_CUDA(c, cudaEventCreate(&c->user_ev[which]));
+    G2V_CUDA(c, cudaEventRecord(c->user_ev[which], c->stream));
+    return GTSFM_OK;
+}
+
+int gtsfm_event_elapsed_ms(gtsfm_ctx* c, int a, int b, double* ms)
+{
+    if (!c || !ms || a < 0 || b < 0 || a >= 8 || b >= 8 || !c->user_ev[a] || !c->user_ev[b]) return GTSFM_E_ARG;
+    cudaSetDevice(c->device);
+    G2V_CUDA(c, cudaEventSynchronize(c->user_ev[b]));
+    float f = 0;
+    G2V_CUDA(c, cudaEventElapsedTime(&f, c->user_ev[a], c->user_ev[b]));
+    *ms = f;
+    return GTSFM_OK;
+}
 
 int gtsfm_store_clear(gtsfm_ctx* c)
 {
@@ -258,7 +329,9 @@ int gtsfm_image_upload(gtsfm_ctx* c, int image_id, const float* desc, int n, int
         a.valid = c->valid.as<uint8_t>() + rec.row0;
         a.img_flags = c->img_flags.as<int>() + 2 * c->images.size();
         a.n = rec.n; a.n_pad = rec.n_pad; a.dim = c->dim; a.kpad = c->kpad;
+        c->prof_begin(P_PREPARE);
         G2V_CUDA(c, launch_prepare(a, c->stream));
+        c->prof_end();
         ++c->launches;
         c->flags_dirty = true;
     }

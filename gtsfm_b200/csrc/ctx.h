@@ -58,6 +58,20 @@ struct gtsfm_ctx {
     int64_t batch_total = 0;
     int batch_n = 0;
 
+    // ---- per-kernel device timing (CUDA events on this context's stream) and user events
+    bool prof_on = false;
+    std::vector<cudaEvent_t> prof_pool;          // recycled events
+    size_t prof_used = 0;
+    struct ProfSpan { int slot; cudaEvent_t a, b; };
+    std::vector<ProfSpan> prof_spans;
+    double prof_ms[16] = {0};
+    int64_t prof_calls[16] = {0};
+    cudaEvent_t user_ev[8] = {nullptr};
+    cudaEvent_t prof_event();
+    void prof_begin(int slot);
+    void prof_end();
+    int prof_collect();
+
     // ---- verifier buffers
     g2v::DevBuf v_bufs[24];
 
@@ -75,4 +89,5 @@ int cuda_fail(gtsfm_ctx* c, cudaError_t e, const char* what);
 
 int store_reserve_rows(gtsfm_ctx* c, long long rows);
 int store_sync_flags(gtsfm_ctx* c);
+enum ProfSlot { P_PREPARE = 0, P_SCREEN, P_RESOLVE_ROWS, P_RESOLVE_COLS, P_EXACT_SCAN, P_MATCH_FINALIZE, P_GATHER, P_SOLVE, P_SCORE, P_VFINALIZE, P_NSLOTS };
 }  // namespace g2v

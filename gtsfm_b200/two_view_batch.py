@@ -1,0 +1,89 @@
+"""Batched two-view front-end: the caller-side replacement of the reference's per-pair submission loops
+(SURVEY.md 8(a) row a12):
+
+  DetDescCorrespondenceGenerator.generate_correspondences   det_desc_correspondence_generator.py:66-85  (match per pair)
+  run_two_view_estimator_as_futures                         two_view_estimator.py:567-587               (verify per pair)
+
+Instead of one Dask task per pair, one call per GPU shard uploads the shard's images once, matches every pair, keeps
+the matches on the device and verifies them there.  Outputs use the reference's dictionary conventions
+(gtsfm_runner_base.py:415-440): {(i1, i2): value}; pairs whose verification failed carry None rotations.
+"""
+from dataclasses import dataclass
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+
+from gtsfm_b200 import _native
+from gtsfm_b200.common.types import Rot3, Unit3, cal_to_tuple
+
+
+@dataclass
+class TwoViewBatchResult:
+    pairs: np.ndarray                     # (P, 2) int32
+    match_offsets: np.ndarray             # (P + 1,) int64
+    matches: np.ndarray                   # (total, 2) uint32 putative correspondences (TwoWayMatcher order)
+    inlier_mask: np.ndarray               # (total,) uint8
+    R: np.ndarray                         # (P, 3, 3) i2Ri1
+    t: np.ndarray                         # (P, 3) i2Ui1
+    n_inliers: np.ndarray                 # (P,)
+    status: np.ndarray                    # (P,) 0 ok, 1 too few matches, 2 no model
+
+    def putative_corr_idxs_dict(self) -> Dict[Tuple[int, int], np.ndarray]:
+        o = self.match_offsets
+        return {(int(a), int(b)): self.matches[o[p]:o[p + 1]] for p, (a, b) in enumerate(self.pairs)}
+
+    def two_view_dicts(self):
+        """(i2Ri1_dict, i2Ui1_dict, v_corr_idxs_dict, inlier_ratio_dict), built lazily from the structure-of-arrays."""
+        o = self.match_offsets
+        Rd, td, vd, rd = {}, {}, {}, {}
+        for p, (a, b) in enumerate(self.pairs):
+            key = (int(a), int(b))
+            m = self.matches[o[p]:o[p + 1]]
+            if self.status[p] != 0:
+                Rd[key], td[key], vd[key], rd[key] = None, None, np.array([], dtype=np.uint64), 0.0
+                continue
+            mask = self.inlier_mask[o[p]:o[p + 1]]
+            Rd[key], td[key] = Rot3(self.R[p].copy()), Unit3(self.t[p].copy())
+            vd[key] = m[mask == 1]
+            rd[key] = float(mask.mean()) if mask.size else 0.0
+        return Rd, td, vd, rd
+
+
+def shard_pairs(pairs: np.ndarray, n_shards: int, cost: Optional[np.ndarray] = None) -> List[np.ndarray]:
+    """Contiguous, cost-balanced split of an i1-sorted pair list: returns index arrays per shard.
+    Contiguity keeps each shard's image set compact, so only those images have to be placed on that GPU."""
+    P = len(pairs)
+    cost = np.ones(P) if cost is None else np.asarray(cost, float)
+    order = np.lexsort((pairs[:, 1], pairs[:, 0])) if P else np.zeros(0, np.int64)
+    csum = np.cumsum(cost[order])
+    total = csum[-1] if P else 0.0
+    bounds = [int(np.searchsorted(csum, total * k / n_shards, side="left")) for k in range(1, n_shards)]
+    return [order[a:b] for a, b in zip([0] + bounds, bounds + [P])]
+
+
+def run_two_view_batch(descriptors: Sequence[np.ndarray], keypoints: Sequence[np.ndarray], intrinsics: Sequence, pairs: np.ndarray,
+                       ratio_test_threshold: Optional[float] = 0.8, estimation_threshold_px: float = 4.0, num_hypotheses: int = 1024,
+                       seed: int = 0, lo_iters: int = 20, device: int = 0, ctx: Optional[_native.Context] = None,
+                       upload: bool = True, fetch_matches: bool = True) -> TwoViewBatchResult:
+    """Match + verify every pair of one shard on one GPU.  Only the images a shard's pairs name are uploaded; image
+    indices in `pairs` refer to the caller's lists.  keypoints: (N, 2) pixel arrays; intrinsics: Cal3Bundler-likes or
+    (f, k1, k2, u0, v0) tuples."""
+    pairs = np.ascontiguousarray(pairs, np.int32).reshape(-1, 2)
+    ctx = ctx or _native.default_context(device)
+    if upload:
+        used = np.unique(pairs)
+        remap = -np.ones(len(descriptors), np.int64)
+        remap[used] = np.arange(len(used))
+        ctx.clear()
+        for k, i in enumerate(used):
+            ctx.upload_image(k, descriptors[i], keypoints[i], cal_to_tuple(intrinsics[i]))
+        local = remap[pairs].astype(np.int32)
+    else:
+        local = pairs
+    p = _native.VerifyParams()
+    p.threshold_px, p.n_hypotheses, p.lo_iters, p.seed = float(estimation_threshold_px), int(num_hypotheses), int(lo_iters), int(seed)
+    keys = (pairs[:, 0].astype(np.uint64) << np.uint64(32)) | pairs[:, 1].astype(np.uint64)   # sampler keys = global pair ids
+    p.pair_keys, p.samples = keys.ctypes.data, None
+    matches, off = ctx.match_batch(local, ratio_test_threshold, fetch=fetch_matches)
+    out = ctx.verify_batch(local, p, total=int(off[-1]))
+    return TwoViewBatchResult(pairs, off, matches, out["mask"], out["R"], out["t"], out["n_inliers"], out["status"])

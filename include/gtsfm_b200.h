@@ -55,6 +55,16 @@ int gtsfm_ctx_set_workspace(gtsfm_ctx* ctx, int64_t bytes);
 /* Number of hand-written kernels launched by this context since creation (bench.py's gpu_launches). */
 int64_t gtsfm_kernel_launches(const gtsfm_ctx* ctx);
 
+/* Per-kernel device timing with CUDA events on the context's stream.  Slots: 0 prepare, 1 screen (tcgen05 GEMM),
+ * 2 resolve rows, 3 resolve columns, 4 exact scan, 5 match finalize, 6 gather/normalise, 7 5-point solve,
+ * 8 MSAC scoring, 9 verifier finalize.  enable(…, 1) resets the totals; get() synchronises and returns the
+ * accumulated milliseconds and launch counts of the first n_slots slots. */
+int gtsfm_profile_enable(gtsfm_ctx* ctx, int on);
+int gtsfm_profile_get(gtsfm_ctx* ctx, double* ms, int64_t* calls, int n_slots);
+/* User events on the context's stream (which in 0..7): record, then elapsed milliseconds between two of them. */
+int gtsfm_event_record(gtsfm_ctx* ctx, int which);
+int gtsfm_event_elapsed_ms(gtsfm_ctx* ctx, int a, int b, double* ms);
+
 /* ---- descriptor / keypoint store (replaces pickling Keypoints + descriptors to every Dask task) ---------------- */
 /* Drop all images. */
 int gtsfm_store_clear(gtsfm_ctx* ctx);
