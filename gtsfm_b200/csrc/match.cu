@@ -11,7 +11,7 @@ namespace g2v {
 cudaError_t launch_match_screen(const CUtensorMap& tm_desc, const CUtensorMap& tm_augq, const CUtensorMap& tm_augt,
                                 const PairDesc* pairs, int n_pairs, int n_items, float* rp_v1, float* rp_v2, uint8_t* rp_g,
                                 float* colraw, int kpad, int n_sm, cudaStream_t stream);
-cudaError_t launch_resolve_int(const StoreView& st, const MatchWork& w, long long total_rows, long long total_cols, cudaStream_t s);
+cudaError_t launch_resolve_int(const StoreView& st, const MatchWork& w, int which, long long total, cudaStream_t s);
 cudaError_t launch_exact_scan(const StoreView& st, const MatchWork& w, int mode, int n_jobs, cudaStream_t s);
 cudaError_t launch_match_finalize(const MatchWork& w, int use_ratio, double ratio, unsigned long long* keys_scratch,
                                   uint2* match_slot, int* match_count, long long* offsets, long long* running, uint2* compact_out,
@@ -123,16 +123,32 @@ int gtsfm_match_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, double ra
         w.flag_cap = static_cast<int>(std::min<long long>(k.rows + k.cols, 0x7fffffff));
         G2V_CUDA(c, cudaMemsetAsync(c->n_flag.p, 0, sizeof(int), s));
         if (k.items > 0) {
+            c->prof_begin(P_SCREEN);
             G2V_CUDA(c, launch_match_screen(c->tm_desc, c->tm_augq, c->tm_augt, w.pairs, w.n_pairs, k.items, c->rp_v1.as<float>(),
                                             c->rp_v2.as<float>(), c->rp_g.as<uint8_t>(), c->colraw.as<float>(), c->kpad, c->n_sm, s));
-            G2V_CUDA(c, launch_resolve_int(st, w, k.rows, k.cols, s));
+            c->prof_end();
+            c->prof_begin(P_RESOLVE_ROWS);
+            G2V_CUDA(c, launch_resolve_int(st, w, 0, k.rows, s));
+            c->prof_end();
+            c->prof_begin(P_RESOLVE_COLS);
+            G2V_CUDA(c, launch_resolve_int(st, w, 1, k.cols, s));
+            c->prof_end();
+            c->prof_begin(P_EXACT_SCAN);
             G2V_CUDA(c, launch_exact_scan(st, w, 1, w.flag_cap, s));
+            c->prof_end();
             c->launches += 4;
         }
-        if (k.jobs > 0) { G2V_CUDA(c, launch_exact_scan(st, w, 0, k.jobs, s)); c->launches += 1; }
+        if (k.jobs > 0) {
+            c->prof_begin(P_EXACT_SCAN);
+            G2V_CUDA(c, launch_exact_scan(st, w, 0, k.jobs, s));
+            c->prof_end();
+            c->launches += 1;
+        }
+        c->prof_begin(P_MATCH_FINALIZE);
         G2V_CUDA(c, launch_match_finalize(w, use_ratio, ratio, c->keys_scratch.as<unsigned long long>(), c->match_slot.as<uint2>(),
                                           c->match_count.as<int>() + k.p0, c->match_offsets.as<long long>() + k.p0,
                                           c->d_total.as<long long>(), c->match_out.as<uint2>(), s));
+        c->prof_end();
         c->launches += 3;
     }
     // ---- counts back to the host (the only synchronisation of the batch)

@@ -190,10 +190,12 @@ __global__ void __launch_bounds__(256) resolve_cols_int_kernel(StoreView st, Mat
     }
 }
 
-cudaError_t launch_resolve_int(const StoreView& st, const MatchWork& w, long long total_rows, long long total_cols, cudaStream_t s)
+// which: 0 = query rows, 1 = train columns
+cudaError_t launch_resolve_int(const StoreView& st, const MatchWork& w, int which, long long total, cudaStream_t s)
 {
-    if (total_rows > 0) resolve_rows_int_kernel<<<static_cast<unsigned>((total_rows + 127) / 128), 128, 0, s>>>(st, w, total_rows);
-    if (total_cols > 0) resolve_cols_int_kernel<<<static_cast<unsigned>((total_cols + 7) / 8), 256, 0, s>>>(st, w, total_cols);
+    if (total <= 0) return cudaSuccess;
+    if (which == 0) resolve_rows_int_kernel<<<static_cast<unsigned>((total + 127) / 128), 128, 0, s>>>(st, w, total);
+    else resolve_cols_int_kernel<<<static_cast<unsigned>((total + 7) / 8), 256, 0, s>>>(st, w, total);
     return cudaGetLastError();
 }
 

@@ -13,7 +13,7 @@ struct VerifyBufs {
     const VPair* pairs; const uint2* match; double4* corr_d; float4* corr_f; float* E32; unsigned char* ncand; float* cost;
     const int* samples; double* R; double* t; double* E; int* ninl; int* status; unsigned char* mask;
 };
-cudaError_t launch_verify_chunk(const StoreView& st, const VerifyBufs& b, const VerifyDims& d, int n_pairs, int max_m, cudaStream_t s);
+cudaError_t launch_verify_step(int step, const StoreView& st, const VerifyBufs& b, const VerifyDims& d, int n_pairs, int max_m, cudaStream_t s);
 }  // namespace g2v
 
 using namespace g2v;
@@ -125,7 +125,11 @@ int gtsfm_verify_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, const ui
         b.ninl = vb[10].as<int>() + p0; b.status = vb[11].as<int>() + p0; b.mask = vb[12].as<unsigned char>();
         int mm = 0;
         for (int p = p0; p < p0 + np; ++p) mm = std::max(mm, vps[p].M);
-        G2V_CUDA(c, launch_verify_chunk(st, b, d, np, mm, s));
+        for (int step = 0; step < 4; ++step) {
+            c->prof_begin(P_GATHER + step);
+            G2V_CUDA(c, launch_verify_step(step, st, b, d, np, mm, s));
+            c->prof_end();
+        }
         c->launches += 4;
     }
     // ---- results back to the host

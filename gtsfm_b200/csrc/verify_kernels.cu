@@ -490,7 +490,8 @@ __global__ void __launch_bounds__(kFinThreads) finalize_kernel(VerifyBufs b, Ver
 }
 
 // ---------------------------------------------------------------------------------------------------------------- launch
-cudaError_t launch_verify_chunk(const StoreView& st, const VerifyBufs& b, const VerifyDims& d, int n_pairs, int max_m, cudaStream_t s)
+// step: 0 gather/normalise, 1 solve, 2 score, 3 finalize
+cudaError_t launch_verify_step(int step, const StoreView& st, const VerifyBufs& b, const VerifyDims& d, int n_pairs, int max_m, cudaStream_t s)
 {
     if (n_pairs <= 0) return cudaSuccess;
     static bool configured = false;
@@ -499,12 +500,17 @@ cudaError_t launch_verify_chunk(const StoreView& st, const VerifyBufs& b, const 
         if (e != cudaSuccess) return e;
         configured = true;
     }
-    const int gx = max_m > 0 ? (max_m + 255) / 256 : 1;
-    gather_normalize_kernel<<<dim3(gx, n_pairs), 256, 0, s>>>(st, b, n_pairs);
-    const long long nh = static_cast<long long>(n_pairs) * d.H;
-    solve_kernel<<<static_cast<unsigned>((nh + 127) / 128), 128, 0, s>>>(b, d, n_pairs);
-    score_kernel<<<dim3((d.H + kScoreHyp - 1) / kScoreHyp, n_pairs), 256, kScoreTile * 16, s>>>(b, d, n_pairs);
-    finalize_kernel<<<n_pairs, kFinThreads, 0, s>>>(b, d, n_pairs);
+    if (step == 0) {
+        const int gx = max_m > 0 ? (max_m + 255) / 256 : 1;
+        gather_normalize_kernel<<<dim3(gx, n_pairs), 256, 0, s>>>(st, b, n_pairs);
+    } else if (step == 1) {
+        const long long nh = static_cast<long long>(n_pairs) * d.H;
+        solve_kernel<<<static_cast<unsigned>((nh + 127) / 128), 128, 0, s>>>(b, d, n_pairs);
+    } else if (step == 2) {
+        score_kernel<<<dim3((d.H + kScoreHyp - 1) / kScoreHyp, n_pairs), 256, kScoreTile * 16, s>>>(b, d, n_pairs);
+    } else {
+        finalize_kernel<<<n_pairs, kFinThreads, 0, s>>>(b, d, n_pairs);
+    }
     return cudaGetLastError();
 }
 
