@@ -11,7 +11,8 @@ namespace g2v {
 cudaError_t launch_match_screen(const CUtensorMap& tm_desc, const CUtensorMap& tm_augq, const CUtensorMap& tm_augt,
                                 const PairDesc* pairs, int n_pairs, int n_items, float* rp_v1, float* rp_v2, uint8_t* rp_g,
                                 float* colraw, int kpad, int n_sm, cudaStream_t stream);
-cudaError_t launch_resolve_int(const StoreView& st, const MatchWork& w, int which, long long total, cudaStream_t s);
+cudaError_t launch_resolve_int(const StoreView& st, const MatchWork& w, int which, long long total, int n_items, int max_class_rows,
+                               cudaStream_t s);
 cudaError_t launch_exact_scan(const StoreView& st, const MatchWork& w, int mode, int n_jobs, cudaStream_t s);
 cudaError_t launch_match_finalize(const MatchWork& w, int use_ratio, double ratio, unsigned long long* keys_scratch,
                                   uint2* match_slot, int* match_count, long long* offsets, long long* running, uint2* compact_out,
@@ -21,7 +22,7 @@ int store_ensure_maps(gtsfm_ctx* c);
 struct Chunk {
     int p0 = 0, p1 = 0;
     long long rp = 0, cr = 0, rows = 0, cols = 0;
-    int items = 0, jobs = 0;
+    int items = 0, jobs = 0, max_class_rows = 0;
 };
 }  // namespace g2v
 
@@ -66,7 +67,9 @@ int gtsfm_match_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, double ra
                                                "(the reference raises ValueError: not enough values to unpack)");
         pd.nq_pad = (pd.nq + kRowPad - 1) / kRowPad * kRowPad;
         pd.nt_pad = (pd.nt + kRowPad - 1) / kRowPad * kRowPad;
-        pd.path = (qa.path == 0 && tb.path == 0 && screen_ok) ? 0 : 1;
+        // the bucketed resolve kernels keep one lane class (nq_pad / 128 rows) in shared memory and use 13-bit half-block ids
+        const bool fits = pd.nq_pad / kTileQ <= kMaxClassRows && pd.nt_pad / kHalfT < 8192;
+        pd.path = (qa.path == 0 && tb.path == 0 && screen_ok && fits) ? 0 : 1;
         const long long rp = pd.path == 0 ? static_cast<long long>(pd.nq_pad) * (pd.nt_pad / kHalfT) : 0;
         const long long cr = pd.path == 0 ? static_cast<long long>(pd.nt_pad) * kTileQ : 0;
         const int items = pd.path == 0 && pd.nq > 0 ? pd.nt_pad / kBlockT : 0;
@@ -76,6 +79,7 @@ int gtsfm_match_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, double ra
         pd.rp_base = cur.rp; pd.cr_base = cur.cr; pd.out_base = cur.rows; pd.cb_base = cur.cols; pd.item0 = cur.items; pd.job0 = cur.jobs;
         cur.rp += rp; cur.cr += cr; cur.rows += pd.nq_pad; cur.cols += pd.nt_pad; cur.items += items; cur.jobs += jobs;
         cur.p1 = p + 1;
+        if (items > 0) cur.max_class_rows = std::max(cur.max_class_rows, pd.nq_pad / kTileQ);
         cur_bytes += bytes;
         out_cap += pd.nq < pd.nt ? pd.nq : pd.nt;
         pds[p] = pd;
@@ -97,6 +101,8 @@ int gtsfm_match_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, double ra
     G2V_CUDA(c, c->col_best.reserve(4 * (m_cols + 1), false, s));
     G2V_CUDA(c, c->col_d1.reserve(4 * (m_cols + 1), false, s));
     G2V_CUDA(c, c->col_d2.reserve(4 * (m_cols + 1), false, s));
+    G2V_CUDA(c, c->row_key.reserve(2 * (m_rows + 16), false, s));
+    G2V_CUDA(c, c->col_key.reserve(m_cols + 16, false, s));
     G2V_CUDA(c, c->flag_list.reserve(8 * (m_rows + m_cols + 1), false, s));
     G2V_CUDA(c, c->n_flag.reserve(sizeof(int), false, s));
     G2V_CUDA(c, c->keys_scratch.reserve(16 * (m_rows + 1), false, s));
@@ -119,6 +125,7 @@ int gtsfm_match_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, double ra
         w.rp_v1 = c->rp_v1.as<float>(); w.rp_v2 = c->rp_v2.as<float>(); w.rp_g = c->rp_g.as<uint8_t>(); w.colraw = c->colraw.as<float>();
         w.row_best = c->row_best.as<int>(); w.row_d1 = c->row_d1.as<float>(); w.row_d2 = c->row_d2.as<float>();
         w.col_best = c->col_best.as<int>(); w.col_d1 = c->col_d1.as<float>(); w.col_d2 = c->col_d2.as<float>();
+        w.row_key = c->row_key.as<unsigned short>(); w.col_key = c->col_key.as<uint8_t>();
         w.flag_list = c->flag_list.as<unsigned long long>(); w.n_flag = c->n_flag.as<int>();
         w.flag_cap = static_cast<int>(std::min<long long>(k.rows + k.cols, 0x7fffffff));
         G2V_CUDA(c, cudaMemsetAsync(c->n_flag.p, 0, sizeof(int), s));
@@ -128,15 +135,15 @@ int gtsfm_match_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, double ra
                                             c->rp_v2.as<float>(), c->rp_g.as<uint8_t>(), c->colraw.as<float>(), c->kpad, c->n_sm, s));
             c->prof_end();
             c->prof_begin(P_RESOLVE_ROWS);
-            G2V_CUDA(c, launch_resolve_int(st, w, 0, k.rows, s));
+            G2V_CUDA(c, launch_resolve_int(st, w, 0, k.rows, k.items, k.max_class_rows, s));
             c->prof_end();
             c->prof_begin(P_RESOLVE_COLS);
-            G2V_CUDA(c, launch_resolve_int(st, w, 1, k.cols, s));
+            G2V_CUDA(c, launch_resolve_int(st, w, 1, k.cols, k.items, k.max_class_rows, s));
             c->prof_end();
             c->prof_begin(P_EXACT_SCAN);
             G2V_CUDA(c, launch_exact_scan(st, w, 1, w.flag_cap, s));
             c->prof_end();
-            c->launches += 4;
+            c->launches += 6;
         }
         if (k.jobs > 0) {
             c->prof_begin(P_EXACT_SCAN);

@@ -31,6 +31,9 @@ struct MatchWork {
     // exact per-row / per-column nearest neighbours, indexed by PairDesc::out_base (+row) and cb_base (+column)
     int* row_best;  float* row_d1;  float* row_d2;
     int* col_best;  float* col_d1;  float* col_d2;
+    // bucket keys of the resolve step: rows -> (winning half block << 3 | winning group), columns -> winning lane class
+    unsigned short* row_key;
+    uint8_t* col_key;
     // rows / columns whose screening result was ambiguous: (pair << 33 | dir << 32 | index), counted by n_flag
     unsigned long long* flag_list;
     int* n_flag;

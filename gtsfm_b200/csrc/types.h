@@ -9,6 +9,7 @@ constexpr int kTileQ = 128;    // query rows per MMA tile (TMEM lanes)
 constexpr int kBlockT = 256;   // train rows held stationary per work item (MMA N)
 constexpr int kHalfT = 128;    // train columns scanned by one epilogue warpgroup
 constexpr int kGroup = 16;     // train columns per "group" whose minimum the screening kernel keeps
+constexpr int kMaxClassRows = 512;   // resolve step: rows of one lane class kept in shared memory (nq <= 65536)
 constexpr int kAugK = 16;      // one extra K step (16 bf16) that folds (|q|^2 + |t|^2) / 2 into the accumulator
 constexpr float kHuge = 1.2676506e30f;   // 2^100: squared norm given to padding / NaN rows so they never win
 
