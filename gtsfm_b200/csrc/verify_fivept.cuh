@@ -7,30 +7,52 @@
 // polish on the ten constraints.  Output: up to 10 unit-Frobenius-norm essential matrices in ascending z.
 // The CPU oracle holds an independent C restatement that is pinned against cv2's own 5-point solver.
 #pragma once
+#include <cstddef>
+
 #include "verify_math.cuh"
 
 namespace vm {
 
 constexpr int kMaxCand = 10;
 
-__device__ __constant__ int c_idx11[4][4] = {{0, 3, 4, 6}, {3, 1, 5, 7}, {4, 5, 2, 8}, {6, 7, 8, 9}};
-__device__ __constant__ int c_idx21[10][4] = {{0, 2, 4, 5},   {3, 1, 6, 7},   {10, 13, 16, 17}, {2, 3, 8, 9},     {4, 8, 10, 11},
-                                              {8, 6, 13, 14}, {5, 9, 11, 12}, {9, 7, 14, 15},   {11, 14, 17, 18}, {12, 15, 18, 19}};
-
-// c (degree 2, 10 coefficients) += s * a (degree 1) * b (degree 1);  monomials x^2 y^2 z^2 xy xz yz x y z 1
-__device__ __forceinline__ void p11_acc(const double* a, const double* b, double s, double* c)
+// Monomial index tables.  They are constexpr functions so that, after full unrolling, every accumulator index is a
+// compile-time constant and the accumulators live in registers (a table in constant memory makes every "+=" a
+// dependent local-memory load / store pair).
+__host__ __device__ constexpr int idx11(int i, int j)
 {
+    constexpr int t[4][4] = {{0, 3, 4, 6}, {3, 1, 5, 7}, {4, 5, 2, 8}, {6, 7, 8, 9}};
+    return t[i][j];
+}
+__host__ __device__ constexpr int idx21(int i, int j)
+{
+    constexpr int t[10][4] = {{0, 2, 4, 5},   {3, 1, 6, 7},   {10, 13, 16, 17}, {2, 3, 8, 9},     {4, 8, 10, 11},
+                              {8, 6, 13, 14}, {5, 9, 11, 12}, {9, 7, 14, 15},   {11, 14, 17, 18}, {12, 15, 18, 19}};
+    return t[i][j];
+}
+
+// c (degree 2, 10 coefficients) += +-a (degree 1) * b (degree 1);  monomials x^2 y^2 z^2 xy xz yz x y z 1
+template <bool NEG> __device__ __forceinline__ void p11_acc(const double* a, const double* b, double* c)
+{
+    double av[4], bv[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { av[i] = NEG ? -a[i] : a[i]; bv[i] = b[i]; }
 #pragma unroll
     for (int i = 0; i < 4; ++i)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) c[c_idx11[i][j]] += s * a[i] * b[j];
+        for (int j = 0; j < 4; ++j) c[idx11(i, j)] = fma(av[i], bv[j], c[idx11(i, j)]);
 }
-// c (degree 3, 20 coefficients) += s * a (degree 2) * b (degree 1)
-__device__ __forceinline__ void p21_acc(const double* a, const double* b, double s, double* c)
+// c (degree 3, 20 coefficients) += +-a (degree 2) * b (degree 1)
+template <bool NEG> __device__ __forceinline__ void p21_acc(const double* a, const double* b, double* c)
 {
-    for (int i = 0; i < 10; ++i)
+    double bv[4];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) c[c_idx21[i][j]] += s * a[i] * b[j];
+    for (int j = 0; j < 4; ++j) bv[j] = NEG ? -b[j] : b[j];
+#pragma unroll
+    for (int i = 0; i < 10; ++i) {
+        const double ai = a[i];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) c[idx21(i, j)] = fma(ai, bv[j], c[idx21(i, j)]);
+    }
 }
 
 __device__ inline bool nullspace_5x9(const double* x1, const double* y1, const double* x2, const double* y2, double N[4][9])
@@ -83,46 +105,67 @@ __device__ __forceinline__ void pmul(const double* a, int da, const double* b, i
     for (int i = 0; i <= da; ++i) for (int j = 0; j <= db; ++j) c[i + j] += a[i] * b[j];
 }
 
-struct Sturm {
-    double S[12][11];
-    int sd[12];
-    int ns;
-    __device__ int changes(double t) const
-    {
-        int cnt = 0, last = 0;
-        for (int s = 0; s < ns; ++s) {
-            const double v = horner(S[s], sd[s], t);
-            const int sg = (v > 0) - (v < 0);
-            if (sg != 0) { if (last != 0 && sg != last) ++cnt; last = sg; }
-        }
-        return cnt;
-    }
-};
+// Sturm chain of a polynomial of degree <= 10, packed triangularly: chain polynomial s (degree <= 10 - s) starts at
+// soff(s) and has 11 - s coefficients, zero-filled above its true degree, so the sign-change count is one fixed,
+// fully unrolled sequence of 55 FMAs for every thread of a warp (no data-dependent control flow).
+constexpr int kSturmLen = 66;
+__host__ __device__ constexpr int soff(int s) { return s * 11 - s * (s - 1) / 2; }
 
-// Real roots (ascending) of a polynomial of degree <= 10; coefficient i multiplies z^i.
-__device__ inline int real_roots_sturm(const double* pin, int deg, double* roots)
+// number of sign changes of the chain at t; *sg0 = sign of the polynomial itself
+__device__ __forceinline__ int sturm_changes(const double* S, double t, int* sg0)
 {
-    double p[11];
+    int cnt = 0, last = 0;
+#pragma unroll
+    for (int s = 0; s < 11; ++s) {
+        const double* q = S + soff(s);
+        double v = q[10 - s];
+#pragma unroll
+        for (int i = 9 - s; i >= 0; --i) v = v * t + q[i];
+        const int sg = (v > 0) - (v < 0);
+        if (s == 0) *sg0 = sg;
+        cnt += (sg != 0 && last != 0 && sg != last) ? 1 : 0;
+        last = (sg != 0) ? sg : last;
+    }
+    return cnt;
+}
+
+// Normalise pin (degree <= 10) into p, build its Sturm chain and isolate every real root: on return lo[r] < hi[r]
+// (ascending, disjoint) brackets exactly one sign change of p when bit r of *mid is clear, and the root is taken as the
+// midpoint of [lo, hi] when the bit is set (multiple / numerically unresolved root, or a root hit exactly).
+// Returns the number of roots; *deg_out = degree after dropping negligible leading coefficients.
+__device__ inline int isolate_roots(const double* pin, double* p, int* deg_out, double* lo_out, double* hi_out, unsigned* mid)
+{
+    int deg = 10;
+    *mid = 0;
+    *deg_out = 0;
     double mx = 0;
     for (int i = 0; i <= deg; ++i) if (fabs(pin[i]) > mx) mx = fabs(pin[i]);
     if (!(mx > 0) || !isfinite(mx)) return 0;
-    for (int i = 0; i <= deg; ++i) p[i] = pin[i] / mx;
+    const double imx = 1.0 / mx;
+    for (int i = 0; i <= 10; ++i) p[i] = pin[i] * imx;
     while (deg > 0 && fabs(p[deg]) < 1e-13) --deg;
+    for (int i = deg + 1; i <= 10; ++i) p[i] = 0;
+    *deg_out = deg;
     if (deg == 0) return 0;
-    Sturm st;
-    for (int i = 0; i <= deg; ++i) st.S[0][i] = p[i];
-    st.sd[0] = deg;
-    for (int i = 1; i <= deg; ++i) st.S[1][i - 1] = i * p[i];
-    st.sd[1] = deg - 1;
-    st.ns = 2;
-    while (st.sd[st.ns - 1] > 0 && st.ns < 12) {
+
+    double S[kSturmLen];
+    for (int i = 0; i < kSturmLen; ++i) S[i] = 0;
+    int sd[12];
+    for (int i = 0; i <= deg; ++i) S[i] = p[i];
+    sd[0] = deg;
+    for (int i = 1; i <= deg; ++i) S[soff(1) + i - 1] = i * p[i];
+    sd[1] = deg - 1;
+    int ns = 2;
+    while (sd[ns - 1] > 0 && ns < 11) {
         double r[11];
-        const int dr = st.sd[st.ns - 2];
-        for (int i = 0; i <= dr; ++i) r[i] = st.S[st.ns - 2][i];
-        const int dd = st.sd[st.ns - 1];
-        const double* d = st.S[st.ns - 1];
+        const int dr = sd[ns - 2];
+        const double* prev = S + soff(ns - 2);
+        for (int i = 0; i <= dr; ++i) r[i] = prev[i];
+        const int dd = sd[ns - 1];
+        const double* d = S + soff(ns - 1);
+        const double idl = 1.0 / d[dd];
         for (int k = dr; k >= dd; --k) {
-            const double f = r[k] / d[dd];
+            const double f = r[k] * idl;
             for (int j = 0; j <= dd; ++j) r[k - dd + j] -= f * d[j];
             r[k] = 0;
         }
@@ -131,61 +174,78 @@ __device__ inline int real_roots_sturm(const double* pin, int deg, double* roots
         for (int i = 0; i <= nd; ++i) if (fabs(r[i]) > rm) rm = fabs(r[i]);
         if (!(rm > 1e-300)) break;
         while (nd > 0 && fabs(r[nd]) < 1e-14 * rm) --nd;
-        for (int i = 0; i <= nd; ++i) st.S[st.ns][i] = -r[i] / rm;
-        st.sd[st.ns] = nd;
-        ++st.ns;
+        const double irm = -1.0 / rm;
+        double* out = S + soff(ns);
+        for (int i = 0; i <= nd; ++i) out[i] = r[i] * irm;
+        sd[ns] = nd;
+        ++ns;
     }
-    double B = 0;
-    for (int k = 1; k <= deg; ++k) { const double v = pow(fabs(p[deg - k] / p[deg]), 1.0 / k); if (v > B) B = v; }
-    B = 2.0 * B + 1e-9;
-    double lo_s[64], hi_s[64];
-    int nlo_s[64], nhi_s[64];
-    int sp = 0, nr = 0;
-    lo_s[0] = -B; hi_s[0] = B; nlo_s[0] = st.changes(-B); nhi_s[0] = st.changes(B); sp = 1;
+    // Fujiwara bound 2 max_k |a_{n-k} / a_n|^(1/k), evaluated in float and inflated
+    float fb = 0.f;
+    const float ilead = 1.0f / static_cast<float>(fabs(p[deg]));
+    for (int k = 1; k <= deg; ++k) {
+        const float a = static_cast<float>(fabs(p[deg - k])) * ilead;
+        const float v = a > 0.f ? exp2f(__log2f(a) / static_cast<float>(k)) : 0.f;
+        fb = fmaxf(fb, v);
+    }
+    const double B = 2.004 * static_cast<double>(fb) + 1e-9;
+
+    // interval stack: entries are disjoint and each holds >= 1 root, so at most 10 are alive
+    double slo[12], shi[12];
+    int sa[12], sb[12];            // sign changes at lo / hi, | (sign of p + 1) << 8
+    int sp = 1, nr = 0, sg;
+    slo[0] = -B; shi[0] = B;
+    sa[0] = sturm_changes(S, -B, &sg); sa[0] |= (sg + 1) << 8;
+    sb[0] = sturm_changes(S, B, &sg);  sb[0] |= (sg + 1) << 8;
     while (sp > 0 && nr < 10) {
         --sp;
-        double lo = lo_s[sp], hi = hi_s[sp];
-        int a = nlo_s[sp];
-        const int b = nhi_s[sp];
+        const double lo = slo[sp], hi = shi[sp];
+        const int A = sa[sp], Bq = sb[sp];
+        const int a = A & 0xff, b = Bq & 0xff, sgl = (A >> 8) - 1, sgh = (Bq >> 8) - 1;
         const int cnt = a - b;
         if (cnt <= 0) continue;
-        if (cnt > 1 && (hi - lo) > 1e-13 * (1.0 + fabs(lo) + fabs(hi))) {
-            const double mid = 0.5 * (lo + hi);
-            const int m = st.changes(mid);
-            if (sp + 2 > 64) continue;
-            lo_s[sp] = mid; hi_s[sp] = hi; nlo_s[sp] = m; nhi_s[sp] = b; ++sp;
-            lo_s[sp] = lo; hi_s[sp] = mid; nlo_s[sp] = a; nhi_s[sp] = m; ++sp;
-            continue;
-        }
-        if (cnt > 1) { roots[nr++] = 0.5 * (lo + hi); continue; }
-        const double flo = horner(p, deg, lo), fhi = horner(p, deg, hi);
-        if (fhi == 0.0) { roots[nr++] = hi; continue; }
-        double x = 0.5 * (lo + hi);
-        if ((flo > 0) == (fhi > 0)) {
-            for (int it = 0; it < 80 && (hi - lo) > 1e-15 * (1.0 + fabs(x)); ++it) {
-                x = 0.5 * (lo + hi);
-                const int m = st.changes(x);
-                if (a - m >= 1) hi = x; else { lo = x; a = m; }
-            }
-            roots[nr++] = 0.5 * (lo + hi);
-            continue;
-        }
-        double dxold = hi - lo;
-        for (int it = 0; it < 200; ++it) {
-            const double f = horner(p, deg, x);
-            if (f == 0.0) break;
-            if ((f > 0) == (flo > 0)) lo = x; else hi = x;
-            double dp = 0;
-            for (int i = deg; i >= 1; --i) dp = dp * x + i * p[i];
-            double xn = (dp != 0.0) ? x - f / dp : x;
-            if (!(xn > lo && xn < hi) || fabs(xn - x) > 0.5 * fabs(dxold)) xn = 0.5 * (lo + hi);
-            dxold = xn - x;
-            if (fabs(dxold) <= 4e-16 * (1.0 + fabs(x))) { x = xn; break; }
-            x = xn;
-        }
-        roots[nr++] = x;
+        const bool tiny = !((hi - lo) > 1e-13 * (1.0 + fabs(lo) + fabs(hi)));
+        if (cnt == 1 && sgh == 0) { lo_out[nr] = hi; hi_out[nr] = hi; *mid |= 1u << nr; ++nr; continue; }
+        if (cnt == 1 && sgl * sgh < 0) { lo_out[nr] = lo; hi_out[nr] = hi; ++nr; continue; }
+        if (tiny) { lo_out[nr] = lo; hi_out[nr] = hi; *mid |= 1u << nr; ++nr; continue; }
+        const double m = 0.5 * (lo + hi);
+        int sgm;
+        const int cm = sturm_changes(S, m, &sgm);
+        const int M = cm | ((sgm + 1) << 8);
+        if (cm - b > 0) { slo[sp] = m; shi[sp] = hi; sa[sp] = M; sb[sp] = Bq; ++sp; }
+        if (a - cm > 0) { slo[sp] = lo; shi[sp] = m; sa[sp] = A; sb[sp] = M; ++sp; }
     }
     return nr;
+}
+
+// Root of p (degree <= 10, zero-filled above its degree) inside the isolating bracket [lo, hi] (opposite signs at the
+// ends): safeguarded Newton.  p and p' come from one unrolled Horner recurrence.
+__device__ inline double refine_root(const double* p, double lo, double hi)
+{
+    double pc[11];
+#pragma unroll
+    for (int i = 0; i <= 10; ++i) pc[i] = p[i];
+    double flo = pc[10];
+#pragma unroll
+    for (int i = 9; i >= 0; --i) flo = flo * lo + pc[i];
+    double x = 0.5 * (lo + hi);
+    double dxold = hi - lo;
+    for (int it = 0; it < 200; ++it) {
+        double f = pc[10], dp = 0.0;
+#pragma unroll
+        for (int i = 9; i >= 0; --i) { dp = dp * x + f; f = f * x + pc[i]; }
+        if (f == 0.0) break;
+        if ((f > 0) == (flo > 0)) lo = x; else hi = x;
+        double xn = (dp != 0.0) ? x - f / dp : x;
+        if (!(xn > lo && xn < hi) || fabs(xn - x) > 0.5 * fabs(dxold)) xn = 0.5 * (lo + hi);
+        const double dx = xn - x, tol = 1.0 + fabs(x);
+        // converged, or Newton has reached its noise floor (ill-conditioned root: the step no longer shrinks)
+        const bool done = fabs(dx) <= 4e-16 * tol || (it >= 6 && fabs(dx) <= 1e-11 * tol && fabs(dx) >= fabs(dxold));
+        dxold = dx;
+        x = xn;
+        if (done) break;
+    }
+    return x;
 }
 
 // r[0] = det E, r[1..9] = 2 E E^T E - tr(E E^T) E
@@ -242,97 +302,177 @@ __device__ inline void polish_xyz(const double N[4][9], double* xyz)
     }
 }
 
-// Five normalised correspondences -> up to kMaxCand essential matrices (row-major, unit Frobenius norm), ascending z.
-__device__ inline int fivept(const double* x1, const double* y1, const double* x2, const double* y2, double* Eout)
+// Everything the per-root phase needs about one hypothesis.  The first kHypDoubles doubles are plain data so the solve
+// kernel can hand the state from the per-hypothesis phase to the per-root phase through shared memory.
+struct HypState {
+    double N[4][9];                          // null-space basis: E = x N0 + y N1 + z N2 + N3
+    double Bx[3][4], By[3][4], Bc[3][5];     // B(z) [x y 1]^T = 0
+    double p[11];                            // normalised degree-10 polynomial det B(z)
+    double lo[10], hi[10];                   // isolating brackets of its real roots, ascending
+    int deg, nr;
+    unsigned mid;                            // bit r: root r = midpoint of its bracket
+};
+constexpr int kHypDoubles = 36 + 12 + 12 + 15 + 11 + 20;
+static_assert(offsetof(HypState, deg) == kHypDoubles * 8, "HypState layout");
+
+// Phase A (once per hypothesis): five normalised correspondences -> null space, the ten cubic constraints, their
+// Gauss-Jordan reduction, det B(z) and the isolating brackets of its real roots.  Returns the number of roots.
+__device__ inline int fivept_isolate(const double* x1, const double* y1, const double* x2, const double* y2, HypState& hs)
 {
-    double N[4][9];
-    if (!nullspace_5x9(x1, y1, x2, y2, N)) return 0;
+    hs.nr = 0; hs.deg = 0; hs.mid = 0;
+    if (!nullspace_5x9(x1, y1, x2, y2, hs.N)) return 0;
     double Ep[9][4];
-    for (int e = 0; e < 9; ++e) for (int k = 0; k < 4; ++k) Ep[e][k] = N[k][e];
+    for (int e = 0; e < 9; ++e) for (int k = 0; k < 4; ++k) Ep[e][k] = hs.N[k][e];
     double C[10][20];
-    for (int i = 0; i < 10; ++i) for (int j = 0; j < 20; ++j) C[i][j] = 0;
     {   // det(E) = 0
-        double m[3][10];
-        for (int i = 0; i < 3; ++i) for (int j = 0; j < 10; ++j) m[i][j] = 0;
-        p11_acc(Ep[4], Ep[8], 1.0, m[0]); p11_acc(Ep[5], Ep[7], -1.0, m[0]);
-        p11_acc(Ep[3], Ep[8], 1.0, m[1]); p11_acc(Ep[5], Ep[6], -1.0, m[1]);
-        p11_acc(Ep[3], Ep[7], 1.0, m[2]); p11_acc(Ep[4], Ep[6], -1.0, m[2]);
-        p21_acc(m[0], Ep[0], 1.0, C[0]); p21_acc(m[1], Ep[1], -1.0, C[0]); p21_acc(m[2], Ep[2], 1.0, C[0]);
+        double m0[10], m1[10], m2[10], row[20];
+#pragma unroll
+        for (int k = 0; k < 10; ++k) { m0[k] = 0; m1[k] = 0; m2[k] = 0; }
+#pragma unroll
+        for (int k = 0; k < 20; ++k) row[k] = 0;
+        p11_acc<false>(Ep[4], Ep[8], m0); p11_acc<true>(Ep[5], Ep[7], m0);
+        p11_acc<false>(Ep[3], Ep[8], m1); p11_acc<true>(Ep[5], Ep[6], m1);
+        p11_acc<false>(Ep[3], Ep[7], m2); p11_acc<true>(Ep[4], Ep[6], m2);
+        p21_acc<false>(m0, Ep[0], row); p21_acc<true>(m1, Ep[1], row); p21_acc<false>(m2, Ep[2], row);
+#pragma unroll
+        for (int k = 0; k < 20; ++k) C[0][k] = row[k];
     }
     {   // (E E^T - 1/2 tr(E E^T) I) E = 0
         double G[3][3][10];
-        for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) for (int k = 0; k < 10; ++k) G[i][j][k] = 0;
+#pragma unroll 1
         for (int i = 0; i < 3; ++i)
+#pragma unroll 1
             for (int j = i; j < 3; ++j) {
-                for (int k = 0; k < 3; ++k) p11_acc(Ep[3 * i + k], Ep[3 * j + k], 1.0, G[i][j]);
-                if (j != i) for (int k = 0; k < 10; ++k) G[j][i][k] = G[i][j][k];
+                double g[10];
+#pragma unroll
+                for (int k = 0; k < 10; ++k) g[k] = 0;
+#pragma unroll
+                for (int k = 0; k < 3; ++k) p11_acc<false>(Ep[3 * i + k], Ep[3 * j + k], g);
+#pragma unroll
+                for (int k = 0; k < 10; ++k) { G[i][j][k] = g[k]; G[j][i][k] = g[k]; }
             }
-        double tr[10];
-        for (int k = 0; k < 10; ++k) tr[k] = 0.5 * (G[0][0][k] + G[1][1][k] + G[2][2][k]);
-        for (int i = 0; i < 3; ++i) for (int k = 0; k < 10; ++k) G[i][i][k] -= tr[k];
+#pragma unroll
+        for (int k = 0; k < 10; ++k) {
+            const double tr = 0.5 * (G[0][0][k] + G[1][1][k] + G[2][2][k]);
+            G[0][0][k] -= tr; G[1][1][k] -= tr; G[2][2][k] -= tr;
+        }
+#pragma unroll 1
         for (int i = 0; i < 3; ++i)
-            for (int j = 0; j < 3; ++j)
-                for (int k = 0; k < 3; ++k) p21_acc(G[i][k], Ep[3 * k + j], 1.0, C[1 + 3 * i + j]);
+#pragma unroll 1
+            for (int j = 0; j < 3; ++j) {
+                double row[20];
+#pragma unroll
+                for (int k = 0; k < 20; ++k) row[k] = 0;
+#pragma unroll
+                for (int k = 0; k < 3; ++k) {
+                    double g[10];
+#pragma unroll
+                    for (int u = 0; u < 10; ++u) g[u] = G[i][k][u];
+                    p21_acc<false>(g, Ep[3 * k + j], row);
+                }
+#pragma unroll
+                for (int k = 0; k < 20; ++k) C[1 + 3 * i + j][k] = row[k];
+            }
     }
-    for (int k = 0; k < 10; ++k) {   // Gauss-Jordan with row pivoting on the first ten columns
-        int pr = k;
-        double best = fabs(C[k][k]);
-        for (int r = k + 1; r < 10; ++r) if (fabs(C[r][k]) > best) { best = fabs(C[r][k]); pr = r; }
+    // Gaussian elimination with row pivoting on the first ten columns.  Rows are not swapped: the pivot row of column k
+    // is read out with a statically indexed, predicated copy (a per-thread row index would scatter the warp's local
+    // memory accesses over 64 cache lines), scaled to unit pivot and kept as P[k]; only rows 4..9 are needed later.
+    double P[6][15];                 // pivot rows 4..9: columns 5..9 (index c - 5) and 10..19 (index c - 5)
+    unsigned used = 0;
+#pragma unroll 1
+    for (int k = 0; k < 10; ++k) {
+        int pr = -1;
+        double best = -1.0, pv = 0.0;
+#pragma unroll
+        for (int r = 0; r < 10; ++r) {
+            const double v = C[r][k], av = fabs(v);
+            if (!((used >> r) & 1u) && av > best) { best = av; pr = r; pv = v; }
+        }
         if (!(best > 1e-300)) return 0;
-        if (pr != k) for (int c = 0; c < 20; ++c) { const double t = C[k][c]; C[k][c] = C[pr][c]; C[pr][c] = t; }
-        const double inv = 1.0 / C[k][k];
-        for (int c = k; c < 20; ++c) C[k][c] *= inv;
+        used |= 1u << pr;
+        double prow[20];
+#pragma unroll
+        for (int c = 0; c < 20; ++c) prow[c] = 0;
+#pragma unroll
         for (int r = 0; r < 10; ++r)
-            if (r != k) { const double f = C[r][k]; if (f != 0.0) for (int c = k; c < 20; ++c) C[r][c] -= f * C[k][c]; }
+            if (r == pr) {
+#pragma unroll
+                for (int c = 0; c < 20; ++c) if (c >= 10 || c > k) prow[c] = C[r][c];
+            }
+        const double inv = 1.0 / pv;
+#pragma unroll
+        for (int c = 0; c < 20; ++c) prow[c] *= inv;
+        if (k >= 4) {
+#pragma unroll
+            for (int c = 5; c < 20; ++c) P[k - 4][c - 5] = prow[c];
+        }
+#pragma unroll
+        for (int r = 0; r < 10; ++r) {
+            if ((used >> r) & 1u) continue;
+            const double f = -C[r][k];
+#pragma unroll
+            for (int c = 0; c < 20; ++c) if (c >= 10 || c > k) C[r][c] = fma(f, prow[c], C[r][c]);
+        }
     }
+    // back substitution of the right half, pivot rows 8..4
+#pragma unroll
+    for (int i = 8; i >= 4; --i)
+#pragma unroll
+        for (int k = i + 1; k < 10; ++k) {
+            const double f = -P[i - 4][k - 5];
+#pragma unroll
+            for (int c = 10; c < 20; ++c) P[i - 4][c - 5] = fma(f, P[k - 4][c - 5], P[i - 4][c - 5]);
+        }
     // B(z) [x y 1]^T = 0; columns 10 xz^2, 11 xz, 12 x, 13 yz^2, 14 yz, 15 y, 16 z^3, 17 z^2, 18 z, 19 1
-    double Bx[3][4], By[3][4], Bc[3][5];
+#pragma unroll
     for (int q = 0; q < 3; ++q) {
-        const double* a = C[4 + 2 * q];
-        const double* b = C[5 + 2 * q];
-        Bx[q][0] = a[12]; Bx[q][1] = a[11] - b[12]; Bx[q][2] = a[10] - b[11]; Bx[q][3] = -b[10];
-        By[q][0] = a[15]; By[q][1] = a[14] - b[15]; By[q][2] = a[13] - b[14]; By[q][3] = -b[13];
-        Bc[q][0] = a[19]; Bc[q][1] = a[18] - b[19]; Bc[q][2] = a[17] - b[18]; Bc[q][3] = a[16] - b[17]; Bc[q][4] = -b[16];
+        const double* a = P[2 * q];          // column c sits at index c - 5
+        const double* b = P[2 * q + 1];
+        hs.Bx[q][0] = a[7];  hs.Bx[q][1] = a[6] - b[7];   hs.Bx[q][2] = a[5] - b[6];  hs.Bx[q][3] = -b[5];
+        hs.By[q][0] = a[10]; hs.By[q][1] = a[9] - b[10];  hs.By[q][2] = a[8] - b[9];  hs.By[q][3] = -b[8];
+        hs.Bc[q][0] = a[14]; hs.Bc[q][1] = a[13] - b[14]; hs.Bc[q][2] = a[12] - b[13]; hs.Bc[q][3] = a[11] - b[12]; hs.Bc[q][4] = -b[11];
     }
     double poly[11], t1[8], t2[8], t3[11];
     for (int i = 0; i < 11; ++i) poly[i] = 0;
-    pmul(By[1], 3, Bc[2], 4, t1); pmul(Bc[1], 4, By[2], 3, t2); for (int i = 0; i < 8; ++i) t1[i] -= t2[i];
-    pmul(Bx[0], 3, t1, 7, t3); for (int i = 0; i < 11; ++i) poly[i] += t3[i];
-    pmul(Bx[1], 3, Bc[2], 4, t1); pmul(Bc[1], 4, Bx[2], 3, t2); for (int i = 0; i < 8; ++i) t1[i] -= t2[i];
-    pmul(By[0], 3, t1, 7, t3); for (int i = 0; i < 11; ++i) poly[i] -= t3[i];
+    pmul(hs.By[1], 3, hs.Bc[2], 4, t1); pmul(hs.Bc[1], 4, hs.By[2], 3, t2); for (int i = 0; i < 8; ++i) t1[i] -= t2[i];
+    pmul(hs.Bx[0], 3, t1, 7, t3); for (int i = 0; i < 11; ++i) poly[i] += t3[i];
+    pmul(hs.Bx[1], 3, hs.Bc[2], 4, t1); pmul(hs.Bc[1], 4, hs.Bx[2], 3, t2); for (int i = 0; i < 8; ++i) t1[i] -= t2[i];
+    pmul(hs.By[0], 3, t1, 7, t3); for (int i = 0; i < 11; ++i) poly[i] -= t3[i];
     {
         double u1[7], u2[7];
-        pmul(Bx[1], 3, By[2], 3, u1); pmul(By[1], 3, Bx[2], 3, u2);
+        pmul(hs.Bx[1], 3, hs.By[2], 3, u1); pmul(hs.By[1], 3, hs.Bx[2], 3, u2);
         for (int i = 0; i < 7; ++i) u1[i] -= u2[i];
-        pmul(Bc[0], 4, u1, 6, t3);
+        pmul(hs.Bc[0], 4, u1, 6, t3);
         for (int i = 0; i < 11; ++i) poly[i] += t3[i];
     }
-    double roots[10];
-    const int nr = real_roots_sturm(poly, 10, roots);
-    int ne = 0;
-    for (int r = 0; r < nr && ne < kMaxCand; ++r) {
-        const double z = roots[r];
-        double bm[3][3];
-        for (int q = 0; q < 3; ++q) { bm[q][0] = horner(Bx[q], 3, z); bm[q][1] = horner(By[q], 3, z); bm[q][2] = horner(Bc[q], 4, z); }
-        double best = -1, bv[3] = {0, 0, 0};
-        for (int a = 0; a < 3; ++a)
-            for (int b = a + 1; b < 3; ++b) {
-                double v[3];
-                cross3(bm[a], bm[b], v);
-                if (fabs(v[2]) > best) { best = fabs(v[2]); bv[0] = v[0]; bv[1] = v[1]; bv[2] = v[2]; }
-            }
-        if (!(best > 0)) continue;
-        double xyz[3] = {bv[0] / bv[2], bv[1] / bv[2], z};
-        if (!isfinite(xyz[0]) || !isfinite(xyz[1])) continue;
-        polish_xyz(N, xyz);
-        double E[9], nn = 0;
-        for (int e = 0; e < 9; ++e) { E[e] = xyz[0] * N[0][e] + xyz[1] * N[1][e] + xyz[2] * N[2][e] + N[3][e]; nn += E[e] * E[e]; }
-        if (!(nn > 0) || !isfinite(nn)) continue;
-        nn = 1.0 / sqrt(nn);
-        for (int e = 0; e < 9; ++e) Eout[9 * ne + e] = E[e] * nn;
-        ++ne;
-    }
-    return ne;
+    hs.nr = isolate_roots(poly, hs.p, &hs.deg, hs.lo, hs.hi, &hs.mid);
+    return hs.nr;
+}
+
+// Phase B (once per real root): root r -> (x, y) from the null vector of B(z), Gauss-Newton polish, unit-norm E.
+// false when the root yields no finite essential matrix.
+__device__ inline bool fivept_root(const HypState& hs, int r, double* Eout)
+{
+    const double z = ((hs.mid >> r) & 1u) ? 0.5 * (hs.lo[r] + hs.hi[r]) : refine_root(hs.p, hs.lo[r], hs.hi[r]);
+    double bm[3][3];
+    for (int q = 0; q < 3; ++q) { bm[q][0] = horner(hs.Bx[q], 3, z); bm[q][1] = horner(hs.By[q], 3, z); bm[q][2] = horner(hs.Bc[q], 4, z); }
+    double best = -1, bv[3] = {0, 0, 0};
+    for (int a = 0; a < 3; ++a)
+        for (int b = a + 1; b < 3; ++b) {
+            double v[3];
+            cross3(bm[a], bm[b], v);
+            if (fabs(v[2]) > best) { best = fabs(v[2]); bv[0] = v[0]; bv[1] = v[1]; bv[2] = v[2]; }
+        }
+    if (!(best > 0)) return false;
+    double xyz[3] = {bv[0] / bv[2], bv[1] / bv[2], z};
+    if (!isfinite(xyz[0]) || !isfinite(xyz[1])) return false;
+    polish_xyz(hs.N, xyz);
+    double E[9], nn = 0;
+    for (int e = 0; e < 9; ++e) { E[e] = xyz[0] * hs.N[0][e] + xyz[1] * hs.N[1][e] + xyz[2] * hs.N[2][e] + hs.N[3][e]; nn += E[e] * E[e]; }
+    if (!(nn > 0) || !isfinite(nn)) return false;
+    nn = 1.0 / sqrt(nn);
+    for (int e = 0; e < 9; ++e) Eout[e] = E[e] * nn;
+    return true;
 }
 
 }  // namespace vm

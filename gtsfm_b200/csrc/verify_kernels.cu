@@ -56,8 +56,8 @@ __device__ __forceinline__ void hypothesis_samples(const VerifyBufs& b, const Ve
     }
 }
 
-// solve hypothesis h of pair p into Es (fp64); returns the number of essential matrices
-__device__ int solve_hypothesis(const VerifyBufs& b, const VerifyDims& d, int p, int h, double* Es)
+// phase A of hypothesis h of pair p
+__device__ int isolate_hypothesis(const VerifyBufs& b, const VerifyDims& d, int p, int h, vm::HypState& hs)
 {
     const VPair& vp = b.pairs[p];
     int s[5];
@@ -68,21 +68,76 @@ __device__ int solve_hypothesis(const VerifyBufs& b, const VerifyDims& d, int p,
         const double4 c = b.corr_d[vp.m0 + idx];
         x1[k] = c.x; y1[k] = c.y; x2[k] = c.z; y2[k] = c.w;
     }
-    return vm::fivept(x1, y1, x2, y2, Es);
+    return vm::fivept_isolate(x1, y1, x2, y2, hs);
 }
 
 // ---------------------------------------------------------------------------------------------------------------- K4
-__global__ void __launch_bounds__(128) solve_kernel(VerifyBufs b, VerifyDims d, int n_pairs)
+// Persistent CTAs over blocks of 128 hypotheses.  Phase A runs one hypothesis per thread and leaves its state in
+// shared memory ([field][thread], conflict-free); the real roots of the block are then compacted so that phase B
+// (root refinement, back-substitution, polish) runs one ROOT per thread with full warps, whatever the number of
+// real roots each hypothesis has.  Slot r of a hypothesis holds the essential matrix of its r-th root (ascending z),
+// NaN when the root gave no finite matrix.
+constexpr int kSolveThreads = 128;
+constexpr int kSolveSmem = vm::kHypDoubles * kSolveThreads * 8;
+
+__global__ void __launch_bounds__(kSolveThreads, 2) solve_kernel(VerifyBufs b, VerifyDims d, int n_pairs)
 {
-    const long long g = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
-    const int p = static_cast<int>(g / d.H), h = static_cast<int>(g - static_cast<long long>(p) * d.H);
-    if (p >= n_pairs) return;
-    if (b.pairs[p].status != 0) { b.ncand[g] = 0; return; }
-    double Es[9 * vm::kMaxCand];
-    const int ne = solve_hypothesis(b, d, p, h, Es);
-    float* dst = b.E32 + g * (9 * vm::kMaxCand);
-    for (int k = 0; k < 9 * ne; ++k) dst[k] = static_cast<float>(Es[k]);
-    b.ncand[g] = static_cast<unsigned char>(ne);
+    extern __shared__ double s_h[];                       // [kHypDoubles][kSolveThreads]
+    __shared__ int s_meta[kSolveThreads];                 // nr | deg << 8
+    __shared__ unsigned s_mid[kSolveThreads];
+    __shared__ int s_off[kSolveThreads + 1];
+    __shared__ unsigned short s_map[kSolveThreads * vm::kMaxCand];
+    __shared__ int s_wsum[kSolveThreads / 32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const long long total = static_cast<long long>(n_pairs) * d.H;
+    const long long n_blocks = (total + kSolveThreads - 1) / kSolveThreads;
+    for (long long blk = blockIdx.x; blk < n_blocks; blk += gridDim.x) {
+        const long long g = blk * kSolveThreads + tid;
+        int nr = 0;
+        if (g < total) {
+            const int p = static_cast<int>(g / d.H), h = static_cast<int>(g - static_cast<long long>(p) * d.H);
+            if (b.pairs[p].status == 0) {
+                vm::HypState hs;
+                nr = isolate_hypothesis(b, d, p, h, hs);
+                if (nr > 0) {
+                    const double* src = reinterpret_cast<const double*>(&hs);
+#pragma unroll 2
+                    for (int f = 0; f < vm::kHypDoubles; ++f) s_h[f * kSolveThreads + tid] = src[f];
+                    s_meta[tid] = nr | (hs.deg << 8);
+                    s_mid[tid] = hs.mid;
+                }
+            }
+            b.ncand[g] = static_cast<unsigned char>(nr);
+        }
+        // exclusive prefix sum of nr over the block
+        int inc = nr;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) { const int v = __shfl_up_sync(0xffffffffu, inc, off); if (lane >= off) inc += v; }
+        if (lane == 31) s_wsum[warp] = inc;
+        __syncthreads();
+        int base = 0;
+        for (int w2 = 0; w2 < warp; ++w2) base += s_wsum[w2];
+        const int excl = base + inc - nr;
+        s_off[tid] = excl;
+        if (tid == kSolveThreads - 1) s_off[kSolveThreads] = excl + nr;
+        for (int r = 0; r < nr; ++r) s_map[excl + r] = static_cast<unsigned short>((tid << 4) | r);
+        __syncthreads();
+        const int n_roots = s_off[kSolveThreads];
+        for (int idx = tid; idx < n_roots; idx += kSolveThreads) {
+            const int code = s_map[idx], j = code >> 4, r = code & 15;
+            vm::HypState hs;
+            double* dst = reinterpret_cast<double*>(&hs);
+#pragma unroll 2
+            for (int f = 0; f < vm::kHypDoubles; ++f) dst[f] = s_h[f * kSolveThreads + j];
+            hs.nr = s_meta[j] & 0xff; hs.deg = s_meta[j] >> 8; hs.mid = s_mid[j];
+            double E[9];
+            const bool ok = vm::fivept_root(hs, r, E);
+            float* out = b.E32 + ((blk * kSolveThreads + j) * vm::kMaxCand + r) * 9;
+#pragma unroll
+            for (int e = 0; e < 9; ++e) out[e] = ok ? static_cast<float>(E[e]) : __int_as_float(0x7fc00000);
+        }
+        __syncthreads();
+    }
 }
 
 // ---------------------------------------------------------------------------------------------------------------- K5
@@ -339,12 +394,22 @@ __global__ void __launch_bounds__(kFinThreads) finalize_kernel(VerifyBufs b, Ver
     }
     if (n_top == 0) { if (tid == 0) b.status[p] = 2; return; }
 
-    // ---- (b) re-solve those hypotheses in fp64
+    // ---- (b) re-solve those hypotheses in fp64; the wanted root is the one whose matrix is closest to the fp32 copy
     if (tid < n_top) {
-        const int h = s_topi[tid] / vm::kMaxCand, c = s_topi[tid] - h * vm::kMaxCand;
-        double Es[9 * vm::kMaxCand];
-        const int ne = solve_hypothesis(b, d, p, h, Es);
-        for (int e = 0; e < 9; ++e) s_Ek[tid][e] = (c < ne) ? Es[9 * c + e] : nan("");
+        const int h = s_topi[tid] / vm::kMaxCand;
+        const float* e32 = b.E32 + (static_cast<long long>(p) * d.H) * (9 * vm::kMaxCand) + static_cast<long long>(s_topi[tid]) * 9;
+        vm::HypState hs;
+        const int nr = isolate_hypothesis(b, d, p, h, hs);
+        double bestdot = -1.0, Eb[9];
+        for (int e = 0; e < 9; ++e) Eb[e] = nan("");
+        for (int r = 0; r < nr; ++r) {
+            double E[9];
+            if (!vm::fivept_root(hs, r, E)) continue;
+            double dot = 0;
+            for (int e = 0; e < 9; ++e) dot += E[e] * static_cast<double>(e32[e]);
+            if (fabs(dot) > bestdot) { bestdot = fabs(dot); for (int e = 0; e < 9; ++e) Eb[e] = E[e]; }
+        }
+        for (int e = 0; e < 9; ++e) s_Ek[tid][e] = Eb[e];
     }
     __syncthreads();
 
@@ -498,14 +563,20 @@ cudaError_t launch_verify_step(int step, const StoreView& st, const VerifyBufs& 
     if (!configured) {
         cudaError_t e = cudaFuncSetAttribute(score_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kScoreTile * 16);
         if (e != cudaSuccess) return e;
+        e = cudaFuncSetAttribute(solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSolveSmem);
+        if (e != cudaSuccess) return e;
         configured = true;
     }
     if (step == 0) {
         const int gx = max_m > 0 ? (max_m + 255) / 256 : 1;
         gather_normalize_kernel<<<dim3(gx, n_pairs), 256, 0, s>>>(st, b, n_pairs);
     } else if (step == 1) {
-        const long long nh = static_cast<long long>(n_pairs) * d.H;
-        solve_kernel<<<static_cast<unsigned>((nh + 127) / 128), 128, 0, s>>>(b, d, n_pairs);
+        const long long nb = (static_cast<long long>(n_pairs) * d.H + kSolveThreads - 1) / kSolveThreads;
+        int n_sm = 148, dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
+        const long long grid = nb < 2LL * n_sm ? nb : 2LL * n_sm;
+        solve_kernel<<<static_cast<unsigned>(grid), kSolveThreads, kSolveSmem, s>>>(b, d, n_pairs);
     } else if (step == 2) {
         score_kernel<<<dim3((d.H + kScoreHyp - 1) / kScoreHyp, n_pairs), 256, kScoreTile * 16, s>>>(b, d, n_pairs);
     } else {
