@@ -15,6 +15,15 @@ namespace vm {
 
 constexpr int kMaxCand = 10;
 
+// Per-thread scratch of kWorkDoubles doubles: element i of the calling thread sits at base[i * STRIDE].  The solve kernel
+// keeps it in shared memory ([element][thread], STRIDE = threads per CTA: conflict-free and out of the L1/L2 path that
+// thread-local arrays take); the finalize kernel does the same for its few re-solving threads.
+constexpr int kWorkDoubles = 200;
+template <int STRIDE> struct Work {
+    double* base;
+    __device__ __forceinline__ double& operator()(int i) const { return base[i * STRIDE]; }
+};
+
 // Monomial index tables.  They are constexpr functions so that, after full unrolling, every accumulator index is a
 // compile-time constant and the accumulators live in registers (a table in constant memory makes every "+=" a
 // dependent local-memory load / store pair).
@@ -112,15 +121,14 @@ constexpr int kSturmLen = 66;
 __host__ __device__ constexpr int soff(int s) { return s * 11 - s * (s - 1) / 2; }
 
 // number of sign changes of the chain at t; *sg0 = sign of the polynomial itself
-__device__ __forceinline__ int sturm_changes(const double* S, double t, int* sg0)
+template <class W> __device__ __forceinline__ int sturm_changes(const W& S, double t, int* sg0)
 {
     int cnt = 0, last = 0;
 #pragma unroll
     for (int s = 0; s < 11; ++s) {
-        const double* q = S + soff(s);
-        double v = q[10 - s];
+        double v = S(soff(s) + 10 - s);
 #pragma unroll
-        for (int i = 9 - s; i >= 0; --i) v = v * t + q[i];
+        for (int i = 9 - s; i >= 0; --i) v = v * t + S(soff(s) + i);
         const int sg = (v > 0) - (v < 0);
         if (s == 0) *sg0 = sg;
         cnt += (sg != 0 && last != 0 && sg != last) ? 1 : 0;
@@ -133,7 +141,8 @@ __device__ __forceinline__ int sturm_changes(const double* S, double t, int* sg0
 // (ascending, disjoint) brackets exactly one sign change of p when bit r of *mid is clear, and the root is taken as the
 // midpoint of [lo, hi] when the bit is set (multiple / numerically unresolved root, or a root hit exactly).
 // Returns the number of roots; *deg_out = degree after dropping negligible leading coefficients.
-__device__ inline int isolate_roots(const double* pin, double* p, int* deg_out, double* lo_out, double* hi_out, unsigned* mid)
+template <class W>
+__device__ inline int isolate_roots(const double* pin, double* p, int* deg_out, double* lo_out, double* hi_out, unsigned* mid, const W& S)
 {
     int deg = 10;
     *mid = 0;
@@ -148,21 +157,19 @@ __device__ inline int isolate_roots(const double* pin, double* p, int* deg_out, 
     *deg_out = deg;
     if (deg == 0) return 0;
 
-    double S[kSturmLen];
-    for (int i = 0; i < kSturmLen; ++i) S[i] = 0;
+    for (int i = 0; i < kSturmLen; ++i) S(i) = 0;
     int sd[12];
-    for (int i = 0; i <= deg; ++i) S[i] = p[i];
+    for (int i = 0; i <= deg; ++i) S(i) = p[i];
     sd[0] = deg;
-    for (int i = 1; i <= deg; ++i) S[soff(1) + i - 1] = i * p[i];
+    for (int i = 1; i <= deg; ++i) S(soff(1) + i - 1) = i * p[i];
     sd[1] = deg - 1;
     int ns = 2;
     while (sd[ns - 1] > 0 && ns < 11) {
-        double r[11];
-        const int dr = sd[ns - 2];
-        const double* prev = S + soff(ns - 2);
-        for (int i = 0; i <= dr; ++i) r[i] = prev[i];
-        const int dd = sd[ns - 1];
-        const double* d = S + soff(ns - 1);
+        double r[11], d[11];
+        const int dr = sd[ns - 2], dd = sd[ns - 1];
+        const int o2 = soff(ns - 2), o1 = soff(ns - 1);
+        for (int i = 0; i <= dr; ++i) r[i] = S(o2 + i);
+        for (int i = 0; i <= dd; ++i) d[i] = S(o1 + i);
         const double idl = 1.0 / d[dd];
         for (int k = dr; k >= dd; --k) {
             const double f = r[k] * idl;
@@ -175,8 +182,8 @@ __device__ inline int isolate_roots(const double* pin, double* p, int* deg_out, 
         if (!(rm > 1e-300)) break;
         while (nd > 0 && fabs(r[nd]) < 1e-14 * rm) --nd;
         const double irm = -1.0 / rm;
-        double* out = S + soff(ns);
-        for (int i = 0; i <= nd; ++i) out[i] = r[i] * irm;
+        const int o0 = soff(ns);
+        for (int i = 0; i <= nd; ++i) S(o0 + i) = r[i] * irm;
         sd[ns] = nd;
         ++ns;
     }
@@ -317,13 +324,14 @@ static_assert(offsetof(HypState, deg) == kHypDoubles * 8, "HypState layout");
 
 // Phase A (once per hypothesis): five normalised correspondences -> null space, the ten cubic constraints, their
 // Gauss-Jordan reduction, det B(z) and the isolating brackets of its real roots.  Returns the number of roots.
-__device__ inline int fivept_isolate(const double* x1, const double* y1, const double* x2, const double* y2, HypState& hs)
+template <class W>
+__device__ inline int fivept_isolate(const double* x1, const double* y1, const double* x2, const double* y2, HypState& hs, const W& wk)
 {
     hs.nr = 0; hs.deg = 0; hs.mid = 0;
     if (!nullspace_5x9(x1, y1, x2, y2, hs.N)) return 0;
     double Ep[9][4];
     for (int e = 0; e < 9; ++e) for (int k = 0; k < 4; ++k) Ep[e][k] = hs.N[k][e];
-    double C[10][20];
+    // C[r][c] = wk(r * 20 + c)
     {   // det(E) = 0
         double m0[10], m1[10], m2[10], row[20];
 #pragma unroll
@@ -335,7 +343,7 @@ __device__ inline int fivept_isolate(const double* x1, const double* y1, const d
         p11_acc<false>(Ep[3], Ep[7], m2); p11_acc<true>(Ep[4], Ep[6], m2);
         p21_acc<false>(m0, Ep[0], row); p21_acc<true>(m1, Ep[1], row); p21_acc<false>(m2, Ep[2], row);
 #pragma unroll
-        for (int k = 0; k < 20; ++k) C[0][k] = row[k];
+        for (int k = 0; k < 20; ++k) wk(k) = row[k];
     }
     {   // (E E^T - 1/2 tr(E E^T) I) E = 0
         double G[3][3][10];
@@ -371,7 +379,7 @@ __device__ inline int fivept_isolate(const double* x1, const double* y1, const d
                     p21_acc<false>(g, Ep[3 * k + j], row);
                 }
 #pragma unroll
-                for (int k = 0; k < 20; ++k) C[1 + 3 * i + j][k] = row[k];
+                for (int k = 0; k < 20; ++k) wk((1 + 3 * i + j) * 20 + k) = row[k];
             }
     }
     // Gaussian elimination with row pivoting on the first ten columns.  Rows are not swapped: the pivot row of column k
@@ -385,7 +393,7 @@ __device__ inline int fivept_isolate(const double* x1, const double* y1, const d
         double best = -1.0, pv = 0.0;
 #pragma unroll
         for (int r = 0; r < 10; ++r) {
-            const double v = C[r][k], av = fabs(v);
+            const double v = wk(r * 20 + k), av = fabs(v);
             if (!((used >> r) & 1u) && av > best) { best = av; pr = r; pv = v; }
         }
         if (!(best > 1e-300)) return 0;
@@ -397,7 +405,7 @@ __device__ inline int fivept_isolate(const double* x1, const double* y1, const d
         for (int r = 0; r < 10; ++r)
             if (r == pr) {
 #pragma unroll
-                for (int c = 0; c < 20; ++c) if (c >= 10 || c > k) prow[c] = C[r][c];
+                for (int c = 0; c < 20; ++c) if (c >= 10 || c > k) prow[c] = wk(r * 20 + c);
             }
         const double inv = 1.0 / pv;
 #pragma unroll
@@ -409,9 +417,9 @@ __device__ inline int fivept_isolate(const double* x1, const double* y1, const d
 #pragma unroll
         for (int r = 0; r < 10; ++r) {
             if ((used >> r) & 1u) continue;
-            const double f = -C[r][k];
+            const double f = -wk(r * 20 + k);
 #pragma unroll
-            for (int c = 0; c < 20; ++c) if (c >= 10 || c > k) C[r][c] = fma(f, prow[c], C[r][c]);
+            for (int c = 0; c < 20; ++c) if (c >= 10 || c > k) wk(r * 20 + c) = fma(f, prow[c], wk(r * 20 + c));
         }
     }
     // back substitution of the right half, pivot rows 8..4
@@ -445,7 +453,7 @@ __device__ inline int fivept_isolate(const double* x1, const double* y1, const d
         pmul(hs.Bc[0], 4, u1, 6, t3);
         for (int i = 0; i < 11; ++i) poly[i] += t3[i];
     }
-    hs.nr = isolate_roots(poly, hs.p, &hs.deg, hs.lo, hs.hi, &hs.mid);
+    hs.nr = isolate_roots(poly, hs.p, &hs.deg, hs.lo, hs.hi, &hs.mid, wk);
     return hs.nr;
 }
 

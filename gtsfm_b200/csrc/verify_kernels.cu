@@ -57,7 +57,8 @@ __device__ __forceinline__ void hypothesis_samples(const VerifyBufs& b, const Ve
 }
 
 // phase A of hypothesis h of pair p
-__device__ int isolate_hypothesis(const VerifyBufs& b, const VerifyDims& d, int p, int h, vm::HypState& hs)
+template <class W>
+__device__ int isolate_hypothesis(const VerifyBufs& b, const VerifyDims& d, int p, int h, vm::HypState& hs, const W& wk)
 {
     const VPair& vp = b.pairs[p];
     int s[5];
@@ -68,21 +69,22 @@ __device__ int isolate_hypothesis(const VerifyBufs& b, const VerifyDims& d, int 
         const double4 c = b.corr_d[vp.m0 + idx];
         x1[k] = c.x; y1[k] = c.y; x2[k] = c.z; y2[k] = c.w;
     }
-    return vm::fivept_isolate(x1, y1, x2, y2, hs);
+    return vm::fivept_isolate(x1, y1, x2, y2, hs, wk);
 }
 
 // ---------------------------------------------------------------------------------------------------------------- K4
-// Persistent CTAs over blocks of 128 hypotheses.  Phase A runs one hypothesis per thread and leaves its state in
+// Persistent CTAs over blocks of kSolveThreads hypotheses.  Phase A runs one hypothesis per thread and leaves its state in
 // shared memory ([field][thread], conflict-free); the real roots of the block are then compacted so that phase B
 // (root refinement, back-substitution, polish) runs one ROOT per thread with full warps, whatever the number of
 // real roots each hypothesis has.  Slot r of a hypothesis holds the essential matrix of its r-th root (ascending z),
 // NaN when the root gave no finite matrix.
-constexpr int kSolveThreads = 128;
-constexpr int kSolveSmem = vm::kHypDoubles * kSolveThreads * 8;
+constexpr int kSolveThreads = 64;
+constexpr int kSolveSmem = vm::kWorkDoubles * kSolveThreads * 8;
+static_assert(vm::kHypDoubles <= vm::kWorkDoubles, "hand-off state must fit the per-thread scratch");
 
 __global__ void __launch_bounds__(kSolveThreads, 2) solve_kernel(VerifyBufs b, VerifyDims d, int n_pairs)
 {
-    extern __shared__ double s_h[];                       // [kHypDoubles][kSolveThreads]
+    extern __shared__ double s_h[];                       // [kWorkDoubles][kSolveThreads]: scratch, then hand-off state
     __shared__ int s_meta[kSolveThreads];                 // nr | deg << 8
     __shared__ unsigned s_mid[kSolveThreads];
     __shared__ int s_off[kSolveThreads + 1];
@@ -98,7 +100,7 @@ __global__ void __launch_bounds__(kSolveThreads, 2) solve_kernel(VerifyBufs b, V
             const int p = static_cast<int>(g / d.H), h = static_cast<int>(g - static_cast<long long>(p) * d.H);
             if (b.pairs[p].status == 0) {
                 vm::HypState hs;
-                nr = isolate_hypothesis(b, d, p, h, hs);
+                nr = isolate_hypothesis(b, d, p, h, hs, vm::Work<kSolveThreads>{s_h + tid});
                 if (nr > 0) {
                     const double* src = reinterpret_cast<const double*>(&hs);
 #pragma unroll 2
@@ -340,6 +342,7 @@ __global__ void __launch_bounds__(kFinThreads) finalize_kernel(VerifyBufs b, Ver
     __shared__ double s_red[kFinThreads / 32][24];
     __shared__ double s_out[24];
     __shared__ double s_Ek[kTopK][9];
+    __shared__ double s_work[vm::kWorkDoubles * kTopK];     // solver scratch of the kTopK re-solving threads
     __shared__ double s_R[9], s_t[3], s_E[9], s_dE[45];
     __shared__ double s_R1[9], s_R2[9], s_tt[3];
     __shared__ float s_topv[kTopK];
@@ -399,7 +402,7 @@ __global__ void __launch_bounds__(kFinThreads) finalize_kernel(VerifyBufs b, Ver
         const int h = s_topi[tid] / vm::kMaxCand;
         const float* e32 = b.E32 + (static_cast<long long>(p) * d.H) * (9 * vm::kMaxCand) + static_cast<long long>(s_topi[tid]) * 9;
         vm::HypState hs;
-        const int nr = isolate_hypothesis(b, d, p, h, hs);
+        const int nr = isolate_hypothesis(b, d, p, h, hs, vm::Work<kTopK>{s_work + tid});
         double bestdot = -1.0, Eb[9];
         for (int e = 0; e < 9; ++e) Eb[e] = nan("");
         for (int r = 0; r < nr; ++r) {
