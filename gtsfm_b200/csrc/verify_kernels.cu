@@ -147,9 +147,19 @@ constexpr int kScoreHyp = 32;      // hypotheses per CTA
 constexpr int kScoreTile = 4096;   // correspondences staged per shared-memory tile (64 KB)
 constexpr int kScoreMaxCand = kScoreHyp * vm::kMaxCand;
 
+// packed fp32x2 arithmetic (FFMA2 / FMUL2 / FADD2 on sm_100a): two correspondences per lane and instruction
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pk2(float a, float b) { f32x2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b)); return r; }
+__device__ __forceinline__ void upk2(f32x2 v, float& a, float& b) { asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); }
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) { f32x2 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
+__device__ __forceinline__ float rcp_fast(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) { f32x2 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+
+// Shared-memory tile: correspondences 2q and 2q + 1 are stored as A[q] = (x1a, x1b, y1a, y1b), B[q] = (x2a, x2b, y2a, y2b)
+// so that one LDS.128 yields two packed operands.
 __global__ void __launch_bounds__(256) score_kernel(VerifyBufs b, VerifyDims d, int n_pairs)
 {
-    extern __shared__ float4 s_corr[];                 // [kScoreTile]
+    extern __shared__ float4 s_corr[];                 // [kScoreTile / 2] A, then [kScoreTile / 2] B
     __shared__ float s_cost[kScoreMaxCand];
     __shared__ unsigned short s_cand[kScoreMaxCand];   // (local hypothesis << 4) | candidate
     __shared__ int s_n;
@@ -173,26 +183,52 @@ __global__ void __launch_bounds__(256) score_kernel(VerifyBufs b, VerifyDims d, 
     if (n == 0) return;
     const float thr2 = static_cast<float>(vp.thr2);
     const float* Ebase = b.E32 + (static_cast<long long>(p) * d.H + h0) * (9 * vm::kMaxCand);
+    float4* sA = s_corr;
+    float4* sB = s_corr + kScoreTile / 2;
     for (int t0 = 0; t0 < vp.M; t0 += kScoreTile) {
         const int tn = min(kScoreTile, vp.M - t0);
+        const int nq = tn >> 1;                        // complete pairs of correspondences
         __syncthreads();
-        for (int k = threadIdx.x; k < tn; k += blockDim.x) s_corr[k] = b.corr_f[vp.m0 + t0 + k];
+        for (int q = threadIdx.x; q < (tn + 1) >> 1; q += blockDim.x) {
+            const float4 ca = b.corr_f[vp.m0 + t0 + 2 * q];
+            const float4 cb = (2 * q + 1 < tn) ? b.corr_f[vp.m0 + t0 + 2 * q + 1] : ca;
+            sA[q] = make_float4(ca.x, cb.x, ca.y, cb.y);
+            sB[q] = make_float4(ca.z, cb.z, ca.w, cb.w);
+        }
         __syncthreads();
         for (int ci = warp; ci < n; ci += 8) {
             const int code = s_cand[ci];
             const float* E = Ebase + ((code >> 4) * vm::kMaxCand + (code & 15)) * 9;
             const float e0 = __ldg(E), e1 = __ldg(E + 1), e2 = __ldg(E + 2), e3 = __ldg(E + 3), e4 = __ldg(E + 4), e5 = __ldg(E + 5),
                         e6 = __ldg(E + 6), e7 = __ldg(E + 7), e8 = __ldg(E + 8);
-            float acc = 0.f;
+            const f32x2 p0 = pk2(e0, e0), p1 = pk2(e1, e1), p2 = pk2(e2, e2), p3 = pk2(e3, e3), p4 = pk2(e4, e4), p5 = pk2(e5, e5),
+                        p6 = pk2(e6, e6), p7 = pk2(e7, e7), p8 = pk2(e8, e8);
+            float acc0 = 0.f, acc1 = 0.f;
 #pragma unroll 2
-            for (int k = lane; k < tn; k += 32) {
-                const float4 c = s_corr[k];
-                const float l0 = fmaf(e0, c.x, fmaf(e1, c.y, e2)), l1 = fmaf(e3, c.x, fmaf(e4, c.y, e5)), l2 = fmaf(e6, c.x, fmaf(e7, c.y, e8));
-                const float m0 = fmaf(e0, c.z, fmaf(e3, c.w, e6)), m1 = fmaf(e1, c.z, fmaf(e4, c.w, e7));
-                const float num = fmaf(c.z, l0, fmaf(c.w, l1, l2));
+            for (int k = lane; k < nq; k += 32) {
+                const ulonglong2 A = *reinterpret_cast<const ulonglong2*>(sA + k);   // x1 pair, y1 pair
+                const ulonglong2 B = *reinterpret_cast<const ulonglong2*>(sB + k);   // x2 pair, y2 pair
+                const f32x2 l0 = fma2(p0, A.x, fma2(p1, A.y, p2)), l1 = fma2(p3, A.x, fma2(p4, A.y, p5)), l2 = fma2(p6, A.x, fma2(p7, A.y, p8));
+                const f32x2 m0 = fma2(p0, B.x, fma2(p3, B.y, p6)), m1 = fma2(p1, B.x, fma2(p4, B.y, p7));
+                const f32x2 num = fma2(B.x, l0, fma2(B.y, l1, l2));
+                const f32x2 den = fma2(l0, l0, fma2(l1, l1, fma2(m0, m0, mul2(m1, m1))));
+                float d0, d1;
+                upk2(den, d0, d1);
+                const f32x2 sq = mul2(mul2(num, num), pk2(rcp_fast(d0), rcp_fast(d1)));
+                float s0, s1;
+                upk2(sq, s0, s1);
+                acc0 += fminf(s0, thr2);               // NaN -> thr2: counts as an outlier
+                acc1 += fminf(s1, thr2);
+            }
+            float acc = acc0 + acc1;
+            if ((tn & 1) && lane == 0) {               // odd tail: first half of the last (duplicated) pair
+                const float4 a4 = sA[nq], b4 = sB[nq];
+                const float x1 = a4.x, y1 = a4.z, x2 = b4.x, y2 = b4.z;
+                const float l0 = fmaf(e0, x1, fmaf(e1, y1, e2)), l1 = fmaf(e3, x1, fmaf(e4, y1, e5)), l2 = fmaf(e6, x1, fmaf(e7, y1, e8));
+                const float m0 = fmaf(e0, x2, fmaf(e3, y2, e6)), m1 = fmaf(e1, x2, fmaf(e4, y2, e7));
+                const float num = fmaf(x2, l0, fmaf(y2, l1, l2));
                 const float den = fmaf(l0, l0, fmaf(l1, l1, fmaf(m0, m0, m1 * m1)));
-                const float s = __fdividef(num * num, den);
-                acc += fminf(s, thr2);                 // NaN -> thr2: counts as an outlier
+                acc += fminf(num * num * rcp_fast(den), thr2);
             }
 #pragma unroll
             for (int off = 16; off > 0; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
