@@ -135,28 +135,62 @@ __device__ __forceinline__ void calibrate(double u, double v, const double* cal,
     *xn = x; *yn = y;
 }
 
+// Right singular vector of the smallest singular value of the 4x4 DLT matrix A (rows r0..r3), i.e. the eigenvector of
+// the smallest eigenvalue of M = A^T A, by LDL^T + inverse iteration: with camera 0 = [I | 0] the leading pivots are
+// >= 1, the last pivot carries the (tiny) smallest eigenvalue, L^-T e3 is already the null vector up to
+// O(lambda_min / lambda_2), and each further solve with M gains that factor again.  ~200 flops, no iteration on the
+// matrix itself (a cyclic Jacobi sweep per inlier and pose candidate dominated the finalize kernel).
+__device__ __forceinline__ void dlt_null4(const double* A, double* Q)
+{
+    double m[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j <= i; ++j) m[i][j] = A[i] * A[j] + A[4 + i] * A[4 + j] + A[8 + i] * A[8 + j] + A[12 + i] * A[12 + j];
+    const double eps = 1e-15 * (m[0][0] + m[1][1] + m[2][2] + m[3][3]) + 1e-300;
+    const double d0 = m[0][0] + eps, i0 = 1.0 / d0;
+    const double l10 = m[1][0] * i0, l20 = m[2][0] * i0, l30 = m[3][0] * i0;
+    const double d1 = m[1][1] + eps - l10 * m[1][0], i1 = 1.0 / d1;
+    const double t21 = m[2][1] - l20 * m[1][0], t31 = m[3][1] - l30 * m[1][0];
+    const double l21 = t21 * i1, l31 = t31 * i1;
+    const double d2 = m[2][2] + eps - l20 * m[2][0] - l21 * t21, i2 = 1.0 / d2;
+    const double t32 = m[3][2] - l30 * m[2][0] - l31 * t21;
+    const double l32 = t32 * i2;
+    double d3 = m[3][3] + eps - l30 * m[3][0] - l31 * t31 - l32 * t32;
+    if (!(d3 > 0)) d3 = eps;
+    const double i3 = 1.0 / d3;
+    // x = L^-T e3
+    double x3 = 1.0, x2 = -l32, x1 = -l21 * x2 - l31, x0 = -l10 * x1 - l20 * x2 - l30;
+#pragma unroll
+    for (int it = 0; it < 3; ++it) {
+        const double sc = 1.0 / fmax(fmax(fabs(x0), fabs(x1)), fmax(fabs(x2), fabs(x3)));
+        x0 *= sc; x1 *= sc; x2 *= sc; x3 *= sc;
+        // L z = x
+        const double z0 = x0, z1 = x1 - l10 * z0, z2 = x2 - l20 * z0 - l21 * z1, z3 = x3 - l30 * z0 - l31 * z1 - l32 * z2;
+        // L^T y = D^-1 z
+        x3 = z3 * i3;
+        x2 = z2 * i2 - l32 * x3;
+        x1 = z1 * i1 - l21 * x2 - l31 * x3;
+        x0 = z0 * i0 - l10 * x1 - l20 * x2 - l30 * x3;
+    }
+    const double n = 1.0 / sqrt(x0 * x0 + x1 * x1 + x2 * x2 + x3 * x3);
+    Q[0] = x0 * n; Q[1] = x1 * n; Q[2] = x2 * n; Q[3] = x3 * n;
+}
+
 // cv::triangulatePoints for one point + the cheirality test of cv::recoverPose (distance threshold 50).
 // P1 = [R | t] row-major 3x4; camera 0 is [I | 0].
 __device__ inline bool cheirality_ok(const double* P1, double ax, double ay, double bx, double by)
 {
-    double A[16], AtA[16], w[4], V[16];
-    const double P0[12] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0};
+    double A[16], Q[4];
+    A[0] = -1.0; A[1] = 0.0; A[2] = ax; A[3] = 0.0;
+    A[4] = 0.0; A[5] = -1.0; A[6] = ay; A[7] = 0.0;
+#pragma unroll
     for (int k = 0; k < 4; ++k) {
-        A[k] = ax * P0[8 + k] - P0[k];
-        A[4 + k] = ay * P0[8 + k] - P0[4 + k];
         A[8 + k] = bx * P1[8 + k] - P1[k];
         A[12 + k] = by * P1[8 + k] - P1[4 + k];
     }
-    for (int i = 0; i < 4; ++i)
-        for (int j = 0; j < 4; ++j) {
-            double s = 0;
-            for (int r = 0; r < 4; ++r) s += A[r * 4 + i] * A[r * 4 + j];
-            AtA[i * 4 + j] = s;
-        }
-    jacobi_eig<4>(AtA, w, V);
-    int m = 0;
-    for (int i = 1; i < 4; ++i) if (w[i] < w[m]) m = i;
-    const double Q0 = V[m], Q1 = V[4 + m], Q2 = V[8 + m], Q3 = V[12 + m];
+    dlt_null4(A, Q);
+    const double Q0 = Q[0], Q1 = Q[1], Q2 = Q[2], Q3 = Q[3];
     bool ok = (Q2 * Q3) > 0;
     const double X = Q0 / Q3, Y = Q1 / Q3, Z = Q2 / Q3;
     ok = ok && (Z < 50.0);
