@@ -42,6 +42,17 @@ def parse_args():
     return ap.parse_args()
 
 
+def load_traffic(args, cfg):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one match_screen_kernel launch, from the committed
+    `ncu --set full` capture of this same workload (profiles/r1_screen_ncu.json); None for any other workload."""
+    path = os.path.join(ROOT, "profiles", "r1_screen_ncu.json")
+    if args.images or args.kps or args.config != "C2" or not os.path.exists(path):
+        return None
+    with open(path) as f:
+        rec = json.load(f)
+    return rec.get("dram_bytes_per_launch")
+
+
 def load_peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -199,18 +210,17 @@ def run_b200(args):
         for i in range(n_img):
             ctx.upload_image(i, desc_pin[i].numpy(), kps_pin[i].numpy(), scene.cal)
 
-    rec = torch.zeros((P, 16), dtype=torch.float64, device="cuda")       # per-pair result record gathered over NVLink
-    gathered = [torch.zeros_like(rec) for _ in range(world)] if world > 1 else None
+    from gtsfm_b200.two_view_batch import TwoViewBatchResult, gather_records, pack_records
+    pair_ids = rank * P + np.arange(P)                                     # every rank owns P pairs of the weak-scaling job
 
     def compute(fetch: bool):
         m, off = ctx.match_batch(pairs, scene.ratio, fetch=fetch)
         out = ctx.verify_batch(pairs, prm, total=int(off[-1]))
         d2h = m.nbytes + out["mask"].nbytes + out["R"].nbytes + out["t"].nbytes + out["E"].nbytes + out["n_inliers"].nbytes + out["status"].nbytes + 4 * P
-        if world > 1:                                                      # results gathered via NCCL (north_star)
-            h = np.concatenate([out["R"].reshape(P, 9), out["t"], out["n_inliers"][:, None], out["status"][:, None],
-                                np.diff(off)[:, None], np.zeros((P, 1))], axis=1)
-            rec.copy_(torch.from_numpy(h), non_blocking=True)
-            dist.all_gather(gathered, rec)
+        if world > 1:                                                      # per-pair result records gathered via NCCL (north_star)
+            res = TwoViewBatchResult(pairs, off, m, out["mask"], out["R"], out["t"], out["n_inliers"], out["status"])
+            table = gather_records(pack_records(res, pair_ids), world * P, dist, device="cuda")
+            assert table.shape[0] == world * P
         return off, out, d2h
 
     def sync_all():
@@ -241,6 +251,7 @@ def run_b200(args):
     for _ in range(args.warmup):
         compute(False)
     ctx.profile_enable(True)
+    ctx.verify_stats(reset=True)
     launches0 = ctx.kernel_launches
     clocks = ClockSampler(local)
     clocks.start()
@@ -249,6 +260,7 @@ def run_b200(args):
     launches = ctx.kernel_launches - launches0
     prof = ctx.profile_get()
     ctx.profile_enable(False)
+    n_cand, n_hyp_solved, n_evals = ctx.verify_stats(reset=True)
     # the device-event time excludes nothing but host gaps after the last kernel; use the larger of the two clocks
     step_ms = max(ms, wall * 1e3) / args.steps
     value = world * P / (step_ms / 1e3)
@@ -276,6 +288,17 @@ def run_b200(args):
                     "algorithmic_flops_per_launch": flops_per_launch, "launch_ms": scr_ms / max(scr_calls, 1),
                     "share_of_step": scr_ms / total_kernel_ms if total_kernel_ms else None,
                     "kernel_ms_per_step": {k: v[0] / args.steps for k, v in prof.items()}}
+        # MSAC scoring against the FP32 SIMT roofline (34 FLOP per candidate x correspondence)
+        sc_ms, sc_calls = prof["score"]
+        sm_mhz = clk.get("sm_mhz") or peaks.get("sm_max_mhz", 1965.0)
+        fp32_peak = 148 * 128 * 2 * sm_mhz * 1e6 / 1e12
+        sc_achieved = 34.0 * n_evals / (sc_ms * 1e-3) / 1e12 if sc_ms > 0 else 0.0
+        roofline["scoring"] = {"bound": "fp32", "kernel": "score_kernel (MSAC cost of every 5-point candidate over all correspondences, FFMA2)",
+                               "achieved": sc_achieved, "peak": fp32_peak, "unit": "TFLOP/s", "frac": sc_achieved / fp32_peak,
+                               "peak_source": "148 SM x 128 lanes x 2 x %.0f MHz (median SM clock sampled during the timed region)" % sm_mhz,
+                               "sampson_evaluations_per_step": n_evals / args.steps, "candidates_per_hypothesis": n_cand / max(n_hyp_solved, 1),
+                               "share_of_step": sc_ms / total_kernel_ms if total_kernel_ms else None}
+        roofline["traffic"] = load_traffic(args, cfg)
         n_match = int(off[-1])
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16 GEMM / f32 scoring / f64 finalize",

@@ -18,7 +18,7 @@ EXPORTS = (
     "gtsfm_ctx_create", "gtsfm_ctx_destroy", "gtsfm_last_error", "gtsfm_ctx_set_workspace", "gtsfm_kernel_launches",
     "gtsfm_store_clear", "gtsfm_image_upload", "gtsfm_match_batch", "gtsfm_match_fetch", "gtsfm_ransac_samples",
     "gtsfm_verify_batch", "gtsfm_match_pair", "gtsfm_verify_pair", "gtsfm_debug_fetch",
-    "gtsfm_profile_enable", "gtsfm_profile_get", "gtsfm_event_record", "gtsfm_event_elapsed_ms",
+    "gtsfm_profile_enable", "gtsfm_profile_get", "gtsfm_event_record", "gtsfm_event_elapsed_ms", "gtsfm_verify_stats",
 )
 
 OK, E_CUDA, E_ARG, E_NO_DEVICE, E_KNN_UNPACK, E_UNSUPPORTED = range(6)
@@ -64,6 +64,7 @@ def lib() -> ctypes.CDLL:
             L.gtsfm_ctx_destroy.restype = None
             L.gtsfm_ctx_set_workspace.argtypes = [ctypes.c_void_p, ctypes.c_int64]
             L.gtsfm_store_clear.argtypes = [ctypes.c_void_p]
+            L.gtsfm_verify_stats.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_int64), ctypes.c_int]
             L.gtsfm_image_upload.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_int,
                                              ctypes.c_void_p, ctypes.c_void_p]
             L.gtsfm_match_batch.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_double, ctypes.c_void_p,
@@ -128,6 +129,12 @@ class Context:
     @property
     def kernel_launches(self) -> int:
         return int(self._L.gtsfm_kernel_launches(self._h))
+
+    def verify_stats(self, reset: bool = False):
+        """(essential-matrix candidates scored, hypotheses solved, Sampson evaluations) since the last reset."""
+        out = (ctypes.c_int64 * 3)()
+        self._check(self._L.gtsfm_verify_stats(self._h, out, 1 if reset else 0))
+        return int(out[0]), int(out[1]), int(out[2])
 
     def set_workspace(self, nbytes: int):
         self._check(self._L.gtsfm_ctx_set_workspace(self._h, int(nbytes)))

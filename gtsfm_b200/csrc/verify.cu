@@ -9,10 +9,6 @@
 #include "verify_types.h"
 
 namespace g2v {
-struct VerifyBufs {
-    const VPair* pairs; const uint2* match; double4* corr_d; float4* corr_f; float* E32; unsigned char* ncand; float* cost;
-    const int* samples; double* R; double* t; double* E; int* ninl; int* status; unsigned char* mask;
-};
 cudaError_t launch_verify_step(int step, const StoreView& st, const VerifyBufs& b, const VerifyDims& d, int n_pairs, int max_m, cudaStream_t s);
 }  // namespace g2v
 
@@ -103,6 +99,7 @@ int gtsfm_verify_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, const ui
     G2V_CUDA(c, vb[10].reserve(4 * static_cast<size_t>(n_pairs), false, s));
     G2V_CUDA(c, vb[11].reserve(4 * static_cast<size_t>(n_pairs), false, s));
     G2V_CUDA(c, vb[12].reserve(static_cast<size_t>(total + 1), false, s));
+    if (!vb[13].p) { G2V_CUDA(c, vb[13].reserve(32, false, s)); G2V_CUDA(c, cudaMemsetAsync(vb[13].p, 0, 32, s)); }
     G2V_CUDA(c, c->h_pairs.reserve(sizeof(VPair) * n_pairs));
     std::memcpy(c->h_pairs.p, vps.data(), sizeof(VPair) * n_pairs);
     G2V_CUDA(c, cudaMemcpyAsync(vb[0].p, c->h_pairs.p, sizeof(VPair) * n_pairs, cudaMemcpyHostToDevice, s));
@@ -117,11 +114,12 @@ int gtsfm_verify_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, const ui
         const int np = std::min(chunk, n_pairs - p0);
         VerifyBufs b{};
         b.pairs = vb[0].as<VPair>() + p0;
-        b.match = c->match_out.as<uint2>();
-        b.corr_d = vb[1].as<double4>(); b.corr_f = vb[2].as<float4>();
+        b.match = c->match_out.p;
+        b.corr_d = vb[1].p; b.corr_f = vb[2].p;
         b.E32 = vb[3].as<float>(); b.ncand = vb[4].as<unsigned char>(); b.cost = vb[5].as<float>();
         b.samples = prm->samples ? vb[6].as<int>() + static_cast<long long>(p0) * H * 5 : nullptr;
         b.R = vb[7].as<double>() + 9ll * p0; b.t = vb[8].as<double>() + 3ll * p0; b.E = vb[9].as<double>() + 9ll * p0;
+        b.stats = vb[13].as<unsigned long long>();
         b.ninl = vb[10].as<int>() + p0; b.status = vb[11].as<int>() + p0; b.mask = vb[12].as<unsigned char>();
         int mm = 0;
         for (int p = p0; p < p0 + np; ++p) mm = std::max(mm, vps[p].M);
@@ -140,6 +138,21 @@ int gtsfm_verify_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, const ui
     if (status) G2V_CUDA(c, cudaMemcpyAsync(status, vb[11].p, 4 * static_cast<size_t>(n_pairs), cudaMemcpyDeviceToHost, s));
     if (inlier_mask && total > 0) G2V_CUDA(c, cudaMemcpyAsync(inlier_mask, vb[12].p, static_cast<size_t>(total), cudaMemcpyDeviceToHost, s));
     G2V_CUDA(c, cudaStreamSynchronize(s));
+    return GTSFM_OK;
+}
+
+int gtsfm_verify_stats(gtsfm_ctx* c, int64_t* out, int reset)
+{
+    if (!c || !out) return GTSFM_E_ARG;
+    cudaSetDevice(c->device);
+    out[0] = out[1] = out[2] = 0;
+    DevBuf& sb = c->v_bufs[13];
+    if (!sb.p) return GTSFM_OK;
+    unsigned long long h[4] = {0, 0, 0, 0};
+    G2V_CUDA(c, cudaMemcpyAsync(h, sb.p, 32, cudaMemcpyDeviceToHost, c->stream));
+    if (reset) G2V_CUDA(c, cudaMemsetAsync(sb.p, 0, 32, c->stream));
+    G2V_CUDA(c, cudaStreamSynchronize(c->stream));
+    for (int k = 0; k < 3; ++k) out[k] = static_cast<int64_t>(h[k]);
     return GTSFM_OK;
 }
 

@@ -16,19 +16,6 @@
 
 namespace g2v {
 
-struct VerifyBufs {
-    const VPair* pairs;        // [P] (this chunk)
-    const uint2* match;        // batch-wide (i1, i2)
-    double4* corr_d;           // [total] x1 y1 x2 y2 (normalised)
-    float4* corr_f;            // [total]
-    float* E32;                // [P][H][10][9]
-    unsigned char* ncand;      // [P][H]
-    float* cost;               // [P][H][10]
-    const int* samples;        // optional explicit [P][H][5] (chunk-relative) or nullptr
-    // outputs (batch-wide pointers already offset to this chunk's first pair)
-    double* R; double* t; double* E; int* ninl; int* status; unsigned char* mask;
-};
-
 // ---------------------------------------------------------------------------------------------------------------- K3
 __global__ void __launch_bounds__(256) gather_normalize_kernel(StoreView st, VerifyBufs b, int n_pairs)
 {
@@ -36,13 +23,13 @@ __global__ void __launch_bounds__(256) gather_normalize_kernel(StoreView st, Ver
     if (p >= n_pairs) return;
     const VPair& vp = b.pairs[p];
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < vp.M; i += gridDim.x * blockDim.x) {
-        const uint2 m = b.match[vp.m0 + i];
+        const uint2 m = static_cast<const uint2*>(b.match)[vp.m0 + i];
         const double2 k1 = st.kps[vp.row1 + m.x], k2 = st.kps[vp.row2 + m.y];
         double x1, y1, x2, y2;
         vm::calibrate(k1.x, k1.y, vp.cal1, &x1, &y1);
         vm::calibrate(k2.x, k2.y, vp.cal2, &x2, &y2);
-        b.corr_d[vp.m0 + i] = make_double4(x1, y1, x2, y2);
-        b.corr_f[vp.m0 + i] = make_float4(static_cast<float>(x1), static_cast<float>(y1), static_cast<float>(x2), static_cast<float>(y2));
+        static_cast<double4*>(b.corr_d)[vp.m0 + i] = make_double4(x1, y1, x2, y2);
+        static_cast<float4*>(b.corr_f)[vp.m0 + i] = make_float4(static_cast<float>(x1), static_cast<float>(y1), static_cast<float>(x2), static_cast<float>(y2));
     }
 }
 
@@ -66,7 +53,7 @@ __device__ int isolate_hypothesis(const VerifyBufs& b, const VerifyDims& d, int 
     double x1[5], y1[5], x2[5], y2[5];
     for (int k = 0; k < 5; ++k) {
         const int idx = min(max(s[k], 0), vp.M - 1);
-        const double4 c = b.corr_d[vp.m0 + idx];
+        const double4 c = static_cast<const double4*>(b.corr_d)[vp.m0 + idx];
         x1[k] = c.x; y1[k] = c.y; x2[k] = c.z; y2[k] = c.w;
     }
     return vm::fivept_isolate(x1, y1, x2, y2, hs, wk);
@@ -125,6 +112,11 @@ __global__ void __launch_bounds__(kSolveThreads, 2) solve_kernel(VerifyBufs b, V
         for (int r = 0; r < nr; ++r) s_map[excl + r] = static_cast<unsigned short>((tid << 4) | r);
         __syncthreads();
         const int n_roots = s_off[kSolveThreads];
+        if (tid == 0 && b.stats) {
+            atomicAdd(b.stats, static_cast<unsigned long long>(n_roots));
+            const long long left = total - blk * kSolveThreads;
+            atomicAdd(b.stats + 1, static_cast<unsigned long long>(left < kSolveThreads ? left : kSolveThreads));
+        }
         for (int idx = tid; idx < n_roots; idx += kSolveThreads) {
             const int code = s_map[idx], j = code >> 4, r = code & 15;
             vm::HypState hs;
@@ -181,6 +173,7 @@ __global__ void __launch_bounds__(256) score_kernel(VerifyBufs b, VerifyDims d, 
     __syncthreads();
     const int n = s_n;
     if (n == 0) return;
+    if (threadIdx.x == 0 && b.stats) atomicAdd(b.stats + 2, static_cast<unsigned long long>(n) * static_cast<unsigned long long>(vp.M));
     const float thr2 = static_cast<float>(vp.thr2);
     const float* Ebase = b.E32 + (static_cast<long long>(p) * d.H + h0) * (9 * vm::kMaxCand);
     float4* sA = s_corr;
@@ -190,8 +183,8 @@ __global__ void __launch_bounds__(256) score_kernel(VerifyBufs b, VerifyDims d, 
         const int nq = tn >> 1;                        // complete pairs of correspondences
         __syncthreads();
         for (int q = threadIdx.x; q < (tn + 1) >> 1; q += blockDim.x) {
-            const float4 ca = b.corr_f[vp.m0 + t0 + 2 * q];
-            const float4 cb = (2 * q + 1 < tn) ? b.corr_f[vp.m0 + t0 + 2 * q + 1] : ca;
+            const float4 ca = static_cast<const float4*>(b.corr_f)[vp.m0 + t0 + 2 * q];
+            const float4 cb = (2 * q + 1 < tn) ? static_cast<const float4*>(b.corr_f)[vp.m0 + t0 + 2 * q + 1] : ca;
             sA[q] = make_float4(ca.x, cb.x, ca.y, cb.y);
             sB[q] = make_float4(ca.z, cb.z, ca.w, cb.w);
         }
@@ -343,7 +336,7 @@ __device__ void lo_pass(const VerifyBufs& b, const VPair& vp, const double* s_R,
     double acc[22];
     for (int i = 0; i < 22; ++i) acc[i] = 0;
     for (int i = threadIdx.x; i < vp.M; i += kFinThreads) {
-        const double4 c = b.corr_d[vp.m0 + i];
+        const double4 c = static_cast<const double4*>(b.corr_d)[vp.m0 + i];
         const double a1 = c.x, c1 = c.y, a2 = c.z, c2 = c.w;
         const double l0 = E[0] * a1 + E[1] * c1 + E[2], l1 = E[3] * a1 + E[4] * c1 + E[5], l2 = E[6] * a1 + E[7] * c1 + E[8];
         const double m0 = E[0] * a2 + E[3] * c2 + E[6], m1 = E[1] * a2 + E[4] * c2 + E[7];
@@ -458,7 +451,7 @@ __global__ void __launch_bounds__(kFinThreads) finalize_kernel(VerifyBufs b, Ver
 #pragma unroll
         for (int k = 0; k < kTopK; ++k) acc[k] = 0;
         for (int i = tid; i < vp.M; i += kFinThreads) {
-            const double4 c = b.corr_d[vp.m0 + i];
+            const double4 c = static_cast<const double4*>(b.corr_d)[vp.m0 + i];
 #pragma unroll
             for (int k = 0; k < kTopK; ++k) {
                 if (k < n_top) {
@@ -547,7 +540,7 @@ __global__ void __launch_bounds__(kFinThreads) finalize_kernel(VerifyBufs b, Ver
     {
         double cnt[1] = {0};
         for (int i = tid; i < vp.M; i += kFinThreads) {
-            const double4 c = b.corr_d[vp.m0 + i];
+            const double4 c = static_cast<const double4*>(b.corr_d)[vp.m0 + i];
             const bool in = vm::sampson_sq(E, c.x, c.y, c.z, c.w) < vp.thr2;
             b.mask[vp.m0 + i] = in ? 1 : 0;
             cnt[0] += in ? 1.0 : 0.0;
@@ -566,7 +559,7 @@ __global__ void __launch_bounds__(kFinThreads) finalize_kernel(VerifyBufs b, Ver
     {
         double good[4] = {0, 0, 0, 0};
         for (int i = tid; i < vp.M; i += kFinThreads) {
-            const double4 c = b.corr_d[vp.m0 + i];
+            const double4 c = static_cast<const double4*>(b.corr_d)[vp.m0 + i];
             if (!(vm::sampson_sq(E, c.x, c.y, c.z, c.w) < vp.thr2)) continue;
 #pragma unroll 1
             for (int cand = 0; cand < 4; ++cand) {

@@ -14,6 +14,21 @@ struct VPair {
     unsigned long long key;  // sampler key
 };
 
+// Device buffers of one verifier chunk (all pointers are device memory).
+struct VerifyBufs {
+    const VPair* pairs;        // [P] (this chunk)
+    const void* match;         // batch-wide (i1, i2) rows, uint2
+    void* corr_d;              // [total] x1 y1 x2 y2 (normalised), double4
+    void* corr_f;              // [total] float4
+    float* E32;                // [P][H][10][9] essential matrices, slot r = r-th real root
+    unsigned char* ncand;      // [P][H] real roots per hypothesis
+    float* cost;               // [P][H][10]
+    const int* samples;        // optional explicit [P][H][5] (chunk-relative) or nullptr
+    // outputs (batch-wide pointers already offset to this chunk's first pair)
+    double* R; double* t; double* E; int* ninl; int* status; unsigned char* mask;
+    unsigned long long* stats; // running totals: [0] candidates (real roots), [1] hypotheses solved, [2] Sampson evaluations
+};
+
 struct VerifyDims {
     int H;                   // hypotheses per pair
     int lo_iters;

@@ -57,7 +57,10 @@ def shard_pairs(pairs: np.ndarray, n_shards: int, cost: Optional[np.ndarray] = N
     order = np.lexsort((pairs[:, 1], pairs[:, 0])) if P else np.zeros(0, np.int64)
     csum = np.cumsum(cost[order])
     total = csum[-1] if P else 0.0
-    bounds = [int(np.searchsorted(csum, total * k / n_shards, side="left")) for k in range(1, n_shards)]
+    # shard k ends with the first pair whose running cost reaches k / n_shards of the total
+    bounds = [min(P, int(np.searchsorted(csum, total * k / n_shards * (1 - 1e-12), side="left")) + 1) if P else 0
+              for k in range(1, n_shards)]
+    bounds = list(np.maximum.accumulate(bounds)) if bounds else bounds
     return [order[a:b] for a, b in zip([0] + bounds, bounds + [P])]
 
 
@@ -87,3 +90,45 @@ def run_two_view_batch(descriptors: Sequence[np.ndarray], keypoints: Sequence[np
     matches, off = ctx.match_batch(local, ratio_test_threshold, fetch=fetch_matches)
     out = ctx.verify_batch(local, p, total=int(off[-1]))
     return TwoViewBatchResult(pairs, off, matches, out["mask"], out["R"], out["t"], out["n_inliers"], out["status"])
+
+
+# ------------------------------------------------------------------------------------------------ multi-GPU result exchange
+RECORD_WIDTH = 16   # R (9) | t (3) | n_inliers | status | n_matches | global pair id
+
+
+def pack_records(result: TwoViewBatchResult, pair_ids: np.ndarray) -> np.ndarray:
+    """Fixed-width per-pair header: the only data that crosses GPUs.  pair_ids are the positions of the
+    shard's pairs in the global pair list, so the receiver can put every record back in place."""
+    P = len(result.pairs)
+    rec = np.zeros((P, RECORD_WIDTH), np.float64)
+    rec[:, 0:9] = result.R.reshape(P, 9)
+    rec[:, 9:12] = result.t
+    rec[:, 12] = result.n_inliers
+    rec[:, 13] = result.status
+    rec[:, 14] = np.diff(result.match_offsets)
+    rec[:, 15] = pair_ids
+    return rec
+
+
+def gather_records(rec, n_global: int, dist=None, device=None) -> np.ndarray:
+    """All-gather the shards' record blocks (NCCL over NVLink on the GPU box, gloo in the CPU tests) and scatter them
+    into global pair order.  Shards may differ in length: blocks are padded to the longest one, padding rows carry id -1."""
+    import torch
+    if dist is None or not dist.is_initialized() or dist.get_world_size() == 1:
+        blocks = [np.asarray(rec)]
+    else:
+        world = dist.get_world_size()
+        n = torch.tensor([len(rec)], dtype=torch.int64, device=device)
+        ns = [torch.zeros_like(n) for _ in range(world)]
+        dist.all_gather(ns, n)
+        longest = max(int(x) for x in ns)
+        pad = torch.full((longest, RECORD_WIDTH), -1.0, dtype=torch.float64, device=device)
+        pad[:len(rec)] = torch.as_tensor(rec, dtype=torch.float64, device=device)
+        out = [torch.zeros_like(pad) for _ in range(world)]
+        dist.all_gather(out, pad)
+        blocks = [o[:int(k)].cpu().numpy() for o, k in zip(out, ns)]
+    table = np.full((n_global, RECORD_WIDTH), np.nan)
+    for blk in blocks:
+        ids = blk[:, 15].astype(np.int64)
+        table[ids] = blk
+    return table

@@ -117,6 +117,11 @@ int gtsfm_verify_pair(gtsfm_ctx* ctx, const double* kps1, int n1, const double* 
                       double* t, int32_t* n_inliers, int32_t* status, uint8_t* inlier_mask, double* E);
 
 /* ---- diagnostics (tests and tools only) --------------------------------------------------------------------------- */
+/* Running totals of the verifier since the last reset, out[3]: [0] essential-matrix candidates scored (real roots of
+ * all 5-point solves, the S_h of SURVEY.md 8(d)), [1] hypotheses solved, [2] Sampson evaluations (sum over pairs of
+ * candidates x correspondences).  reset != 0 zeroes them afterwards. */
+int gtsfm_verify_stats(gtsfm_ctx* ctx, int64_t* out, int reset);
+
 /* Copy an internal device buffer of the last chunk to the host.  what: 0 rp_v1 (f32), 1 rp_v2 (f32), 2 rp_g (u8),
  * 3 colraw (f32), 4 row_best (i32), 5 row_d1 (f32), 6 row_d2 (f32), 7 col_best (i32), 8 col_d1 (f32), 9 col_d2 (f32),
  * 10 number of rows / columns flagged for the exact re-scan (i32). */
