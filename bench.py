@@ -25,6 +25,7 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 METRIC = "image_pairs_per_sec_match_plus_ransac_verify"
+_REAL_STDOUT = sys.stdout
 UNIT = "pairs/s"
 
 
@@ -152,7 +153,7 @@ def run_reference(args):
             "data": "synthetic", "config": {"workload": workload_name(args, cfg, n_pairs), "n_hypotheses": "cv2 USAC_ACCURATE default (maxIters 1000)"},
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=_REAL_STDOUT, flush=True)
 
 
 # ------------------------------------------------------------------------------------------------ B200 arm
@@ -311,13 +312,23 @@ def run_b200(args):
                 "roofline": roofline, "cpu_baseline": cpu,
                 "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": int(d2h_bytes)},
                 "gpu_launches": int(launches), "clocks": clk, "device_event_ms_per_step": ms / args.steps}
-        print(json.dumps(line), flush=True)
+        print(json.dumps(line), file=_REAL_STDOUT, flush=True)
     ctx.close()
     if world > 1:
         dist.destroy_process_group()
 
 
+def _claim_stdout():
+    """Libraries (NCCL's version banner, torchrun children) print to fd 1; the contract is ONE JSON line on stdout.
+    Keep a private copy of the real stdout for that line and point fd 1 at stderr for everything else."""
+    sys.stdout.flush()
+    real = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    return real
+
+
 if __name__ == "__main__":
+    _REAL_STDOUT = _claim_stdout()
     a = parse_args()
     if a.impl == "reference":
         run_reference(a)
