@@ -19,6 +19,7 @@ EXPORTS = (
     "gtsfm_store_clear", "gtsfm_image_upload", "gtsfm_match_batch", "gtsfm_match_fetch", "gtsfm_ransac_samples",
     "gtsfm_verify_batch", "gtsfm_match_pair", "gtsfm_verify_pair", "gtsfm_debug_fetch",
     "gtsfm_profile_enable", "gtsfm_profile_get", "gtsfm_event_record", "gtsfm_event_elapsed_ms", "gtsfm_verify_stats",
+    "gtsfm_host_alloc", "gtsfm_host_free", "gtsfm_match_fetch_async", "gtsfm_sync",
 )
 
 OK, E_CUDA, E_ARG, E_NO_DEVICE, E_KNN_UNPACK, E_UNSUPPORTED = range(6)
@@ -64,6 +65,11 @@ def lib() -> ctypes.CDLL:
             L.gtsfm_ctx_destroy.restype = None
             L.gtsfm_ctx_set_workspace.argtypes = [ctypes.c_void_p, ctypes.c_int64]
             L.gtsfm_store_clear.argtypes = [ctypes.c_void_p]
+            L.gtsfm_host_alloc.argtypes = [ctypes.POINTER(ctypes.c_void_p), ctypes.c_int64]
+            L.gtsfm_host_free.argtypes = [ctypes.c_void_p]
+            L.gtsfm_host_free.restype = None
+            L.gtsfm_match_fetch_async.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+            L.gtsfm_sync.argtypes = [ctypes.c_void_p]
             L.gtsfm_verify_stats.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_int64), ctypes.c_int]
             L.gtsfm_image_upload.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_int,
                                              ctypes.c_void_p, ctypes.c_void_p]
@@ -102,12 +108,38 @@ class Context:
             raise GtsfmB200Error(f"gtsfm_ctx_create failed ({rc}): {self._L.gtsfm_last_error(None).decode()}")
         self._h = h
         self._keep = []   # host arrays whose asynchronous upload may still be in flight
+        self._arena = {}  # name -> (pinned pointer, capacity in bytes): result buffers of the reuse_outputs mode
         self.device = int(device)
 
     def close(self):
         if getattr(self, "_h", None):
+            for ptr, _ in self._arena.values():
+                self._L.gtsfm_host_free(ptr)
+            self._arena = {}
             self._L.gtsfm_ctx_destroy(self._h)
             self._h = None
+
+    def _pinned(self, name: str, shape, dtype) -> np.ndarray:
+        """A view of the context's pinned result arena (grown on demand, never shrunk).  Valid until the next call that
+        asks for the same name: the reuse_outputs mode trades ownership for full-speed, asynchronous D2H copies."""
+        dtype = np.dtype(dtype)
+        n = int(np.prod(shape))
+        nbytes = max(n * dtype.itemsize, 1)
+        ptr, cap = self._arena.get(name, (None, 0))
+        if cap < nbytes:
+            if ptr:
+                self._L.gtsfm_host_free(ptr)
+            cap = int(nbytes * 1.25) + 4096
+            p = ctypes.c_void_p()
+            self._check(self._L.gtsfm_host_alloc(ctypes.byref(p), cap))
+            ptr = p.value
+            self._arena[name] = (ptr, cap)
+        buf = (ctypes.c_char * nbytes).from_address(ptr)
+        return np.frombuffer(buf, dtype=dtype, count=n).reshape(shape)
+
+    def sync(self):
+        """Wait for all kernels and asynchronous copies of this context."""
+        self._check(self._L.gtsfm_sync(self._h))
 
     def __del__(self):
         try:
@@ -165,8 +197,10 @@ class Context:
         self._check(self._L.gtsfm_image_upload(self._h, int(image_id), _ptr(desc), int(n), int(dim), _ptr(kps), _ptr(calv)))
 
     # ---- matcher
-    def match_batch(self, pairs: np.ndarray, ratio: Optional[float], fetch: bool = True):
-        """Returns (matches (total, 2) uint32, offsets (P + 1) int64); fetch=False leaves the matches on the device."""
+    def match_batch(self, pairs: np.ndarray, ratio: Optional[float], fetch=True, reuse_outputs: bool = False):
+        """Returns (matches (total, 2) uint32, offsets (P + 1) int64); fetch=False leaves the matches on the device.
+        fetch="async" (implies reuse_outputs) only enqueues the copy, which then overlaps verify_batch: the returned
+        array is a view of the context's pinned arena and must not be read before sync()."""
         pairs = np.ascontiguousarray(pairs, np.int32).reshape(-1, 2)
         P = pairs.shape[0]
         counts = np.zeros(P, np.int32)
@@ -174,9 +208,14 @@ class Context:
         r = float("nan") if ratio is None else float(ratio)
         self._check(self._L.gtsfm_match_batch(self._h, _ptr(pairs), P, r, _ptr(counts), ctypes.byref(total)))
         self._keep.clear()
-        out = np.empty((total.value if fetch else 0, 2), np.uint32)
-        if fetch:
-            self._check(self._L.gtsfm_match_fetch(self._h, _ptr(out)))
+        if fetch == "async":
+            out = self._pinned("matches", (total.value, 2), np.uint32)
+            self._check(self._L.gtsfm_match_fetch_async(self._h, _ptr(out)))
+        else:
+            shape = (total.value if fetch else 0, 2)
+            out = self._pinned("matches", shape, np.uint32) if (reuse_outputs and fetch) else np.empty(shape, np.uint32)
+            if fetch:
+                self._check(self._L.gtsfm_match_fetch(self._h, _ptr(out)))
         offsets = np.zeros(P + 1, np.int64)
         np.cumsum(counts, out=offsets[1:])
         return out, offsets
@@ -223,17 +262,23 @@ class Context:
 
     # ---- verifier
     def verify_batch(self, pairs: np.ndarray, params: "VerifyParams", match_idx: Optional[np.ndarray] = None,
-                     match_offsets: Optional[np.ndarray] = None, total: Optional[int] = None):
-        """Verify the last match batch (match_idx None) or caller-supplied matches.  Returns a dict of arrays."""
+                     match_offsets: Optional[np.ndarray] = None, total: Optional[int] = None, reuse_outputs: bool = False):
+        """Verify the last match batch (match_idx None) or caller-supplied matches.  Returns a dict of arrays; with
+        reuse_outputs they are views of the context's pinned arena, valid until the next verify_batch."""
         pairs = np.ascontiguousarray(pairs, np.int32).reshape(-1, 2)
         P = pairs.shape[0]
         if match_idx is not None:
             match_idx = np.ascontiguousarray(match_idx, np.uint32).reshape(-1, 2)
             match_offsets = np.ascontiguousarray(match_offsets, np.int64)
             total = int(match_offsets[-1])
-        R = np.zeros((P, 9)); t = np.zeros((P, 3)); E = np.zeros((P, 9))
-        ninl = np.zeros(P, np.int32); status = np.zeros(P, np.int32)
-        mask = np.zeros(max(int(total or 0), 1), np.uint8)
+        if reuse_outputs:
+            R = self._pinned("R", (P, 9), np.float64); t = self._pinned("t", (P, 3), np.float64); E = self._pinned("E", (P, 9), np.float64)
+            ninl = self._pinned("ninl", (P,), np.int32); status = self._pinned("status", (P,), np.int32)
+            mask = self._pinned("mask", (max(int(total or 0), 1),), np.uint8)
+        else:
+            R = np.zeros((P, 9)); t = np.zeros((P, 3)); E = np.zeros((P, 9))
+            ninl = np.zeros(P, np.int32); status = np.zeros(P, np.int32)
+            mask = np.zeros(max(int(total or 0), 1), np.uint8)
         self._check(self._L.gtsfm_verify_batch(self._h, _ptr(pairs), P, _ptr(match_idx), _ptr(match_offsets), ctypes.byref(params),
                                                _ptr(R), _ptr(t), _ptr(ninl), _ptr(status), _ptr(mask), _ptr(E)))
         return dict(R=R.reshape(P, 3, 3), t=t, n_inliers=ninl, status=status, mask=mask[: int(total or 0)], E=E.reshape(P, 3, 3))

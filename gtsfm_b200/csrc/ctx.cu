@@ -195,6 +195,11 @@ int gtsfm_ctx_create(int device, gtsfm_ctx** out)
     c->device = device;
     c->n_sm = prop.multiProcessorCount;
     if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return fail(nullptr, GTSFM_E_CUDA, "cudaStreamCreate failed"); }
+    if (cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->match_done, cudaEventDisableTiming) != cudaSuccess) {
+        delete c;
+        return fail(nullptr, GTSFM_E_CUDA, "cudaStreamCreate failed");
+    }
     *out = c;
     return GTSFM_OK;
 }
@@ -214,6 +219,8 @@ void gtsfm_ctx_destroy(gtsfm_ctx* c)
     c->h_small.release();
     for (cudaEvent_t e : c->prof_pool) cudaEventDestroy(e);
     for (cudaEvent_t e : c->user_ev) if (e) cudaEventDestroy(e);
+    if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
+    if (c->match_done) cudaEventDestroy(c->match_done);
     cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -339,6 +346,28 @@ int gtsfm_image_upload(gtsfm_ctx* c, int image_id, const float* desc, int n, int
         G2V_CUDA(c, cudaMemcpyAsync(c->kps.as<double2>() + rec.row0, kps, static_cast<size_t>(n) * 16, cudaMemcpyHostToDevice, c->stream));
     c->images.push_back(rec);
     c->rows_used += n_rows;
+    return GTSFM_OK;
+}
+
+int gtsfm_host_alloc(void** p, int64_t bytes)
+{
+    if (!p || bytes < 0) return GTSFM_E_ARG;
+    *p = nullptr;
+    if (bytes == 0) return GTSFM_OK;
+    return cudaHostAlloc(p, static_cast<size_t>(bytes), cudaHostAllocPortable) == cudaSuccess ? GTSFM_OK : GTSFM_E_CUDA;
+}
+
+void gtsfm_host_free(void* p)
+{
+    if (p) cudaFreeHost(p);
+}
+
+int gtsfm_sync(gtsfm_ctx* c)
+{
+    if (!c) return GTSFM_E_ARG;
+    cudaSetDevice(c->device);
+    G2V_CUDA(c, cudaStreamSynchronize(c->stream));
+    G2V_CUDA(c, cudaStreamSynchronize(c->copy_stream));
     return GTSFM_OK;
 }
 

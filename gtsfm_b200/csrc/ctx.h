@@ -35,6 +35,8 @@ struct gtsfm_ctx {
     int device = 0;
     int n_sm = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t copy_stream = nullptr;     // device -> host copies that overlap the next kernels (gtsfm_match_fetch_async)
+    cudaEvent_t match_done = nullptr;       // recorded on `stream` when the compacted matches of a batch are complete
     std::string err;
     int64_t launches = 0;
     int64_t workspace_bytes = 4ll << 30;

@@ -40,6 +40,7 @@ int gtsfm_match_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, double ra
     c->batch_n = 0;
     c->batch_total = 0;
     if (total) *total = 0;
+    G2V_CUDA(c, cudaStreamSynchronize(c->copy_stream));      // an asynchronous fetch of the previous batch may still read match_out
     if (n_pairs == 0) return GTSFM_OK;
     const int n_img = static_cast<int>(c->images.size());
 
@@ -158,6 +159,7 @@ int gtsfm_match_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, double ra
         c->prof_end();
         c->launches += 3;
     }
+    G2V_CUDA(c, cudaEventRecord(c->match_done, s));
     // ---- counts back to the host (the only synchronisation of the batch)
     G2V_CUDA(c, c->h_small.reserve(4 * static_cast<size_t>(n_pairs) + 16));
     G2V_CUDA(c, cudaMemcpyAsync(c->h_small.p, c->match_count.p, 4 * static_cast<size_t>(n_pairs), cudaMemcpyDeviceToHost, s));
@@ -180,6 +182,17 @@ int gtsfm_match_fetch(gtsfm_ctx* c, uint32_t* out)
     if (!out) return fail(c, GTSFM_E_ARG, "out is NULL");
     G2V_CUDA(c, cudaMemcpyAsync(out, c->match_out.p, 8 * static_cast<size_t>(c->batch_total), cudaMemcpyDeviceToHost, c->stream));
     G2V_CUDA(c, cudaStreamSynchronize(c->stream));
+    return GTSFM_OK;
+}
+
+int gtsfm_match_fetch_async(gtsfm_ctx* c, uint32_t* out)
+{
+    if (!c) return GTSFM_E_ARG;
+    cudaSetDevice(c->device);
+    if (c->batch_total == 0) return GTSFM_OK;
+    if (!out) return fail(c, GTSFM_E_ARG, "out is NULL");
+    G2V_CUDA(c, cudaStreamWaitEvent(c->copy_stream, c->match_done, 0));
+    G2V_CUDA(c, cudaMemcpyAsync(out, c->match_out.p, 8 * static_cast<size_t>(c->batch_total), cudaMemcpyDeviceToHost, c->copy_stream));
     return GTSFM_OK;
 }
 

@@ -47,6 +47,7 @@ int gtsfm_verify_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, const ui
         }
     } else {
         if (!match_offsets) return fail(c, GTSFM_E_ARG, "match_offsets is NULL");
+        G2V_CUDA(c, cudaStreamSynchronize(c->copy_stream));
         for (int p = 0; p <= n_pairs; ++p) off[p] = match_offsets[p];
         for (int p = 0; p < n_pairs; ++p) if (off[p + 1] < off[p]) return fail(c, GTSFM_E_ARG, "match_offsets must be non-decreasing");
         if (off[n_pairs] > 0 && !match_idx) return fail(c, GTSFM_E_ARG, "match_idx is NULL");

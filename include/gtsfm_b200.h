@@ -117,6 +117,16 @@ int gtsfm_verify_pair(gtsfm_ctx* ctx, const double* kps1, int n1, const double* 
                       double* t, int32_t* n_inliers, int32_t* status, uint8_t* inlier_mask, double* E);
 
 /* ---- diagnostics (tests and tools only) --------------------------------------------------------------------------- */
+/* Pinned (page-locked) host memory for result buffers: device -> host copies into it run at full PCIe speed and
+ * asynchronously.  Any host pointer is accepted by the fetch / verify calls; pageable ones just copy slower. */
+int gtsfm_host_alloc(void** ptr, int64_t bytes);
+void gtsfm_host_free(void* ptr);
+/* Like gtsfm_match_fetch, but the copy is only enqueued (on a second stream, ordered after the match kernels) so that it
+ * overlaps gtsfm_verify_batch; `out` must stay valid and must not be read until gtsfm_sync() returns. */
+int gtsfm_match_fetch_async(gtsfm_ctx* ctx, uint32_t* out);
+/* Wait for everything this context has enqueued (kernels and asynchronous copies). */
+int gtsfm_sync(gtsfm_ctx* ctx);
+
 /* Running totals of the verifier since the last reset, out[3]: [0] essential-matrix candidates scored (real roots of
  * all 5-point solves, the S_h of SURVEY.md 8(d)), [1] hypotheses solved, [2] Sampson evaluations (sum over pairs of
  * candidates x correspondences).  reset != 0 zeroes them afterwards. */

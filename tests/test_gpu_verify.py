@@ -207,3 +207,25 @@ def test_match_then_verify_on_device(ctx):
     check_against_oracle(got, kp1, kp2, m, cal, cal, 4.0, samples)
     assert rot_angle_deg(out["R"][0], R) < 1.0
     assert out["n_inliers"][0] > 0.5 * len(m)
+
+
+def test_async_fetch_and_pinned_outputs_equal_the_plain_path(ctx):
+    """gtsfm_match_fetch_async + pinned result buffers (the end-to-end leg of bench.py) return the same arrays as the
+    synchronous, caller-owned path, twice in a row (the arena is reused)."""
+    from gtsfm_b200 import synthetic
+    scene = synthetic.make_scene(n_images=4, n_kps=1024, seed=77)
+    ctx.clear()
+    for i in range(4):
+        ctx.upload_image(i, scene.descriptors[i], scene.keypoints[i], scene.cal)
+    prm = params(4.0, 128, seed=9)
+    m0, off0 = ctx.match_batch(scene.pairs, 0.8)
+    out0 = ctx.verify_batch(scene.pairs, prm, total=len(m0))
+    ref = {k: np.array(v, copy=True) for k, v in out0.items()}
+    for _ in range(2):
+        m1, off1 = ctx.match_batch(scene.pairs, 0.8, fetch="async")
+        out1 = ctx.verify_batch(scene.pairs, prm, total=int(off1[-1]), reuse_outputs=True)
+        ctx.sync()
+        np.testing.assert_array_equal(off1, off0)
+        np.testing.assert_array_equal(m1, m0)
+        for k in ("R", "t", "E", "n_inliers", "status", "mask"):
+            np.testing.assert_array_equal(out1[k], ref[k])
