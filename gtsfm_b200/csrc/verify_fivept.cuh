@@ -64,41 +64,65 @@ template <bool NEG> __device__ __forceinline__ void p21_acc(const double* a, con
     }
 }
 
-__device__ inline bool nullspace_5x9(const double* x1, const double* y1, const double* x2, const double* y2, double N[4][9])
+// Null space of the 5x9 epipolar system by Gauss-Jordan with complete pivoting.  The matrix lives in the caller's
+// scratch (element i at wk(i)): with the [element][thread] shared-memory layout a per-thread row / column index costs
+// nothing (every thread stays in its own bank pair), whereas a thread-local array indexed that way scatters a warp's
+// access over up to 64 cache lines.
+template <class W>
+__device__ inline bool nullspace_5x9(const double* x1, const double* y1, const double* x2, const double* y2, double N[4][9], const W& wk)
 {
-    double A[5][9];
+    // A[r][c] = wk(r * 9 + c); the null vectors are assembled in wk(45 + j * 9 + c)
     int perm[9];
+#pragma unroll
     for (int r = 0; r < 5; ++r) {
-        A[r][0] = x2[r] * x1[r]; A[r][1] = x2[r] * y1[r]; A[r][2] = x2[r];
-        A[r][3] = y2[r] * x1[r]; A[r][4] = y2[r] * y1[r]; A[r][5] = y2[r];
-        A[r][6] = x1[r];         A[r][7] = y1[r];         A[r][8] = 1.0;
+        wk(r * 9 + 0) = x2[r] * x1[r]; wk(r * 9 + 1) = x2[r] * y1[r]; wk(r * 9 + 2) = x2[r];
+        wk(r * 9 + 3) = y2[r] * x1[r]; wk(r * 9 + 4) = y2[r] * y1[r]; wk(r * 9 + 5) = y2[r];
+        wk(r * 9 + 6) = x1[r];         wk(r * 9 + 7) = y1[r];         wk(r * 9 + 8) = 1.0;
     }
+#pragma unroll
     for (int c = 0; c < 9; ++c) perm[c] = c;
+#pragma unroll 1
     for (int k = 0; k < 5; ++k) {
         int pr = k, pc = k;
         double best = -1.0;
         for (int r = k; r < 5; ++r)
-            for (int c = k; c < 9; ++c) { const double v = fabs(A[r][c]); if (v > best) { best = v; pr = r; pc = c; } }
+            for (int c = k; c < 9; ++c) { const double v = fabs(wk(r * 9 + c)); if (v > best) { best = v; pr = r; pc = c; } }
         if (!(best > 1e-14)) return false;
-        if (pr != k) for (int c = 0; c < 9; ++c) { const double t = A[k][c]; A[k][c] = A[pr][c]; A[pr][c] = t; }
+        if (pr != k) for (int c = 0; c < 9; ++c) { const double t = wk(k * 9 + c); wk(k * 9 + c) = wk(pr * 9 + c); wk(pr * 9 + c) = t; }
         if (pc != k) {
-            for (int r = 0; r < 5; ++r) { const double t = A[r][k]; A[r][k] = A[r][pc]; A[r][pc] = t; }
+            for (int r = 0; r < 5; ++r) { const double t = wk(r * 9 + k); wk(r * 9 + k) = wk(r * 9 + pc); wk(r * 9 + pc) = t; }
             const int t = perm[k]; perm[k] = perm[pc]; perm[pc] = t;
         }
-        const double inv = 1.0 / A[k][k];
-        for (int c = k; c < 9; ++c) A[k][c] *= inv;
-        for (int r = 0; r < 5; ++r)
-            if (r != k) { const double f = A[r][k]; if (f != 0.0) for (int c = k; c < 9; ++c) A[r][c] -= f * A[k][c]; }
+        const double inv = 1.0 / wk(k * 9 + k);
+        double prow[9];
+#pragma unroll
+        for (int c = 0; c < 9; ++c) { prow[c] = wk(k * 9 + c) * inv; wk(k * 9 + c) = prow[c]; }
+#pragma unroll
+        for (int r = 0; r < 5; ++r) {
+            if (r == k) continue;
+            const double f = -wk(r * 9 + k);
+#pragma unroll
+            for (int c = 0; c < 9; ++c) wk(r * 9 + c) = fma(f, prow[c], wk(r * 9 + c));
+        }
     }
+#pragma unroll 1
     for (int j = 0; j < 4; ++j) {
         double v[9];
-        for (int r = 0; r < 5; ++r) v[r] = -A[r][5 + j];
+#pragma unroll
+        for (int r = 0; r < 5; ++r) v[r] = -wk(r * 9 + 5 + j);
+#pragma unroll
         for (int c = 5; c < 9; ++c) v[c] = (c == 5 + j) ? 1.0 : 0.0;
         double nn = 0;
+#pragma unroll
         for (int c = 0; c < 9; ++c) nn += v[c] * v[c];
         nn = 1.0 / sqrt(nn);
-        for (int c = 0; c < 9; ++c) N[j][perm[c]] = v[c] * nn;
+#pragma unroll
+        for (int c = 0; c < 9; ++c) wk(45 + j * 9 + perm[c]) = v[c] * nn;
     }
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+#pragma unroll
+        for (int c = 0; c < 9; ++c) N[j][c] = wk(45 + j * 9 + c);
     return true;
 }
 
@@ -225,13 +249,17 @@ __device__ inline int isolate_roots(const double* pin, double* p, int* deg_out, 
     return nr;
 }
 
+// Offsets of the HypState fields inside the hand-off block of kHypDoubles doubles.
+constexpr int kOffN = 0, kOffBx = 36, kOffBy = 48, kOffBc = 60, kOffP = 75, kOffLo = 86, kOffHi = 96;
+
 // Root of p (degree <= 10, zero-filled above its degree) inside the isolating bracket [lo, hi] (opposite signs at the
-// ends): safeguarded Newton.  p and p' come from one unrolled Horner recurrence.
-__device__ inline double refine_root(const double* p, double lo, double hi)
+// ends): safeguarded Newton.  p and p' come from one unrolled Horner recurrence.  The root only has to be good to
+// ~1e-10: the Gauss-Newton polish on (x, y, z) that follows converges quadratically from there.
+template <class HV> __device__ inline double refine_root(const HV& h, double lo, double hi)
 {
     double pc[11];
 #pragma unroll
-    for (int i = 0; i <= 10; ++i) pc[i] = p[i];
+    for (int i = 0; i <= 10; ++i) pc[i] = h(kOffP + i);
     double flo = pc[10];
 #pragma unroll
     for (int i = 9; i >= 0; --i) flo = flo * lo + pc[i];
@@ -245,9 +273,8 @@ __device__ inline double refine_root(const double* p, double lo, double hi)
         if ((f > 0) == (flo > 0)) lo = x; else hi = x;
         double xn = (dp != 0.0) ? x - f / dp : x;
         if (!(xn > lo && xn < hi) || fabs(xn - x) > 0.5 * fabs(dxold)) xn = 0.5 * (lo + hi);
-        const double dx = xn - x, tol = 1.0 + fabs(x);
-        // converged, or Newton has reached its noise floor (ill-conditioned root: the step no longer shrinks)
-        const bool done = fabs(dx) <= 4e-16 * tol || (it >= 6 && fabs(dx) <= 1e-11 * tol && fabs(dx) >= fabs(dxold));
+        const double dx = xn - x;
+        const bool done = fabs(dx) <= 1e-10 * (1.0 + fabs(x));
         dxold = dx;
         x = xn;
         if (done) break;
@@ -269,11 +296,12 @@ __device__ inline void ess_residual(const double* E, double* r)
 
 // Gauss-Newton polish of a root (x, y, z) of the ten cubic constraints; Jacobian columns are the analytic directional
 // derivatives of (det, 2 E E^T E - tr(E E^T) E) along N0, N1, N2.
-__device__ inline void polish_xyz(const double N[4][9], double* xyz)
+template <class HV> __device__ inline void polish_xyz(const HV& h, double* xyz)
 {
     for (int it = 0; it < 3; ++it) {
         double E[9], r[10], J[10][3];
-        for (int e = 0; e < 9; ++e) E[e] = xyz[0] * N[0][e] + xyz[1] * N[1][e] + xyz[2] * N[2][e] + N[3][e];
+#pragma unroll
+        for (int e = 0; e < 9; ++e) E[e] = xyz[0] * h(kOffN + e) + xyz[1] * h(kOffN + 9 + e) + xyz[2] * h(kOffN + 18 + e) + h(kOffN + 27 + e);
         ess_residual(E, r);
         double EEt[9], EtE[9], cof[9];
         for (int i = 0; i < 3; ++i)
@@ -286,7 +314,9 @@ __device__ inline void polish_xyz(const double N[4][9], double* xyz)
         cof[3] = E[2] * E[7] - E[1] * E[8]; cof[4] = E[0] * E[8] - E[2] * E[6]; cof[5] = E[1] * E[6] - E[0] * E[7];
         cof[6] = E[1] * E[5] - E[2] * E[4]; cof[7] = E[2] * E[3] - E[0] * E[5]; cof[8] = E[0] * E[4] - E[1] * E[3];
         for (int d = 0; d < 3; ++d) {
-            const double* D = N[d];
+            double D[9];
+#pragma unroll
+            for (int k = 0; k < 9; ++k) D[k] = h(kOffN + 9 * d + k);
             double T1[9], T2[9], T3[9], Dt[9], EDt[9], ip = 0, dd = 0;
             for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) Dt[3 * i + j] = D[3 * j + i];
             mat3_mul(D, EtE, T1); mat3_mul(E, Dt, EDt); mat3_mul(EDt, E, T2); mat3_mul(EEt, D, T3);
@@ -321,6 +351,7 @@ struct HypState {
 };
 constexpr int kHypDoubles = 36 + 12 + 12 + 15 + 11 + 20;
 static_assert(offsetof(HypState, deg) == kHypDoubles * 8, "HypState layout");
+static_assert(offsetof(HypState, Bx) == 36 * 8 && offsetof(HypState, p) == 75 * 8 && offsetof(HypState, lo) == 86 * 8 && offsetof(HypState, hi) == 96 * 8, "HypState layout");
 
 // Phase A (once per hypothesis): five normalised correspondences -> null space, the ten cubic constraints, their
 // Gauss-Jordan reduction, det B(z) and the isolating brackets of its real roots.  Returns the number of roots.
@@ -328,7 +359,7 @@ template <class W>
 __device__ inline int fivept_isolate(const double* x1, const double* y1, const double* x2, const double* y2, HypState& hs, const W& wk)
 {
     hs.nr = 0; hs.deg = 0; hs.mid = 0;
-    if (!nullspace_5x9(x1, y1, x2, y2, hs.N)) return 0;
+    if (!nullspace_5x9(x1, y1, x2, y2, hs.N, wk)) return 0;
     double Ep[9][4];
     for (int e = 0; e < 9; ++e) for (int k = 0; k < 4; ++k) Ep[e][k] = hs.N[k][e];
     // C[r][c] = wk(r * 20 + c)
@@ -457,15 +488,32 @@ __device__ inline int fivept_isolate(const double* x1, const double* y1, const d
     return hs.nr;
 }
 
+// Read-only views of a hand-off block: element f of the block at base[f * STRIDE].
+template <int STRIDE> struct HypView {
+    const double* base;
+    __device__ __forceinline__ double operator()(int f) const { return base[f * STRIDE]; }
+};
+
 // Phase B (once per real root): root r -> (x, y) from the null vector of B(z), Gauss-Newton polish, unit-norm E.
 // false when the root yields no finite essential matrix.
-__device__ inline bool fivept_root(const HypState& hs, int r, double* Eout)
+template <class HV> __device__ inline bool fivept_root(const HV& h, unsigned mid, int r, double* Eout)
 {
-    const double z = ((hs.mid >> r) & 1u) ? 0.5 * (hs.lo[r] + hs.hi[r]) : refine_root(hs.p, hs.lo[r], hs.hi[r]);
+    const double lo = h(kOffLo + r), hi = h(kOffHi + r);
+    const double z = ((mid >> r) & 1u) ? 0.5 * (lo + hi) : refine_root(h, lo, hi);
     double bm[3][3];
-    for (int q = 0; q < 3; ++q) { bm[q][0] = horner(hs.Bx[q], 3, z); bm[q][1] = horner(hs.By[q], 3, z); bm[q][2] = horner(hs.Bc[q], 4, z); }
+#pragma unroll
+    for (int q = 0; q < 3; ++q) {
+        double vx = h(kOffBx + 4 * q + 3), vy = h(kOffBy + 4 * q + 3), vc = h(kOffBc + 5 * q + 4);
+#pragma unroll
+        for (int i = 2; i >= 0; --i) { vx = vx * z + h(kOffBx + 4 * q + i); vy = vy * z + h(kOffBy + 4 * q + i); }
+#pragma unroll
+        for (int i = 3; i >= 0; --i) vc = vc * z + h(kOffBc + 5 * q + i);
+        bm[q][0] = vx; bm[q][1] = vy; bm[q][2] = vc;
+    }
     double best = -1, bv[3] = {0, 0, 0};
+#pragma unroll
     for (int a = 0; a < 3; ++a)
+#pragma unroll
         for (int b = a + 1; b < 3; ++b) {
             double v[3];
             cross3(bm[a], bm[b], v);
@@ -474,11 +522,16 @@ __device__ inline bool fivept_root(const HypState& hs, int r, double* Eout)
     if (!(best > 0)) return false;
     double xyz[3] = {bv[0] / bv[2], bv[1] / bv[2], z};
     if (!isfinite(xyz[0]) || !isfinite(xyz[1])) return false;
-    polish_xyz(hs.N, xyz);
+    polish_xyz(h, xyz);
     double E[9], nn = 0;
-    for (int e = 0; e < 9; ++e) { E[e] = xyz[0] * hs.N[0][e] + xyz[1] * hs.N[1][e] + xyz[2] * hs.N[2][e] + hs.N[3][e]; nn += E[e] * E[e]; }
+#pragma unroll
+    for (int e = 0; e < 9; ++e) {
+        E[e] = xyz[0] * h(kOffN + e) + xyz[1] * h(kOffN + 9 + e) + xyz[2] * h(kOffN + 18 + e) + h(kOffN + 27 + e);
+        nn += E[e] * E[e];
+    }
     if (!(nn > 0) || !isfinite(nn)) return false;
     nn = 1.0 / sqrt(nn);
+#pragma unroll
     for (int e = 0; e < 9; ++e) Eout[e] = E[e] * nn;
     return true;
 }

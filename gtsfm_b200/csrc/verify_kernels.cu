@@ -119,13 +119,8 @@ __global__ void __launch_bounds__(kSolveThreads, 2) solve_kernel(VerifyBufs b, V
         }
         for (int idx = tid; idx < n_roots; idx += kSolveThreads) {
             const int code = s_map[idx], j = code >> 4, r = code & 15;
-            vm::HypState hs;
-            double* dst = reinterpret_cast<double*>(&hs);
-#pragma unroll 2
-            for (int f = 0; f < vm::kHypDoubles; ++f) dst[f] = s_h[f * kSolveThreads + j];
-            hs.nr = s_meta[j] & 0xff; hs.deg = s_meta[j] >> 8; hs.mid = s_mid[j];
             double E[9];
-            const bool ok = vm::fivept_root(hs, r, E);
+            const bool ok = vm::fivept_root(vm::HypView<kSolveThreads>{s_h + j}, s_mid[j], r, E);
             float* out = b.E32 + ((blk * kSolveThreads + j) * vm::kMaxCand + r) * 9;
 #pragma unroll
             for (int e = 0; e < 9; ++e) out[e] = ok ? static_cast<float>(E[e]) : __int_as_float(0x7fc00000);
@@ -436,7 +431,7 @@ __global__ void __launch_bounds__(kFinThreads) finalize_kernel(VerifyBufs b, Ver
         for (int e = 0; e < 9; ++e) Eb[e] = nan("");
         for (int r = 0; r < nr; ++r) {
             double E[9];
-            if (!vm::fivept_root(hs, r, E)) continue;
+            if (!vm::fivept_root(vm::HypView<1>{reinterpret_cast<const double*>(&hs)}, hs.mid, r, E)) continue;
             double dot = 0;
             for (int e = 0; e < 9; ++e) dot += E[e] * static_cast<double>(e32[e]);
             if (fabs(dot) > bestdot) { bestdot = fabs(dot); for (int e = 0; e < 9; ++e) Eb[e] = E[e]; }
