@@ -264,7 +264,7 @@ def run_b200(args):
     launches = ctx.kernel_launches - launches0
     prof = ctx.profile_get()
     ctx.profile_enable(False)
-    n_cand, n_hyp_solved, n_evals = ctx.verify_stats(reset=True)
+    n_cand, n_hyp_solved, n_evals, n_evals_exec = ctx.verify_stats(reset=True)
     # the device-event time excludes nothing but host gaps after the last kernel; use the larger of the two clocks
     step_ms = max(ms, wall * 1e3) / args.steps
     value = world * P / (step_ms / 1e3)
@@ -300,7 +300,9 @@ def run_b200(args):
         roofline["scoring"] = {"bound": "fp32", "kernel": "score_kernel (MSAC cost of every 5-point candidate over all correspondences, FFMA2)",
                                "achieved": sc_achieved, "peak": fp32_peak, "unit": "TFLOP/s", "frac": sc_achieved / fp32_peak,
                                "peak_source": "148 SM x 128 lanes x 2 x %.0f MHz (median SM clock sampled during the timed region)" % sm_mhz,
-                               "sampson_evaluations_per_step": n_evals / args.steps, "candidates_per_hypothesis": n_cand / max(n_hyp_solved, 1),
+                               "sampson_evaluations_per_step": n_evals / args.steps,
+                               "executed_evaluations_per_step": n_evals_exec / args.steps,
+                               "executed_tflops": 34.0 * n_evals_exec / (sc_ms * 1e-3) / 1e12 if sc_ms > 0 else 0.0, "candidates_per_hypothesis": n_cand / max(n_hyp_solved, 1),
                                "share_of_step": sc_ms / total_kernel_ms if total_kernel_ms else None}
         roofline["traffic"] = load_traffic(args, cfg)
         n_match = int(off[-1])

@@ -163,10 +163,10 @@ class Context:
         return int(self._L.gtsfm_kernel_launches(self._h))
 
     def verify_stats(self, reset: bool = False):
-        """(essential-matrix candidates scored, hypotheses solved, Sampson evaluations) since the last reset."""
-        out = (ctypes.c_int64 * 3)()
+        """(candidates scored, hypotheses solved, algorithmic Sampson evaluations, executed evaluations) since the last reset."""
+        out = (ctypes.c_int64 * 4)()
         self._check(self._L.gtsfm_verify_stats(self._h, out, 1 if reset else 0))
-        return int(out[0]), int(out[1]), int(out[2])
+        return int(out[0]), int(out[1]), int(out[2]), int(out[3])
 
     def set_workspace(self, nbytes: int):
         self._check(self._L.gtsfm_ctx_set_workspace(self._h, int(nbytes)))

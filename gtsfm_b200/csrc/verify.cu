@@ -101,6 +101,7 @@ int gtsfm_verify_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, const ui
     G2V_CUDA(c, vb[11].reserve(4 * static_cast<size_t>(n_pairs), false, s));
     G2V_CUDA(c, vb[12].reserve(static_cast<size_t>(total + 1), false, s));
     if (!vb[13].p) { G2V_CUDA(c, vb[13].reserve(32, false, s)); G2V_CUDA(c, cudaMemsetAsync(vb[13].p, 0, 32, s)); }
+    G2V_CUDA(c, vb[14].reserve(4 * static_cast<size_t>(chunk), false, s));
     G2V_CUDA(c, c->h_pairs.reserve(sizeof(VPair) * n_pairs));
     std::memcpy(c->h_pairs.p, vps.data(), sizeof(VPair) * n_pairs);
     G2V_CUDA(c, cudaMemcpyAsync(vb[0].p, c->h_pairs.p, sizeof(VPair) * n_pairs, cudaMemcpyHostToDevice, s));
@@ -121,6 +122,8 @@ int gtsfm_verify_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, const ui
         b.samples = prm->samples ? vb[6].as<int>() + static_cast<long long>(p0) * H * 5 : nullptr;
         b.R = vb[7].as<double>() + 9ll * p0; b.t = vb[8].as<double>() + 3ll * p0; b.E = vb[9].as<double>() + 9ll * p0;
         b.stats = vb[13].as<unsigned long long>();
+        b.best_cost = vb[14].as<unsigned int>();
+        G2V_CUDA(c, cudaMemsetAsync(vb[14].p, 0x7f, 4 * static_cast<size_t>(np), s));   // 0x7f7f7f7f = 3.4e38f
         b.ninl = vb[10].as<int>() + p0; b.status = vb[11].as<int>() + p0; b.mask = vb[12].as<unsigned char>();
         int mm = 0;
         for (int p = p0; p < p0 + np; ++p) mm = std::max(mm, vps[p].M);
@@ -146,14 +149,14 @@ int gtsfm_verify_stats(gtsfm_ctx* c, int64_t* out, int reset)
 {
     if (!c || !out) return GTSFM_E_ARG;
     cudaSetDevice(c->device);
-    out[0] = out[1] = out[2] = 0;
+    out[0] = out[1] = out[2] = out[3] = 0;
     DevBuf& sb = c->v_bufs[13];
     if (!sb.p) return GTSFM_OK;
     unsigned long long h[4] = {0, 0, 0, 0};
     G2V_CUDA(c, cudaMemcpyAsync(h, sb.p, 32, cudaMemcpyDeviceToHost, c->stream));
     if (reset) G2V_CUDA(c, cudaMemsetAsync(sb.p, 0, 32, c->stream));
     G2V_CUDA(c, cudaStreamSynchronize(c->stream));
-    for (int k = 0; k < 3; ++k) out[k] = static_cast<int64_t>(h[k]);
+    for (int k = 0; k < 4; ++k) out[k] = static_cast<int64_t>(h[k]);
     return GTSFM_OK;
 }
 

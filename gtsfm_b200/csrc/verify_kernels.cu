@@ -133,6 +133,7 @@ __global__ void __launch_bounds__(kSolveThreads, 2) solve_kernel(VerifyBufs b, V
 constexpr int kScoreHyp = 32;      // hypotheses per CTA
 constexpr int kScoreTile = 4096;   // correspondences staged per shared-memory tile (64 KB)
 constexpr int kScoreMaxCand = kScoreHyp * vm::kMaxCand;
+constexpr int kScoreCheck = 256;   // packed pairs (512 correspondences) between two early-exit checks
 
 // packed fp32x2 arithmetic (FFMA2 / FMUL2 / FADD2 on sm_100a): two correspondences per lane and instruction
 typedef unsigned long long f32x2;
@@ -149,6 +150,8 @@ __global__ void __launch_bounds__(256) score_kernel(VerifyBufs b, VerifyDims d, 
     extern __shared__ float4 s_corr[];                 // [kScoreTile / 2] A, then [kScoreTile / 2] B
     __shared__ float s_cost[kScoreMaxCand];
     __shared__ unsigned short s_cand[kScoreMaxCand];   // (local hypothesis << 4) | candidate
+    __shared__ unsigned char s_dead[kScoreMaxCand];    // candidate left the race (partial cost above the pair's best)
+    __shared__ unsigned long long s_exec;
     __shared__ int s_n;
     const int p = blockIdx.y;
     if (p >= n_pairs) return;
@@ -164,18 +167,21 @@ __global__ void __launch_bounds__(256) score_kernel(VerifyBufs b, VerifyDims d, 
         }
         s_n = n;
     }
-    for (int k = threadIdx.x; k < kScoreMaxCand; k += blockDim.x) s_cost[k] = 0.f;
+    for (int k = threadIdx.x; k < kScoreMaxCand; k += blockDim.x) { s_cost[k] = 0.f; s_dead[k] = 0; }
+    if (threadIdx.x == 0) s_exec = 0ull;
     __syncthreads();
     const int n = s_n;
     if (n == 0) return;
     if (threadIdx.x == 0 && b.stats) atomicAdd(b.stats + 2, static_cast<unsigned long long>(n) * static_cast<unsigned long long>(vp.M));
     const float thr2 = static_cast<float>(vp.thr2);
     const float* Ebase = b.E32 + (static_cast<long long>(p) * d.H + h0) * (9 * vm::kMaxCand);
+    const volatile float* best = reinterpret_cast<const volatile float*>(b.best_cost + p);
     float4* sA = s_corr;
     float4* sB = s_corr + kScoreTile / 2;
     for (int t0 = 0; t0 < vp.M; t0 += kScoreTile) {
         const int tn = min(kScoreTile, vp.M - t0);
         const int nq = tn >> 1;                        // complete pairs of correspondences
+        const bool last_tile = t0 + kScoreTile >= vp.M;
         __syncthreads();
         for (int q = threadIdx.x; q < (tn + 1) >> 1; q += blockDim.x) {
             const float4 ca = static_cast<const float4*>(b.corr_f)[vp.m0 + t0 + 2 * q];
@@ -185,31 +191,45 @@ __global__ void __launch_bounds__(256) score_kernel(VerifyBufs b, VerifyDims d, 
         }
         __syncthreads();
         for (int ci = warp; ci < n; ci += 8) {
+            if (s_dead[ci]) continue;
             const int code = s_cand[ci];
             const float* E = Ebase + ((code >> 4) * vm::kMaxCand + (code & 15)) * 9;
             const float e0 = __ldg(E), e1 = __ldg(E + 1), e2 = __ldg(E + 2), e3 = __ldg(E + 3), e4 = __ldg(E + 4), e5 = __ldg(E + 5),
                         e6 = __ldg(E + 6), e7 = __ldg(E + 7), e8 = __ldg(E + 8);
             const f32x2 p0 = pk2(e0, e0), p1 = pk2(e1, e1), p2 = pk2(e2, e2), p3 = pk2(e3, e3), p4 = pk2(e4, e4), p5 = pk2(e5, e5),
                         p6 = pk2(e6, e6), p7 = pk2(e7, e7), p8 = pk2(e8, e8);
+            const float before = s_cost[ci];           // cost over the previous tiles
             float acc0 = 0.f, acc1 = 0.f;
+            bool dead = false;
+            int done = 0;
+            // Early exit (exact): the MSAC cost only grows, so a candidate whose partial cost already exceeds the lowest
+            // COMPLETE cost of the pair (by more than the fp32 accumulation noise) cannot be the minimum.
+            for (int c0 = 0; c0 < nq; c0 += kScoreCheck) {
+                const int c1 = min(nq, c0 + kScoreCheck);
 #pragma unroll 2
-            for (int k = lane; k < nq; k += 32) {
-                const ulonglong2 A = *reinterpret_cast<const ulonglong2*>(sA + k);   // x1 pair, y1 pair
-                const ulonglong2 B = *reinterpret_cast<const ulonglong2*>(sB + k);   // x2 pair, y2 pair
-                const f32x2 l0 = fma2(p0, A.x, fma2(p1, A.y, p2)), l1 = fma2(p3, A.x, fma2(p4, A.y, p5)), l2 = fma2(p6, A.x, fma2(p7, A.y, p8));
-                const f32x2 m0 = fma2(p0, B.x, fma2(p3, B.y, p6)), m1 = fma2(p1, B.x, fma2(p4, B.y, p7));
-                const f32x2 num = fma2(B.x, l0, fma2(B.y, l1, l2));
-                const f32x2 den = fma2(l0, l0, fma2(l1, l1, fma2(m0, m0, mul2(m1, m1))));
-                float d0, d1;
-                upk2(den, d0, d1);
-                const f32x2 sq = mul2(mul2(num, num), pk2(rcp_fast(d0), rcp_fast(d1)));
-                float s0, s1;
-                upk2(sq, s0, s1);
-                acc0 += fminf(s0, thr2);               // NaN -> thr2: counts as an outlier
-                acc1 += fminf(s1, thr2);
+                for (int k = c0 + lane; k < c1; k += 32) {
+                    const ulonglong2 A = *reinterpret_cast<const ulonglong2*>(sA + k);   // x1 pair, y1 pair
+                    const ulonglong2 B = *reinterpret_cast<const ulonglong2*>(sB + k);   // x2 pair, y2 pair
+                    const f32x2 l0 = fma2(p0, A.x, fma2(p1, A.y, p2)), l1 = fma2(p3, A.x, fma2(p4, A.y, p5)), l2 = fma2(p6, A.x, fma2(p7, A.y, p8));
+                    const f32x2 m0 = fma2(p0, B.x, fma2(p3, B.y, p6)), m1 = fma2(p1, B.x, fma2(p4, B.y, p7));
+                    const f32x2 num = fma2(B.x, l0, fma2(B.y, l1, l2));
+                    const f32x2 den = fma2(l0, l0, fma2(l1, l1, fma2(m0, m0, mul2(m1, m1))));
+                    float d0, d1;
+                    upk2(den, d0, d1);
+                    const f32x2 sq = mul2(mul2(num, num), pk2(rcp_fast(d0), rcp_fast(d1)));
+                    float s0, s1;
+                    upk2(sq, s0, s1);
+                    acc0 += fminf(s0, thr2);               // NaN -> thr2: counts as an outlier
+                    acc1 += fminf(s1, thr2);
+                }
+                done = c1;
+                float part = acc0 + acc1;
+#pragma unroll
+                for (int off = 16; off > 0; off >>= 1) part += __shfl_xor_sync(0xffffffffu, part, off);
+                if (before + part > *best * 1.001f) { dead = true; break; }
             }
             float acc = acc0 + acc1;
-            if ((tn & 1) && lane == 0) {               // odd tail: first half of the last (duplicated) pair
+            if (!dead && (tn & 1) && lane == 0) {      // odd tail: first half of the last (duplicated) pair
                 const float4 a4 = sA[nq], b4 = sB[nq];
                 const float x1 = a4.x, y1 = a4.z, x2 = b4.x, y2 = b4.z;
                 const float l0 = fmaf(e0, x1, fmaf(e1, y1, e2)), l1 = fmaf(e3, x1, fmaf(e4, y1, e5)), l2 = fmaf(e6, x1, fmaf(e7, y1, e8));
@@ -220,7 +240,13 @@ __global__ void __launch_bounds__(256) score_kernel(VerifyBufs b, VerifyDims d, 
             }
 #pragma unroll
             for (int off = 16; off > 0; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
-            if (lane == 0) s_cost[ci] += acc;
+            if (lane == 0) {
+                const float total = before + acc;
+                s_cost[ci] = total;
+                if (dead) s_dead[ci] = 1;
+                else if (last_tile) atomicMin(b.best_cost + p, __float_as_uint(total));
+                atomicAdd(&s_exec, static_cast<unsigned long long>(2 * done + (dead ? 0 : (tn & 1))));
+            }
         }
     }
     __syncthreads();
@@ -228,6 +254,7 @@ __global__ void __launch_bounds__(256) score_kernel(VerifyBufs b, VerifyDims d, 
         const int code = s_cand[ci];
         b.cost[(static_cast<long long>(p) * d.H + h0 + (code >> 4)) * vm::kMaxCand + (code & 15)] = s_cost[ci];
     }
+    if (threadIdx.x == 0 && b.stats) atomicAdd(b.stats + 3, s_exec);
 }
 
 // ---------------------------------------------------------------------------------------------------------------- K6/K7

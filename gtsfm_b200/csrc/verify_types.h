@@ -27,6 +27,8 @@ struct VerifyBufs {
     // outputs (batch-wide pointers already offset to this chunk's first pair)
     double* R; double* t; double* E; int* ninl; int* status; unsigned char* mask;
     unsigned long long* stats; // running totals: [0] candidates (real roots), [1] hypotheses solved, [2] Sampson evaluations
+                               // (algorithmic: candidates x correspondences), [3] evaluations executed after early exit
+    unsigned int* best_cost;   // [P] (this chunk) bit pattern of the lowest complete fp32 MSAC cost seen so far
 };
 
 struct VerifyDims {

@@ -127,9 +127,10 @@ int gtsfm_match_fetch_async(gtsfm_ctx* ctx, uint32_t* out);
 /* Wait for everything this context has enqueued (kernels and asynchronous copies). */
 int gtsfm_sync(gtsfm_ctx* ctx);
 
-/* Running totals of the verifier since the last reset, out[3]: [0] essential-matrix candidates scored (real roots of
- * all 5-point solves, the S_h of SURVEY.md 8(d)), [1] hypotheses solved, [2] Sampson evaluations (sum over pairs of
- * candidates x correspondences).  reset != 0 zeroes them afterwards. */
+/* Running totals of the verifier since the last reset, out[4]: [0] essential-matrix candidates scored (real roots of
+ * all 5-point solves, the S_h of SURVEY.md 8(d)), [1] hypotheses solved, [2] algorithmic Sampson evaluations (sum over
+ * pairs of candidates x correspondences), [3] evaluations actually executed (the scoring kernel drops a candidate once
+ * its partial cost exceeds the pair's best complete cost).  reset != 0 zeroes them afterwards. */
 int gtsfm_verify_stats(gtsfm_ctx* ctx, int64_t* out, int reset);
 
 /* Copy an internal device buffer of the last chunk to the host.  what: 0 rp_v1 (f32), 1 rp_v2 (f32), 2 rp_g (u8),
