@@ -19,6 +19,10 @@ cudaError_t launch_match_finalize(const MatchWork& w, int use_ratio, double rati
                                   cudaStream_t s);
 int store_ensure_maps(gtsfm_ctx* c);
 
+// Flagged rows / columns per chunk that the exact re-scan can take (merge cells of 16 B each).  A chunk is cut short
+// before its rows + columns exceed this, so the flag list can never overflow.
+constexpr long long kFlagScratchCap = 1ll << 23;
+
 struct Chunk {
     int p0 = 0, p1 = 0;
     long long rp = 0, cr = 0, rows = 0, cols = 0;
@@ -76,7 +80,7 @@ int gtsfm_match_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, double ra
         const int items = pd.path == 0 && pd.nq > 0 ? pd.nt_pad / kBlockT : 0;
         const int jobs = pd.path == 1 && pd.nq > 0 ? (pd.nq + 31) / 32 + (pd.nt + 31) / 32 : 0;
         const long long bytes = rp * 9 + cr * 4 + static_cast<long long>(pd.nq_pad) * (12 + 16 + 8 + 8) + static_cast<long long>(pd.nt_pad) * (12 + 8);
-        if (cur.p1 > cur.p0 && cur_bytes + bytes > c->workspace_bytes) { chunks.push_back(cur); cur = Chunk{}; cur.p0 = cur.p1 = p; cur_bytes = 0; }
+        if (cur.p1 > cur.p0 && (cur_bytes + bytes > c->workspace_bytes || cur.rows + cur.cols + pd.nq_pad + pd.nt_pad > kFlagScratchCap)) { chunks.push_back(cur); cur = Chunk{}; cur.p0 = cur.p1 = p; cur_bytes = 0; }
         pd.rp_base = cur.rp; pd.cr_base = cur.cr; pd.out_base = cur.rows; pd.cb_base = cur.cols; pd.item0 = cur.items; pd.job0 = cur.jobs;
         cur.rp += rp; cur.cr += cr; cur.rows += pd.nq_pad; cur.cols += pd.nt_pad; cur.items += items; cur.jobs += jobs;
         cur.p1 = p + 1;
@@ -106,6 +110,7 @@ int gtsfm_match_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, double ra
     G2V_CUDA(c, c->col_key.reserve(m_cols + 16, false, s));
     G2V_CUDA(c, c->flag_list.reserve(8 * (m_rows + m_cols + 1), false, s));
     G2V_CUDA(c, c->n_flag.reserve(sizeof(int), false, s));
+    G2V_CUDA(c, c->flag_scratch.reserve(16 * static_cast<size_t>(kFlagScratchCap), false, s));
     G2V_CUDA(c, c->keys_scratch.reserve(16 * (m_rows + 1), false, s));
     G2V_CUDA(c, c->match_slot.reserve(8 * (m_rows + 1), false, s));
     G2V_CUDA(c, c->match_count.reserve(4 * static_cast<size_t>(n_pairs), false, s));
@@ -128,8 +133,10 @@ int gtsfm_match_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, double ra
         w.col_best = c->col_best.as<int>(); w.col_d1 = c->col_d1.as<float>(); w.col_d2 = c->col_d2.as<float>();
         w.row_key = c->row_key.as<unsigned short>(); w.col_key = c->col_key.as<uint8_t>();
         w.flag_list = c->flag_list.as<unsigned long long>(); w.n_flag = c->n_flag.as<int>();
-        w.flag_cap = static_cast<int>(std::min<long long>(k.rows + k.cols, 0x7fffffff));
+        w.flag_scratch = c->flag_scratch.as<unsigned long long>();
+        w.flag_cap = static_cast<int>(std::min<long long>(k.rows + k.cols, kFlagScratchCap));
         G2V_CUDA(c, cudaMemsetAsync(c->n_flag.p, 0, sizeof(int), s));
+        G2V_CUDA(c, cudaMemsetAsync(c->flag_scratch.p, 0xff, 16 * static_cast<size_t>(w.flag_cap), s));
         if (k.items > 0) {
             c->prof_begin(P_SCREEN);
             G2V_CUDA(c, launch_match_screen(c->tm_desc, c->tm_augq, c->tm_augt, w.pairs, w.n_pairs, k.items, c->rp_v1.as<float>(),

@@ -16,6 +16,7 @@ namespace g2v {
 
 constexpr int kScanRows = 32;   // scan-side rows per CTA (4 per warp)
 constexpr int kScanTile = 64;   // other-side rows staged per shared-memory tile
+constexpr int kScanSeg = 64;    // flagged rows: the other side is scanned by this many CTAs, merged with atomics
 
 __device__ __forceinline__ int find_by_job0(const PairDesc* pairs, int n, int job)
 {
@@ -37,9 +38,11 @@ __global__ void __launch_bounds__(256) exact_scan_kernel(StoreView st, MatchWork
     float* stile = sm + kScanRows * dim;              // [kScanTile][tstride]
     __shared__ unsigned char svalid[kScanTile];
 
-    const int n_jobs = mode == 0 ? n_range_jobs : min(*w.n_flag, w.flag_cap);
-    for (int job = blockIdx.x; job < n_jobs; job += gridDim.x) {
+    const int n_jobs = mode == 0 ? n_range_jobs : min(*w.n_flag, w.flag_cap) * kScanSeg;
+    for (int item = blockIdx.x; item < n_jobs; item += gridDim.x) {
     __syncthreads();
+    const int job = mode == 0 ? item : item / kScanSeg;
+    const int seg = mode == 0 ? 0 : item - job * kScanSeg;
     int p, dir, row0, cnt;
     if (mode == 0) {
         p = find_by_job0(w.pairs, w.n_pairs, job);
@@ -81,9 +84,13 @@ __global__ void __launch_bounds__(256) exact_scan_kernel(StoreView st, MatchWork
     const int qrow0 = single ? 0 : warp * 4;
     const int it0 = single ? warp * (kScanTile / 16) : 0, it1 = single ? (warp + 1) * (kScanTile / 16) : kScanTile / 2;
 
-    for (int t0 = 0; t0 < other_n; t0 += kScanTile) {
+    // mode 1: this CTA scans segment `seg` of the other side; the segments of a job meet in w.flag_scratch
+    const int seg_len = single ? ((other_n + kScanSeg * kScanTile - 1) / (kScanSeg * kScanTile)) * kScanTile : other_n;
+    const int t_begin = single ? min(other_n, seg * seg_len) : 0;
+    const int t_end = single ? min(other_n, t_begin + seg_len) : other_n;
+    for (int t0 = t_begin; t0 < t_end; t0 += kScanTile) {
         __syncthreads();
-        const int tn = min(kScanTile, other_n - t0);
+        const int tn = min(kScanTile, t_end - t0);
         if ((dim & 3) == 0) {
             const int d4 = dim >> 2;
             for (int k = threadIdx.x; k < tn * d4; k += blockDim.x) {
@@ -159,10 +166,28 @@ __global__ void __launch_bounds__(256) exact_scan_kernel(StoreView st, MatchWork
                         b2 = fminf(fminf(b2, m_f2[k]), ls);
                         if (tk) { b1 = m_f1[k]; bi = m_i1[k]; }
                     }
-                    const bool valid = st.valid[scan_base + row0] && bi != INT_MAX;
-                    o_best[out0] = valid ? bi : -1;
-                    o_d1[out0] = valid ? b1 : FLT_MAX;
-                    o_d2[out0] = valid ? b2 : FLT_MAX;
+                    // Merge with the other segments: lowest (distance, index) by a 64-bit atomicMin; every key that
+                    // loses a comparison is a candidate for the second-best distance.  0xff-filled scratch = +infinity.
+                    unsigned long long* k1p = w.flag_scratch + 2 * static_cast<long long>(job);
+                    unsigned int* m2p = reinterpret_cast<unsigned int*>(k1p + 1);
+                    unsigned int* cntp = m2p + 1;
+                    if (bi != INT_MAX) {
+                        const unsigned long long key = (static_cast<unsigned long long>(__float_as_uint(b1)) << 32) | static_cast<unsigned int>(bi);
+                        const unsigned long long old = atomicMin(k1p, key);
+                        const unsigned long long loser = old > key ? old : key;
+                        atomicMin(m2p, min(static_cast<unsigned int>(loser >> 32), __float_as_uint(b2)));
+                    }
+                    __threadfence();
+                    const unsigned int arrived = atomicAdd(cntp, 1u);              // starts at 0xffffffff
+                    if (arrived == static_cast<unsigned int>(kScanSeg - 2)) {        // last segment of the job
+                        __threadfence();
+                        const unsigned long long kf = *reinterpret_cast<volatile unsigned long long*>(k1p);
+                        const unsigned int m2 = *reinterpret_cast<volatile unsigned int*>(m2p);
+                        const bool valid = st.valid[scan_base + row0] && kf != ~0ull;
+                        o_best[out0] = valid ? static_cast<int>(kf & 0xffffffffu) : -1;
+                        o_d1[out0] = valid ? __uint_as_float(static_cast<unsigned int>(kf >> 32)) : FLT_MAX;
+                        o_d2[out0] = (valid && m2 < 0x7f800000u) ? __uint_as_float(m2) : FLT_MAX;
+                    }
                 }
             }
             continue;
@@ -189,7 +214,8 @@ cudaError_t launch_exact_scan(const StoreView& st, const MatchWork& w, int mode,
         if (e != cudaSuccess) return e;
         configured = smem;
     }
-    const int grid = mode == 0 ? n_jobs : (n_jobs < 1184 ? n_jobs : 1184);
+    const long long items = mode == 0 ? n_jobs : static_cast<long long>(n_jobs) * kScanSeg;
+    const int grid = static_cast<int>(items < 1184 ? items : 1184);
     exact_scan_kernel<<<grid, 256, smem, s>>>(st, w, mode, n_jobs);
     return cudaGetLastError();
 }

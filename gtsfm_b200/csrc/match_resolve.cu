@@ -96,44 +96,51 @@ __global__ void __launch_bounds__(128) merge_rows_kernel(StoreView st, MatchWork
     w.row_key[pos] = static_cast<unsigned short>((hb1 << 3) | g1);
 }
 
-// merge, columns: one warp per train column.  col_d1 <- k1, col_d2 <- k2, col_key <- winning lane class.
+// merge, columns: one warp per train column, kColsPerCta columns per CTA (every CTA lies inside one pair because column
+// ranges start on multiples of 256, so the pair lookup is done once per CTA).  col_d1 <- k1, col_d2 <- k2, col_key <-
+// winning lane class.
+constexpr int kColsPerCta = 64;
 __global__ void __launch_bounds__(256) merge_cols_kernel(StoreView st, MatchWork w, long long total_cols)
 {
-    const int lane = threadIdx.x & 31;
-    const long long pos = static_cast<long long>(blockIdx.x) * 8 + (threadIdx.x >> 5);
-    if (pos >= total_cols) return;
-    const int p = find_by_cb_base(w.pairs, w.n_pairs, static_cast<long long>(blockIdx.x) * 8);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const long long pos0 = static_cast<long long>(blockIdx.x) * kColsPerCta;
+    if (pos0 >= total_cols) return;
+    const int p = find_by_cb_base(w.pairs, w.n_pairs, pos0);
     const PairDesc pd = w.pairs[p];
     if (pd.path != 0) return;
-    const int j = static_cast<int>(pos - pd.cb_base);
-    if (j >= pd.nt || !st.valid[pd.t_row0 + j]) {
-        if (lane == 0) {
-            w.col_key[pos] = 0xffu;
-            if (j < pd.nt) { w.col_best[pos] = -1; w.col_d1[pos] = FLT_MAX; w.col_d2[pos] = FLT_MAX; }
+#pragma unroll 2
+    for (int u0 = warp; u0 < kColsPerCta; u0 += 8) {
+        const long long pos = pos0 + u0;
+        const int j = static_cast<int>(pos - pd.cb_base);
+        if (j >= pd.nt || !st.valid[pd.t_row0 + j]) {
+            if (lane == 0) {
+                w.col_key[pos] = 0xffu;
+                if (j < pd.nt) { w.col_best[pos] = -1; w.col_d1[pos] = FLT_MAX; w.col_d2[pos] = FLT_MAX; }
+            }
+            continue;
         }
-        return;
-    }
-    const float4 c4 = *reinterpret_cast<const float4*>(w.colraw + pd.cr_base + static_cast<long long>(j) * kTileQ + lane * 4);
-    const float cv[4] = {c4.x, c4.y, c4.z, c4.w};
-    float k1 = kHuge * 8.0f, k2 = kHuge * 8.0f;
-    int c1 = 0;
+        const float4 c4 = *reinterpret_cast<const float4*>(w.colraw + pd.cr_base + static_cast<long long>(j) * kTileQ + lane * 4);
+        const float cv[4] = {c4.x, c4.y, c4.z, c4.w};
+        float k1 = kHuge * 8.0f, k2 = kHuge * 8.0f;
+        int c1 = 0;
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
-        if (cv[u] < k1) { k2 = k1; k1 = cv[u]; c1 = lane * 4 + u; } else k2 = fminf(k2, cv[u]);
-    }
+        for (int u = 0; u < 4; ++u) {
+            if (cv[u] < k1) { k2 = k1; k1 = cv[u]; c1 = lane * 4 + u; } else k2 = fminf(k2, cv[u]);
+        }
 #pragma unroll
-    for (int off = 16; off > 0; off >>= 1) {
-        const float o1 = __shfl_xor_sync(0xffffffffu, k1, off), o2 = __shfl_xor_sync(0xffffffffu, k2, off);
-        const int oc = __shfl_xor_sync(0xffffffffu, c1, off);
-        const bool take = (o1 < k1) || (o1 == k1 && oc < c1);
-        const float lose = take ? k1 : o1;
-        k2 = fminf(fminf(k2, o2), lose);
-        if (take) { k1 = o1; c1 = oc; }
-    }
-    if (lane == 0) {
-        w.col_d1[pos] = k1;
-        w.col_d2[pos] = k2;
-        w.col_key[pos] = static_cast<uint8_t>(c1);
+        for (int off = 16; off > 0; off >>= 1) {
+            const float o1 = __shfl_xor_sync(0xffffffffu, k1, off), o2 = __shfl_xor_sync(0xffffffffu, k2, off);
+            const int oc = __shfl_xor_sync(0xffffffffu, c1, off);
+            const bool take = (o1 < k1) || (o1 == k1 && oc < c1);
+            const float lose = take ? k1 : o1;
+            k2 = fminf(fminf(k2, o2), lose);
+            if (take) { k1 = o1; c1 = oc; }
+        }
+        if (lane == 0) {
+            w.col_d1[pos] = k1;
+            w.col_d2[pos] = k2;
+            w.col_key[pos] = static_cast<uint8_t>(c1);
+        }
     }
 }
 
@@ -358,7 +365,7 @@ cudaError_t launch_resolve_int(const StoreView& st, const MatchWork& w, int whic
         if (st.kpad == 64) bucket_rows_kernel<4><<<2 * n_items, 128, 0, s>>>(st, w, 2 * n_items);
         else bucket_rows_kernel<8><<<2 * n_items, 128, 0, s>>>(st, w, 2 * n_items);
     } else {
-        merge_cols_kernel<<<static_cast<unsigned>((total + 7) / 8), 256, 0, s>>>(st, w, total);
+        merge_cols_kernel<<<static_cast<unsigned>((total + kColsPerCta - 1) / kColsPerCta), 256, 0, s>>>(st, w, total);
         cudaError_t e = st.kpad == 64 ? launch_bucket_cols<4>(st, w, max_class_rows, s) : launch_bucket_cols<8>(st, w, max_class_rows, s);
         if (e != cudaSuccess) return e;
     }
