@@ -85,14 +85,14 @@ int gtsfm_verify_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, const ui
 
     // ---- buffers
     DevBuf* vb = c->v_bufs;
-    const size_t per_pair = static_cast<size_t>(H) * (9 * 10 * 4 + 1 + 10 * 4);
+    const size_t per_pair = static_cast<size_t>(H) * (9 * 10 * 4 + 2 + 10 * 4);
     int chunk = static_cast<int>(std::max<long long>(1, std::min<long long>(c->workspace_bytes / static_cast<long long>(per_pair), 32768)));
     chunk = std::min(chunk, n_pairs);
     G2V_CUDA(c, vb[0].reserve(sizeof(VPair) * n_pairs, false, s));
     G2V_CUDA(c, vb[1].reserve(32 * static_cast<size_t>(total + 1), false, s));
     G2V_CUDA(c, vb[2].reserve(16 * static_cast<size_t>(total + 1), false, s));
     G2V_CUDA(c, vb[3].reserve(static_cast<size_t>(chunk) * H * 360, false, s));
-    G2V_CUDA(c, vb[4].reserve(static_cast<size_t>(chunk) * H, false, s));
+    G2V_CUDA(c, vb[4].reserve(static_cast<size_t>(chunk) * H * 2, false, s));
     G2V_CUDA(c, vb[5].reserve(static_cast<size_t>(chunk) * H * 40, false, s));
     G2V_CUDA(c, vb[7].reserve(72 * static_cast<size_t>(n_pairs), false, s));
     G2V_CUDA(c, vb[8].reserve(24 * static_cast<size_t>(n_pairs), false, s));
@@ -118,7 +118,7 @@ int gtsfm_verify_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, const ui
         b.pairs = vb[0].as<VPair>() + p0;
         b.match = c->match_out.p;
         b.corr_d = vb[1].p; b.corr_f = vb[2].p;
-        b.E32 = vb[3].as<float>(); b.ncand = vb[4].as<unsigned char>(); b.cost = vb[5].as<float>();
+        b.E32 = vb[3].as<float>(); b.vmask = vb[4].as<unsigned short>(); b.cost = vb[5].as<float>();
         b.samples = prm->samples ? vb[6].as<int>() + static_cast<long long>(p0) * H * 5 : nullptr;
         b.R = vb[7].as<double>() + 9ll * p0; b.t = vb[8].as<double>() + 3ll * p0; b.E = vb[9].as<double>() + 9ll * p0;
         b.stats = vb[13].as<unsigned long long>();

@@ -250,7 +250,7 @@ __device__ inline int isolate_roots(const double* pin, double* p, int* deg_out, 
 }
 
 // Offsets of the HypState fields inside the hand-off block of kHypDoubles doubles.
-constexpr int kOffN = 0, kOffBx = 36, kOffBy = 48, kOffBc = 60, kOffP = 75, kOffLo = 86, kOffHi = 96;
+constexpr int kOffN = 0, kOffBx = 36, kOffBy = 48, kOffBc = 60, kOffP = 75, kOffLo = 86, kOffHi = 96, kOffS = 106;
 
 // Root of p (degree <= 10, zero-filled above its degree) inside the isolating bracket [lo, hi] (opposite signs at the
 // ends): safeguarded Newton.  p and p' come from one unrolled Horner recurrence.  The root only has to be good to
@@ -346,12 +346,14 @@ struct HypState {
     double Bx[3][4], By[3][4], Bc[3][5];     // B(z) [x y 1]^T = 0
     double p[11];                            // normalised degree-10 polynomial det B(z)
     double lo[10], hi[10];                   // isolating brackets of its real roots, ascending
+    double sx1[5], sy1[5], sx2[5], sy2[5];   // the five sample correspondences (model validity test)
     int deg, nr;
     unsigned mid;                            // bit r: root r = midpoint of its bracket
 };
-constexpr int kHypDoubles = 36 + 12 + 12 + 15 + 11 + 20;
+constexpr int kHypDoubles = 36 + 12 + 12 + 15 + 11 + 20 + 20;
 static_assert(offsetof(HypState, deg) == kHypDoubles * 8, "HypState layout");
-static_assert(offsetof(HypState, Bx) == 36 * 8 && offsetof(HypState, p) == 75 * 8 && offsetof(HypState, lo) == 86 * 8 && offsetof(HypState, hi) == 96 * 8, "HypState layout");
+static_assert(offsetof(HypState, Bx) == 36 * 8 && offsetof(HypState, p) == 75 * 8 && offsetof(HypState, lo) == 86 * 8 && offsetof(HypState, hi) == 96 * 8 &&
+              offsetof(HypState, sx1) == 106 * 8, "HypState layout");
 
 // Phase A (once per hypothesis): five normalised correspondences -> null space, the ten cubic constraints, their
 // Gauss-Jordan reduction, det B(z) and the isolating brackets of its real roots.  Returns the number of roots.
@@ -359,6 +361,8 @@ template <class W>
 __device__ inline int fivept_isolate(const double* x1, const double* y1, const double* x2, const double* y2, HypState& hs, const W& wk)
 {
     hs.nr = 0; hs.deg = 0; hs.mid = 0;
+#pragma unroll
+    for (int k = 0; k < 5; ++k) { hs.sx1[k] = x1[k]; hs.sy1[k] = y1[k]; hs.sx2[k] = x2[k]; hs.sy2[k] = y2[k]; }
     if (!nullspace_5x9(x1, y1, x2, y2, hs.N, wk)) return 0;
     double Ep[9][4];
     for (int e = 0; e < 9; ++e) for (int k = 0; k < 4; ++k) Ep[e][k] = hs.N[k][e];
@@ -488,6 +492,34 @@ __device__ inline int fivept_isolate(const double* x1, const double* y1, const d
     return hs.nr;
 }
 
+// Model validity test of USAC-style estimators (the oriented epipolar constraint of Chum, Werner and Matas, 2004; cv2's
+// USAC applies it to every minimal-sample model before scoring): with e2 the epipole in image 2 (E^T e2 = 0), the
+// vectors e2 x x2 and E x1 must point the same way for every sample correspondence, or the opposite way for every one.
+// A model that mixes signs cannot have all five points in front of both cameras.
+__device__ __forceinline__ bool oriented_sample_ok(const double* E, const double* x1, const double* y1, const double* x2, const double* y2)
+{
+    const double c0[3] = {E[0], E[3], E[6]}, c1[3] = {E[1], E[4], E[7]}, c2[3] = {E[2], E[5], E[8]};
+    double v01[3], v02[3], v12[3];
+    cross3(c0, c1, v01); cross3(c0, c2, v02); cross3(c1, c2, v12);
+    const double n01 = v01[0] * v01[0] + v01[1] * v01[1] + v01[2] * v01[2];
+    const double n02 = v02[0] * v02[0] + v02[1] * v02[1] + v02[2] * v02[2];
+    const double n12 = v12[0] * v12[0] + v12[1] * v12[1] + v12[2] * v12[2];
+    double e[3] = {v01[0], v01[1], v01[2]};
+    double nb = n01;
+    if (n02 > nb) { nb = n02; e[0] = v02[0]; e[1] = v02[1]; e[2] = v02[2]; }
+    if (n12 > nb) { nb = n12; e[0] = v12[0]; e[1] = v12[1]; e[2] = v12[2]; }
+    int pos = 0, neg = 0;
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+        const double l0 = E[0] * x1[k] + E[1] * y1[k] + E[2], l1 = E[3] * x1[k] + E[4] * y1[k] + E[5], l2 = E[6] * x1[k] + E[7] * y1[k] + E[8];
+        const double w0 = e[1] - e[2] * y2[k], w1 = e[2] * x2[k] - e[0], w2 = e[0] * y2[k] - e[1] * x2[k];   // e x (x2, y2, 1)
+        const double sgn = w0 * l0 + w1 * l1 + w2 * l2;
+        pos += sgn > 0.0;
+        neg += sgn < 0.0;
+    }
+    return pos == 5 || neg == 5;
+}
+
 // Read-only views of a hand-off block: element f of the block at base[f * STRIDE].
 template <int STRIDE> struct HypView {
     const double* base;
@@ -522,6 +554,15 @@ template <class HV> __device__ inline bool fivept_root(const HV& h, unsigned mid
     if (!(best > 0)) return false;
     double xyz[3] = {bv[0] / bv[2], bv[1] / bv[2], z};
     if (!isfinite(xyz[0]) || !isfinite(xyz[1])) return false;
+    double sx1[5], sy1[5], sx2[5], sy2[5];
+#pragma unroll
+    for (int k = 0; k < 5; ++k) { sx1[k] = h(kOffS + k); sy1[k] = h(kOffS + 5 + k); sx2[k] = h(kOffS + 10 + k); sy2[k] = h(kOffS + 15 + k); }
+    {   // validity of the unpolished model: most wrong roots leave here, before the Gauss-Newton polish
+        double E0[9];
+#pragma unroll
+        for (int e = 0; e < 9; ++e) E0[e] = xyz[0] * h(kOffN + e) + xyz[1] * h(kOffN + 9 + e) + xyz[2] * h(kOffN + 18 + e) + h(kOffN + 27 + e);
+        if (!oriented_sample_ok(E0, sx1, sy1, sx2, sy2)) return false;
+    }
     polish_xyz(h, xyz);
     double E[9], nn = 0;
 #pragma unroll
@@ -530,6 +571,7 @@ template <class HV> __device__ inline bool fivept_root(const HV& h, unsigned mid
         nn += E[e] * E[e];
     }
     if (!(nn > 0) || !isfinite(nn)) return false;
+    if (!oriented_sample_ok(E, sx1, sy1, sx2, sy2)) return false;
     nn = 1.0 / sqrt(nn);
 #pragma unroll
     for (int e = 0; e < 9; ++e) Eout[e] = E[e] * nn;

@@ -74,6 +74,7 @@ __global__ void __launch_bounds__(kSolveThreads, 2) solve_kernel(VerifyBufs b, V
     extern __shared__ double s_h[];                       // [kWorkDoubles][kSolveThreads]: scratch, then hand-off state
     __shared__ int s_meta[kSolveThreads];                 // nr | deg << 8
     __shared__ unsigned s_mid[kSolveThreads];
+    __shared__ unsigned s_valid[kSolveThreads];           // bit r: root r of the thread's hypothesis gave a valid model
     __shared__ int s_off[kSolveThreads + 1];
     __shared__ unsigned short s_map[kSolveThreads * vm::kMaxCand];
     __shared__ int s_wsum[kSolveThreads / 32];
@@ -83,6 +84,7 @@ __global__ void __launch_bounds__(kSolveThreads, 2) solve_kernel(VerifyBufs b, V
     for (long long blk = blockIdx.x; blk < n_blocks; blk += gridDim.x) {
         const long long g = blk * kSolveThreads + tid;
         int nr = 0;
+        s_valid[tid] = 0u;
         if (g < total) {
             const int p = static_cast<int>(g / d.H), h = static_cast<int>(g - static_cast<long long>(p) * d.H);
             if (b.pairs[p].status == 0) {
@@ -96,7 +98,6 @@ __global__ void __launch_bounds__(kSolveThreads, 2) solve_kernel(VerifyBufs b, V
                     s_mid[tid] = hs.mid;
                 }
             }
-            b.ncand[g] = static_cast<unsigned char>(nr);
         }
         // exclusive prefix sum of nr over the block
         int inc = nr;
@@ -113,7 +114,6 @@ __global__ void __launch_bounds__(kSolveThreads, 2) solve_kernel(VerifyBufs b, V
         __syncthreads();
         const int n_roots = s_off[kSolveThreads];
         if (tid == 0 && b.stats) {
-            atomicAdd(b.stats, static_cast<unsigned long long>(n_roots));
             const long long left = total - blk * kSolveThreads;
             atomicAdd(b.stats + 1, static_cast<unsigned long long>(left < kSolveThreads ? left : kSolveThreads));
         }
@@ -121,11 +121,21 @@ __global__ void __launch_bounds__(kSolveThreads, 2) solve_kernel(VerifyBufs b, V
             const int code = s_map[idx], j = code >> 4, r = code & 15;
             double E[9];
             const bool ok = vm::fivept_root(vm::HypView<kSolveThreads>{s_h + j}, s_mid[j], r, E);
-            float* out = b.E32 + ((blk * kSolveThreads + j) * vm::kMaxCand + r) * 9;
+            if (ok) {
+                float* out = b.E32 + ((blk * kSolveThreads + j) * vm::kMaxCand + r) * 9;
 #pragma unroll
-            for (int e = 0; e < 9; ++e) out[e] = ok ? static_cast<float>(E[e]) : __int_as_float(0x7fc00000);
+                for (int e = 0; e < 9; ++e) out[e] = static_cast<float>(E[e]);
+                atomicOr(&s_valid[j], 1u << r);
+            }
         }
         __syncthreads();
+        if (g < total) b.vmask[g] = static_cast<unsigned short>(s_valid[tid]);
+        if (b.stats) {
+            int nv = __popc(s_valid[tid]);
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) nv += __shfl_xor_sync(0xffffffffu, nv, off);
+            if (lane == 0 && nv) atomicAdd(b.stats, static_cast<unsigned long long>(nv));
+        }
     }
 }
 
@@ -162,8 +172,8 @@ __global__ void __launch_bounds__(256) score_kernel(VerifyBufs b, VerifyDims d, 
     if (threadIdx.x == 0) {
         int n = 0;
         for (int hh = 0; hh < kScoreHyp && h0 + hh < d.H; ++hh) {
-            const int ne = b.ncand[static_cast<long long>(p) * d.H + h0 + hh];
-            for (int c = 0; c < ne; ++c) s_cand[n++] = static_cast<unsigned short>((hh << 4) | c);
+            unsigned m = b.vmask[static_cast<long long>(p) * d.H + h0 + hh];
+            while (m) { const int c = __ffs(m) - 1; m &= m - 1; s_cand[n++] = static_cast<unsigned short>((hh << 4) | c); }
         }
         s_n = n;
     }
@@ -415,14 +425,14 @@ __global__ void __launch_bounds__(kFinThreads) finalize_kernel(VerifyBufs b, Ver
     // ---- (a) the kTopK best candidates by fp32 MSAC cost (ties: lowest candidate id = h * 10 + c)
     const int n_slots = d.H * vm::kMaxCand;
     const float* cost = b.cost + static_cast<long long>(p) * n_slots;
-    const unsigned char* ncand = b.ncand + static_cast<long long>(p) * d.H;
+    const unsigned short* vmask = b.vmask + static_cast<long long>(p) * d.H;
     int n_top = 0;
     for (int k = 0; k < kTopK; ++k) {
         float bv = FLT_MAX;
         int bi = INT_MAX;
         for (int sidx = tid; sidx < n_slots; sidx += kFinThreads) {
             const int h = sidx / vm::kMaxCand, c = sidx - h * vm::kMaxCand;
-            if (c >= ncand[h]) continue;
+            if (!((vmask[h] >> c) & 1u)) continue;
             bool used = false;
             for (int j = 0; j < k; ++j) used |= (s_topi[j] == sidx);
             const float v = cost[sidx];

@@ -20,8 +20,8 @@ struct VerifyBufs {
     const void* match;         // batch-wide (i1, i2) rows, uint2
     void* corr_d;              // [total] x1 y1 x2 y2 (normalised), double4
     void* corr_f;              // [total] float4
-    float* E32;                // [P][H][10][9] essential matrices, slot r = r-th real root
-    unsigned char* ncand;      // [P][H] real roots per hypothesis
+    float* E32;                // [P][H][10][9] essential matrices, slot r = r-th real root (valid slots only)
+    unsigned short* vmask;     // [P][H] bit r set: root r of the hypothesis gave a valid essential matrix (slot r of E32)
     float* cost;               // [P][H][10]
     const int* samples;        // optional explicit [P][H][5] (chunk-relative) or nullptr
     // outputs (batch-wide pointers already offset to this chunk's first pair)

@@ -16,7 +16,7 @@
  * USAC_ACCURATE) whose sample sets are not observable; what is restated here is its published
  * structure: Nister's 5-point minimal solver (Nister, TPAMI 2004 -- cited at ransac.py:6), MSAC
  * scoring sum(min(sampson^2, thr^2)), best model = lowest cost (ties: lowest hypothesis/candidate
- * index), a local optimisation (Levenberg-Marquardt on the Sampson residuals of the current inliers)
+ * index) among the models that pass the oriented epipolar constraint on their own sample, a local optimisation (Levenberg-Marquardt on the Sampson residuals of the current inliers)
  * and the final mask sampson^2 < thr^2 (strict).  PARITY NOTE: the minimal solver is pinned against
  * cv2's own 5-point solver per sample (tests/test_oracle_verify.py), recover_pose against
  * cv2.recoverPose, the Sampson arithmetic against the reference's numpy functions and the reference
@@ -723,6 +723,34 @@ double oracle_lo_refine(const double* E_in, const double* x1, const double* y1, 
 #define VSTAT_TOO_FEW 1      /* M < 5 or M < 6 -> failure tuple (opencv_verifier_base.py:69-78) */
 #define VSTAT_NO_MODEL 2     /* no essential matrix from any sample / no inliers */
 
+/* Model validity test of USAC-style estimators: the oriented epipolar constraint (Chum, Werner, Matas, "Epipolar
+ * geometry estimation via RANSAC benefits from the oriented epipolar constraint", ICPR 2004), which cv2's USAC framework
+ * (the estimator behind ransac.py:74) applies to every model of a minimal sample before scoring it.  With e2 the
+ * epipole in image 2 (E^T e2 = 0, taken as the largest cross product of two columns of E), e2 x x2 and E x1 must have
+ * the same orientation for all five sample correspondences, or the opposite one for all five. */
+int oracle_oriented_ok(const double* E, const double* x1, const double* y1, const double* x2, const double* y2)
+{
+    const double c0[3] = {E[0], E[3], E[6]}, c1[3] = {E[1], E[4], E[7]}, c2[3] = {E[2], E[5], E[8]};
+    double v01[3], v02[3], v12[3], e[3];
+    cross3(c0, c1, v01); cross3(c0, c2, v02); cross3(c1, c2, v12);
+    double n01 = v01[0] * v01[0] + v01[1] * v01[1] + v01[2] * v01[2];
+    double n02 = v02[0] * v02[0] + v02[1] * v02[1] + v02[2] * v02[2];
+    double n12 = v12[0] * v12[0] + v12[1] * v12[1] + v12[2] * v12[2];
+    double nb = n01;
+    memcpy(e, v01, sizeof(e));
+    if (n02 > nb) { nb = n02; memcpy(e, v02, sizeof(e)); }
+    if (n12 > nb) { nb = n12; memcpy(e, v12, sizeof(e)); }
+    int pos = 0, neg = 0;
+    for (int k = 0; k < 5; ++k) {
+        double l0 = E[0] * x1[k] + E[1] * y1[k] + E[2], l1 = E[3] * x1[k] + E[4] * y1[k] + E[5], l2 = E[6] * x1[k] + E[7] * y1[k] + E[8];
+        double w0 = e[1] - e[2] * y2[k], w1 = e[2] * x2[k] - e[0], w2 = e[0] * y2[k] - e[1] * x2[k];
+        double sgn = w0 * l0 + w1 * l1 + w2 * l2;
+        pos += sgn > 0.0;
+        neg += sgn < 0.0;
+    }
+    return pos == 5 || neg == 5;
+}
+
 /* OpencvVerifierBase.verify + Ransac.estimate_E, essential-matrix mode, with explicit samples.
  *   kp1 (n1,2), kp2 (n2,2): pixel coordinates, float64 row-major
  *   mi1, mi2 (M): match indices into kp1 / kp2
@@ -755,6 +783,7 @@ int oracle_verify_pair(const double* kp1, const double* kp2, const int32_t* mi1,
         int ne = oracle_fivept(sx1, sy1, sx2, sy2, Es);
         for (int c = 0; c < ne; ++c) {
             int ni;
+            if (!oracle_oriented_ok(Es + 9 * c, sx1, sy1, sx2, sy2)) continue;      /* invalid models are never scored */
             double cst = msac_cost(Es + 9 * c, x1, y1, x2, y2, M, thr2, &ni);
             ++ncand;
             if (cst < best_cost) { best_cost = cst; best_id = h * MAXC + c; memcpy(E_min, Es + 9 * c, sizeof(double) * 9); }
