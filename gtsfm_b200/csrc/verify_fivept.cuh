@@ -526,9 +526,9 @@ template <int STRIDE> struct HypView {
     __device__ __forceinline__ double operator()(int f) const { return base[f * STRIDE]; }
 };
 
-// Phase B (once per real root): root r -> (x, y) from the null vector of B(z), Gauss-Newton polish, unit-norm E.
-// false when the root yields no finite essential matrix.
-template <class HV> __device__ inline bool fivept_root(const HV& h, unsigned mid, int r, double* Eout)
+// Phase B1 (once per real root): root r -> z (Newton), (x, y) from the null vector of B(z), and the validity of the
+// unpolished model.  false when the root yields no finite, valid essential matrix: most wrong roots leave here.
+template <class HV> __device__ inline bool fivept_root_xyz(const HV& h, unsigned mid, int r, double* xyz)
 {
     const double lo = h(kOffLo + r), hi = h(kOffHi + r);
     const double z = ((mid >> r) & 1u) ? 0.5 * (lo + hi) : refine_root(h, lo, hi);
@@ -552,17 +552,19 @@ template <class HV> __device__ inline bool fivept_root(const HV& h, unsigned mid
             if (fabs(v[2]) > best) { best = fabs(v[2]); bv[0] = v[0]; bv[1] = v[1]; bv[2] = v[2]; }
         }
     if (!(best > 0)) return false;
-    double xyz[3] = {bv[0] / bv[2], bv[1] / bv[2], z};
+    xyz[0] = bv[0] / bv[2]; xyz[1] = bv[1] / bv[2]; xyz[2] = z;
     if (!isfinite(xyz[0]) || !isfinite(xyz[1])) return false;
-    double sx1[5], sy1[5], sx2[5], sy2[5];
+    double sx1[5], sy1[5], sx2[5], sy2[5], E0[9];
 #pragma unroll
     for (int k = 0; k < 5; ++k) { sx1[k] = h(kOffS + k); sy1[k] = h(kOffS + 5 + k); sx2[k] = h(kOffS + 10 + k); sy2[k] = h(kOffS + 15 + k); }
-    {   // validity of the unpolished model: most wrong roots leave here, before the Gauss-Newton polish
-        double E0[9];
 #pragma unroll
-        for (int e = 0; e < 9; ++e) E0[e] = xyz[0] * h(kOffN + e) + xyz[1] * h(kOffN + 9 + e) + xyz[2] * h(kOffN + 18 + e) + h(kOffN + 27 + e);
-        if (!oriented_sample_ok(E0, sx1, sy1, sx2, sy2)) return false;
-    }
+    for (int e = 0; e < 9; ++e) E0[e] = xyz[0] * h(kOffN + e) + xyz[1] * h(kOffN + 9 + e) + xyz[2] * h(kOffN + 18 + e) + h(kOffN + 27 + e);
+    return oriented_sample_ok(E0, sx1, sy1, sx2, sy2);
+}
+
+// Phase B2 (once per root that passed B1): Gauss-Newton polish, unit-norm E, validity of the final model.
+template <class HV> __device__ inline bool fivept_root_polish(const HV& h, double* xyz, double* Eout)
+{
     polish_xyz(h, xyz);
     double E[9], nn = 0;
 #pragma unroll
@@ -571,11 +573,20 @@ template <class HV> __device__ inline bool fivept_root(const HV& h, unsigned mid
         nn += E[e] * E[e];
     }
     if (!(nn > 0) || !isfinite(nn)) return false;
+    double sx1[5], sy1[5], sx2[5], sy2[5];
+#pragma unroll
+    for (int k = 0; k < 5; ++k) { sx1[k] = h(kOffS + k); sy1[k] = h(kOffS + 5 + k); sx2[k] = h(kOffS + 10 + k); sy2[k] = h(kOffS + 15 + k); }
     if (!oriented_sample_ok(E, sx1, sy1, sx2, sy2)) return false;
     nn = 1.0 / sqrt(nn);
 #pragma unroll
     for (int e = 0; e < 9; ++e) Eout[e] = E[e] * nn;
     return true;
+}
+
+template <class HV> __device__ inline bool fivept_root(const HV& h, unsigned mid, int r, double* Eout)
+{
+    double xyz[3];
+    return fivept_root_xyz(h, mid, r, xyz) && fivept_root_polish(h, xyz, Eout);
 }
 
 }  // namespace vm

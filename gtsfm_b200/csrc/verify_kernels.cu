@@ -67,7 +67,8 @@ __device__ int isolate_hypothesis(const VerifyBufs& b, const VerifyDims& d, int 
 // NaN when the root gave no finite matrix.
 constexpr int kSolveThreads = 64;
 constexpr int kSolveSmem = vm::kWorkDoubles * kSolveThreads * 8;
-static_assert(vm::kHypDoubles <= vm::kWorkDoubles, "hand-off state must fit the per-thread scratch");
+static_assert(vm::kHypDoubles * kSolveThreads + 3 * kSolveThreads * vm::kMaxCand <= vm::kWorkDoubles * kSolveThreads,
+              "hand-off state and the parked (x, y, z) of every root must fit the scratch");
 
 __global__ void __launch_bounds__(kSolveThreads, 2) solve_kernel(VerifyBufs b, VerifyDims d, int n_pairs)
 {
@@ -75,6 +76,8 @@ __global__ void __launch_bounds__(kSolveThreads, 2) solve_kernel(VerifyBufs b, V
     __shared__ int s_meta[kSolveThreads];                 // nr | deg << 8
     __shared__ unsigned s_mid[kSolveThreads];
     __shared__ unsigned s_valid[kSolveThreads];           // bit r: root r of the thread's hypothesis gave a valid model
+    __shared__ unsigned short s_map2[kSolveThreads * vm::kMaxCand];
+    __shared__ int s_n2;
     __shared__ int s_off[kSolveThreads + 1];
     __shared__ unsigned short s_map[kSolveThreads * vm::kMaxCand];
     __shared__ int s_wsum[kSolveThreads / 32];
@@ -85,6 +88,7 @@ __global__ void __launch_bounds__(kSolveThreads, 2) solve_kernel(VerifyBufs b, V
         const long long g = blk * kSolveThreads + tid;
         int nr = 0;
         s_valid[tid] = 0u;
+        if (tid == 0) s_n2 = 0;
         if (g < total) {
             const int p = static_cast<int>(g / d.H), h = static_cast<int>(g - static_cast<long long>(p) * d.H);
             if (b.pairs[p].status == 0) {
@@ -117,11 +121,25 @@ __global__ void __launch_bounds__(kSolveThreads, 2) solve_kernel(VerifyBufs b, V
             const long long left = total - blk * kSolveThreads;
             atomicAdd(b.stats + 1, static_cast<unsigned long long>(left < kSolveThreads ? left : kSolveThreads));
         }
+        // phase B1: one root per thread -> (x, y, z) and the validity of the unpolished model; survivors are compacted
+        // once more (their xyz parked in the unused tail of the scratch) so that the polish runs on full warps
+        double* s_xyz = s_h + vm::kHypDoubles * kSolveThreads;
         for (int idx = tid; idx < n_roots; idx += kSolveThreads) {
             const int code = s_map[idx], j = code >> 4, r = code & 15;
-            double E[9];
-            const bool ok = vm::fivept_root(vm::HypView<kSolveThreads>{s_h + j}, s_mid[j], r, E);
-            if (ok) {
+            double xyz[3];
+            if (vm::fivept_root_xyz(vm::HypView<kSolveThreads>{s_h + j}, s_mid[j], r, xyz)) {
+                const int pos = atomicAdd(&s_n2, 1);
+                s_map2[pos] = static_cast<unsigned short>(code);
+                s_xyz[3 * pos] = xyz[0]; s_xyz[3 * pos + 1] = xyz[1]; s_xyz[3 * pos + 2] = xyz[2];
+            }
+        }
+        __syncthreads();
+        const int n_ok = s_n2;
+        // phase B2: polish + final model of the survivors
+        for (int idx = tid; idx < n_ok; idx += kSolveThreads) {
+            const int code = s_map2[idx], j = code >> 4, r = code & 15;
+            double xyz[3] = {s_xyz[3 * idx], s_xyz[3 * idx + 1], s_xyz[3 * idx + 2]}, E[9];
+            if (vm::fivept_root_polish(vm::HypView<kSolveThreads>{s_h + j}, xyz, E)) {
                 float* out = b.E32 + ((blk * kSolveThreads + j) * vm::kMaxCand + r) * 9;
 #pragma unroll
                 for (int e = 0; e < 9; ++e) out[e] = static_cast<float>(E[e]);
