@@ -133,3 +133,18 @@ def test_batch_of_pairs_matches_single_pair_calls(ctx):
     ctx.set_workspace(4 << 30)
     for p, (i, j) in enumerate(pairs):
         check(m[off[p]:off[p + 1]], O.twoway_match(imgs[i], imgs[j], 0.8).reshape(-1, 2))
+
+
+def test_superpoint_like_batch_ratio_off(ctx):
+    """C4-shaped inputs: unit-norm float 256-d descriptors, ratio test off, several pairs in one batch."""
+    from gtsfm_b200 import synthetic
+    from oracle import oracle as O
+    scene = synthetic.make_scene(n_images=4, n_kps=700, dim=256, kind="superpoint", seed=20260004, ratio=None)
+    ctx.clear()
+    for i, d in enumerate(scene.descriptors):
+        ctx.upload_image(i, d)
+    m, off = ctx.match_batch(scene.pairs, None)
+    for p, (i, j) in enumerate(scene.pairs):
+        want = O.twoway_match(scene.descriptors[i], scene.descriptors[j], None).reshape(-1, 2)
+        check(m[off[p]:off[p + 1]], want)
+    assert off[-1] > 0

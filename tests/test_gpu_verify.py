@@ -229,3 +229,61 @@ def test_async_fetch_and_pinned_outputs_equal_the_plain_path(ctx):
         np.testing.assert_array_equal(m1, m0)
         for k in ("R", "t", "E", "n_inliers", "status", "mask"):
             np.testing.assert_array_equal(out1[k], ref[k])
+
+
+def test_low_inlier_rate_many_hypotheses(ctx):
+    """C5-shaped pair: 25 % inliers and several thousand hypotheses; same-sample parity with the oracle."""
+    import gtsfm_b200
+    rng = np.random.default_rng(55)
+    n, H = 1200, 4096
+    kp1, kp2, R, t, cal = make_pixel_scene(rng, n, out_frac=0.75)
+    mi = np.stack([np.arange(n), np.arange(n)], 1).astype(np.uint32)
+    samples = gtsfm_b200.ransac_samples(21, 7, n, H)
+    prm = params(4.0, H, seed=21)
+    keys = np.array([7], np.uint64)
+    prm.pair_keys = keys.ctypes.data
+    ctx.clear()
+    ctx.upload_image(0, None, kp1, cal)
+    ctx.upload_image(1, None, kp2, cal)
+    out = ctx.verify_batch(np.array([[0, 1]], np.int32), prm, mi, np.array([0, n], np.int64))
+    got = dict(status=out["status"][0], mask=out["mask"], R=out["R"][0], t=out["t"][0], n_inliers=out["n_inliers"][0])
+    check_against_oracle(got, kp1, kp2, mi, cal, cal, 4.0, samples)
+    assert rot_angle_deg(out["R"][0], R) < 1.0
+    cand, hyps, evals, executed = ctx.verify_stats(reset=True)
+    assert hyps >= H and 0 < executed <= evals
+
+
+def test_full_size_properties_c2_pair(ctx):
+    """Size-independent properties at the BASELINE size (8192 keypoints per image, 1024 hypotheses), where the oracle is
+    too slow to run inside the suite: the inlier mask IS sampson^2 < thr^2 of the returned E (fp64, strict), E = [t]x R
+    up to scale, R is a rotation, t a unit vector, the pose is the scene's, and matching is symmetric under swapping the
+    images (mutual nearest neighbours with the ratio test off)."""
+    from gtsfm_b200 import synthetic
+    from oracle import oracle as O
+    scene = synthetic.make_scene(n_images=2, n_kps=8192, seed=20260002)
+    ctx.clear()
+    for i in range(2):
+        ctx.upload_image(i, scene.descriptors[i], scene.keypoints[i], scene.cal)
+    pairs = np.array([[0, 1]], np.int32)
+    m, off = ctx.match_batch(pairs, 0.8)
+    out = ctx.verify_batch(pairs, params(4.0, 1024, seed=1), total=len(m))
+    assert out["status"][0] == 0 and len(m) > 4000
+    R, t, E, mask = out["R"][0], out["t"][0], out["E"][0], out["mask"]
+    assert np.allclose(R @ R.T, np.eye(3), atol=1e-9) and abs(np.linalg.det(R) - 1) < 1e-9 and abs(np.linalg.norm(t) - 1) < 1e-9
+    tx = np.array([[0, -t[2], t[1]], [t[2], 0, -t[0]], [-t[1], t[0], 0]])
+    En, Ep = E / np.linalg.norm(E), (tx @ R) / np.linalg.norm(tx @ R)
+    assert min(np.abs(En - Ep).max(), np.abs(En + Ep).max()) < 1e-6
+    n1 = O.calibrate(scene.keypoints[0][m[:, 0]], scene.cal)
+    n2 = O.calibrate(scene.keypoints[1][m[:, 1]], scene.cal)
+    s = O.sampson_sq(E, n1, n2) / (4.0 / scene.cal[0]) ** 2
+    differ = (s < 1.0) != (mask == 1)
+    assert not (differ & (np.abs(s - 1.0) > BAND)).any()
+    assert out["n_inliers"][0] == int(mask.sum())
+    Rgt, tgt = scene.relative_pose(0, 1)
+    assert rot_angle_deg(R, Rgt) < 0.5 and np.degrees(np.arccos(np.clip(t @ tgt, -1, 1))) < 2.0
+    # symmetry of mutual nearest neighbours
+    m01, _ = ctx.match_batch(pairs, None)
+    m10, _ = ctx.match_batch(np.array([[1, 0]], np.int32), None)
+    assert {(int(a), int(b)) for a, b in m01} == {(int(b), int(a)) for a, b in m10}
+    # every ratio-test match is also a mutual nearest neighbour
+    assert {(int(a), int(b)) for a, b in m} <= {(int(a), int(b)) for a, b in m01}
