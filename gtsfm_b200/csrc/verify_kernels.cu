@@ -416,7 +416,7 @@ __device__ void lo_pass(const VerifyBufs& b, const VPair& vp, const double* s_R,
     block_sum<22>(acc, s_red, s_out);
 }
 
-__global__ void __launch_bounds__(kFinThreads) finalize_kernel(VerifyBufs b, VerifyDims d, int n_pairs)
+__global__ void __launch_bounds__(kFinThreads, 2) finalize_kernel(VerifyBufs b, VerifyDims d, int n_pairs)
 {
     __shared__ double s_red[kFinThreads / 32][24];
     __shared__ double s_out[24];
@@ -477,21 +477,29 @@ __global__ void __launch_bounds__(kFinThreads) finalize_kernel(VerifyBufs b, Ver
     if (n_top == 0) { if (tid == 0) b.status[p] = 2; return; }
 
     // ---- (b) re-solve those hypotheses in fp64; the wanted root is the one whose matrix is closest to the fp32 copy
-    if (tid < n_top) {
-        const int h = s_topi[tid] / vm::kMaxCand;
-        const float* e32 = b.E32 + (static_cast<long long>(p) * d.H) * (9 * vm::kMaxCand) + static_cast<long long>(s_topi[tid]) * 9;
+    if ((tid & 31) == 0 && (tid >> 5) < n_top) {       // one re-solve per warp: no divergence between them
+        const int k = tid >> 5;
+        const int h = s_topi[k] / vm::kMaxCand, c = s_topi[k] - h * vm::kMaxCand;
+        const float* e32 = b.E32 + (static_cast<long long>(p) * d.H) * (9 * vm::kMaxCand) + static_cast<long long>(s_topi[k]) * 9;
         vm::HypState hs;
-        const int nr = isolate_hypothesis(b, d, p, h, hs, vm::Work<kTopK>{s_work + tid});
-        double bestdot = -1.0, Eb[9];
+        const int nr = isolate_hypothesis(b, d, p, h, hs, vm::Work<kTopK>{s_work + k});
+        const vm::HypView<1> hv{reinterpret_cast<const double*>(&hs)};
+        double bestdot = -1.0, Eb[9], E[9];
         for (int e = 0; e < 9; ++e) Eb[e] = nan("");
-        for (int r = 0; r < nr; ++r) {
-            double E[9];
-            if (!vm::fivept_root(vm::HypView<1>{reinterpret_cast<const double*>(&hs)}, hs.mid, r, E)) continue;
+        // slot c of E32 is root c of the same deterministic isolation; accept it when it reproduces the fp32 copy,
+        // otherwise (a root count that differs in the last bit) take the closest of all roots
+        if (c < nr && vm::fivept_root(hv, hs.mid, c, E)) {
             double dot = 0;
             for (int e = 0; e < 9; ++e) dot += E[e] * static_cast<double>(e32[e]);
-            if (fabs(dot) > bestdot) { bestdot = fabs(dot); for (int e = 0; e < 9; ++e) Eb[e] = E[e]; }
+            if (fabs(dot) > 0.999999) { bestdot = 2.0; for (int e = 0; e < 9; ++e) Eb[e] = E[e]; }
         }
-        for (int e = 0; e < 9; ++e) s_Ek[tid][e] = Eb[e];
+        for (int r = 0; r < nr && bestdot < 2.0; ++r) {
+            if (!vm::fivept_root(hv, hs.mid, r, E)) continue;
+            double dot = 0;
+            for (int e = 0; e < 9; ++e) dot += E[e] * static_cast<double>(e32[e]);
+            if (fabs(dot) > bestdot && fabs(dot) < 2.0) { bestdot = fabs(dot); for (int e = 0; e < 9; ++e) Eb[e] = E[e]; }
+        }
+        for (int e = 0; e < 9; ++e) s_Ek[k][e] = Eb[e];
     }
     __syncthreads();
 
