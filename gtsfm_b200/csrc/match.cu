@@ -14,6 +14,8 @@ cudaError_t launch_match_screen(const CUtensorMap& tm_desc, const CUtensorMap& t
 cudaError_t launch_resolve_int(const StoreView& st, const MatchWork& w, int which, long long total, int n_items, int max_class_rows,
                                cudaStream_t s);
 cudaError_t launch_exact_scan(const StoreView& st, const MatchWork& w, int mode, int n_jobs, cudaStream_t s);
+cudaError_t launch_exact_tile(const StoreView& st, const MatchWork& w, int n_jobs, long long total_cols, cudaStream_t s);
+bool exact_tile_supported(const StoreView& st);
 cudaError_t launch_match_finalize(const MatchWork& w, int use_ratio, double ratio, unsigned long long* keys_scratch,
                                   uint2* match_slot, int* match_count, long long* offsets, long long* running, uint2* compact_out,
                                   cudaStream_t s);
@@ -110,6 +112,9 @@ int gtsfm_match_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, double ra
     G2V_CUDA(c, c->col_key.reserve(m_cols + 16, false, s));
     G2V_CUDA(c, c->flag_list.reserve(8 * (m_rows + m_cols + 1), false, s));
     G2V_CUDA(c, c->n_flag.reserve(sizeof(int), false, s));
+    bool any_float = false;
+    for (const Chunk& k : chunks) any_float |= k.jobs > 0;
+    if (any_float) G2V_CUDA(c, c->col_cells.reserve(16 * static_cast<size_t>(m_cols + 1), false, s));
     G2V_CUDA(c, c->flag_scratch.reserve(16 * static_cast<size_t>(kFlagScratchCap), false, s));
     G2V_CUDA(c, c->keys_scratch.reserve(16 * (m_rows + 1), false, s));
     G2V_CUDA(c, c->match_slot.reserve(8 * (m_rows + 1), false, s));
@@ -134,6 +139,7 @@ int gtsfm_match_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, double ra
         w.row_key = c->row_key.as<unsigned short>(); w.col_key = c->col_key.as<uint8_t>();
         w.flag_list = c->flag_list.as<unsigned long long>(); w.n_flag = c->n_flag.as<int>();
         w.flag_scratch = c->flag_scratch.as<unsigned long long>();
+        w.col_cells = c->col_cells.as<unsigned long long>();
         w.flag_cap = static_cast<int>(std::min<long long>(k.rows + k.cols, kFlagScratchCap));
         G2V_CUDA(c, cudaMemsetAsync(c->n_flag.p, 0, sizeof(int), s));
         G2V_CUDA(c, cudaMemsetAsync(c->flag_scratch.p, 0xff, 16 * static_cast<size_t>(w.flag_cap), s));
@@ -155,7 +161,8 @@ int gtsfm_match_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, double ra
         }
         if (k.jobs > 0) {
             c->prof_begin(P_EXACT_SCAN);
-            G2V_CUDA(c, launch_exact_scan(st, w, 0, k.jobs, s));
+            if (exact_tile_supported(st)) { G2V_CUDA(c, launch_exact_tile(st, w, k.jobs, k.cols, s)); c->launches += 1; }
+            else G2V_CUDA(c, launch_exact_scan(st, w, 0, k.jobs, s));
             c->prof_end();
             c->launches += 1;
         }

@@ -35,6 +35,7 @@ struct MatchWork {
     unsigned short* row_key;
     uint8_t* col_key;
     // rows / columns whose screening result was ambiguous: (pair << 33 | dir << 32 | index), counted by n_flag
+    unsigned long long* col_cells;      // float path: 16 B per train column (0xff-filled): merge cell of exact_tile_kernel
     unsigned long long* flag_scratch;   // 16 B per flagged entry (0xff-filled): merge cell of the segmented exact scan
     unsigned long long* flag_list;
     int* n_flag;
