@@ -212,7 +212,8 @@ void gtsfm_ctx_destroy(gtsfm_ctx* c)
     DevBuf* bufs[] = {&c->desc_bf16, &c->desc_u8, &c->desc_f32, &c->augq, &c->augt, &c->norm_i, &c->valid, &c->kps, &c->img_flags, &c->stage,
                       &c->d_pairs, &c->rp_v1, &c->rp_v2, &c->rp_g, &c->colraw, &c->row_best, &c->row_d1, &c->row_d2, &c->col_best, &c->col_d1,
                       &c->col_d2, &c->flag_list, &c->n_flag, &c->keys_scratch, &c->match_slot, &c->match_count, &c->match_offsets,
-                      &c->match_out, &c->d_total};
+                      &c->match_out, &c->d_total, &c->row_key, &c->col_key, &c->row_cnt, &c->col_cnt, &c->row_list, &c->col_list,
+                      &c->flag_scratch, &c->col_cells};
     for (DevBuf* b : bufs) b->release();
     for (DevBuf& b : c->v_bufs) b.release();
     c->h_pairs.release();

@@ -11,7 +11,7 @@ namespace g2v {
 cudaError_t launch_match_screen(const CUtensorMap& tm_desc, const CUtensorMap& tm_augq, const CUtensorMap& tm_augt,
                                 const PairDesc* pairs, int n_pairs, int n_items, float* rp_v1, float* rp_v2, uint8_t* rp_g,
                                 float* colraw, int kpad, int n_sm, cudaStream_t stream);
-cudaError_t launch_resolve_int(const StoreView& st, const MatchWork& w, int which, long long total, int n_items, int max_class_rows,
+cudaError_t launch_resolve_int(const StoreView& st, const MatchWork& w, int which, long long total, int max_class_rows,
                                cudaStream_t s);
 cudaError_t launch_exact_scan(const StoreView& st, const MatchWork& w, int mode, int n_jobs, cudaStream_t s);
 cudaError_t launch_exact_tile(const StoreView& st, const MatchWork& w, int n_jobs, long long total_cols, cudaStream_t s);
@@ -28,7 +28,7 @@ constexpr long long kFlagScratchCap = 1ll << 23;
 struct Chunk {
     int p0 = 0, p1 = 0;
     long long rp = 0, cr = 0, rows = 0, cols = 0;
-    int items = 0, jobs = 0, max_class_rows = 0;
+    int items = 0, jobs = 0, max_class_rows = 0, max_hb = 0;
 };
 }  // namespace g2v
 
@@ -81,12 +81,12 @@ int gtsfm_match_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, double ra
         const long long cr = pd.path == 0 ? static_cast<long long>(pd.nt_pad) * kTileQ : 0;
         const int items = pd.path == 0 && pd.nq > 0 ? pd.nt_pad / kBlockT : 0;
         const int jobs = pd.path == 1 && pd.nq > 0 ? (pd.nq + 31) / 32 + (pd.nt + 31) / 32 : 0;
-        const long long bytes = rp * 9 + cr * 4 + static_cast<long long>(pd.nq_pad) * (12 + 16 + 8 + 8) + static_cast<long long>(pd.nt_pad) * (12 + 8);
+        const long long bytes = rp * 9 + cr * 4 + static_cast<long long>(pd.nq_pad) * (12 + 16 + 8 + 8 + 8) + static_cast<long long>(pd.nt_pad) * (12 + 8 + 8);
         if (cur.p1 > cur.p0 && (cur_bytes + bytes > c->workspace_bytes || cur.rows + cur.cols + pd.nq_pad + pd.nt_pad > kFlagScratchCap)) { chunks.push_back(cur); cur = Chunk{}; cur.p0 = cur.p1 = p; cur_bytes = 0; }
         pd.rp_base = cur.rp; pd.cr_base = cur.cr; pd.out_base = cur.rows; pd.cb_base = cur.cols; pd.item0 = cur.items; pd.job0 = cur.jobs;
         cur.rp += rp; cur.cr += cr; cur.rows += pd.nq_pad; cur.cols += pd.nt_pad; cur.items += items; cur.jobs += jobs;
         cur.p1 = p + 1;
-        if (items > 0) cur.max_class_rows = std::max(cur.max_class_rows, pd.nq_pad / kTileQ);
+        if (items > 0) { cur.max_class_rows = std::max(cur.max_class_rows, pd.nq_pad / kTileQ); cur.max_hb = std::max(cur.max_hb, pd.nt_pad / kHalfT); }
         cur_bytes += bytes;
         out_cap += pd.nq < pd.nt ? pd.nq : pd.nt;
         pds[p] = pd;
@@ -94,7 +94,11 @@ int gtsfm_match_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, double ra
     chunks.push_back(cur);
 
     // ---- buffers
-    long long m_rp = 0, m_cr = 0, m_rows = 0, m_cols = 0;
+    long long m_rp = 0, m_cr = 0, m_rows = 0, m_cols = 0, m_rcnt = 0, m_ccnt = 0;
+    for (const Chunk& k : chunks) {
+        m_rcnt = std::max(m_rcnt, static_cast<long long>(k.p1 - k.p0) * (k.max_hb + 1));
+        m_ccnt = std::max(m_ccnt, static_cast<long long>(k.p1 - k.p0) * (kTileQ + 1));
+    }
     for (const Chunk& k : chunks) { m_rp = std::max(m_rp, k.rp); m_cr = std::max(m_cr, k.cr); m_rows = std::max(m_rows, k.rows); m_cols = std::max(m_cols, k.cols); }
     cudaStream_t s = c->stream;
     G2V_CUDA(c, c->d_pairs.reserve(sizeof(PairDesc) * n_pairs, false, s));
@@ -108,8 +112,12 @@ int gtsfm_match_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, double ra
     G2V_CUDA(c, c->col_best.reserve(4 * (m_cols + 1), false, s));
     G2V_CUDA(c, c->col_d1.reserve(4 * (m_cols + 1), false, s));
     G2V_CUDA(c, c->col_d2.reserve(4 * (m_cols + 1), false, s));
-    G2V_CUDA(c, c->row_key.reserve(2 * (m_rows + 16), false, s));
-    G2V_CUDA(c, c->col_key.reserve(m_cols + 16, false, s));
+    G2V_CUDA(c, c->row_key.reserve(4 * (m_rows + 16), false, s));
+    G2V_CUDA(c, c->col_key.reserve(4 * (m_cols + 16), false, s));
+    G2V_CUDA(c, c->row_list.reserve(4 * (m_rows + 16), false, s));
+    G2V_CUDA(c, c->col_list.reserve(4 * (m_cols + 16), false, s));
+    G2V_CUDA(c, c->row_cnt.reserve(4 * (m_rcnt + 16), false, s));
+    G2V_CUDA(c, c->col_cnt.reserve(4 * (m_ccnt + 16), false, s));
     G2V_CUDA(c, c->flag_list.reserve(8 * (m_rows + m_cols + 1), false, s));
     G2V_CUDA(c, c->n_flag.reserve(sizeof(int), false, s));
     bool any_float = false;
@@ -136,7 +144,9 @@ int gtsfm_match_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, double ra
         w.rp_v1 = c->rp_v1.as<float>(); w.rp_v2 = c->rp_v2.as<float>(); w.rp_g = c->rp_g.as<uint8_t>(); w.colraw = c->colraw.as<float>();
         w.row_best = c->row_best.as<int>(); w.row_d1 = c->row_d1.as<float>(); w.row_d2 = c->row_d2.as<float>();
         w.col_best = c->col_best.as<int>(); w.col_d1 = c->col_d1.as<float>(); w.col_d2 = c->col_d2.as<float>();
-        w.row_key = c->row_key.as<unsigned short>(); w.col_key = c->col_key.as<uint8_t>();
+        w.row_key = c->row_key.as<unsigned int>(); w.col_key = c->col_key.as<unsigned int>();
+        w.row_cnt = c->row_cnt.as<int>(); w.col_cnt = c->col_cnt.as<int>(); w.row_list = c->row_list.as<int>(); w.col_list = c->col_list.as<int>();
+        w.max_hb = k.max_hb;
         w.flag_list = c->flag_list.as<unsigned long long>(); w.n_flag = c->n_flag.as<int>();
         w.flag_scratch = c->flag_scratch.as<unsigned long long>();
         w.col_cells = c->col_cells.as<unsigned long long>();
@@ -149,15 +159,15 @@ int gtsfm_match_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, double ra
                                             c->rp_v2.as<float>(), c->rp_g.as<uint8_t>(), c->colraw.as<float>(), c->kpad, c->n_sm, s));
             c->prof_end();
             c->prof_begin(P_RESOLVE_ROWS);
-            G2V_CUDA(c, launch_resolve_int(st, w, 0, k.rows, k.items, k.max_class_rows, s));
+            G2V_CUDA(c, launch_resolve_int(st, w, 0, k.rows, k.max_class_rows, s));
             c->prof_end();
             c->prof_begin(P_RESOLVE_COLS);
-            G2V_CUDA(c, launch_resolve_int(st, w, 1, k.cols, k.items, k.max_class_rows, s));
+            G2V_CUDA(c, launch_resolve_int(st, w, 1, k.cols, k.max_class_rows, s));
             c->prof_end();
             c->prof_begin(P_EXACT_SCAN);
             G2V_CUDA(c, launch_exact_scan(st, w, 1, w.flag_cap, s));
             c->prof_end();
-            c->launches += 6;
+            c->launches += 10;
         }
         if (k.jobs > 0) {
             c->prof_begin(P_EXACT_SCAN);
@@ -215,8 +225,8 @@ int gtsfm_debug_fetch(gtsfm_ctx* c, int what, void* dst, int64_t bytes)
     if (!c || !dst || bytes < 0) return GTSFM_E_ARG;
     cudaSetDevice(c->device);
     const DevBuf* b[] = {&c->rp_v1, &c->rp_v2, &c->rp_g, &c->colraw, &c->row_best, &c->row_d1, &c->row_d2,
-                         &c->col_best, &c->col_d1, &c->col_d2, &c->n_flag};
-    if (what < 0 || what > 10) return fail(c, GTSFM_E_ARG, "unknown buffer");
+                         &c->col_best, &c->col_d1, &c->col_d2, &c->n_flag, &c->row_cnt, &c->col_cnt, &c->row_list, &c->col_list};
+    if (what < 0 || what > 14) return fail(c, GTSFM_E_ARG, "unknown buffer");
     if (static_cast<size_t>(bytes) > b[what]->cap) return fail(c, GTSFM_E_ARG, "buffer smaller than requested");
     G2V_CUDA(c, cudaMemcpyAsync(dst, b[what]->p, bytes, cudaMemcpyDeviceToHost, c->stream));
     G2V_CUDA(c, cudaStreamSynchronize(c->stream));

@@ -10,20 +10,21 @@
 // runner-up group (class) could tie with the winner in float32-distance space the row (column) is flagged and
 // re-scanned exhaustively by exact_scan_kernel (match_exact.cu), so the result never depends on the screening order.
 //
-// Two kernels per direction:
-//   merge   : reduces the screening partials of a row (column) to (k1, k2, bucket key); coalesced, HBM/L2 streaming.
+// Four kernels per direction (a counting sort of the rows / columns by the descriptor block they must be compared with):
+//   merge   : reduces the screening partials of a row (column) to (k1, k2, bucket) and takes a slot in the bucket
+//             (one atomicAdd on the bucket counter); coalesced, HBM streaming.
+//   prefix  : bucket counters -> exclusive offsets, one CTA per pair.
+//   scatter : writes every row (column) into its pair's member list at offset[bucket] + slot.
 //   bucket  : one CTA per bucket -- (pair, 128-column half block) for rows, (pair, lane class) for columns.  The CTA
 //             stages the <= 128 (class: nq/128) descriptor rows every member of the bucket is compared against in
-//             shared memory ONCE, collects the members by scanning the key array, and recomputes the candidates from
-//             shared memory.  Per pair this reads each descriptor row about once (2 MB) instead of gathering the same
-//             rows once per member through L2 (80 MB for 8192 x 8192).
+//             shared memory ONCE and recomputes the candidates of its members from there.  Per pair this reads each
+//             descriptor row about once (2 MB) instead of gathering the same rows once per member through L2 (80 MB
+//             for 8192 x 8192).
 #include <cfloat>
 
 #include "store.h"
 
 namespace g2v {
-
-constexpr int kListCap = 4096;
 
 __device__ __forceinline__ int find_by_out_base(const PairDesc* pairs, int n, long long pos)
 {
@@ -43,16 +44,6 @@ __device__ __forceinline__ int find_by_cb_base(const PairDesc* pairs, int n, lon
     }
     return lo;
 }
-__device__ __forceinline__ int find_by_item0(const PairDesc* pairs, int n, int item)
-{
-    int lo = 0, hi = n - 1;
-    while (lo < hi) {
-        int mid = (lo + hi + 1) >> 1;
-        if (pairs[mid].item0 <= item) lo = mid; else hi = mid - 1;
-    }
-    return lo;
-}
-
 __device__ __forceinline__ void flag(const MatchWork& w, int pair, int dir, int idx)
 {
     const int k = atomicAdd(w.n_flag, 1);
@@ -67,7 +58,8 @@ __device__ __forceinline__ float dist_from_d2(int d2) { return sqrtf(static_cast
 __device__ __forceinline__ float dist_from_half(float h) { return h >= kHuge * 0.25f ? FLT_MAX : sqrtf(h + h); }
 
 // ---------------------------------------------------------------------------------------------------------------
-// merge, rows: one thread per query row.  row_d1 <- k1, row_d2 <- k2 (halved squared distances), row_key <- bucket.
+// merge, rows: one thread per query row.  row_d1 <- k1, row_d2 <- k2 (halved squared distances), row_key <- winning
+// half block << 3 | winning group | slot in the bucket << 16.
 __global__ void __launch_bounds__(128) merge_rows_kernel(StoreView st, MatchWork w, long long total_rows)
 {
     const long long pos = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -77,58 +69,70 @@ __global__ void __launch_bounds__(128) merge_rows_kernel(StoreView st, MatchWork
     if (pd.path != 0) return;
     const int i = static_cast<int>(pos - pd.out_base);
     if (i >= pd.nq || !st.valid[pd.q_row0 + i]) {
-        w.row_key[pos] = 0xffffu;
+        w.row_key[pos] = 0xffffffffu;
         if (i < pd.nq) { w.row_best[pos] = -1; w.row_d1[pos] = FLT_MAX; w.row_d2[pos] = FLT_MAX; }
         return;
     }
     const int n_hb = pd.nt_pad / kHalfT;
     float k1 = kHuge * 8.0f, k2 = kHuge * 8.0f;
-    int hb1 = 0, g1 = 0;
+    int hb1 = 0;
     const long long e0 = pd.rp_base + i;
+    // the loads of a batch are independent of the running minimum, so they are all in flight together; the group id of
+    // the winner is fetched once at the end (a load inside the compare would serialise on every new minimum)
+#pragma unroll 8
     for (int hb = 0; hb < n_hb; ++hb) {
         const long long e = e0 + static_cast<long long>(hb) * pd.nq_pad;
-        const float a = w.rp_v1[e], b = w.rp_v2[e];
-        if (a < k1) { k2 = fminf(k1, b); k1 = a; hb1 = hb; g1 = w.rp_g[e]; }
-        else k2 = fminf(k2, a);
+        const float a = __ldg(w.rp_v1 + e), b = __ldg(w.rp_v2 + e);
+        const bool lt = a < k1;                                   // strict: the lowest half block wins ties
+        k2 = lt ? fminf(k1, b) : fminf(k2, a);
+        hb1 = lt ? hb : hb1;
+        k1 = fminf(k1, a);
     }
+    const int g1 = w.rp_g[e0 + static_cast<long long>(hb1) * pd.nq_pad];
     w.row_d1[pos] = k1;
     w.row_d2[pos] = k2;
-    w.row_key[pos] = static_cast<unsigned short>((hb1 << 3) | g1);
+    const unsigned slot = static_cast<unsigned>(atomicAdd(w.row_cnt + static_cast<long long>(p) * (w.max_hb + 1) + hb1, 1));
+    w.row_key[pos] = static_cast<unsigned>((hb1 << 3) | g1) | (slot << 16);
 }
 
-// merge, columns: one warp per train column, kColsPerCta columns per CTA (every CTA lies inside one pair because column
-// ranges start on multiples of 256, so the pair lookup is done once per CTA).  col_d1 <- k1, col_d2 <- k2, col_key <-
-// winning lane class.
+// merge, columns: eight lanes per train column (four float4 loads each: a column's 512 bytes are read in 128-byte
+// pieces), kColsPerCta columns per CTA.  Every CTA lies inside one pair because column ranges start on multiples of 256,
+// so the pair lookup is done once per CTA.  col_d1 <- k1, col_d2 <- k2, col_key <- winning lane class | slot << 8.
 constexpr int kColsPerCta = 64;
 __global__ void __launch_bounds__(256) merge_cols_kernel(StoreView st, MatchWork w, long long total_cols)
 {
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int l8 = threadIdx.x & 7, sub = threadIdx.x >> 3;       // 32 columns per pass
     const long long pos0 = static_cast<long long>(blockIdx.x) * kColsPerCta;
     if (pos0 >= total_cols) return;
     const int p = find_by_cb_base(w.pairs, w.n_pairs, pos0);
     const PairDesc pd = w.pairs[p];
     if (pd.path != 0) return;
-#pragma unroll 2
-    for (int u0 = warp; u0 < kColsPerCta; u0 += 8) {
-        const long long pos = pos0 + u0;
+#pragma unroll
+    for (int u0 = 0; u0 < kColsPerCta; u0 += 32) {
+        const long long pos = pos0 + u0 + sub;
         const int j = static_cast<int>(pos - pd.cb_base);
-        if (j >= pd.nt || !st.valid[pd.t_row0 + j]) {
-            if (lane == 0) {
-                w.col_key[pos] = 0xffu;
-                if (j < pd.nt) { w.col_best[pos] = -1; w.col_d1[pos] = FLT_MAX; w.col_d2[pos] = FLT_MAX; }
-            }
-            continue;
-        }
-        const float4 c4 = *reinterpret_cast<const float4*>(w.colraw + pd.cr_base + static_cast<long long>(j) * kTileQ + lane * 4);
-        const float cv[4] = {c4.x, c4.y, c4.z, c4.w};
+        const bool live = j < pd.nt && st.valid[pd.t_row0 + j];
         float k1 = kHuge * 8.0f, k2 = kHuge * 8.0f;
         int c1 = 0;
+        if (live) {
+            const float4* src = reinterpret_cast<const float4*>(w.colraw + pd.cr_base + static_cast<long long>(j) * kTileQ) + l8;
+            float4 c4[4];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            if (cv[u] < k1) { k2 = k1; k1 = cv[u]; c1 = lane * 4 + u; } else k2 = fminf(k2, cv[u]);
+            for (int u = 0; u < 4; ++u) c4[u] = __ldg(src + 8 * u);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const float cv[4] = {c4[u].x, c4[u].y, c4[u].z, c4[u].w};
+#pragma unroll
+                for (int v = 0; v < 4; ++v) {
+                    const bool lt = cv[v] < k1;                   // ascending class order: the lowest class wins ties
+                    k2 = lt ? k1 : fminf(k2, cv[v]);
+                    c1 = lt ? 32 * u + 4 * l8 + v : c1;
+                    k1 = fminf(k1, cv[v]);
+                }
+            }
         }
 #pragma unroll
-        for (int off = 16; off > 0; off >>= 1) {
+        for (int off = 4; off > 0; off >>= 1) {
             const float o1 = __shfl_xor_sync(0xffffffffu, k1, off), o2 = __shfl_xor_sync(0xffffffffu, k2, off);
             const int oc = __shfl_xor_sync(0xffffffffu, c1, off);
             const bool take = (o1 < k1) || (o1 == k1 && oc < c1);
@@ -136,12 +140,73 @@ __global__ void __launch_bounds__(256) merge_cols_kernel(StoreView st, MatchWork
             k2 = fminf(fminf(k2, o2), lose);
             if (take) { k1 = o1; c1 = oc; }
         }
-        if (lane == 0) {
-            w.col_d1[pos] = k1;
-            w.col_d2[pos] = k2;
-            w.col_key[pos] = static_cast<uint8_t>(c1);
+        if (l8 == 0) {
+            if (live) {
+                w.col_d1[pos] = k1;
+                w.col_d2[pos] = k2;
+                const unsigned slot = static_cast<unsigned>(atomicAdd(w.col_cnt + static_cast<long long>(p) * (kTileQ + 1) + c1, 1));
+                w.col_key[pos] = static_cast<unsigned>(c1) | (slot << 8);
+            } else {
+                w.col_key[pos] = 0xffffffffu;
+                if (j < pd.nt) { w.col_best[pos] = -1; w.col_d1[pos] = FLT_MAX; w.col_d2[pos] = FLT_MAX; }
+            }
         }
     }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// prefix: cnt[p][0 .. stride - 2] (bucket sizes) -> exclusive offsets in place, cnt[p][stride - 1] <- the total.
+__global__ void __launch_bounds__(128) prefix_counts_kernel(int* cnt, int stride)
+{
+    __shared__ int s_w[4];
+    __shared__ int s_carry;
+    int* c = cnt + static_cast<long long>(blockIdx.x) * stride;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) s_carry = 0;
+    __syncthreads();
+    for (int base = 0; base < stride; base += 128) {
+        const int k = base + tid;
+        const int v = (k < stride - 1) ? c[k] : 0;
+        int inc = v;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) { const int o = __shfl_up_sync(0xffffffffu, inc, off); if (lane >= off) inc += o; }
+        if (lane == 31) s_w[warp] = inc;
+        __syncthreads();
+        int before = s_carry;
+        for (int w2 = 0; w2 < warp; ++w2) before += s_w[w2];
+        if (k < stride) c[k] = before + inc - v;
+        __syncthreads();
+        if (tid == 127) s_carry = before + inc;
+        __syncthreads();
+    }
+}
+
+// scatter: member lists.  Rows: entry = row << 3 | group at list[out_base + offset[half block] + slot];
+// columns: entry = column at list[cb_base + offset[class] + slot].
+__global__ void __launch_bounds__(256) scatter_rows_kernel(MatchWork w, long long total_rows)
+{
+    const long long pos = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (pos >= total_rows) return;
+    const int p = find_by_out_base(w.pairs, w.n_pairs, static_cast<long long>(blockIdx.x) * blockDim.x);
+    if (w.pairs[p].path != 0) return;
+    const unsigned key = w.row_key[pos];
+    if (key == 0xffffffffu) return;
+    const long long ob = w.pairs[p].out_base;
+    const int hb = static_cast<int>(key & 0xffffu) >> 3;
+    const int off = w.row_cnt[static_cast<long long>(p) * (w.max_hb + 1) + hb];
+    w.row_list[ob + off + (key >> 16)] = (static_cast<int>(pos - ob) << 3) | static_cast<int>(key & 7u);
+}
+__global__ void __launch_bounds__(256) scatter_cols_kernel(MatchWork w, long long total_cols)
+{
+    const long long pos = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (pos >= total_cols) return;
+    const int p = find_by_cb_base(w.pairs, w.n_pairs, static_cast<long long>(blockIdx.x) * blockDim.x);
+    if (w.pairs[p].path != 0) return;
+    const unsigned key = w.col_key[pos];
+    if (key == 0xffffffffu) return;
+    const long long cb = w.pairs[p].cb_base;
+    const int off = w.col_cnt[static_cast<long long>(p) * (kTileQ + 1) + static_cast<int>(key & 0xffu)];
+    w.col_list[cb + off + (key >> 8)] = static_cast<int>(pos - cb);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -160,24 +225,51 @@ __device__ __forceinline__ unsigned dot_regs_smem(const RowRegs<N16>& a, const u
     return acc;
 }
 
-// bucket, rows: one CTA per (pair, half block of 128 train columns).  Staged rows are padded by 16 B per row and a
-// further 16 B per group of 16, so threads working on different groups of the half block hit different banks.
+// Running (best, second best, index of the best) over integer squared distances.  sqrtf is strictly increasing on the
+// integers below 2^22 (neighbouring square roots are more than one float32 ulp apart), so the order of the float32
+// distances cv2 compares is the order of the integers; candidates are visited by ascending index and '<' is strict, so
+// the lowest index wins ties.  A best distance of 2^22 or more makes the caller flag the entry for the exhaustive scan.
+constexpr int kSqrtMonotoneBelow = 1 << 22;
+struct Top2 {
+    int b1, b2, i1;
+    __device__ __forceinline__ void push(int d2, int idx)
+    {
+        const bool lt = d2 < b1;
+        b2 = lt ? b1 : min(b2, d2);
+        i1 = lt ? idx : i1;
+        b1 = min(b1, d2);
+    }
+    // merge with the partner lane `off` lanes away (all lanes of the warp call this)
+    __device__ __forceinline__ void merge_xor(int off)
+    {
+        const int o1 = __shfl_xor_sync(0xffffffffu, b1, off), o2 = __shfl_xor_sync(0xffffffffu, b2, off);
+        const int oi = __shfl_xor_sync(0xffffffffu, i1, off);
+        const bool take = (o1 < b1) || (o1 == b1 && oi < i1);
+        const int lose = take ? b1 : o1;
+        b2 = min(min(b2, o2), lose);
+        if (take) { b1 = o1; i1 = oi; }
+    }
+};
+__device__ __forceinline__ float dist_or_max(int d2) { return d2 == INT_MAX ? FLT_MAX : dist_from_d2(d2); }
+
+// bucket, rows: one CTA per (pair, half block of 128 train columns); four lanes share a member row (four of the sixteen
+// group columns each).  Staged rows are padded by 16 B per row and a further 16 B per group of 16, so lanes working on
+// different groups of the half block hit different banks.
 template <int N16>
-__global__ void __launch_bounds__(128) bucket_rows_kernel(StoreView st, MatchWork w, int n_half)
+__global__ void __launch_bounds__(128) bucket_rows_kernel(StoreView st, MatchWork w)
 {
     constexpr int kStride = N16 + 1;
     __shared__ uint4 s_t[kHalfT * kStride + kHalfT / kGroup];
     __shared__ int s_norm[kHalfT];
     __shared__ uint8_t s_valid[kHalfT];
-    __shared__ int s_list[kListCap];
-    __shared__ int s_n;
 
     const int tid = threadIdx.x;
-    const int p = find_by_item0(w.pairs, w.n_pairs, blockIdx.x >> 1);
+    const int p = blockIdx.x / w.max_hb, hb = blockIdx.x - p * w.max_hb;
     const PairDesc pd = w.pairs[p];
-    if (pd.path != 0 || pd.nq == 0) return;
-    const int hb = static_cast<int>(blockIdx.x) - 2 * pd.item0;
-    if (hb * kHalfT >= pd.nt) return;                              // only padding columns: never a winner
+    if (pd.path != 0 || pd.nq == 0 || hb * kHalfT >= pd.nt) return;   // padding columns are never a winner
+    const int* off = w.row_cnt + static_cast<long long>(p) * (w.max_hb + 1) + hb;
+    const int start = off[0], n = off[1] - start;
+    if (n <= 0) return;
     const long long trow0 = static_cast<long long>(pd.t_row0) + hb * kHalfT;
     const uint4* tsrc = reinterpret_cast<const uint4*>(st.desc_u8) + trow0 * N16;
     for (int idx = tid; idx < kHalfT * N16; idx += 128) {
@@ -186,78 +278,61 @@ __global__ void __launch_bounds__(128) bucket_rows_kernel(StoreView st, MatchWor
     }
     s_norm[tid] = st.norm_i[trow0 + tid];
     s_valid[tid] = st.valid[trow0 + tid];
-    if (tid == 0) s_n = 0;
     __syncthreads();
 
-    const unsigned short* keys = w.row_key + pd.out_base;
-    for (int base = 0; base < pd.nq_pad; base += 1024) {
-        const int i0 = base + tid * 8;
-        if (i0 < pd.nq_pad) {
-            const uint4 kk = *reinterpret_cast<const uint4*>(keys + i0);
-            const unsigned kw[4] = {kk.x, kk.y, kk.z, kk.w};
+    const int* list = w.row_list + pd.out_base + start;
+    const int l4 = tid & 3;
+    const int n_round = (n + 31) & ~31;
+    for (int idx = tid >> 2; idx < n_round; idx += 32) {
+        const bool active = idx < n;
+        const int e = active ? list[idx] : 0;
+        const int i = e >> 3, g = e & 7;
+        RowRegs<N16> q;
+        const uint4* qrow = reinterpret_cast<const uint4*>(st.desc_u8) + static_cast<long long>(pd.q_row0 + i) * N16;
 #pragma unroll
-            for (int u = 0; u < 8; ++u) {
-                const unsigned key = (kw[u >> 1] >> ((u & 1) * 16)) & 0xffffu;
-                if (key != 0xffffu && static_cast<int>(key >> 3) == hb) s_list[atomicAdd(&s_n, 1)] = ((i0 + u) << 3) | (key & 7);
-            }
+        for (int k = 0; k < N16; ++k) q.v[k] = __ldg(qrow + k);
+        const int nq2 = st.norm_i[pd.q_row0 + i];
+        Top2 t{INT_MAX, INT_MAX, INT_MAX};
+#pragma unroll
+        for (int u = 0; u < kGroup / 4; ++u) {
+            const int r = g * kGroup + l4 + 4 * u;
+            const int j = hb * kHalfT + r;
+            const int d2 = nq2 + s_norm[r] - 2 * static_cast<int>(dot_regs_smem<N16>(q, s_t + r * kStride + g));
+            if (active && j < pd.nt && s_valid[r]) t.push(d2, j);
         }
-        __syncthreads();
-        const int n = s_n;
-        const bool last = base + 1024 >= pd.nq_pad;
-        if (n > kListCap - 1024 || last) {
-            for (int idx = tid; idx < n; idx += 128) {
-                const int e = s_list[idx];
-                const int i = e >> 3, g = e & 7;
-                const long long pos = pd.out_base + i;
-                RowRegs<N16> q;
-                const uint4* qrow = reinterpret_cast<const uint4*>(st.desc_u8) + static_cast<long long>(pd.q_row0 + i) * N16;
-#pragma unroll
-                for (int k = 0; k < N16; ++k) q.v[k] = __ldg(qrow + k);
-                const int nq2 = st.norm_i[pd.q_row0 + i];
-                const float k1 = w.row_d1[pos], k2 = w.row_d2[pos];
-                float f1 = FLT_MAX, f2 = FLT_MAX;
-                int j1 = -1, dmin = INT_MAX;
-#pragma unroll 4
-                for (int c = 0; c < kGroup; ++c) {
-                    const int r = g * kGroup + c;
-                    const int j = hb * kHalfT + r;
-                    if (j >= pd.nt || !s_valid[r]) continue;
-                    const int d2 = nq2 + s_norm[r] - 2 * static_cast<int>(dot_regs_smem<N16>(q, s_t + r * kStride + g));
-                    dmin = min(dmin, d2);
-                    const float f = dist_from_d2(d2);
-                    if (f < f2) { if (f < f1) { f2 = f1; f1 = f; j1 = j; } else f2 = f; }
-                }
-                const float f2o = dist_from_half(k2);
-                // Ambiguous when another group may hold an equal (float32) distance at a lower index, or when the
-                // recomputed minimum does not reproduce the screened value (never expected; keeps the result
-                // independent of screening).
-                const bool ambiguous = (j1 < 0) || (f2o <= f1) || (static_cast<float>(dmin) != k1 + k1);
-                if (ambiguous) flag(w, p, 0, i);
-                w.row_best[pos] = j1;
-                w.row_d1[pos] = f1;
-                w.row_d2[pos] = fminf(f2, f2o);
-            }
-            __syncthreads();
-            if (tid == 0) s_n = 0;
-            __syncthreads();
+        t.merge_xor(1);
+        t.merge_xor(2);
+        if (active && l4 == 0) {
+            const long long pos = pd.out_base + i;
+            const float k1 = w.row_d1[pos], k2 = w.row_d2[pos];
+            const float f1 = dist_or_max(t.b1), f2 = dist_or_max(t.b2), f2o = dist_from_half(k2);
+            // Ambiguous when another group may hold an equal (float32) distance at a lower index, or when the
+            // recomputed minimum does not reproduce the screened value (never expected; keeps the result
+            // independent of screening).
+            const bool ambiguous = (t.i1 == INT_MAX) || (f2o <= f1) || (static_cast<float>(t.b1) != k1 + k1) || (t.b1 >= kSqrtMonotoneBelow);
+            if (ambiguous) flag(w, p, 0, i);
+            w.row_best[pos] = (t.i1 == INT_MAX) ? -1 : t.i1;
+            w.row_d1[pos] = f1;
+            w.row_d2[pos] = fminf(f2, f2o);
         }
     }
 }
 
 // bucket, columns: one CTA per (pair, lane class c).  The class rows c, c + 128, ... of the query image are staged in
-// shared memory; two threads share a column (even / odd class rows).
+// shared memory; eight lanes share a member column (class rows t = lane, lane + 8, ...).
 template <int N16>
 __global__ void __launch_bounds__(128) bucket_cols_kernel(StoreView st, MatchWork w)
 {
     constexpr int kStride = N16 + 1;
     extern __shared__ uint4 s_dyn[];
-    __shared__ int s_list[kListCap];
-    __shared__ int s_n;
 
     const int tid = threadIdx.x;
     const int p = blockIdx.x >> 7, c = blockIdx.x & 127;
     const PairDesc pd = w.pairs[p];
     if (pd.path != 0 || pd.nq == 0 || pd.nt == 0 || c >= pd.nq) return;
+    const int* off = w.col_cnt + static_cast<long long>(p) * (kTileQ + 1) + c;
+    const int start = off[0], n = off[1] - start;
+    if (n <= 0) return;
     const int n_cls = pd.nq_pad / kTileQ;
     uint4* s_q = s_dyn;
     int* s_norm = reinterpret_cast<int*>(s_dyn + n_cls * kStride);
@@ -272,70 +347,39 @@ __global__ void __launch_bounds__(128) bucket_cols_kernel(StoreView st, MatchWor
         s_norm[t] = st.norm_i[row];
         s_valid[t] = (c + t * kTileQ < pd.nq) ? st.valid[row] : 0;
     }
-    if (tid == 0) s_n = 0;
     __syncthreads();
 
-    const uint8_t* keys = w.col_key + pd.cb_base;
-    const int par = tid & 1;
-    for (int base = 0; base < pd.nt_pad; base += 2048) {
-        const int j0 = base + tid * 16;
-        if (j0 < pd.nt_pad) {
-            const uint4 kk = *reinterpret_cast<const uint4*>(keys + j0);
-            const unsigned kw[4] = {kk.x, kk.y, kk.z, kk.w};
+    const int* list = w.col_list + pd.cb_base + start;
+    const int l8 = tid & 7;
+    const int n_round = (n + 15) & ~15;
+    for (int idx = tid >> 3; idx < n_round; idx += 16) {
+        const bool active = idx < n;
+        const int j = active ? list[idx] : 0;
+        RowRegs<N16> tr;
+        const uint4* trow = reinterpret_cast<const uint4*>(st.desc_u8) + static_cast<long long>(pd.t_row0 + j) * N16;
 #pragma unroll
-            for (int u = 0; u < 16; ++u) {
-                const unsigned key = (kw[u >> 2] >> ((u & 3) * 8)) & 0xffu;
-                if (static_cast<int>(key) == c) s_list[atomicAdd(&s_n, 1)] = j0 + u;
+        for (int k = 0; k < N16; ++k) tr.v[k] = __ldg(trow + k);
+        const int nt2 = st.norm_i[pd.t_row0 + j];
+        Top2 t2{INT_MAX, INT_MAX, INT_MAX};
+        if (active) {
+#pragma unroll 2
+            for (int t = l8; t < n_cls; t += 8) {
+                const int d2 = nt2 + s_norm[t] - 2 * static_cast<int>(dot_regs_smem<N16>(tr, s_q + t * kStride));
+                if (s_valid[t]) t2.push(d2, c + t * kTileQ);
             }
         }
-        __syncthreads();
-        const int n = s_n;
-        const bool last = base + 2048 >= pd.nt_pad;
-        if (n > kListCap - 2048 || last) {
-            const int n_round = (n + 63) & ~63;
-            for (int idx = tid >> 1; idx < n_round; idx += 64) {
-                const bool active = idx < n;
-                const int j = active ? s_list[idx] : 0;
-                const long long pos = pd.cb_base + j;
-                RowRegs<N16> tr;
-                const uint4* trow = reinterpret_cast<const uint4*>(st.desc_u8) + static_cast<long long>(pd.t_row0 + j) * N16;
-#pragma unroll
-                for (int k = 0; k < N16; ++k) tr.v[k] = __ldg(trow + k);
-                const int nt2 = st.norm_i[pd.t_row0 + j];
-                float f1 = FLT_MAX, f2 = FLT_MAX;
-                int i1 = INT_MAX, dmin = INT_MAX;
-                if (active) {
-                    for (int t = par; t < n_cls; t += 2) {
-                        if (!s_valid[t]) continue;
-                        const int d2 = nt2 + s_norm[t] - 2 * static_cast<int>(dot_regs_smem<N16>(tr, s_q + t * kStride));
-                        dmin = min(dmin, d2);
-                        const float f = dist_from_d2(d2);
-                        if (f < f2) { if (f < f1) { f2 = f1; f1 = f; i1 = c + t * kTileQ; } else f2 = f; }
-                    }
-                }
-                {
-                    const float o1 = __shfl_xor_sync(0xffffffffu, f1, 1), o2 = __shfl_xor_sync(0xffffffffu, f2, 1);
-                    const int oi = __shfl_xor_sync(0xffffffffu, i1, 1);
-                    const int od = __shfl_xor_sync(0xffffffffu, dmin, 1);
-                    dmin = min(dmin, od);
-                    const bool take = (o1 < f1) || (o1 == f1 && oi < i1);
-                    const float lose = take ? f1 : o1;
-                    f2 = fminf(fminf(f2, o2), lose);
-                    if (take) { f1 = o1; i1 = oi; }
-                }
-                if (active && par == 0) {
-                    const float k1 = w.col_d1[pos], k2 = w.col_d2[pos];
-                    const float f2o = dist_from_half(k2);
-                    const bool ambiguous = (i1 == INT_MAX) || (f2o <= f1) || (static_cast<float>(dmin) != k1 + k1);
-                    if (ambiguous) flag(w, p, 1, j);
-                    w.col_best[pos] = (i1 == INT_MAX) ? -1 : i1;
-                    w.col_d1[pos] = f1;
-                    w.col_d2[pos] = fminf(f2, f2o);
-                }
-            }
-            __syncthreads();
-            if (tid == 0) s_n = 0;
-            __syncthreads();
+        t2.merge_xor(1);
+        t2.merge_xor(2);
+        t2.merge_xor(4);
+        if (active && l8 == 0) {
+            const long long pos = pd.cb_base + j;
+            const float k1 = w.col_d1[pos], k2 = w.col_d2[pos];
+            const float f1 = dist_or_max(t2.b1), f2 = dist_or_max(t2.b2), f2o = dist_from_half(k2);
+            const bool ambiguous = (t2.i1 == INT_MAX) || (f2o <= f1) || (static_cast<float>(t2.b1) != k1 + k1) || (t2.b1 >= kSqrtMonotoneBelow);
+            if (ambiguous) flag(w, p, 1, j);
+            w.col_best[pos] = (t2.i1 == INT_MAX) ? -1 : t2.i1;
+            w.col_d1[pos] = f1;
+            w.col_d2[pos] = fminf(f2, f2o);
         }
     }
 }
@@ -354,19 +398,28 @@ template <int N16> static cudaError_t launch_bucket_cols(const StoreView& st, co
     return cudaGetLastError();
 }
 
-// which: 0 = query rows, 1 = train columns.  n_items = 256-column screening items of the chunk.
-cudaError_t launch_resolve_int(const StoreView& st, const MatchWork& w, int which, long long total, int n_items, int max_class_rows,
-                               cudaStream_t s)
+// which: 0 = query rows, 1 = train columns.
+cudaError_t launch_resolve_int(const StoreView& st, const MatchWork& w, int which, long long total, int max_class_rows, cudaStream_t s)
 {
-    if (total <= 0 || n_items <= 0) return cudaSuccess;
+    if (total <= 0 || w.n_pairs <= 0 || w.max_hb <= 0) return cudaSuccess;
     if (st.kpad != 64 && st.kpad != 128) return cudaErrorInvalidValue;
+    cudaError_t e;
     if (which == 0) {
+        const int stride = w.max_hb + 1;
+        if ((e = cudaMemsetAsync(w.row_cnt, 0, sizeof(int) * static_cast<size_t>(w.n_pairs) * stride, s)) != cudaSuccess) return e;
         merge_rows_kernel<<<static_cast<unsigned>((total + 127) / 128), 128, 0, s>>>(st, w, total);
-        if (st.kpad == 64) bucket_rows_kernel<4><<<2 * n_items, 128, 0, s>>>(st, w, 2 * n_items);
-        else bucket_rows_kernel<8><<<2 * n_items, 128, 0, s>>>(st, w, 2 * n_items);
+        prefix_counts_kernel<<<w.n_pairs, 128, 0, s>>>(w.row_cnt, stride);
+        scatter_rows_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, s>>>(w, total);
+        const unsigned grid = static_cast<unsigned>(w.n_pairs) * w.max_hb;
+        if (st.kpad == 64) bucket_rows_kernel<4><<<grid, 128, 0, s>>>(st, w);
+        else bucket_rows_kernel<8><<<grid, 128, 0, s>>>(st, w);
     } else {
+        const int stride = kTileQ + 1;
+        if ((e = cudaMemsetAsync(w.col_cnt, 0, sizeof(int) * static_cast<size_t>(w.n_pairs) * stride, s)) != cudaSuccess) return e;
         merge_cols_kernel<<<static_cast<unsigned>((total + kColsPerCta - 1) / kColsPerCta), 256, 0, s>>>(st, w, total);
-        cudaError_t e = st.kpad == 64 ? launch_bucket_cols<4>(st, w, max_class_rows, s) : launch_bucket_cols<8>(st, w, max_class_rows, s);
+        prefix_counts_kernel<<<w.n_pairs, 128, 0, s>>>(w.col_cnt, stride);
+        scatter_cols_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, s>>>(w, total);
+        e = st.kpad == 64 ? launch_bucket_cols<4>(st, w, max_class_rows, s) : launch_bucket_cols<8>(st, w, max_class_rows, s);
         if (e != cudaSuccess) return e;
     }
     return cudaGetLastError();

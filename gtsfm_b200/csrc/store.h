@@ -31,9 +31,14 @@ struct MatchWork {
     // exact per-row / per-column nearest neighbours, indexed by PairDesc::out_base (+row) and cb_base (+column)
     int* row_best;  float* row_d1;  float* row_d2;
     int* col_best;  float* col_d1;  float* col_d2;
-    // bucket keys of the resolve step: rows -> (winning half block << 3 | winning group), columns -> winning lane class
-    unsigned short* row_key;
-    uint8_t* col_key;
+    // resolve step (counting sort by bucket): key = bucket | slot in the bucket (rows: half block << 3 | group | slot << 16,
+    // columns: lane class | slot << 8); per-pair bucket counters / offsets (rows: max_hb + 1 per pair, columns: 129 per
+    // pair); member lists indexed like the per-row / per-column arrays
+    unsigned int* row_key;
+    unsigned int* col_key;
+    int* row_cnt;  int* col_cnt;
+    int* row_list; int* col_list;
+    int max_hb;                         // largest number of 128-column half blocks of a pair of the chunk
     // rows / columns whose screening result was ambiguous: (pair << 33 | dir << 32 | index), counted by n_flag
     unsigned long long* col_cells;      // float path: 16 B per train column (0xff-filled): merge cell of exact_tile_kernel
     unsigned long long* flag_scratch;   // 16 B per flagged entry (0xff-filled): merge cell of the segmented exact scan

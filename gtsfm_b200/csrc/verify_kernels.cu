@@ -158,7 +158,7 @@ __global__ void __launch_bounds__(kSolveThreads, 2) solve_kernel(VerifyBufs b, V
 }
 
 // ---------------------------------------------------------------------------------------------------------------- K5
-constexpr int kScoreHyp = 32;      // hypotheses per CTA
+constexpr int kScoreHyp = 128;     // hypotheses per CTA (the staged correspondences are shared by all their candidates)
 constexpr int kScoreTile = 4096;   // correspondences staged per shared-memory tile (64 KB)
 constexpr int kScoreMaxCand = kScoreHyp * vm::kMaxCand;
 constexpr int kScoreCheck = 256;   // packed pairs (512 correspondences) between two early-exit checks
@@ -180,23 +180,34 @@ __global__ void __launch_bounds__(256) score_kernel(VerifyBufs b, VerifyDims d, 
     __shared__ unsigned short s_cand[kScoreMaxCand];   // (local hypothesis << 4) | candidate
     __shared__ unsigned char s_dead[kScoreMaxCand];    // candidate left the race (partial cost above the pair's best)
     __shared__ unsigned long long s_exec;
-    __shared__ int s_n;
+    __shared__ int s_n, s_next;
+    __shared__ int s_wcnt[kScoreHyp / 32];
     const int p = blockIdx.y;
     if (p >= n_pairs) return;
     const VPair& vp = b.pairs[p];
     if (vp.status != 0) return;
     const int h0 = blockIdx.x * kScoreHyp;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    if (threadIdx.x == 0) {
-        int n = 0;
-        for (int hh = 0; hh < kScoreHyp && h0 + hh < d.H; ++hh) {
-            unsigned m = b.vmask[static_cast<long long>(p) * d.H + h0 + hh];
-            while (m) { const int c = __ffs(m) - 1; m &= m - 1; s_cand[n++] = static_cast<unsigned short>((hh << 4) | c); }
-        }
-        s_n = n;
+    // candidate list of the CTA's hypotheses, in ascending (hypothesis, root) order: one hypothesis per thread
+    unsigned vm_bits = 0;
+    int incl = 0;
+    if (threadIdx.x < kScoreHyp) {
+        vm_bits = (h0 + threadIdx.x < d.H) ? b.vmask[static_cast<long long>(p) * d.H + h0 + threadIdx.x] : 0u;
+        incl = __popc(vm_bits);
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) { const int v = __shfl_up_sync(0xffffffffu, incl, off); if (lane >= off) incl += v; }
+        if (lane == 31) s_wcnt[warp] = incl;
     }
     for (int k = threadIdx.x; k < kScoreMaxCand; k += blockDim.x) { s_cost[k] = 0.f; s_dead[k] = 0; }
-    if (threadIdx.x == 0) s_exec = 0ull;
+    if (threadIdx.x == 0) { s_exec = 0ull; s_next = 0; }
+    __syncthreads();
+    if (threadIdx.x < kScoreHyp) {
+        int pos = incl - __popc(vm_bits);
+        for (int w2 = 0; w2 < warp; ++w2) pos += s_wcnt[w2];
+        unsigned m = vm_bits;
+        while (m) { const int c = __ffs(m) - 1; m &= m - 1; s_cand[pos++] = static_cast<unsigned short>((threadIdx.x << 4) | c); }
+        if (threadIdx.x == kScoreHyp - 1) s_n = pos;
+    }
     __syncthreads();
     const int n = s_n;
     if (n == 0) return;
@@ -217,8 +228,14 @@ __global__ void __launch_bounds__(256) score_kernel(VerifyBufs b, VerifyDims d, 
             sA[q] = make_float4(ca.x, cb.x, ca.y, cb.y);
             sB[q] = make_float4(ca.z, cb.z, ca.w, cb.w);
         }
+        if (threadIdx.x == 0) s_next = 0;
         __syncthreads();
-        for (int ci = warp; ci < n; ci += 8) {
+        for (;;) {
+            // candidates are handed out dynamically: early exits make their cost very uneven
+            int ci = 0;
+            if (lane == 0) ci = atomicAdd(&s_next, 1);
+            ci = __shfl_sync(0xffffffffu, ci, 0);
+            if (ci >= n) break;
             if (s_dead[ci]) continue;
             const int code = s_cand[ci];
             const float* E = Ebase + ((code >> 4) * vm::kMaxCand + (code & 15)) * 9;
@@ -234,6 +251,7 @@ __global__ void __launch_bounds__(256) score_kernel(VerifyBufs b, VerifyDims d, 
             // COMPLETE cost of the pair (by more than the fp32 accumulation noise) cannot be the minimum.
             for (int c0 = 0; c0 < nq; c0 += kScoreCheck) {
                 const int c1 = min(nq, c0 + kScoreCheck);
+                const float bestv = *best;                 // issued here, consumed after the segment: latency hidden
 #pragma unroll 2
                 for (int k = c0 + lane; k < c1; k += 32) {
                     const ulonglong2 A = *reinterpret_cast<const ulonglong2*>(sA + k);   // x1 pair, y1 pair
@@ -254,7 +272,7 @@ __global__ void __launch_bounds__(256) score_kernel(VerifyBufs b, VerifyDims d, 
                 float part = acc0 + acc1;
 #pragma unroll
                 for (int off = 16; off > 0; off >>= 1) part += __shfl_xor_sync(0xffffffffu, part, off);
-                if (before + part > *best * 1.001f) { dead = true; break; }
+                if (before + part > bestv * 1.001f) { dead = true; break; }
             }
             float acc = acc0 + acc1;
             if (!dead && (tn & 1) && lane == 0) {      // odd tail: first half of the last (duplicated) pair

@@ -1,13 +1,15 @@
 """Aggregate the warp-stall samples / executed instructions of an .ncu-rep by CUDA source line (needs -lineinfo and
---import-source on):  python tools/ncu_lines.py report.ncu-rep [top_n]"""
+--import-source on):  python tools/ncu_lines.py report.ncu-rep [top_n] [kernel-name regex] [launch index among matches]"""
 import csv
 import subprocess
 import sys
 
 
-def main(path, top=40):
-    out = subprocess.run(["ncu", "-i", path, "--page", "source", "--csv", "--print-source", "cuda,sass"],
-                         capture_output=True, text=True).stdout
+def main(path, top=40, kernel=None, skip=0):
+    cmd = ["ncu", "-i", path, "--page", "source", "--csv", "--print-source", "cuda,sass"]
+    if kernel:
+        cmd += ["-k", "regex:" + kernel, "--launch-skip", str(skip), "--launch-count", "1"]
+    out = subprocess.run(cmd, capture_output=True, text=True).stdout
     cur, agg = None, {}
     for r in csv.reader(out.splitlines()):
         if len(r) == 2 and r[0] == "File Path":
@@ -30,4 +32,5 @@ def main(path, top=40):
 
 
 if __name__ == "__main__":
-    main(sys.argv[1], int(sys.argv[2]) if len(sys.argv) > 2 else 40)
+    main(sys.argv[1], int(sys.argv[2]) if len(sys.argv) > 2 else 40, sys.argv[3] if len(sys.argv) > 3 else None,
+         int(sys.argv[4]) if len(sys.argv) > 4 else 0)
