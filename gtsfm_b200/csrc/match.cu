@@ -96,7 +96,7 @@ int gtsfm_match_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, double ra
     // ---- buffers
     long long m_rp = 0, m_cr = 0, m_rows = 0, m_cols = 0, m_rcnt = 0, m_ccnt = 0;
     for (const Chunk& k : chunks) {
-        m_rcnt = std::max(m_rcnt, static_cast<long long>(k.p1 - k.p0) * (k.max_hb + 1));
+        m_rcnt = std::max(m_rcnt, static_cast<long long>(k.p1 - k.p0) * (8 * k.max_hb + 1));
         m_ccnt = std::max(m_ccnt, static_cast<long long>(k.p1 - k.p0) * (kTileQ + 1));
     }
     for (const Chunk& k : chunks) { m_rp = std::max(m_rp, k.rp); m_cr = std::max(m_cr, k.cr); m_rows = std::max(m_rows, k.rows); m_cols = std::max(m_cols, k.cols); }

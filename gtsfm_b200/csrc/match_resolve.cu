@@ -91,7 +91,7 @@ __global__ void __launch_bounds__(128) merge_rows_kernel(StoreView st, MatchWork
     const int g1 = w.rp_g[e0 + static_cast<long long>(hb1) * pd.nq_pad];
     w.row_d1[pos] = k1;
     w.row_d2[pos] = k2;
-    const unsigned slot = static_cast<unsigned>(atomicAdd(w.row_cnt + static_cast<long long>(p) * (w.max_hb + 1) + hb1, 1));
+    const unsigned slot = static_cast<unsigned>(atomicAdd(w.row_cnt + static_cast<long long>(p) * (8 * w.max_hb + 1) + ((hb1 << 3) | g1), 1));
     w.row_key[pos] = static_cast<unsigned>((hb1 << 3) | g1) | (slot << 16);
 }
 
@@ -181,8 +181,8 @@ __global__ void __launch_bounds__(128) prefix_counts_kernel(int* cnt, int stride
     }
 }
 
-// scatter: member lists.  Rows: entry = row << 3 | group at list[out_base + offset[half block] + slot];
-// columns: entry = column at list[cb_base + offset[class] + slot].
+// scatter: member lists.  Rows: list[out_base + offset[half block << 3 | group] + slot] = row;
+// columns: list[cb_base + offset[class] + slot] = column.
 __global__ void __launch_bounds__(256) scatter_rows_kernel(MatchWork w, long long total_rows)
 {
     const long long pos = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -192,9 +192,8 @@ __global__ void __launch_bounds__(256) scatter_rows_kernel(MatchWork w, long lon
     const unsigned key = w.row_key[pos];
     if (key == 0xffffffffu) return;
     const long long ob = w.pairs[p].out_base;
-    const int hb = static_cast<int>(key & 0xffffu) >> 3;
-    const int off = w.row_cnt[static_cast<long long>(p) * (w.max_hb + 1) + hb];
-    w.row_list[ob + off + (key >> 16)] = (static_cast<int>(pos - ob) << 3) | static_cast<int>(key & 7u);
+    const int off = w.row_cnt[static_cast<long long>(p) * (8 * w.max_hb + 1) + static_cast<int>(key & 0xffffu)];
+    w.row_list[ob + off + (key >> 16)] = static_cast<int>(pos - ob);
 }
 __global__ void __launch_bounds__(256) scatter_cols_kernel(MatchWork w, long long total_cols)
 {
@@ -210,20 +209,22 @@ __global__ void __launch_bounds__(256) scatter_cols_kernel(MatchWork w, long lon
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-template <int N16> struct RowRegs { uint4 v[N16]; };
-
-template <int N16>
-__device__ __forceinline__ unsigned dot_regs_smem(const RowRegs<N16>& a, const uint4* __restrict__ b)
+// Exact integer dot products of the bucket kernels: warp-level IMMA, D(16 x 8, s32) += A(16 x 32, u8) * B(32 x 8, u8).
+// A rows = members of the bucket (gathered from the store straight into the fragment registers), B columns = the staged
+// descriptor rows they are compared with, so a staged row read from shared memory serves 16 members at once (a thread
+// per member would read it once per member and leave the kernel bound by shared-memory bandwidth).
+// Fragment layout (g = lane >> 2, q = lane & 3): a0 / a2 = row g, a1 / a3 = row g + 8, b0 / b1 = column g; the k index
+// of a register only has to agree between A and B, so lane q simply takes bytes [64 s + 16 q, +16) of its rows: one
+// 16-byte load feeds two k-steps.  c0, c1 = (row g, columns 2q, 2q + 1), c2, c3 = (row g + 8, same columns).
+__device__ __forceinline__ void imma_u8(int (&c)[4], unsigned a0, unsigned a1, unsigned a2, unsigned a3, unsigned b0, unsigned b1)
 {
-    unsigned acc = 0;
-#pragma unroll
-    for (int k = 0; k < N16; ++k) {
-        const uint4 y = b[k];
-        acc = __dp4a(a.v[k].x, y.x, acc); acc = __dp4a(a.v[k].y, y.y, acc);
-        acc = __dp4a(a.v[k].z, y.z, acc); acc = __dp4a(a.v[k].w, y.w, acc);
-    }
-    return acc;
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.u8.s32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+                 : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
 }
+// staged row stride in 16-byte units, = 4 (mod 8): the eight lanes of a quarter warp then read eight different 16-byte
+// bank groups when they fetch their B fragments
+template <int N16> struct Staged { static constexpr int kStride = (N16 % 8 == 4) ? N16 : N16 + 4; };
 
 // Running (best, second best, index of the best) over integer squared distances.  sqrtf is strictly increasing on the
 // integers below 2^22 (neighbouring square roots are more than one float32 ulp apart), so the order of the float32
@@ -252,57 +253,82 @@ struct Top2 {
 };
 __device__ __forceinline__ float dist_or_max(int d2) { return d2 == INT_MAX ? FLT_MAX : dist_from_d2(d2); }
 
-// bucket, rows: one CTA per (pair, half block of 128 train columns); four lanes share a member row (four of the sixteen
-// group columns each).  Staged rows are padded by 16 B per row and a further 16 B per group of 16, so lanes working on
-// different groups of the half block hit different banks.
+// bucket, rows: one CTA per (pair, half block of 128 train columns).  The members of the half block are sorted by group;
+// a warp takes 16 members of one group at a time and multiplies them with the group's 16 staged train rows.
 template <int N16>
 __global__ void __launch_bounds__(128) bucket_rows_kernel(StoreView st, MatchWork w)
 {
-    constexpr int kStride = N16 + 1;
-    __shared__ uint4 s_t[kHalfT * kStride + kHalfT / kGroup];
+    constexpr int kStride = Staged<N16>::kStride;
+    __shared__ uint4 s_t[kHalfT * kStride];
     __shared__ int s_norm[kHalfT];
     __shared__ uint8_t s_valid[kHalfT];
 
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, gid = lane >> 2, q = lane & 3;
     const int p = blockIdx.x / w.max_hb, hb = blockIdx.x - p * w.max_hb;
     const PairDesc pd = w.pairs[p];
     if (pd.path != 0 || pd.nq == 0 || hb * kHalfT >= pd.nt) return;   // padding columns are never a winner
-    const int* off = w.row_cnt + static_cast<long long>(p) * (w.max_hb + 1) + hb;
-    const int start = off[0], n = off[1] - start;
-    if (n <= 0) return;
+    const int* off = w.row_cnt + static_cast<long long>(p) * (8 * w.max_hb + 1) + 8 * hb;
+    int o[kHalfT / kGroup + 1];
+#pragma unroll
+    for (int g = 0; g <= kHalfT / kGroup; ++g) o[g] = off[g];
+    if (o[kHalfT / kGroup] == o[0]) return;
     const long long trow0 = static_cast<long long>(pd.t_row0) + hb * kHalfT;
     const uint4* tsrc = reinterpret_cast<const uint4*>(st.desc_u8) + trow0 * N16;
     for (int idx = tid; idx < kHalfT * N16; idx += 128) {
         const int r = idx / N16, k = idx % N16;
-        s_t[r * kStride + (r >> 4) + k] = __ldg(tsrc + idx);
+        s_t[r * kStride + k] = __ldg(tsrc + idx);
     }
     s_norm[tid] = st.norm_i[trow0 + tid];
-    s_valid[tid] = st.valid[trow0 + tid];
+    s_valid[tid] = (hb * kHalfT + tid < pd.nt) ? st.valid[trow0 + tid] : 0;
     __syncthreads();
 
-    const int* list = w.row_list + pd.out_base + start;
-    const int l4 = tid & 3;
-    const int n_round = (n + 31) & ~31;
-    for (int idx = tid >> 2; idx < n_round; idx += 32) {
-        const bool active = idx < n;
-        const int e = active ? list[idx] : 0;
-        const int i = e >> 3, g = e & 7;
-        RowRegs<N16> q;
-        const uint4* qrow = reinterpret_cast<const uint4*>(st.desc_u8) + static_cast<long long>(pd.q_row0 + i) * N16;
+    int tiles = 0;
 #pragma unroll
-        for (int k = 0; k < N16; ++k) q.v[k] = __ldg(qrow + k);
-        const int nq2 = st.norm_i[pd.q_row0 + i];
-        Top2 t{INT_MAX, INT_MAX, INT_MAX};
+    for (int g = 0; g < kHalfT / kGroup; ++g) tiles += (o[g + 1] - o[g] + 15) >> 4;
+    for (int tile = warp; tile < tiles; tile += 4) {
+        int g = 0, local = tile, first = o[0], n_g = o[1] - o[0];
 #pragma unroll
-        for (int u = 0; u < kGroup / 4; ++u) {
-            const int r = g * kGroup + l4 + 4 * u;
-            const int j = hb * kHalfT + r;
-            const int d2 = nq2 + s_norm[r] - 2 * static_cast<int>(dot_regs_smem<N16>(q, s_t + r * kStride + g));
-            if (active && j < pd.nt && s_valid[r]) t.push(d2, j);
+        for (int gg = 0; gg < kHalfT / kGroup; ++gg) {
+            const int tg = (o[gg + 1] - o[gg] + 15) >> 4;
+            const bool here = local >= 0 && local < tg;
+            if (here) { g = gg; first = o[gg] + 16 * local; n_g = o[gg + 1] - first; }
+            local -= here ? (1 << 30) : tg;
         }
-        t.merge_xor(1);
-        t.merge_xor(2);
-        if (active && l4 == 0) {
+        const int* list = w.row_list + pd.out_base + first;
+        const bool act_lo = gid < n_g, act_hi = gid + 8 < n_g;
+        const int i_lo = act_lo ? list[gid] : list[0], i_hi = act_hi ? list[gid + 8] : i_lo;
+        const uint4* r_lo = reinterpret_cast<const uint4*>(st.desc_u8) + static_cast<long long>(pd.q_row0 + i_lo) * N16 + q;
+        const uint4* r_hi = reinterpret_cast<const uint4*>(st.desc_u8) + static_cast<long long>(pd.q_row0 + i_hi) * N16 + q;
+        uint4 L[N16 / 4], H[N16 / 4];
+#pragma unroll
+        for (int k = 0; k < N16 / 4; ++k) { L[k] = __ldg(r_lo + 4 * k); H[k] = __ldg(r_hi + 4 * k); }
+        const int n_lo = st.norm_i[pd.q_row0 + i_lo], n_hi = st.norm_i[pd.q_row0 + i_hi];
+        Top2 tl{INT_MAX, INT_MAX, INT_MAX}, th{INT_MAX, INT_MAX, INT_MAX};
+#pragma unroll
+        for (int nt = 0; nt < kGroup / 8; ++nt) {
+            int acc[4] = {0, 0, 0, 0};
+            const uint4* brow = s_t + (g * kGroup + nt * 8 + gid) * kStride + q;
+#pragma unroll
+            for (int k = 0; k < N16 / 4; ++k) {
+                const uint4 B = brow[4 * k];
+                imma_u8(acc, L[k].x, H[k].x, L[k].y, H[k].y, B.x, B.y);
+                imma_u8(acc, L[k].z, H[k].z, L[k].w, H[k].w, B.z, B.w);
+            }
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+                const int r = g * kGroup + nt * 8 + 2 * q + u;
+                if (s_valid[r]) {
+                    const int j = hb * kHalfT + r, nn = s_norm[r];
+                    tl.push(n_lo + nn - 2 * acc[u], j);
+                    th.push(n_hi + nn - 2 * acc[2 + u], j);
+                }
+            }
+        }
+        tl.merge_xor(1); tl.merge_xor(2);
+        th.merge_xor(1); th.merge_xor(2);
+        if ((q == 0 && act_lo) || (q == 1 && act_hi)) {
+            const Top2 t = (q == 0) ? tl : th;
+            const int i = (q == 0) ? i_lo : i_hi;
             const long long pos = pd.out_base + i;
             const float k1 = w.row_d1[pos], k2 = w.row_d2[pos];
             const float f1 = dist_or_max(t.b1), f2 = dist_or_max(t.b2), f2o = dist_from_half(k2);
@@ -319,59 +345,73 @@ __global__ void __launch_bounds__(128) bucket_rows_kernel(StoreView st, MatchWor
 }
 
 // bucket, columns: one CTA per (pair, lane class c).  The class rows c, c + 128, ... of the query image are staged in
-// shared memory; eight lanes share a member column (class rows t = lane, lane + 8, ...).
+// shared memory (padded to a multiple of eight rows); a warp takes 16 member columns at a time.
 template <int N16>
 __global__ void __launch_bounds__(128) bucket_cols_kernel(StoreView st, MatchWork w)
 {
-    constexpr int kStride = N16 + 1;
+    constexpr int kStride = Staged<N16>::kStride;
     extern __shared__ uint4 s_dyn[];
 
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, gid = lane >> 2, q = lane & 3;
     const int p = blockIdx.x >> 7, c = blockIdx.x & 127;
     const PairDesc pd = w.pairs[p];
     if (pd.path != 0 || pd.nq == 0 || pd.nt == 0 || c >= pd.nq) return;
     const int* off = w.col_cnt + static_cast<long long>(p) * (kTileQ + 1) + c;
     const int start = off[0], n = off[1] - start;
     if (n <= 0) return;
-    const int n_cls = pd.nq_pad / kTileQ;
+    const int n_cls = pd.nq_pad / kTileQ, n_cls8 = (n_cls + 7) & ~7;
     uint4* s_q = s_dyn;
-    int* s_norm = reinterpret_cast<int*>(s_dyn + n_cls * kStride);
-    uint8_t* s_valid = reinterpret_cast<uint8_t*>(s_norm + n_cls);
+    int* s_norm = reinterpret_cast<int*>(s_dyn + n_cls8 * kStride);
+    uint8_t* s_valid = reinterpret_cast<uint8_t*>(s_norm + n_cls8);
     const uint4* qsrc = reinterpret_cast<const uint4*>(st.desc_u8) + (static_cast<long long>(pd.q_row0) + c) * N16;
-    for (int idx = tid; idx < n_cls * N16; idx += 128) {
+    for (int idx = tid; idx < n_cls8 * N16; idx += 128) {
         const int t = idx / N16, k = idx % N16;
-        s_q[t * kStride + k] = __ldg(qsrc + static_cast<long long>(t) * kTileQ * N16 + k);
+        s_q[t * kStride + k] = (t < n_cls) ? __ldg(qsrc + static_cast<long long>(t) * kTileQ * N16 + k) : make_uint4(0u, 0u, 0u, 0u);
     }
-    for (int t = tid; t < n_cls; t += 128) {
+    for (int t = tid; t < n_cls8; t += 128) {
+        const bool real = t < n_cls && c + t * kTileQ < pd.nq;
         const long long row = static_cast<long long>(pd.q_row0) + c + t * kTileQ;
-        s_norm[t] = st.norm_i[row];
-        s_valid[t] = (c + t * kTileQ < pd.nq) ? st.valid[row] : 0;
+        s_norm[t] = real ? st.norm_i[row] : 0;
+        s_valid[t] = real ? st.valid[row] : 0;
     }
     __syncthreads();
 
     const int* list = w.col_list + pd.cb_base + start;
-    const int l8 = tid & 7;
-    const int n_round = (n + 15) & ~15;
-    for (int idx = tid >> 3; idx < n_round; idx += 16) {
-        const bool active = idx < n;
-        const int j = active ? list[idx] : 0;
-        RowRegs<N16> tr;
-        const uint4* trow = reinterpret_cast<const uint4*>(st.desc_u8) + static_cast<long long>(pd.t_row0 + j) * N16;
+    for (int first = 16 * warp; first < n; first += 64) {
+        const bool act_lo = first + gid < n, act_hi = first + gid + 8 < n;
+        const int j_lo = act_lo ? list[first + gid] : list[first], j_hi = act_hi ? list[first + gid + 8] : j_lo;
+        const uint4* r_lo = reinterpret_cast<const uint4*>(st.desc_u8) + static_cast<long long>(pd.t_row0 + j_lo) * N16 + q;
+        const uint4* r_hi = reinterpret_cast<const uint4*>(st.desc_u8) + static_cast<long long>(pd.t_row0 + j_hi) * N16 + q;
+        uint4 L[N16 / 4], H[N16 / 4];
 #pragma unroll
-        for (int k = 0; k < N16; ++k) tr.v[k] = __ldg(trow + k);
-        const int nt2 = st.norm_i[pd.t_row0 + j];
-        Top2 t2{INT_MAX, INT_MAX, INT_MAX};
-        if (active) {
+        for (int k = 0; k < N16 / 4; ++k) { L[k] = __ldg(r_lo + 4 * k); H[k] = __ldg(r_hi + 4 * k); }
+        const int n_lo = st.norm_i[pd.t_row0 + j_lo], n_hi = st.norm_i[pd.t_row0 + j_hi];
+        Top2 tl{INT_MAX, INT_MAX, INT_MAX}, th{INT_MAX, INT_MAX, INT_MAX};
 #pragma unroll 2
-            for (int t = l8; t < n_cls; t += 8) {
-                const int d2 = nt2 + s_norm[t] - 2 * static_cast<int>(dot_regs_smem<N16>(tr, s_q + t * kStride));
-                if (s_valid[t]) t2.push(d2, c + t * kTileQ);
+        for (int nt = 0; nt < n_cls8 / 8; ++nt) {
+            int acc[4] = {0, 0, 0, 0};
+            const uint4* brow = s_q + (nt * 8 + gid) * kStride + q;
+#pragma unroll
+            for (int k = 0; k < N16 / 4; ++k) {
+                const uint4 B = brow[4 * k];
+                imma_u8(acc, L[k].x, H[k].x, L[k].y, H[k].y, B.x, B.y);
+                imma_u8(acc, L[k].z, H[k].z, L[k].w, H[k].w, B.z, B.w);
+            }
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+                const int t = nt * 8 + 2 * q + u;
+                if (s_valid[t]) {
+                    const int i = c + t * kTileQ, nn = s_norm[t];
+                    tl.push(n_lo + nn - 2 * acc[u], i);
+                    th.push(n_hi + nn - 2 * acc[2 + u], i);
+                }
             }
         }
-        t2.merge_xor(1);
-        t2.merge_xor(2);
-        t2.merge_xor(4);
-        if (active && l8 == 0) {
+        tl.merge_xor(1); tl.merge_xor(2);
+        th.merge_xor(1); th.merge_xor(2);
+        if ((q == 0 && act_lo) || (q == 1 && act_hi)) {
+            const Top2 t2 = (q == 0) ? tl : th;
+            const int j = (q == 0) ? j_lo : j_hi;
             const long long pos = pd.cb_base + j;
             const float k1 = w.col_d1[pos], k2 = w.col_d2[pos];
             const float f1 = dist_or_max(t2.b1), f2 = dist_or_max(t2.b2), f2o = dist_from_half(k2);
@@ -387,9 +427,9 @@ __global__ void __launch_bounds__(128) bucket_cols_kernel(StoreView st, MatchWor
 template <int N16> static cudaError_t launch_bucket_cols(const StoreView& st, const MatchWork& w, int max_class_rows, cudaStream_t s)
 {
     static int configured = 0;
-    const int smem = max_class_rows * ((N16 + 1) * 16 + 5) + 16;
+    const int smem = ((max_class_rows + 7) & ~7) * (Staged<N16>::kStride * 16 + 5) + 16;
     if (smem > configured) {
-        const int want = kMaxClassRows * ((N16 + 1) * 16 + 5) + 16;
+        const int want = kMaxClassRows * (Staged<N16>::kStride * 16 + 5) + 16;
         cudaError_t e = cudaFuncSetAttribute(bucket_cols_kernel<N16>, cudaFuncAttributeMaxDynamicSharedMemorySize, want);
         if (e != cudaSuccess) return e;
         configured = want;
@@ -405,7 +445,7 @@ cudaError_t launch_resolve_int(const StoreView& st, const MatchWork& w, int whic
     if (st.kpad != 64 && st.kpad != 128) return cudaErrorInvalidValue;
     cudaError_t e;
     if (which == 0) {
-        const int stride = w.max_hb + 1;
+        const int stride = 8 * w.max_hb + 1;
         if ((e = cudaMemsetAsync(w.row_cnt, 0, sizeof(int) * static_cast<size_t>(w.n_pairs) * stride, s)) != cudaSuccess) return e;
         merge_rows_kernel<<<static_cast<unsigned>((total + 127) / 128), 128, 0, s>>>(st, w, total);
         prefix_counts_kernel<<<w.n_pairs, 128, 0, s>>>(w.row_cnt, stride);

@@ -32,7 +32,7 @@ struct MatchWork {
     int* row_best;  float* row_d1;  float* row_d2;
     int* col_best;  float* col_d1;  float* col_d2;
     // resolve step (counting sort by bucket): key = bucket | slot in the bucket (rows: half block << 3 | group | slot << 16,
-    // columns: lane class | slot << 8); per-pair bucket counters / offsets (rows: max_hb + 1 per pair, columns: 129 per
+    // columns: lane class | slot << 8); per-pair bucket counters / offsets (rows: 8 max_hb + 1 per pair, columns: 129 per
     // pair); member lists indexed like the per-row / per-column arrays
     unsigned int* row_key;
     unsigned int* col_key;
