@@ -16,13 +16,37 @@ namespace vm {
 constexpr int kMaxCand = 10;
 
 // Per-thread scratch of kWorkDoubles doubles: element i of the calling thread sits at base[i * STRIDE].  The solve kernel
-// keeps it in shared memory ([element][thread], STRIDE = threads per CTA: conflict-free and out of the L1/L2 path that
-// thread-local arrays take); the finalize kernel does the same for its few re-solving threads.
+// keeps it in shared memory ([element][thread], STRIDE = threads per CTA: conflict-free, a per-thread dynamic index costs
+// nothing, and it stays out of the L1/L2 path that thread-local arrays take); the finalize kernel does the same for its
+// few re-solving threads.  Everything the solver indexes dynamically lives here, never in a thread-local array.
+//
+// Use of the 200 slots over the life of a hypothesis:
+//   null space     0..80    the 5 x 9 system and the four null vectors
+//   constraints    0..199   the 10 x 20 coefficient matrix C[r][c] at r * 20 + c, eliminated in place
+//   hand-off       kOffN (36)  null-space basis      kOffBx/By/Bc (39)  B(z)        kOffLo/kOffHi (10 + 10) root brackets
+//                  kOffS (20)  the five sample correspondences (written last)       kOffP (11) normalised polynomial
+//   isolation      kOffSturm (66) Sturm chain, its first polynomial IS the hand-off polynomial; kOffS.. doubles as the
+//                  remainder buffer while the chain is built and as the interval stack afterwards, kOffTag as its tags
+//   per-root phase kOffXyz.. (x, y, z) of the roots that passed the first validity test (solve kernel only)
 constexpr int kWorkDoubles = 200;
+constexpr int kOffN = 0, kOffBx = 36, kOffBy = 48, kOffBc = 60, kOffTag = 75, kOffLo = 86, kOffHi = 96, kOffS = 106;
+constexpr int kOffSturm = 134, kOffP = kOffSturm, kOffXyz = 145;
 template <int STRIDE> struct Work {
     double* base;
     __device__ __forceinline__ double& operator()(int i) const { return base[i * STRIDE]; }
 };
+
+// 1 / a to within an ulp or two: hardware seed (about 20 bits) and two Newton steps.  Used where the quotient only scales
+// a row or steps an iteration, so the last bit does not matter; far shorter than the IEEE division sequence.
+__device__ __forceinline__ double rcp_nr(double a)
+{
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(a));
+    double e = fma(-a, r, 1.0);
+    r = fma(r, e, r);
+    e = fma(-a, r, 1.0);
+    return fma(r, e, r);
+}
 
 // Monomial index tables.  They are constexpr functions so that, after full unrolling, every accumulator index is a
 // compile-time constant and the accumulators live in registers (a table in constant memory makes every "+=" a
@@ -71,16 +95,14 @@ template <bool NEG> __device__ __forceinline__ void p21_acc(const double* a, con
 template <class W>
 __device__ inline bool nullspace_5x9(const double* x1, const double* y1, const double* x2, const double* y2, double N[4][9], const W& wk)
 {
-    // A[r][c] = wk(r * 9 + c); the null vectors are assembled in wk(45 + j * 9 + c)
-    int perm[9];
+    // A[r][c] = wk(r * 9 + c); the null vectors are assembled in wk(45 + j * 9 + c); column permutation in nibbles
+    unsigned long long perm = 0x876543210ull;
 #pragma unroll
     for (int r = 0; r < 5; ++r) {
         wk(r * 9 + 0) = x2[r] * x1[r]; wk(r * 9 + 1) = x2[r] * y1[r]; wk(r * 9 + 2) = x2[r];
         wk(r * 9 + 3) = y2[r] * x1[r]; wk(r * 9 + 4) = y2[r] * y1[r]; wk(r * 9 + 5) = y2[r];
         wk(r * 9 + 6) = x1[r];         wk(r * 9 + 7) = y1[r];         wk(r * 9 + 8) = 1.0;
     }
-#pragma unroll
-    for (int c = 0; c < 9; ++c) perm[c] = c;
 #pragma unroll 1
     for (int k = 0; k < 5; ++k) {
         int pr = k, pc = k;
@@ -91,9 +113,10 @@ __device__ inline bool nullspace_5x9(const double* x1, const double* y1, const d
         if (pr != k) for (int c = 0; c < 9; ++c) { const double t = wk(k * 9 + c); wk(k * 9 + c) = wk(pr * 9 + c); wk(pr * 9 + c) = t; }
         if (pc != k) {
             for (int r = 0; r < 5; ++r) { const double t = wk(r * 9 + k); wk(r * 9 + k) = wk(r * 9 + pc); wk(r * 9 + pc) = t; }
-            const int t = perm[k]; perm[k] = perm[pc]; perm[pc] = t;
+            const unsigned long long x = ((perm >> (4 * k)) ^ (perm >> (4 * pc))) & 15ull;
+            perm ^= (x << (4 * k)) | (x << (4 * pc));
         }
-        const double inv = 1.0 / wk(k * 9 + k);
+        const double inv = rcp_nr(wk(k * 9 + k));
         double prow[9];
 #pragma unroll
         for (int c = 0; c < 9; ++c) { prow[c] = wk(k * 9 + c) * inv; wk(k * 9 + c) = prow[c]; }
@@ -117,7 +140,7 @@ __device__ inline bool nullspace_5x9(const double* x1, const double* y1, const d
         for (int c = 0; c < 9; ++c) nn += v[c] * v[c];
         nn = 1.0 / sqrt(nn);
 #pragma unroll
-        for (int c = 0; c < 9; ++c) wk(45 + j * 9 + perm[c]) = v[c] * nn;
+        for (int c = 0; c < 9; ++c) wk(45 + j * 9 + static_cast<int>((perm >> (4 * c)) & 15ull)) = v[c] * nn;
     }
 #pragma unroll
     for (int j = 0; j < 4; ++j)
@@ -145,14 +168,14 @@ constexpr int kSturmLen = 66;
 __host__ __device__ constexpr int soff(int s) { return s * 11 - s * (s - 1) / 2; }
 
 // number of sign changes of the chain at t; *sg0 = sign of the polynomial itself
-template <class W> __device__ __forceinline__ int sturm_changes(const W& S, double t, int* sg0)
+template <class W> __device__ __forceinline__ int sturm_changes(const W& wk, double t, int* sg0)
 {
     int cnt = 0, last = 0;
 #pragma unroll
     for (int s = 0; s < 11; ++s) {
-        double v = S(soff(s) + 10 - s);
+        double v = wk(kOffSturm + soff(s) + 10 - s);
 #pragma unroll
-        for (int i = 9 - s; i >= 0; --i) v = v * t + S(soff(s) + i);
+        for (int i = 9 - s; i >= 0; --i) v = v * t + wk(kOffSturm + soff(s) + i);
         const int sg = (v > 0) - (v < 0);
         if (s == 0) *sg0 = sg;
         cnt += (sg != 0 && last != 0 && sg != last) ? 1 : 0;
@@ -161,96 +184,91 @@ template <class W> __device__ __forceinline__ int sturm_changes(const W& S, doub
     return cnt;
 }
 
-// Normalise pin (degree <= 10) into p, build its Sturm chain and isolate every real root: on return lo[r] < hi[r]
-// (ascending, disjoint) brackets exactly one sign change of p when bit r of *mid is clear, and the root is taken as the
-// midpoint of [lo, hi] when the bit is set (multiple / numerically unresolved root, or a root hit exactly).
-// Returns the number of roots; *deg_out = degree after dropping negligible leading coefficients.
+// Normalise pin (degree <= 10) into the hand-off polynomial, build its Sturm chain and isolate every real root: on return
+// the brackets lo[r] < hi[r] (ascending, disjoint; hand-off slots kOffLo + r, kOffHi + r) hold exactly one sign change of
+// p when bit r of *mid is clear, and the root is taken as the midpoint of [lo, hi] when the bit is set (multiple /
+// numerically unresolved root, or a root hit exactly).  Returns the number of roots.
 template <class W>
-__device__ inline int isolate_roots(const double* pin, double* p, int* deg_out, double* lo_out, double* hi_out, unsigned* mid, const W& S)
+__device__ inline int isolate_roots(const double* pin, unsigned* mid, const W& wk)
 {
-    int deg = 10;
     *mid = 0;
-    *deg_out = 0;
     double mx = 0;
-    for (int i = 0; i <= deg; ++i) if (fabs(pin[i]) > mx) mx = fabs(pin[i]);
+#pragma unroll
+    for (int i = 0; i <= 10; ++i) mx = fmax(mx, fabs(pin[i]));
     if (!(mx > 0) || !isfinite(mx)) return 0;
     const double imx = 1.0 / mx;
-    for (int i = 0; i <= 10; ++i) p[i] = pin[i] * imx;
-    while (deg > 0 && fabs(p[deg]) < 1e-13) --deg;
-    for (int i = deg + 1; i <= 10; ++i) p[i] = 0;
-    *deg_out = deg;
+    int deg = 0;                                  // degree after dropping negligible leading coefficients
+#pragma unroll
+    for (int i = 1; i <= 10; ++i) if (fabs(pin[i] * imx) >= 1e-13) deg = i;
     if (deg == 0) return 0;
-
-    for (int i = 0; i < kSturmLen; ++i) S(i) = 0;
-    int sd[12];
-    for (int i = 0; i <= deg; ++i) S(i) = p[i];
-    sd[0] = deg;
-    for (int i = 1; i <= deg; ++i) S(soff(1) + i - 1) = i * p[i];
-    sd[1] = deg - 1;
+    const auto S = [&wk](int i) -> double& { return wk(kOffSturm + i); };
+    const auto R = [&wk](int i) -> double& { return wk(kOffS + i); };       // remainder buffer (11)
+#pragma unroll
+    for (int i = 0; i <= 10; ++i) S(i) = (i <= deg) ? pin[i] * imx : 0.0;
+#pragma unroll
+    for (int i = 11; i < kSturmLen; ++i) S(i) = 0.0;
+#pragma unroll
+    for (int i = 1; i <= 10; ++i) if (i <= deg) S(soff(1) + i - 1) = i * (pin[i] * imx);
+    unsigned long long sd = static_cast<unsigned long long>(deg) | (static_cast<unsigned long long>(deg - 1) << 4);   // chain degrees, one nibble each
     int ns = 2;
-    while (sd[ns - 1] > 0 && ns < 11) {
-        double r[11], d[11];
-        const int dr = sd[ns - 2], dd = sd[ns - 1];
+    while (static_cast<int>((sd >> (4 * (ns - 1))) & 15ull) > 0 && ns < 11) {
+        const int dr = static_cast<int>((sd >> (4 * (ns - 2))) & 15ull), dd = static_cast<int>((sd >> (4 * (ns - 1))) & 15ull);
         const int o2 = soff(ns - 2), o1 = soff(ns - 1);
-        for (int i = 0; i <= dr; ++i) r[i] = S(o2 + i);
-        for (int i = 0; i <= dd; ++i) d[i] = S(o1 + i);
-        const double idl = 1.0 / d[dd];
+        for (int i = 0; i <= dr; ++i) R(i) = S(o2 + i);
+        const double idl = rcp_nr(S(o1 + dd));
         for (int k = dr; k >= dd; --k) {
-            const double f = r[k] * idl;
-            for (int j = 0; j <= dd; ++j) r[k - dd + j] -= f * d[j];
-            r[k] = 0;
+            const double f = R(k) * idl;
+            for (int j = 0; j < dd; ++j) R(k - dd + j) = fma(-f, S(o1 + j), R(k - dd + j));     // R(k) itself is never read again
         }
         int nd = dd - 1;
         double rm = 0;
-        for (int i = 0; i <= nd; ++i) if (fabs(r[i]) > rm) rm = fabs(r[i]);
+        for (int i = 0; i <= nd; ++i) rm = fmax(rm, fabs(R(i)));
         if (!(rm > 1e-300)) break;
-        while (nd > 0 && fabs(r[nd]) < 1e-14 * rm) --nd;
-        const double irm = -1.0 / rm;
+        while (nd > 0 && fabs(R(nd)) < 1e-14 * rm) --nd;
+        const double irm = -rcp_nr(rm);
         const int o0 = soff(ns);
-        for (int i = 0; i <= nd; ++i) S(o0 + i) = r[i] * irm;
-        sd[ns] = nd;
+        for (int i = 0; i <= nd; ++i) S(o0 + i) = R(i) * irm;
+        sd |= static_cast<unsigned long long>(nd) << (4 * ns);
         ++ns;
     }
     // Fujiwara bound 2 max_k |a_{n-k} / a_n|^(1/k), evaluated in float and inflated
     float fb = 0.f;
-    const float ilead = 1.0f / static_cast<float>(fabs(p[deg]));
+    const float ilead = 1.0f / static_cast<float>(fabs(S(deg)));
     for (int k = 1; k <= deg; ++k) {
-        const float a = static_cast<float>(fabs(p[deg - k])) * ilead;
+        const float a = static_cast<float>(fabs(S(deg - k))) * ilead;
         const float v = a > 0.f ? exp2f(__log2f(a) / static_cast<float>(k)) : 0.f;
         fb = fmaxf(fb, v);
     }
     const double B = 2.004 * static_cast<double>(fb) + 1e-9;
 
-    // interval stack: entries are disjoint and each holds >= 1 root, so at most 10 are alive
-    double slo[12], shi[12];
-    int sa[12], sb[12];            // sign changes at lo / hi, | (sign of p + 1) << 8
+    // interval stack: entries are disjoint and each holds >= 1 root, so at most 10 are alive.  lo at kOffS + i, hi at
+    // kOffS + 10 + i, tag at kOffTag + i = (sign changes | (sign of p + 1) << 8) at lo (high word) and at hi (low word)
     int sp = 1, nr = 0, sg;
-    slo[0] = -B; shi[0] = B;
-    sa[0] = sturm_changes(S, -B, &sg); sa[0] |= (sg + 1) << 8;
-    sb[0] = sturm_changes(S, B, &sg);  sb[0] |= (sg + 1) << 8;
+    {
+        int A = sturm_changes(wk, -B, &sg); A |= (sg + 1) << 8;
+        int Bq = sturm_changes(wk, B, &sg); Bq |= (sg + 1) << 8;
+        wk(kOffS) = -B; wk(kOffS + 10) = B; wk(kOffTag) = __hiloint2double(A, Bq);
+    }
     while (sp > 0 && nr < 10) {
         --sp;
-        const double lo = slo[sp], hi = shi[sp];
-        const int A = sa[sp], Bq = sb[sp];
+        const double lo = wk(kOffS + sp), hi = wk(kOffS + 10 + sp), tag = wk(kOffTag + sp);
+        const int A = __double2hiint(tag), Bq = __double2loint(tag);
         const int a = A & 0xff, b = Bq & 0xff, sgl = (A >> 8) - 1, sgh = (Bq >> 8) - 1;
         const int cnt = a - b;
         if (cnt <= 0) continue;
         const bool tiny = !((hi - lo) > 1e-13 * (1.0 + fabs(lo) + fabs(hi)));
-        if (cnt == 1 && sgh == 0) { lo_out[nr] = hi; hi_out[nr] = hi; *mid |= 1u << nr; ++nr; continue; }
-        if (cnt == 1 && sgl * sgh < 0) { lo_out[nr] = lo; hi_out[nr] = hi; ++nr; continue; }
-        if (tiny) { lo_out[nr] = lo; hi_out[nr] = hi; *mid |= 1u << nr; ++nr; continue; }
+        if (cnt == 1 && sgh == 0) { wk(kOffLo + nr) = hi; wk(kOffHi + nr) = hi; *mid |= 1u << nr; ++nr; continue; }
+        if (cnt == 1 && sgl * sgh < 0) { wk(kOffLo + nr) = lo; wk(kOffHi + nr) = hi; ++nr; continue; }
+        if (tiny) { wk(kOffLo + nr) = lo; wk(kOffHi + nr) = hi; *mid |= 1u << nr; ++nr; continue; }
         const double m = 0.5 * (lo + hi);
         int sgm;
-        const int cm = sturm_changes(S, m, &sgm);
+        const int cm = sturm_changes(wk, m, &sgm);
         const int M = cm | ((sgm + 1) << 8);
-        if (cm - b > 0) { slo[sp] = m; shi[sp] = hi; sa[sp] = M; sb[sp] = Bq; ++sp; }
-        if (a - cm > 0) { slo[sp] = lo; shi[sp] = m; sa[sp] = A; sb[sp] = M; ++sp; }
+        if (cm - b > 0 && sp < 10) { wk(kOffS + sp) = m; wk(kOffS + 10 + sp) = hi; wk(kOffTag + sp) = __hiloint2double(M, Bq); ++sp; }
+        if (a - cm > 0 && sp < 10) { wk(kOffS + sp) = lo; wk(kOffS + 10 + sp) = m; wk(kOffTag + sp) = __hiloint2double(A, M); ++sp; }
     }
     return nr;
 }
-
-// Offsets of the HypState fields inside the hand-off block of kHypDoubles doubles.
-constexpr int kOffN = 0, kOffBx = 36, kOffBy = 48, kOffBc = 60, kOffP = 75, kOffLo = 86, kOffHi = 96, kOffS = 106;
 
 // Root of p (degree <= 10, zero-filled above its degree) inside the isolating bracket [lo, hi] (opposite signs at the
 // ends): safeguarded Newton.  p and p' come from one unrolled Horner recurrence.  The root only has to be good to
@@ -271,7 +289,7 @@ template <class HV> __device__ inline double refine_root(const HV& h, double lo,
         for (int i = 9; i >= 0; --i) { dp = dp * x + f; f = f * x + pc[i]; }
         if (f == 0.0) break;
         if ((f > 0) == (flo > 0)) lo = x; else hi = x;
-        double xn = (dp != 0.0) ? x - f / dp : x;
+        double xn = fma(-f, rcp_nr(dp), x);                    // dp = 0 gives a non-finite step: bisection below
         if (!(xn > lo && xn < hi) || fabs(xn - x) > 0.5 * fabs(dxold)) xn = 0.5 * (lo + hi);
         const double dx = xn - x;
         const bool done = fabs(dx) <= 1e-10 * (1.0 + fabs(x));
@@ -339,33 +357,17 @@ template <class HV> __device__ inline void polish_xyz(const HV& h, double* xyz)
     }
 }
 
-// Everything the per-root phase needs about one hypothesis.  The first kHypDoubles doubles are plain data so the solve
-// kernel can hand the state from the per-hypothesis phase to the per-root phase through shared memory.
-struct HypState {
-    double N[4][9];                          // null-space basis: E = x N0 + y N1 + z N2 + N3
-    double Bx[3][4], By[3][4], Bc[3][5];     // B(z) [x y 1]^T = 0
-    double p[11];                            // normalised degree-10 polynomial det B(z)
-    double lo[10], hi[10];                   // isolating brackets of its real roots, ascending
-    double sx1[5], sy1[5], sx2[5], sy2[5];   // the five sample correspondences (model validity test)
-    int deg, nr;
-    unsigned mid;                            // bit r: root r = midpoint of its bracket
-};
-constexpr int kHypDoubles = 36 + 12 + 12 + 15 + 11 + 20 + 20;
-static_assert(offsetof(HypState, deg) == kHypDoubles * 8, "HypState layout");
-static_assert(offsetof(HypState, Bx) == 36 * 8 && offsetof(HypState, p) == 75 * 8 && offsetof(HypState, lo) == 86 * 8 && offsetof(HypState, hi) == 96 * 8 &&
-              offsetof(HypState, sx1) == 106 * 8, "HypState layout");
-
 // Phase A (once per hypothesis): five normalised correspondences -> null space, the ten cubic constraints, their
-// Gauss-Jordan reduction, det B(z) and the isolating brackets of its real roots.  Returns the number of roots.
+// Gauss-Jordan reduction, det B(z) and the isolating brackets of its real roots.  Returns the number of roots and leaves
+// the hand-off block (all but the sample correspondences at kOffS, which the caller writes) in the scratch.
 template <class W>
-__device__ inline int fivept_isolate(const double* x1, const double* y1, const double* x2, const double* y2, HypState& hs, const W& wk)
+__device__ inline int fivept_isolate(const double* x1, const double* y1, const double* x2, const double* y2, const W& wk, unsigned* mid)
 {
-    hs.nr = 0; hs.deg = 0; hs.mid = 0;
-#pragma unroll
-    for (int k = 0; k < 5; ++k) { hs.sx1[k] = x1[k]; hs.sy1[k] = y1[k]; hs.sx2[k] = x2[k]; hs.sy2[k] = y2[k]; }
-    if (!nullspace_5x9(x1, y1, x2, y2, hs.N, wk)) return 0;
+    *mid = 0;
+    double N[4][9];
+    if (!nullspace_5x9(x1, y1, x2, y2, N, wk)) return 0;
     double Ep[9][4];
-    for (int e = 0; e < 9; ++e) for (int k = 0; k < 4; ++k) Ep[e][k] = hs.N[k][e];
+    for (int e = 0; e < 9; ++e) for (int k = 0; k < 4; ++k) Ep[e][k] = N[k][e];
     // C[r][c] = wk(r * 20 + c)
     {   // det(E) = 0
         double m0[10], m1[10], m2[10], row[20];
@@ -417,79 +419,96 @@ __device__ inline int fivept_isolate(const double* x1, const double* y1, const d
                 for (int k = 0; k < 20; ++k) wk((1 + 3 * i + j) * 20 + k) = row[k];
             }
     }
-    // Gaussian elimination with row pivoting on the first ten columns.  Rows are not swapped: the pivot row of column k
-    // is read out with a statically indexed, predicated copy (a per-thread row index would scatter the warp's local
-    // memory accesses over 64 cache lines), scaled to unit pivot and kept as P[k]; only rows 4..9 are needed later.
-    double P[6][15];                 // pivot rows 4..9: columns 5..9 (index c - 5) and 10..19 (index c - 5)
-    unsigned used = 0;
+    // Gauss-Jordan on the first ten columns with partial pivoting.  The pivot row is swapped into place: in the
+    // [element][thread] scratch a per-thread row index is free, so row k is the pivot row of column k afterwards and
+    // the update loop only touches the rows below it (their range is the same for every thread of the warp).  Only
+    // pivot rows 4..9 are needed later, so the rows above the pivot are never updated and rows 0..3 not written back.
 #pragma unroll 1
     for (int k = 0; k < 10; ++k) {
-        int pr = -1;
+        int pr = k;
         double best = -1.0, pv = 0.0;
 #pragma unroll
         for (int r = 0; r < 10; ++r) {
-            const double v = wk(r * 20 + k), av = fabs(v);
-            if (!((used >> r) & 1u) && av > best) { best = av; pr = r; pv = v; }
+            if (r >= k) {
+                const double v = wk(r * 20 + k), av = fabs(v);
+                if (av > best) { best = av; pr = r; pv = v; }
+            }
         }
         if (!(best > 1e-300)) return 0;
-        used |= 1u << pr;
+        const double inv = rcp_nr(pv);
+        wk(pr * 20 + k) = wk(k * 20 + k);
         double prow[20];
 #pragma unroll
-        for (int c = 0; c < 20; ++c) prow[c] = 0;
-#pragma unroll
-        for (int r = 0; r < 10; ++r)
-            if (r == pr) {
-#pragma unroll
-                for (int c = 0; c < 20; ++c) if (c >= 10 || c > k) prow[c] = wk(r * 20 + c);
+        for (int c = 0; c < 20; ++c) {
+            prow[c] = 0;
+            if (c >= 10 || c > k) {
+                const double a = wk(pr * 20 + c);
+                wk(pr * 20 + c) = wk(k * 20 + c);
+                prow[c] = a * inv;
+                if (k >= 4) wk(k * 20 + c) = prow[c];
             }
-        const double inv = 1.0 / pv;
-#pragma unroll
-        for (int c = 0; c < 20; ++c) prow[c] *= inv;
-        if (k >= 4) {
-#pragma unroll
-            for (int c = 5; c < 20; ++c) P[k - 4][c - 5] = prow[c];
         }
 #pragma unroll
-        for (int r = 0; r < 10; ++r) {
-            if ((used >> r) & 1u) continue;
-            const double f = -wk(r * 20 + k);
+        for (int r = 1; r < 10; ++r) {
+            if (r > k) {
+                const double f = -wk(r * 20 + k);
 #pragma unroll
-            for (int c = 0; c < 20; ++c) if (c >= 10 || c > k) wk(r * 20 + c) = fma(f, prow[c], wk(r * 20 + c));
+                for (int c = 0; c < 20; ++c) if (c >= 10 || c > k) wk(r * 20 + c) = fma(f, prow[c], wk(r * 20 + c));
+            }
         }
     }
-    // back substitution of the right half, pivot rows 8..4
+    // back substitution of the right half, pivot rows 8..4, in place
 #pragma unroll
-    for (int i = 8; i >= 4; --i)
+    for (int i = 8; i >= 4; --i) {
+        double acc[10];
+#pragma unroll
+        for (int c = 0; c < 10; ++c) acc[c] = wk(i * 20 + 10 + c);
 #pragma unroll
         for (int k = i + 1; k < 10; ++k) {
-            const double f = -P[i - 4][k - 5];
+            const double f = -wk(i * 20 + k);
 #pragma unroll
-            for (int c = 10; c < 20; ++c) P[i - 4][c - 5] = fma(f, P[k - 4][c - 5], P[i - 4][c - 5]);
+            for (int c = 0; c < 10; ++c) acc[c] = fma(f, wk(k * 20 + 10 + c), acc[c]);
         }
+#pragma unroll
+        for (int c = 0; c < 10; ++c) wk(i * 20 + 10 + c) = acc[c];
+    }
+    // hand-off: null-space basis (rows 0..3 of C are dead by now)
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+#pragma unroll
+        for (int e = 0; e < 9; ++e) wk(kOffN + 9 * k + e) = N[k][e];
     // B(z) [x y 1]^T = 0; columns 10 xz^2, 11 xz, 12 x, 13 yz^2, 14 yz, 15 y, 16 z^3, 17 z^2, 18 z, 19 1
+    double Bx[3][4], By[3][4], Bc[3][5];
 #pragma unroll
     for (int q = 0; q < 3; ++q) {
-        const double* a = P[2 * q];          // column c sits at index c - 5
-        const double* b = P[2 * q + 1];
-        hs.Bx[q][0] = a[7];  hs.Bx[q][1] = a[6] - b[7];   hs.Bx[q][2] = a[5] - b[6];  hs.Bx[q][3] = -b[5];
-        hs.By[q][0] = a[10]; hs.By[q][1] = a[9] - b[10];  hs.By[q][2] = a[8] - b[9];  hs.By[q][3] = -b[8];
-        hs.Bc[q][0] = a[14]; hs.Bc[q][1] = a[13] - b[14]; hs.Bc[q][2] = a[12] - b[13]; hs.Bc[q][3] = a[11] - b[12]; hs.Bc[q][4] = -b[11];
+        double a[10], b[10];                       // pivot rows 4 + 2q and 5 + 2q, columns 10..19
+#pragma unroll
+        for (int c = 0; c < 10; ++c) { a[c] = wk((4 + 2 * q) * 20 + 10 + c); b[c] = wk((5 + 2 * q) * 20 + 10 + c); }
+        Bx[q][0] = a[2]; Bx[q][1] = a[1] - b[2]; Bx[q][2] = a[0] - b[1]; Bx[q][3] = -b[0];
+        By[q][0] = a[5]; By[q][1] = a[4] - b[5]; By[q][2] = a[3] - b[4]; By[q][3] = -b[3];
+        Bc[q][0] = a[9]; Bc[q][1] = a[8] - b[9]; Bc[q][2] = a[7] - b[8]; Bc[q][3] = a[6] - b[7]; Bc[q][4] = -b[6];
+    }
+#pragma unroll
+    for (int q = 0; q < 3; ++q) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { wk(kOffBx + 4 * q + i) = Bx[q][i]; wk(kOffBy + 4 * q + i) = By[q][i]; }
+#pragma unroll
+        for (int i = 0; i < 5; ++i) wk(kOffBc + 5 * q + i) = Bc[q][i];
     }
     double poly[11], t1[8], t2[8], t3[11];
     for (int i = 0; i < 11; ++i) poly[i] = 0;
-    pmul(hs.By[1], 3, hs.Bc[2], 4, t1); pmul(hs.Bc[1], 4, hs.By[2], 3, t2); for (int i = 0; i < 8; ++i) t1[i] -= t2[i];
-    pmul(hs.Bx[0], 3, t1, 7, t3); for (int i = 0; i < 11; ++i) poly[i] += t3[i];
-    pmul(hs.Bx[1], 3, hs.Bc[2], 4, t1); pmul(hs.Bc[1], 4, hs.Bx[2], 3, t2); for (int i = 0; i < 8; ++i) t1[i] -= t2[i];
-    pmul(hs.By[0], 3, t1, 7, t3); for (int i = 0; i < 11; ++i) poly[i] -= t3[i];
+    pmul(By[1], 3, Bc[2], 4, t1); pmul(Bc[1], 4, By[2], 3, t2); for (int i = 0; i < 8; ++i) t1[i] -= t2[i];
+    pmul(Bx[0], 3, t1, 7, t3); for (int i = 0; i < 11; ++i) poly[i] += t3[i];
+    pmul(Bx[1], 3, Bc[2], 4, t1); pmul(Bc[1], 4, Bx[2], 3, t2); for (int i = 0; i < 8; ++i) t1[i] -= t2[i];
+    pmul(By[0], 3, t1, 7, t3); for (int i = 0; i < 11; ++i) poly[i] -= t3[i];
     {
         double u1[7], u2[7];
-        pmul(hs.Bx[1], 3, hs.By[2], 3, u1); pmul(hs.By[1], 3, hs.Bx[2], 3, u2);
+        pmul(Bx[1], 3, By[2], 3, u1); pmul(By[1], 3, Bx[2], 3, u2);
         for (int i = 0; i < 7; ++i) u1[i] -= u2[i];
-        pmul(hs.Bc[0], 4, u1, 6, t3);
+        pmul(Bc[0], 4, u1, 6, t3);
         for (int i = 0; i < 11; ++i) poly[i] += t3[i];
     }
-    hs.nr = isolate_roots(poly, hs.p, &hs.deg, hs.lo, hs.hi, &hs.mid, wk);
-    return hs.nr;
+    return isolate_roots(poly, mid, wk);
 }
 
 // Model validity test of USAC-style estimators (the oriented epipolar constraint of Chum, Werner and Matas, 2004; cv2's

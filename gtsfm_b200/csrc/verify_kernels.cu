@@ -43,20 +43,35 @@ __device__ __forceinline__ void hypothesis_samples(const VerifyBufs& b, const Ve
     }
 }
 
-// phase A of hypothesis h of pair p
+// phase A of hypothesis h of pair p: returns the number of real roots and leaves the hand-off block in the scratch
 template <class W>
-__device__ int isolate_hypothesis(const VerifyBufs& b, const VerifyDims& d, int p, int h, vm::HypState& hs, const W& wk)
+__device__ int isolate_hypothesis(const VerifyBufs& b, const VerifyDims& d, int p, int h, const W& wk, unsigned* mid)
 {
     const VPair& vp = b.pairs[p];
     int s[5];
     hypothesis_samples(b, d, p, h, vp, s);
-    double x1[5], y1[5], x2[5], y2[5];
-    for (int k = 0; k < 5; ++k) {
-        const int idx = min(max(s[k], 0), vp.M - 1);
-        const double4 c = static_cast<const double4*>(b.corr_d)[vp.m0 + idx];
-        x1[k] = c.x; y1[k] = c.y; x2[k] = c.z; y2[k] = c.w;
+    const double4* corr = static_cast<const double4*>(b.corr_d) + vp.m0;
+    int nr;
+    {
+        double x1[5], y1[5], x2[5], y2[5];
+#pragma unroll
+        for (int k = 0; k < 5; ++k) {
+            s[k] = min(max(s[k], 0), vp.M - 1);
+            const double4 c = corr[s[k]];
+            x1[k] = c.x; y1[k] = c.y; x2[k] = c.z; y2[k] = c.w;
+        }
+        nr = vm::fivept_isolate(x1, y1, x2, y2, wk, mid);
     }
-    return vm::fivept_isolate(x1, y1, x2, y2, hs, wk);
+    if (nr > 0) {
+        // the sample correspondences of the hand-off block are re-read (cache hits) rather than kept alive in
+        // registers through the whole solve
+#pragma unroll
+        for (int k = 0; k < 5; ++k) {
+            const double4 c = corr[s[k]];
+            wk(vm::kOffS + k) = c.x; wk(vm::kOffS + 5 + k) = c.y; wk(vm::kOffS + 10 + k) = c.z; wk(vm::kOffS + 15 + k) = c.w;
+        }
+    }
+    return nr;
 }
 
 // ---------------------------------------------------------------------------------------------------------------- K4
@@ -67,13 +82,12 @@ __device__ int isolate_hypothesis(const VerifyBufs& b, const VerifyDims& d, int 
 // NaN when the root gave no finite matrix.
 constexpr int kSolveThreads = 64;
 constexpr int kSolveSmem = vm::kWorkDoubles * kSolveThreads * 8;
-static_assert(vm::kHypDoubles * kSolveThreads + 3 * kSolveThreads * vm::kMaxCand <= vm::kWorkDoubles * kSolveThreads,
-              "hand-off state and the parked (x, y, z) of every root must fit the scratch");
+static_assert(vm::kOffXyz >= vm::kOffP + 11 && vm::kOffXyz + 3 * vm::kMaxCand <= vm::kWorkDoubles,
+              "the parked (x, y, z) of every root must fit the scratch behind the hand-off polynomial");
 
 __global__ void __launch_bounds__(kSolveThreads, 2) solve_kernel(VerifyBufs b, VerifyDims d, int n_pairs)
 {
     extern __shared__ double s_h[];                       // [kWorkDoubles][kSolveThreads]: scratch, then hand-off state
-    __shared__ int s_meta[kSolveThreads];                 // nr | deg << 8
     __shared__ unsigned s_mid[kSolveThreads];
     __shared__ unsigned s_valid[kSolveThreads];           // bit r: root r of the thread's hypothesis gave a valid model
     __shared__ unsigned short s_map2[kSolveThreads * vm::kMaxCand];
@@ -92,15 +106,9 @@ __global__ void __launch_bounds__(kSolveThreads, 2) solve_kernel(VerifyBufs b, V
         if (g < total) {
             const int p = static_cast<int>(g / d.H), h = static_cast<int>(g - static_cast<long long>(p) * d.H);
             if (b.pairs[p].status == 0) {
-                vm::HypState hs;
-                nr = isolate_hypothesis(b, d, p, h, hs, vm::Work<kSolveThreads>{s_h + tid});
-                if (nr > 0) {
-                    const double* src = reinterpret_cast<const double*>(&hs);
-#pragma unroll 2
-                    for (int f = 0; f < vm::kHypDoubles; ++f) s_h[f * kSolveThreads + tid] = src[f];
-                    s_meta[tid] = nr | (hs.deg << 8);
-                    s_mid[tid] = hs.mid;
-                }
+                unsigned mid = 0;
+                nr = isolate_hypothesis(b, d, p, h, vm::Work<kSolveThreads>{s_h + tid}, &mid);
+                s_mid[tid] = mid;
             }
         }
         // exclusive prefix sum of nr over the block
@@ -123,7 +131,7 @@ __global__ void __launch_bounds__(kSolveThreads, 2) solve_kernel(VerifyBufs b, V
         }
         // phase B1: one root per thread -> (x, y, z) and the validity of the unpolished model; survivors are compacted
         // once more (their xyz parked in the unused tail of the scratch) so that the polish runs on full warps
-        double* s_xyz = s_h + vm::kHypDoubles * kSolveThreads;
+        double* s_xyz = s_h + vm::kOffXyz * kSolveThreads;
         for (int idx = tid; idx < n_roots; idx += kSolveThreads) {
             const int code = s_map[idx], j = code >> 4, r = code & 15;
             double xyz[3];
@@ -499,20 +507,20 @@ __global__ void __launch_bounds__(kFinThreads, 2) finalize_kernel(VerifyBufs b, 
         const int k = tid >> 5;
         const int h = s_topi[k] / vm::kMaxCand, c = s_topi[k] - h * vm::kMaxCand;
         const float* e32 = b.E32 + (static_cast<long long>(p) * d.H) * (9 * vm::kMaxCand) + static_cast<long long>(s_topi[k]) * 9;
-        vm::HypState hs;
-        const int nr = isolate_hypothesis(b, d, p, h, hs, vm::Work<kTopK>{s_work + k});
-        const vm::HypView<1> hv{reinterpret_cast<const double*>(&hs)};
+        unsigned mid = 0;
+        const int nr = isolate_hypothesis(b, d, p, h, vm::Work<kTopK>{s_work + k}, &mid);
+        const vm::HypView<kTopK> hv{s_work + k};
         double bestdot = -1.0, Eb[9], E[9];
         for (int e = 0; e < 9; ++e) Eb[e] = nan("");
         // slot c of E32 is root c of the same deterministic isolation; accept it when it reproduces the fp32 copy,
         // otherwise (a root count that differs in the last bit) take the closest of all roots
-        if (c < nr && vm::fivept_root(hv, hs.mid, c, E)) {
+        if (c < nr && vm::fivept_root(hv, mid, c, E)) {
             double dot = 0;
             for (int e = 0; e < 9; ++e) dot += E[e] * static_cast<double>(e32[e]);
             if (fabs(dot) > 0.999999) { bestdot = 2.0; for (int e = 0; e < 9; ++e) Eb[e] = E[e]; }
         }
         for (int r = 0; r < nr && bestdot < 2.0; ++r) {
-            if (!vm::fivept_root(hv, hs.mid, r, E)) continue;
+            if (!vm::fivept_root(hv, mid, r, E)) continue;
             double dot = 0;
             for (int e = 0; e < 9; ++e) dot += E[e] * static_cast<double>(e32[e]);
             if (fabs(dot) > bestdot && fabs(dot) < 2.0) { bestdot = fabs(dot); for (int e = 0; e < 9; ++e) Eb[e] = E[e]; }
