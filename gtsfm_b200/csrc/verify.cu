@@ -102,6 +102,8 @@ int gtsfm_verify_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, const ui
     G2V_CUDA(c, vb[12].reserve(static_cast<size_t>(total + 1), false, s));
     if (!vb[13].p) { G2V_CUDA(c, vb[13].reserve(32, false, s)); G2V_CUDA(c, cudaMemsetAsync(vb[13].p, 0, 32, s)); }
     G2V_CUDA(c, vb[14].reserve(4 * static_cast<size_t>(chunk), false, s));
+    G2V_CUDA(c, vb[15].reserve(32 * static_cast<size_t>(chunk), false, s));
+    G2V_CUDA(c, vb[16].reserve(576 * static_cast<size_t>(chunk), false, s));
     G2V_CUDA(c, c->h_pairs.reserve(sizeof(VPair) * n_pairs));
     std::memcpy(c->h_pairs.p, vps.data(), sizeof(VPair) * n_pairs);
     G2V_CUDA(c, cudaMemcpyAsync(vb[0].p, c->h_pairs.p, sizeof(VPair) * n_pairs, cudaMemcpyHostToDevice, s));
@@ -123,6 +125,7 @@ int gtsfm_verify_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, const ui
         b.R = vb[7].as<double>() + 9ll * p0; b.t = vb[8].as<double>() + 3ll * p0; b.E = vb[9].as<double>() + 9ll * p0;
         b.stats = vb[13].as<unsigned long long>();
         b.best_cost = vb[14].as<unsigned int>();
+        b.topi = vb[15].as<int>(); b.Ek = vb[16].as<double>();
         G2V_CUDA(c, cudaMemsetAsync(vb[14].p, 0x7f, 4 * static_cast<size_t>(np), s));   // 0x7f7f7f7f = 3.4e38f
         b.ninl = vb[10].as<int>() + p0; b.status = vb[11].as<int>() + p0; b.mask = vb[12].as<unsigned char>();
         int mm = 0;
@@ -132,7 +135,7 @@ int gtsfm_verify_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, const ui
             G2V_CUDA(c, launch_verify_step(step, st, b, d, np, mm, s));
             c->prof_end();
         }
-        c->launches += 4;
+        c->launches += 6;
     }
     // ---- results back to the host
     if (R) G2V_CUDA(c, cudaMemcpyAsync(R, vb[7].p, 72 * static_cast<size_t>(n_pairs), cudaMemcpyDeviceToHost, s));

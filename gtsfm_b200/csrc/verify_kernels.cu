@@ -313,7 +313,7 @@ __global__ void __launch_bounds__(256) score_kernel(VerifyBufs b, VerifyDims d, 
 
 // ---------------------------------------------------------------------------------------------------------------- K6/K7
 constexpr int kTopK = 8;            // candidates re-scored in fp64 (fp32 scoring only has to rank the best few)
-constexpr int kFinThreads = 256;
+constexpr int kFinThreads = 128;
 
 // deterministic block sum of NV doubles per thread: warp shuffle tree, then warps added in order by thread 0
 template <int NV> __device__ void block_sum(double* v, double (*s_red)[24], double* s_out)
@@ -442,45 +442,34 @@ __device__ void lo_pass(const VerifyBufs& b, const VPair& vp, const double* s_R,
     block_sum<22>(acc, s_red, s_out);
 }
 
-__global__ void __launch_bounds__(kFinThreads, 2) finalize_kernel(VerifyBufs b, VerifyDims d, int n_pairs)
+// K6a: the kTopK best candidates of a pair by fp32 MSAC cost (ties: lowest candidate id = h * 10 + root).
+__global__ void __launch_bounds__(256) topk_select_kernel(VerifyBufs b, VerifyDims d, int n_pairs)
 {
-    __shared__ double s_red[kFinThreads / 32][24];
-    __shared__ double s_out[24];
-    __shared__ double s_Ek[kTopK][9];
-    __shared__ double s_work[vm::kWorkDoubles * kTopK];     // solver scratch of the kTopK re-solving threads
-    __shared__ double s_R[9], s_t[3], s_E[9], s_dE[45];
-    __shared__ double s_R1[9], s_R2[9], s_tt[3];
-    __shared__ float s_topv[kTopK];
     __shared__ int s_topi[kTopK];
-    __shared__ float s_wv[kFinThreads / 32];
-    __shared__ int s_wi[kFinThreads / 32];
-    __shared__ int s_ctrl;
-
+    __shared__ float s_wv[8];
+    __shared__ int s_wi[8];
     const int p = blockIdx.x;
     if (p >= n_pairs) return;
-    const VPair& vp = b.pairs[p];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    for (int i = tid; i < vp.M; i += kFinThreads) b.mask[vp.m0 + i] = 0;
-    if (tid < 9) { b.R[p * 9 + tid] = 0; b.E[p * 9 + tid] = 0; }
-    if (tid < 3) b.t[p * 3 + tid] = 0;
-    if (tid == 0) { b.ninl[p] = 0; b.status[p] = vp.status; }
-    if (vp.status != 0) return;
-
-    // ---- (a) the kTopK best candidates by fp32 MSAC cost (ties: lowest candidate id = h * 10 + c)
+    if (tid < kTopK) b.topi[p * kTopK + tid] = INT_MAX;
+    if (b.pairs[p].status != 0) return;
     const int n_slots = d.H * vm::kMaxCand;
     const float* cost = b.cost + static_cast<long long>(p) * n_slots;
     const unsigned short* vmask = b.vmask + static_cast<long long>(p) * d.H;
-    int n_top = 0;
     for (int k = 0; k < kTopK; ++k) {
         float bv = FLT_MAX;
         int bi = INT_MAX;
-        for (int sidx = tid; sidx < n_slots; sidx += kFinThreads) {
-            const int h = sidx / vm::kMaxCand, c = sidx - h * vm::kMaxCand;
-            if (!((vmask[h] >> c) & 1u)) continue;
-            bool used = false;
-            for (int j = 0; j < k; ++j) used |= (s_topi[j] == sidx);
-            const float v = cost[sidx];
-            if (!used && (v < bv)) { bv = v; bi = sidx; }     // ascending scan: first minimum = lowest id
+        for (int h = tid; h < d.H; h += 256) {             // ascending scan: first minimum = lowest id
+            unsigned m = vmask[h];
+            while (m) {
+                const int c = __ffs(m) - 1;
+                m &= m - 1;
+                const int sidx = h * vm::kMaxCand + c;
+                bool used = false;
+                for (int j = 0; j < k; ++j) used |= (s_topi[j] == sidx);
+                const float v = cost[sidx];
+                if (!used && (v < bv)) { bv = v; bi = sidx; }
+            }
         }
 #pragma unroll
         for (int off = 16; off > 0; off >>= 1) {
@@ -491,27 +480,35 @@ __global__ void __launch_bounds__(kFinThreads, 2) finalize_kernel(VerifyBufs b, 
         if (lane == 0) { s_wv[warp] = bv; s_wi[warp] = bi; }
         __syncthreads();
         if (tid == 0) {
-            for (int w = 1; w < kFinThreads / 32; ++w)
+            for (int w = 1; w < 8; ++w)
                 if (s_wv[w] < bv || (s_wv[w] == bv && s_wi[w] < bi)) { bv = s_wv[w]; bi = s_wi[w]; }
-            s_topv[k] = bv;
             s_topi[k] = bi;
+            b.topi[p * kTopK + k] = bi;
         }
         __syncthreads();
         if (s_topi[k] == INT_MAX) break;
-        ++n_top;
     }
-    if (n_top == 0) { if (tid == 0) b.status[p] = 2; return; }
+}
 
-    // ---- (b) re-solve those hypotheses in fp64; the wanted root is the one whose matrix is closest to the fp32 copy
-    if ((tid & 31) == 0 && (tid >> 5) < n_top) {       // one re-solve per warp: no divergence between them
-        const int k = tid >> 5;
-        const int h = s_topi[k] / vm::kMaxCand, c = s_topi[k] - h * vm::kMaxCand;
-        const float* e32 = b.E32 + (static_cast<long long>(p) * d.H) * (9 * vm::kMaxCand) + static_cast<long long>(s_topi[k]) * 9;
+// K6b: re-solve the selected hypotheses in fp64, one (pair, candidate) per thread with the solver scratch in shared
+// memory as in the solve kernel.  The wanted root is the one whose matrix reproduces the fp32 copy.
+__global__ void __launch_bounds__(kSolveThreads, 2) topk_solve_kernel(VerifyBufs b, VerifyDims d, int n_pairs)
+{
+    extern __shared__ double s_h[];
+    const long long g = static_cast<long long>(blockIdx.x) * kSolveThreads + threadIdx.x;
+    if (g >= static_cast<long long>(n_pairs) * kTopK) return;
+    const int p = static_cast<int>(g / kTopK);
+    double Eb[9];
+    for (int e = 0; e < 9; ++e) Eb[e] = nan("");
+    const int sidx = b.topi[g];
+    if (sidx != INT_MAX && b.pairs[p].status == 0) {
+        const int h = sidx / vm::kMaxCand, c = sidx - h * vm::kMaxCand;
+        const float* e32 = b.E32 + (static_cast<long long>(p) * d.H) * (9 * vm::kMaxCand) + static_cast<long long>(sidx) * 9;
         unsigned mid = 0;
-        const int nr = isolate_hypothesis(b, d, p, h, vm::Work<kTopK>{s_work + k}, &mid);
-        const vm::HypView<kTopK> hv{s_work + k};
-        double bestdot = -1.0, Eb[9], E[9];
-        for (int e = 0; e < 9; ++e) Eb[e] = nan("");
+        const vm::Work<kSolveThreads> wk{s_h + threadIdx.x};
+        const int nr = isolate_hypothesis(b, d, p, h, wk, &mid);
+        const vm::HypView<kSolveThreads> hv{s_h + threadIdx.x};
+        double bestdot = -1.0, E[9];
         // slot c of E32 is root c of the same deterministic isolation; accept it when it reproduces the fp32 copy,
         // otherwise (a root count that differs in the last bit) take the closest of all roots
         if (c < nr && vm::fivept_root(hv, mid, c, E)) {
@@ -525,9 +522,37 @@ __global__ void __launch_bounds__(kFinThreads, 2) finalize_kernel(VerifyBufs b, 
             for (int e = 0; e < 9; ++e) dot += E[e] * static_cast<double>(e32[e]);
             if (fabs(dot) > bestdot && fabs(dot) < 2.0) { bestdot = fabs(dot); for (int e = 0; e < 9; ++e) Eb[e] = E[e]; }
         }
-        for (int e = 0; e < 9; ++e) s_Ek[k][e] = Eb[e];
     }
+    for (int e = 0; e < 9; ++e) b.Ek[g * 9 + e] = Eb[e];
+}
+
+__global__ void __launch_bounds__(kFinThreads, 4) finalize_kernel(VerifyBufs b, VerifyDims d, int n_pairs)
+{
+    __shared__ double s_red[kFinThreads / 32][24];
+    __shared__ double s_out[24];
+    __shared__ double s_Ek[kTopK][9];
+    __shared__ double s_R[9], s_t[3], s_E[9], s_dE[45];
+    __shared__ double s_R1[9], s_R2[9], s_tt[3];
+    __shared__ int s_topi[kTopK];
+    __shared__ int s_ctrl;
+
+    const int p = blockIdx.x;
+    if (p >= n_pairs) return;
+    const VPair& vp = b.pairs[p];
+    const int tid = threadIdx.x;
+    for (int i = tid; i < vp.M; i += kFinThreads) b.mask[vp.m0 + i] = 0;
+    if (tid < 9) { b.R[p * 9 + tid] = 0; b.E[p * 9 + tid] = 0; }
+    if (tid < 3) b.t[p * 3 + tid] = 0;
+    if (tid == 0) { b.ninl[p] = 0; b.status[p] = vp.status; }
+    if (vp.status != 0) return;
+
+    // ---- (a, b) the kTopK best candidates by fp32 cost and their fp64 matrices (topk_select_kernel, topk_solve_kernel)
+    if (tid < kTopK) s_topi[tid] = b.topi[p * kTopK + tid];
+    if (tid < kTopK * 9) (&s_Ek[0][0])[tid] = b.Ek[static_cast<long long>(p) * kTopK * 9 + tid];
     __syncthreads();
+    int n_top = 0;
+    while (n_top < kTopK && s_topi[n_top] != INT_MAX) ++n_top;
+    if (n_top == 0) { if (tid == 0) b.status[p] = 2; return; }
 
     // ---- (c) fp64 MSAC cost of the kTopK candidates, then the minimum (ties: lowest id)
     {
@@ -681,6 +706,8 @@ cudaError_t launch_verify_step(int step, const StoreView& st, const VerifyBufs& 
         if (e != cudaSuccess) return e;
         e = cudaFuncSetAttribute(solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSolveSmem);
         if (e != cudaSuccess) return e;
+        e = cudaFuncSetAttribute(topk_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSolveSmem);
+        if (e != cudaSuccess) return e;
         configured = true;
     }
     if (step == 0) {
@@ -696,6 +723,9 @@ cudaError_t launch_verify_step(int step, const StoreView& st, const VerifyBufs& 
     } else if (step == 2) {
         score_kernel<<<dim3((d.H + kScoreHyp - 1) / kScoreHyp, n_pairs), 256, kScoreTile * 16, s>>>(b, d, n_pairs);
     } else {
+        topk_select_kernel<<<n_pairs, 256, 0, s>>>(b, d, n_pairs);
+        const unsigned nb = static_cast<unsigned>((static_cast<long long>(n_pairs) * kTopK + kSolveThreads - 1) / kSolveThreads);
+        topk_solve_kernel<<<nb, kSolveThreads, kSolveSmem, s>>>(b, d, n_pairs);
         finalize_kernel<<<n_pairs, kFinThreads, 0, s>>>(b, d, n_pairs);
     }
     return cudaGetLastError();

@@ -28,6 +28,8 @@ struct VerifyBufs {
     double* R; double* t; double* E; int* ninl; int* status; unsigned char* mask;
     unsigned long long* stats; // running totals: [0] candidates (real roots), [1] hypotheses solved, [2] Sampson evaluations
                                // (algorithmic: candidates x correspondences), [3] evaluations executed after early exit
+    int* topi;                 // [P][8] (this chunk) candidate ids (h * 10 + root) of the lowest fp32 costs, INT_MAX when absent
+    double* Ek;                // [P][8][9] (this chunk) their essential matrices re-solved in fp64 (NaN when absent)
     unsigned int* best_cost;   // [P] (this chunk) bit pattern of the lowest complete fp32 MSAC cost seen so far
 };
 
