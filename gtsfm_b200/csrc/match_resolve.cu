@@ -303,6 +303,8 @@ __global__ void __launch_bounds__(128) bucket_rows_kernel(StoreView st, MatchWor
 #pragma unroll
         for (int k = 0; k < N16 / 4; ++k) { L[k] = __ldg(r_lo + 4 * k); H[k] = __ldg(r_hi + 4 * k); }
         const int n_lo = st.norm_i[pd.q_row0 + i_lo], n_hi = st.norm_i[pd.q_row0 + i_hi];
+        const long long pos = pd.out_base + ((q & 1) ? i_hi : i_lo);      // lane q = 0 finishes row g, lane q = 1 row g + 8
+        const float k1 = w.row_d1[pos], k2 = w.row_d2[pos];              // screened values, in flight during the products
         Top2 tl{INT_MAX, INT_MAX, INT_MAX}, th{INT_MAX, INT_MAX, INT_MAX};
 #pragma unroll
         for (int nt = 0; nt < kGroup / 8; ++nt) {
@@ -329,8 +331,6 @@ __global__ void __launch_bounds__(128) bucket_rows_kernel(StoreView st, MatchWor
         if ((q == 0 && act_lo) || (q == 1 && act_hi)) {
             const Top2 t = (q == 0) ? tl : th;
             const int i = (q == 0) ? i_lo : i_hi;
-            const long long pos = pd.out_base + i;
-            const float k1 = w.row_d1[pos], k2 = w.row_d2[pos];
             const float f1 = dist_or_max(t.b1), f2 = dist_or_max(t.b2), f2o = dist_from_half(k2);
             // Ambiguous when another group may hold an equal (float32) distance at a lower index, or when the
             // recomputed minimum does not reproduce the screened value (never expected; keeps the result
@@ -386,6 +386,8 @@ __global__ void __launch_bounds__(128) bucket_cols_kernel(StoreView st, MatchWor
 #pragma unroll
         for (int k = 0; k < N16 / 4; ++k) { L[k] = __ldg(r_lo + 4 * k); H[k] = __ldg(r_hi + 4 * k); }
         const int n_lo = st.norm_i[pd.t_row0 + j_lo], n_hi = st.norm_i[pd.t_row0 + j_hi];
+        const long long pos = pd.cb_base + ((q & 1) ? j_hi : j_lo);
+        const float k1 = w.col_d1[pos], k2 = w.col_d2[pos];
         Top2 tl{INT_MAX, INT_MAX, INT_MAX}, th{INT_MAX, INT_MAX, INT_MAX};
 #pragma unroll 2
         for (int nt = 0; nt < n_cls8 / 8; ++nt) {
@@ -412,8 +414,6 @@ __global__ void __launch_bounds__(128) bucket_cols_kernel(StoreView st, MatchWor
         if ((q == 0 && act_lo) || (q == 1 && act_hi)) {
             const Top2 t2 = (q == 0) ? tl : th;
             const int j = (q == 0) ? j_lo : j_hi;
-            const long long pos = pd.cb_base + j;
-            const float k1 = w.col_d1[pos], k2 = w.col_d2[pos];
             const float f1 = dist_or_max(t2.b1), f2 = dist_or_max(t2.b2), f2o = dist_from_half(k2);
             const bool ambiguous = (t2.i1 == INT_MAX) || (f2o <= f1) || (static_cast<float>(t2.b1) != k1 + k1) || (t2.b1 >= kSqrtMonotoneBelow);
             if (ambiguous) flag(w, p, 1, j);

@@ -221,6 +221,7 @@ __global__ void __launch_bounds__(256) score_kernel(VerifyBufs b, VerifyDims d, 
     if (n == 0) return;
     if (threadIdx.x == 0 && b.stats) atomicAdd(b.stats + 2, static_cast<unsigned long long>(n) * static_cast<unsigned long long>(vp.M));
     const float thr2 = static_cast<float>(vp.thr2);
+    const float q_inv = thr2 * static_cast<float>(vp.M) * (1.0f / 1073741824.0f), q_scale = 1.0f / q_inv;
     const float* Ebase = b.E32 + (static_cast<long long>(p) * d.H + h0) * (9 * vm::kMaxCand);
     const volatile float* best = reinterpret_cast<const volatile float*>(b.best_cost + p);
     float4* sA = s_corr;
@@ -277,9 +278,11 @@ __global__ void __launch_bounds__(256) score_kernel(VerifyBufs b, VerifyDims d, 
                     acc1 += fminf(s1, thr2);
                 }
                 done = c1;
-                float part = acc0 + acc1;
-#pragma unroll
-                for (int off = 16; off > 0; off >>= 1) part += __shfl_xor_sync(0xffffffffu, part, off);
+                // warp total of the partial costs in fixed point (one REDUX instead of a five-step shuffle tree): every
+                // lane's share is below thr2 * M, so 2^30 / (thr2 * M) per unit cannot overflow; the rounding (< 2^-25
+                // of the full scale) is far inside the 1.001 margin of the test
+                const int part_q = __float2int_rn((acc0 + acc1) * q_scale);
+                const float part = static_cast<float>(__reduce_add_sync(0xffffffffu, part_q)) * q_inv;
                 if (before + part > bestv * 1.001f) { dead = true; break; }
             }
             float acc = acc0 + acc1;
