@@ -676,6 +676,9 @@ static int solve_lm5(const double* JtJ, const double* Jtr, double lambda, double
 
 #define LO_MAX_ITERS 20
 
+/* diagnostics: Levenberg-Marquardt trial steps taken by the last oracle_lo_refine call */
+int oracle_lo_trials_last = 0;
+
 /* Local optimisation: Levenberg-Marquardt on (R,t) starting from the decomposition (R1, t) of E_in,
  * minimising the MSAC cost; each accepted step re-selects the inliers.  E_out = [t]x R (norm sqrt 2). */
 double oracle_lo_refine(const double* E_in, const double* x1, const double* y1, const double* x2, const double* y2,
@@ -686,8 +689,10 @@ double oracle_lo_refine(const double* E_in, const double* x1, const double* y1, 
     oracle_decompose_essential(E_in, R, R2, t);
     double cost = lo_pass(R, t, x1, y1, x2, y2, n, thr2, &ninl, JtJ, Jtr);
     double lambda = 1e-4;
+    oracle_lo_trials_last = 0;
     for (int it = 0; it < max_iters; ++it) {
         if (ninl < 5) break;
+        ++oracle_lo_trials_last;
         double d[5];
         if (!solve_lm5(JtJ, Jtr, lambda, d)) { lambda *= 10.0; if (lambda > 1e4) break; continue; }
         double dR[9], Rn[9], tn[3], b1[3], b2[3], JtJn[25], Jtrn[5];
