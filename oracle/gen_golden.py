@@ -187,14 +187,58 @@ def gen_sampson(rng):
     np.savez_compressed(os.path.join(OUT, "sampson.npz"), c1=c1, c2=c2, F=F, ref=s)
 
 
+def gen_fmat():
+    """Fundamental-matrix mode (ransac.py:84-111): cv2's 7-point solver on minimal sets, and the UNMODIFIED reference
+    Ransac(use_intrinsics_in_verification=False).verify on a synthetic pair.  Own seed: `python gen_golden.py fmat`
+    adds these files without touching the others."""
+    rng = np.random.default_rng(20260007)
+    n, f = 1500, 1000.0
+    X = rng.uniform([-4, -4, 6], [4, 4, 12], (n, 3))
+    Rgt = cv2.Rodrigues(np.array([0.03, 0.25, -0.02]))[0]
+    tgt = np.array([1.0, 0.15, 0.25])
+    K = np.array([[f, 0, 640.0], [0, f, 480.0], [0, 0, 1]])
+    p1 = (K @ X.T).T
+    p2 = (K @ ((Rgt @ X.T).T + tgt).T).T
+    kp1 = p1[:, :2] / p1[:, 2:] + rng.normal(0, 0.6, (n, 2))
+    kp2 = p2[:, :2] / p2[:, 2:] + rng.normal(0, 0.6, (n, 2))
+    kp2[:500] = rng.uniform(0, 1, (500, 2)) * [1280, 960]
+    perm = rng.permutation(n)
+    mi = np.c_[perm, perm].astype(np.uint32)
+    cal = (f, 0.0, 0.0, 640.0, 480.0)
+    # minimal sets drawn from the true correspondences
+    sets = np.stack([500 + rng.choice(n - 500, 7, replace=False) for _ in range(64)])
+    F7 = np.full((64, 3, 3, 3), np.nan)
+    n7 = np.zeros(64, np.int32)
+    for k, idx in enumerate(sets):
+        Fs, _ = cv2.findFundamentalMat(kp1[idx].astype(np.float32), kp2[idx].astype(np.float32), cv2.FM_7POINT)
+        if Fs is not None:
+            n7[k] = Fs.shape[0] // 3
+            F7[k, :n7[k]] = Fs.reshape(-1, 3, 3)
+    # cv2's own model and mask on all matches (the error / mask rule is pinned on these)
+    Fcv, mcv = cv2.findFundamentalMat(kp1[mi[:, 0]], kp2[mi[:, 1]], method=cv2.FM_RANSAC, ransacReprojThreshold=4.0,
+                                      confidence=0.999999, maxIters=1000000)
+    R, U, v, ratio = Ransac(False, 4.0).verify(Keypoints(kp1), Keypoints(kp2), mi, Cal3Bundler(*cal), Cal3Bundler(*cal))
+    np.savez_compressed(os.path.join(OUT, "fmat_synth1500.npz"), kp1=kp1, kp2=kp2, mi=mi, cal=np.array(cal), R_gt=Rgt, t_gt=tgt,
+                        sets=sets.astype(np.int32), F7=F7, n7=n7, cv_F=Fcv, cv_mask=mcv.ravel().astype(np.uint8),
+                        ref_R=R.matrix(), ref_t=U.point3(), ref_idx=v.astype(np.uint32), ref_ratio=np.float64(ratio))
+    print("fmat_synth1500: ref verified", v.shape, "ratio", ratio, "7pt solutions", n7.sum())
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
+    if sys.argv[1:] == ["fmat"]:
+        gen_fmat()
+        with open(os.path.join(OUT, "PROVENANCE.txt"), "a") as fh:
+            fh.write(f"fmat_*.npz: oracle/gen_golden.py fmat, /root/reference (commit bc04d78b), cv2 {cv2.__version__}, "
+                     f"numpy {np.__version__}, gtsam={GTSAM}\n")
+        sys.exit(0)
     rng = np.random.default_rng(20260001)
     print("gtsam:", GTSAM, "cv2:", cv2.__version__)
     gen_matcher(rng)
     gen_lund()
     gen_verifier(rng)
     gen_sampson(rng)
+    gen_fmat()
     with open(os.path.join(OUT, "PROVENANCE.txt"), "w") as fh:
         fh.write(f"generated by oracle/gen_golden.py from /root/reference (commit bc04d78b), cv2 {cv2.__version__}, "
                  f"numpy {np.__version__}, gtsam={GTSAM}\n")

@@ -164,3 +164,55 @@ def verify_pair(kp1: np.ndarray, kp2: np.ndarray, match_indices: np.ndarray, cal
     return dict(status=int(st), E_min=E_min.reshape(3, 3), E=E.reshape(3, 3), mask=mask[:M], R=R.reshape(3, 3),
                 t=t, ninl=int(info[0]), best_id=int(info[1]), ncand=int(info[2]), cost_min=float(cost[0]),
                 cost=float(cost[1]))
+
+
+# ---------------------------------------------------------------- fundamental-matrix mode (ransac.py:84-111)
+def sevenpt(p1: np.ndarray, p2: np.ndarray) -> np.ndarray:
+    """7-point solver on seven pixel correspondences (cv2.findFundamentalMat(FM_7POINT)) -> (k,3,3) unit-norm F."""
+    p1 = np.asarray(p1, np.float64)
+    p2 = np.asarray(p2, np.float64)
+    x1, y1, x2, y2 = (np.ascontiguousarray(v) for v in (p1[:, 0], p1[:, 1], p2[:, 0], p2[:, 1]))
+    out = np.zeros(27)
+    n = lib().oracle_sevenpt(_d(x1), _d(y1), _d(x2), _d(y2), _d(out))
+    return out[: 9 * n].reshape(n, 3, 3).copy()
+
+
+def fm_error(F: np.ndarray, c1: np.ndarray, c2: np.ndarray) -> np.ndarray:
+    """cv2's FM_RANSAC error: max of the two squared point-to-epipolar-line distances, float32 (double arithmetic on the
+    float32-rounded pixel coordinates)."""
+    F = np.ascontiguousarray(F, np.float64)
+    c1 = np.asarray(c1, np.float32)
+    c2 = np.asarray(c2, np.float32)
+    x1, y1, x2, y2 = (np.ascontiguousarray(v) for v in (c1[:, 0], c1[:, 1], c2[:, 0], c2[:, 1]))
+    out = np.empty(x1.shape[0], np.float32)
+    lib().oracle_fm_error_batch(_d(F), x1.ctypes.data_as(_fp), y1.ctypes.data_as(_fp), x2.ctypes.data_as(_fp),
+                                y2.ctypes.data_as(_fp), int(x1.shape[0]), out.ctypes.data_as(_fp))
+    return out
+
+
+def verify_pair_F(kp1: np.ndarray, kp2: np.ndarray, match_indices: np.ndarray, cal1, cal2, thr_px: float,
+                  samples: np.ndarray) -> dict:
+    """OpencvVerifierBase.verify with use_intrinsics_in_verification=False and an explicit (H,7) sample array.
+
+    Returns a dict: status, F, E, mask (M,) uint8, R, t, ninl, best_id, ncand.
+    """
+    kp1 = np.ascontiguousarray(kp1, np.float64).reshape(-1, 2)
+    kp2 = np.ascontiguousarray(kp2, np.float64).reshape(-1, 2)
+    mi = np.asarray(match_indices).reshape(-1, 2)
+    M = mi.shape[0]
+    m1 = np.ascontiguousarray(mi[:, 0], np.int32)
+    m2 = np.ascontiguousarray(mi[:, 1], np.int32)
+    c1 = np.asarray(cal1, np.float64)
+    c2 = np.asarray(cal2, np.float64)
+    samples = np.ascontiguousarray(samples, np.int32).reshape(-1, 7)
+    F = np.zeros(9)
+    E = np.zeros(9)
+    mask = np.zeros(max(M, 1), np.uint8)
+    R = np.zeros(9)
+    t = np.zeros(3)
+    info = np.zeros(3, np.int32)
+    st = lib().oracle_verify_pair_F(_d(kp1), _d(kp2), m1.ctypes.data_as(_ip), m2.ctypes.data_as(_ip), M, _d(c1), _d(c2),
+                                    ctypes.c_double(thr_px), samples.ctypes.data_as(_ip), int(samples.shape[0]),
+                                    _d(F), _d(E), mask.ctypes.data_as(_bp), _d(R), _d(t), info.ctypes.data_as(_ip))
+    return dict(status=int(st), F=F.reshape(3, 3), E=E.reshape(3, 3), mask=mask[:M], R=R.reshape(3, 3), t=t,
+                ninl=int(info[0]), best_id=int(info[1]), ncand=int(info[2]))

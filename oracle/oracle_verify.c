@@ -814,3 +814,155 @@ int oracle_verify_pair(const double* kp1, const double* kp2, const int32_t* mi1,
     free(ix1); free(x1);
     return VSTAT_OK;
 }
+
+/* ================================================================ fundamental-matrix mode
+ * Ransac(use_intrinsics_in_verification=False): Ransac.estimate_F -> cv2.findFundamentalMat(FM_RANSAC, thr px)
+ * (gtsfm/frontend/verifier/ransac.py:84-111), then E = K2^T F K1 (utils/verification.py:97-110,
+ * opencv_verifier_base.py:90-96) and the same pose recovery as the essential-matrix mode.
+ *
+ * OpenCV (un-vendored dependency of the reference, opencv-python 4.13) runs its classic RANSAC here: 7-point minimal
+ * solver on the float32 pixel coordinates, error = max of the two squared point-to-epipolar-line distances, inlier
+ * <=> error <= thr^2, model with the most inliers wins (the first one found among equal counts), no refit.  Restated
+ * below with explicit (H,7) sample sets.  PARITY UNPINNED for the loop itself (cv2 neither takes nor reports its samples
+ * and stops adaptively); pinned: the 7-point solver against cv2.findFundamentalMat(FM_7POINT) and the error / mask rule
+ * against the mask cv2 returns for its own F (tests/golden/fmat_*.npz). */
+
+/* cv::FMEstimatorCallback::computeError: double arithmetic on float32 points, result rounded to float32. */
+float oracle_fm_error(const double* F, float fx1, float fy1, float fx2, float fy2)
+{
+    const double x1 = fx1, y1 = fy1, x2 = fx2, y2 = fy2;
+    double a = F[0] * x1 + F[1] * y1 + F[2];
+    double b = F[3] * x1 + F[4] * y1 + F[5];
+    double c = F[6] * x1 + F[7] * y1 + F[8];
+    const double s2 = 1. / (a * a + b * b);
+    const double d2 = x2 * a + y2 * b + c;
+    a = F[0] * x2 + F[3] * y2 + F[6];
+    b = F[1] * x2 + F[4] * y2 + F[7];
+    c = F[2] * x2 + F[5] * y2 + F[8];
+    const double s1 = 1. / (a * a + b * b);
+    const double d1 = x1 * a + y1 * b + c;
+    const double e1 = d1 * d1 * s1, e2 = d2 * d2 * s2;
+    return (float)(e1 > e2 ? e1 : e2);
+}
+
+void oracle_fm_error_batch(const double* F, const float* x1, const float* y1, const float* x2, const float* y2, int n, float* out)
+{
+    for (int i = 0; i < n; ++i) out[i] = oracle_fm_error(F, x1[i], y1[i], x2[i], y2[i]);
+}
+
+/* Null space (2 vectors) of the 7x9 epipolar system, Gauss-Jordan with complete pivoting (as nullspace_5x9). */
+static int nullspace_7x9(const double* x1, const double* y1, const double* x2, const double* y2, double N[2][9])
+{
+    double A[7][9]; int perm[9];
+    for (int r = 0; r < 7; ++r) {
+        A[r][0] = x2[r] * x1[r]; A[r][1] = x2[r] * y1[r]; A[r][2] = x2[r];
+        A[r][3] = y2[r] * x1[r]; A[r][4] = y2[r] * y1[r]; A[r][5] = y2[r];
+        A[r][6] = x1[r];         A[r][7] = y1[r];         A[r][8] = 1.0;
+    }
+    for (int c = 0; c < 9; ++c) perm[c] = c;
+    for (int k = 0; k < 7; ++k) {
+        int pr = k, pc = k; double best = -1.0;
+        for (int r = k; r < 7; ++r) for (int c = k; c < 9; ++c) { double v = fabs(A[r][c]); if (v > best) { best = v; pr = r; pc = c; } }
+        if (!(best > 1e-14)) return 0;
+        if (pr != k) for (int c = 0; c < 9; ++c) { double t = A[k][c]; A[k][c] = A[pr][c]; A[pr][c] = t; }
+        if (pc != k) { for (int r = 0; r < 7; ++r) { double t = A[r][k]; A[r][k] = A[r][pc]; A[r][pc] = t; } int t = perm[k]; perm[k] = perm[pc]; perm[pc] = t; }
+        double inv = 1.0 / A[k][k];
+        for (int c = k; c < 9; ++c) A[k][c] *= inv;
+        for (int r = 0; r < 7; ++r) if (r != k) { double f = A[r][k]; if (f != 0.0) for (int c = k; c < 9; ++c) A[r][c] -= f * A[k][c]; }
+    }
+    for (int j = 0; j < 2; ++j) {
+        double v[9];
+        for (int r = 0; r < 7; ++r) v[r] = -A[r][7 + j];
+        for (int c = 7; c < 9; ++c) v[c] = (c == 7 + j) ? 1.0 : 0.0;
+        double nn = 0; for (int c = 0; c < 9; ++c) nn += v[c] * v[c];
+        nn = 1.0 / sqrt(nn);
+        for (int c = 0; c < 9; ++c) N[j][perm[c]] = v[c] * nn;
+    }
+    return 1;
+}
+
+static double det3c(const double* a, const double* b, const double* c)   /* det of the matrix with COLUMNS a, b, c */
+{
+    return a[0] * (b[1] * c[2] - b[2] * c[1]) - b[0] * (a[1] * c[2] - a[2] * c[1]) + c[0] * (a[1] * b[2] - a[2] * b[1]);
+}
+
+/* cv::FMEstimatorCallback::run7Point restated: F(l) = l N0 + (1 - l) N1 over the two null vectors, det F(l) = 0 is a
+ * cubic in l; one fundamental matrix per real root (ascending l), unit Frobenius norm.  Returns their number (<= 3). */
+int oracle_sevenpt(const double* x1, const double* y1, const double* x2, const double* y2, double* Fout)
+{
+    double N[2][9], A[9], a[3][3], b[3][3];
+    if (!nullspace_7x9(x1, y1, x2, y2, N)) return 0;
+    for (int i = 0; i < 9; ++i) A[i] = N[0][i] - N[1][i];        /* F(l) = l A + B, B = N1 */
+    for (int j = 0; j < 3; ++j) for (int i = 0; i < 3; ++i) { a[j][i] = A[3 * i + j]; b[j][i] = N[1][3 * i + j]; }   /* columns */
+    double p[4], roots[10];
+    p[3] = det3c(a[0], a[1], a[2]);
+    p[2] = det3c(b[0], a[1], a[2]) + det3c(a[0], b[1], a[2]) + det3c(a[0], a[1], b[2]);
+    p[1] = det3c(a[0], b[1], b[2]) + det3c(b[0], a[1], b[2]) + det3c(b[0], b[1], a[2]);
+    p[0] = det3c(b[0], b[1], b[2]);
+    int nr = real_roots_sturm(p, 3, roots);
+    int n = 0;
+    for (int k = 0; k < nr && n < 3; ++k) {
+        double F[9], nn = 0;
+        for (int i = 0; i < 9; ++i) { F[i] = roots[k] * A[i] + N[1][i]; nn += F[i] * F[i]; }
+        if (!(nn > 0) || !isfinite(nn)) continue;
+        nn = 1.0 / sqrt(nn);
+        for (int i = 0; i < 9; ++i) Fout[9 * n + i] = F[i] * nn;
+        ++n;
+    }
+    return n;
+}
+
+/* OpencvVerifierBase.verify in fundamental-matrix mode with explicit samples.
+ *   samples (H,7) int32.  Outputs: F (best model), E = K2^T F K1, mask (M), R, t,
+ *   info[0] = #inliers, info[1] = best candidate id (h*3 + root), info[2] = #candidates scored. */
+int oracle_verify_pair_F(const double* kp1, const double* kp2, const int32_t* mi1, const int32_t* mi2, int M,
+                         const double* cal1, const double* cal2, double thr_px, const int32_t* samples, int H,
+                         double* F, double* E, uint8_t* mask, double* R, double* t, int32_t* info)
+{
+    info[0] = info[1] = info[2] = 0;
+    if (M < 8) return VSTAT_TOO_FEW;                             /* NUM_MATCHES_REQ_F_MATRIX, opencv_verifier_base.py:38-40,69 */
+    float* px = (float*)malloc(sizeof(float) * 4 * (size_t)M);   /* cv2 converts the points to float32 */
+    float *fx1 = px, *fy1 = px + M, *fx2 = fy1 + M, *fy2 = fx2 + M;
+    for (int i = 0; i < M; ++i) {
+        fx1[i] = (float)kp1[2 * mi1[i]]; fy1[i] = (float)kp1[2 * mi1[i] + 1];
+        fx2[i] = (float)kp2[2 * mi2[i]]; fy2[i] = (float)kp2[2 * mi2[i] + 1];
+    }
+    const double thr2 = thr_px * thr_px;
+    int best_cnt = 6, best_id = -1, ncand = 0;                   /* cv2: goodCount > max(maxGoodCount, modelPoints - 1) */
+    for (int h = 0; h < H; ++h) {
+        double sx1[7], sy1[7], sx2[7], sy2[7], Fs[27];
+        for (int k = 0; k < 7; ++k) { int s = samples[7 * h + k]; sx1[k] = fx1[s]; sy1[k] = fy1[s]; sx2[k] = fx2[s]; sy2[k] = fy2[s]; }
+        int nf = oracle_sevenpt(sx1, sy1, sx2, sy2, Fs);
+        for (int c = 0; c < nf; ++c) {
+            int cnt = 0;
+            for (int i = 0; i < M; ++i) cnt += oracle_fm_error(Fs + 9 * c, fx1[i], fy1[i], fx2[i], fy2[i]) <= thr2;
+            ++ncand;
+            if (cnt > best_cnt) { best_cnt = cnt; best_id = h * 3 + c; memcpy(F, Fs + 9 * c, sizeof(double) * 9); }
+        }
+    }
+    info[1] = best_id; info[2] = ncand;
+    if (best_id < 0) { free(px); return VSTAT_NO_MODEL; }
+    int ninl = 0;
+    for (int i = 0; i < M; ++i) { mask[i] = oracle_fm_error(F, fx1[i], fy1[i], fx2[i], fy2[i]) <= thr2; ninl += mask[i]; }
+    info[0] = ninl;
+    /* E = K2^T F K1 (utils/verification.py:110), K = [f 0 u0; 0 f v0; 0 0 1] */
+    {
+        const double K1[9] = {cal1[0], 0, cal1[3], 0, cal1[0], cal1[4], 0, 0, 1};
+        const double K2t[9] = {cal2[0], 0, 0, 0, cal2[0], 0, cal2[3], cal2[4], 1};
+        double T[9];
+        mat3_mul(K2t, F, T);
+        mat3_mul(T, K1, E);
+    }
+    double* ix1 = (double*)malloc(sizeof(double) * 4 * (size_t)ninl);
+    double *iy1 = ix1 + ninl, *ix2 = iy1 + ninl, *iy2 = ix2 + ninl;
+    int k = 0;
+    for (int i = 0; i < M; ++i) if (mask[i]) {
+        oracle_calibrate(kp1[2 * mi1[i]], kp1[2 * mi1[i] + 1], cal1[0], cal1[1], cal1[2], cal1[3], cal1[4], &ix1[k], &iy1[k]);
+        oracle_calibrate(kp2[2 * mi2[i]], kp2[2 * mi2[i] + 1], cal2[0], cal2[1], cal2[2], cal2[3], cal2[4], &ix2[k], &iy2[k]);
+        ++k;
+    }
+    int good[4];
+    oracle_recover_pose(E, ix1, iy1, ix2, iy2, ninl, R, t, good);
+    free(ix1); free(px);
+    return VSTAT_OK;
+}
