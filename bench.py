@@ -40,6 +40,9 @@ def parse_args():
     ap.add_argument("--kps", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--ref-pairs", type=int, default=0, help="pairs per reference step (default: 2 per host core)")
+    ap.add_argument("--verifier", default="essential", choices=["essential", "fundamental"],
+                    help="essential = Ransac(use_intrinsics_in_verification=True) (BASELINE configs); fundamental = the "
+                         "reference's F-matrix mode (ransac.py:84-111), a SURVEY 8(f) row measured with the same harness")
     return ap.parse_args()
 
 
@@ -110,11 +113,15 @@ def make_scene(args, rank: int):
     if args.kps:
         cfg["n_kps"] = args.kps
     cfg["seed"] = cfg["seed"] + 1000 * rank          # every rank its own shard of the same shape (weak scaling)
-    return synthetic.make_scene(**cfg), cfg
+    scene = synthetic.make_scene(**cfg)
+    scene.fundamental = args.verifier == "fundamental"
+    return scene, cfg
 
 
 def workload_name(args, cfg, n_pairs):
     s = f"{args.config}: synthetic {cfg['n_images']} images x {cfg['n_kps']} {cfg['kind']}-{cfg['dim']} keypoints, {n_pairs} pairs ({cfg['pairs']})"
+    if args.verifier == "fundamental":
+        s += " [verifier in fundamental-matrix mode - not the BASELINE configuration]"
     if args.images or args.kps:
         s += " [SHRUNK - not the BASELINE configuration]"
     return s
@@ -150,7 +157,8 @@ def run_reference(args):
     sample = f"{per_step} random pairs per step, one task per pair on {cores} single-threaded cv2 workers"
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": 1e3 * secs / max(args.steps, 1), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-            "data": "synthetic", "config": {"workload": workload_name(args, cfg, n_pairs), "n_hypotheses": "cv2 USAC_ACCURATE default (maxIters 1000)"},
+            "data": "synthetic", "config": {"workload": workload_name(args, cfg, n_pairs),
+                       "n_hypotheses": "cv2 FM_RANSAC (adaptive, maxIters 1e6)" if args.verifier == "fundamental" else "cv2 USAC_ACCURATE default (maxIters 1000)"},
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
     print(json.dumps(line), file=_REAL_STDOUT, flush=True)
@@ -205,6 +213,7 @@ def run_b200(args):
     prm.threshold_px, prm.n_hypotheses, prm.lo_iters, prm.seed = scene.threshold_px, scene.n_hyp, 20, 20260002
     keys = (pairs[:, 0].astype(np.uint64) << np.uint64(32)) | pairs[:, 1].astype(np.uint64)
     prm.pair_keys, prm.samples = keys.ctypes.data, None
+    prm.estimate_fundamental = 1 if args.verifier == "fundamental" else 0
 
     def upload():
         ctx.clear()
@@ -297,7 +306,9 @@ def run_b200(args):
         sm_mhz = clk.get("sm_mhz") or peaks.get("sm_max_mhz", 1965.0)
         fp32_peak = 148 * 128 * 2 * sm_mhz * 1e6 / 1e12
         sc_achieved = 34.0 * n_evals / (sc_ms * 1e-3) / 1e12 if sc_ms > 0 else 0.0
-        roofline["scoring"] = {"bound": "fp32", "kernel": "score_kernel (MSAC cost of every 5-point candidate over all correspondences, FFMA2)",
+        sc_name = ("count_kernel (inlier count of every 7-point candidate over all correspondences, fp32 test with a rigorous error band, fp64 inside the band)"
+                   if args.verifier == "fundamental" else "score_kernel (MSAC cost of every 5-point candidate over all correspondences, FFMA2)")
+        roofline["scoring"] = {"bound": "fp32", "kernel": sc_name,
                                "achieved": sc_achieved, "peak": fp32_peak, "unit": "TFLOP/s", "frac": sc_achieved / fp32_peak,
                                "peak_source": "148 SM x 128 lanes x 2 x %.0f MHz (median SM clock sampled during the timed region)" % sm_mhz,
                                "sampson_evaluations_per_step": n_evals / args.steps,

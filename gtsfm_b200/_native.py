@@ -16,7 +16,7 @@ LIB_PATH = os.path.join(_HERE, "libgtsfm_b200.so")
 # every symbol include/gtsfm_b200.h declares
 EXPORTS = (
     "gtsfm_ctx_create", "gtsfm_ctx_destroy", "gtsfm_last_error", "gtsfm_ctx_set_workspace", "gtsfm_kernel_launches",
-    "gtsfm_store_clear", "gtsfm_image_upload", "gtsfm_match_batch", "gtsfm_match_fetch", "gtsfm_ransac_samples",
+    "gtsfm_store_clear", "gtsfm_image_upload", "gtsfm_match_batch", "gtsfm_match_fetch", "gtsfm_ransac_samples", "gtsfm_ransac_samples_k",
     "gtsfm_verify_batch", "gtsfm_match_pair", "gtsfm_verify_pair", "gtsfm_debug_fetch",
     "gtsfm_profile_enable", "gtsfm_profile_get", "gtsfm_event_record", "gtsfm_event_elapsed_ms", "gtsfm_verify_stats",
     "gtsfm_host_alloc", "gtsfm_host_free", "gtsfm_match_fetch_async", "gtsfm_sync",
@@ -38,6 +38,7 @@ class VerifyParams(ctypes.Structure):
         ("seed", ctypes.c_uint64),
         ("pair_keys", ctypes.c_void_p),
         ("samples", ctypes.c_void_p),
+        ("estimate_fundamental", ctypes.c_int),
     ]
 
 
@@ -77,6 +78,8 @@ def lib() -> ctypes.CDLL:
                                             ctypes.POINTER(ctypes.c_int64)]
             L.gtsfm_match_fetch.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
             L.gtsfm_ransac_samples.argtypes = [ctypes.c_uint64, ctypes.c_uint64, ctypes.c_int, ctypes.c_int, ctypes.c_void_p]
+            L.gtsfm_ransac_samples_k.argtypes = [ctypes.c_uint64, ctypes.c_uint64, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                                 ctypes.c_void_p]
             L.gtsfm_verify_batch.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p,
                                              ctypes.POINTER(VerifyParams)] + [ctypes.c_void_p] * 6
             L.gtsfm_match_pair.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int,
@@ -298,12 +301,13 @@ class Context:
         return dict(R=R.reshape(3, 3), t=t, n_inliers=ninl.value, status=status.value, mask=mask[:M], E=E.reshape(3, 3))
 
 
-def ransac_samples(seed: int, pair_key: int, n_matches: int, n_hyp: int) -> np.ndarray:
-    """The (n_hyp, 5) sample-index set the device draws for (seed, pair_key): feed it to the CPU oracle."""
-    out = np.zeros((n_hyp, 5), np.int32)
-    rc = lib().gtsfm_ransac_samples(int(seed), int(pair_key), int(n_matches), int(n_hyp), _ptr(out))
+def ransac_samples(seed: int, pair_key: int, n_matches: int, n_hyp: int, sample_size: int = 5) -> np.ndarray:
+    """The (n_hyp, sample_size) sample-index set the device draws for (seed, pair_key): feed it to the CPU oracle.
+    sample_size 5 = essential-matrix mode, 7 = fundamental-matrix mode."""
+    out = np.zeros((n_hyp, sample_size), np.int32)
+    rc = lib().gtsfm_ransac_samples_k(int(seed), int(pair_key), int(n_matches), int(n_hyp), int(sample_size), _ptr(out))
     if rc != OK:
-        raise GtsfmB200Error(f"gtsfm_ransac_samples failed ({rc})")
+        raise GtsfmB200Error(f"gtsfm_ransac_samples_k failed ({rc})")
     return out
 
 

@@ -10,6 +10,7 @@
 
 namespace g2v {
 cudaError_t launch_verify_step(int step, const StoreView& st, const VerifyBufs& b, const VerifyDims& d, int n_pairs, int max_m, cudaStream_t s);
+cudaError_t launch_verify_step_f(int step, const StoreView& st, const VerifyBufs& b, const VerifyDims& d, int n_pairs, int max_m, cudaStream_t s);
 }  // namespace g2v
 
 using namespace g2v;
@@ -20,6 +21,14 @@ int gtsfm_ransac_samples(uint64_t seed, uint64_t pair_key, int n_matches, int n_
 {
     if (!out || n_matches < 5 || n_hyp < 0) return GTSFM_E_ARG;
     for (int h = 0; h < n_hyp; ++h) sample5(seed, pair_key, static_cast<uint32_t>(h), static_cast<uint32_t>(n_matches), out + 5 * h);
+    return GTSFM_OK;
+}
+
+int gtsfm_ransac_samples_k(uint64_t seed, uint64_t pair_key, int n_matches, int n_hyp, int sample_size, int32_t* out)
+{
+    if (sample_size == 5) return gtsfm_ransac_samples(seed, pair_key, n_matches, n_hyp, out);
+    if (sample_size != 7 || !out || n_matches < 7 || n_hyp < 0) return GTSFM_E_ARG;
+    for (int h = 0; h < n_hyp; ++h) sample_k<7>(seed, pair_key, static_cast<uint32_t>(h), static_cast<uint32_t>(n_matches), out + 7 * h);
     return GTSFM_OK;
 }
 
@@ -35,6 +44,9 @@ int gtsfm_verify_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, const ui
     cudaStream_t s = c->stream;
     const int n_img = static_cast<int>(c->images.size());
     const int H = prm->n_hypotheses;
+    const bool fmode = prm->estimate_fundamental != 0;     // Ransac(use_intrinsics_in_verification=False), ransac.py:84-111
+    const int min_m = fmode ? 8 : 6;                       // opencv_verifier_base.py:38-40,69-78
+    const int ssz = fmode ? 7 : 5;
 
     // ---- match rows: the device-resident result of the last match batch, or the caller's arrays
     std::vector<long long> off(n_pairs + 1, 0);
@@ -70,14 +82,14 @@ int gtsfm_verify_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, const ui
         v.m0 = off[p];
         v.M = static_cast<int>(off[p + 1] - off[p]);
         // opencv_verifier_base.py:69-78: fewer than 5 (then fewer than 6) correspondences -> failure tuple
-        v.status = v.M < 6 ? GTSFM_V_TOO_FEW : GTSFM_V_OK;
+        v.status = v.M < min_m ? GTSFM_V_TOO_FEW : GTSFM_V_OK;
         if (v.status == GTSFM_V_OK && (!i1.has_kps || !i2.has_kps)) return fail(c, GTSFM_E_ARG, "verification needs keypoints for every image of the pair list");
         v.row1 = i1.row0; v.row2 = i2.row0;
         std::memcpy(v.cal1, i1.cal, sizeof(v.cal1));
         std::memcpy(v.cal2, i2.cal, sizeof(v.cal2));
         const double fx = std::max(i1.cal[0], i2.cal[0]);                 // opencv_verifier_base.py:86
         const double thr = prm->threshold_px / fx;                         // ransac.py:79
-        v.thr2 = thr * thr;
+        v.thr2 = fmode ? prm->threshold_px * prm->threshold_px : thr * thr;   // F mode works in pixels (ransac.py:103-109)
         v.key = prm->pair_keys ? prm->pair_keys[p] : static_cast<unsigned long long>(p);
         max_m = std::max(max_m, v.M);
         vps[p] = v;
@@ -85,7 +97,7 @@ int gtsfm_verify_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, const ui
 
     // ---- buffers
     DevBuf* vb = c->v_bufs;
-    const size_t per_pair = static_cast<size_t>(H) * (9 * 10 * 4 + 2 + 10 * 4);
+    const size_t per_pair = static_cast<size_t>(H) * (9 * 10 * 4 + 2 + 10 * 4);   // F mode needs less (216 + 1 + 12 per hypothesis)
     int chunk = static_cast<int>(std::max<long long>(1, std::min<long long>(c->workspace_bytes / static_cast<long long>(per_pair), 32768)));
     chunk = std::min(chunk, n_pairs);
     G2V_CUDA(c, vb[0].reserve(sizeof(VPair) * n_pairs, false, s));
@@ -104,16 +116,17 @@ int gtsfm_verify_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, const ui
     G2V_CUDA(c, vb[14].reserve(4 * static_cast<size_t>(chunk), false, s));
     G2V_CUDA(c, vb[15].reserve(32 * static_cast<size_t>(chunk), false, s));
     G2V_CUDA(c, vb[16].reserve(576 * static_cast<size_t>(chunk), false, s));
+    if (fmode) G2V_CUDA(c, vb[17].reserve(16 * static_cast<size_t>(chunk), false, s));
     G2V_CUDA(c, c->h_pairs.reserve(sizeof(VPair) * n_pairs));
     std::memcpy(c->h_pairs.p, vps.data(), sizeof(VPair) * n_pairs);
     G2V_CUDA(c, cudaMemcpyAsync(vb[0].p, c->h_pairs.p, sizeof(VPair) * n_pairs, cudaMemcpyHostToDevice, s));
     if (prm->samples) {
-        const size_t nb = static_cast<size_t>(n_pairs) * H * 5 * 4;
+        const size_t nb = static_cast<size_t>(n_pairs) * H * ssz * 4;
         G2V_CUDA(c, vb[6].reserve(nb, false, s));
         G2V_CUDA(c, cudaMemcpyAsync(vb[6].p, prm->samples, nb, cudaMemcpyHostToDevice, s));
     }
     const StoreView st = c->view();
-    VerifyDims d{H, prm->lo_iters, prm->seed};
+    VerifyDims d{H, prm->lo_iters, prm->seed, prm->threshold_px};
     for (int p0 = 0; p0 < n_pairs; p0 += chunk) {
         const int np = std::min(chunk, n_pairs - p0);
         VerifyBufs b{};
@@ -121,21 +134,28 @@ int gtsfm_verify_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, const ui
         b.match = c->match_out.p;
         b.corr_d = vb[1].p; b.corr_f = vb[2].p;
         b.E32 = vb[3].as<float>(); b.vmask = vb[4].as<unsigned short>(); b.cost = vb[5].as<float>();
-        b.samples = prm->samples ? vb[6].as<int>() + static_cast<long long>(p0) * H * 5 : nullptr;
+        b.samples = prm->samples ? vb[6].as<int>() + static_cast<long long>(p0) * H * ssz : nullptr;
         b.R = vb[7].as<double>() + 9ll * p0; b.t = vb[8].as<double>() + 3ll * p0; b.E = vb[9].as<double>() + 9ll * p0;
         b.stats = vb[13].as<unsigned long long>();
         b.best_cost = vb[14].as<unsigned int>();
         b.topi = vb[15].as<int>(); b.Ek = vb[16].as<double>();
-        G2V_CUDA(c, cudaMemsetAsync(vb[14].p, 0x7f, 4 * static_cast<size_t>(np), s));   // 0x7f7f7f7f = 3.4e38f
+        if (fmode) {
+            b.Fd = vb[3].as<double>(); b.nroot = vb[4].as<unsigned char>(); b.cnt = vb[5].as<int>();
+            b.cmax = vb[17].as<float>(); b.best_cnt = vb[14].as<int>();
+            G2V_CUDA(c, cudaMemsetAsync(vb[14].p, 0, 4 * static_cast<size_t>(np), s));
+            G2V_CUDA(c, cudaMemsetAsync(vb[17].p, 0, 16 * static_cast<size_t>(np), s));
+        } else {
+            G2V_CUDA(c, cudaMemsetAsync(vb[14].p, 0x7f, 4 * static_cast<size_t>(np), s));   // 0x7f7f7f7f = 3.4e38f
+        }
         b.ninl = vb[10].as<int>() + p0; b.status = vb[11].as<int>() + p0; b.mask = vb[12].as<unsigned char>();
         int mm = 0;
         for (int p = p0; p < p0 + np; ++p) mm = std::max(mm, vps[p].M);
         for (int step = 0; step < 4; ++step) {
             c->prof_begin(P_GATHER + step);
-            G2V_CUDA(c, launch_verify_step(step, st, b, d, np, mm, s));
+            G2V_CUDA(c, fmode ? launch_verify_step_f(step, st, b, d, np, mm, s) : launch_verify_step(step, st, b, d, np, mm, s));
             c->prof_end();
         }
-        c->launches += 6;
+        c->launches += fmode ? 4 : 6;
     }
     // ---- results back to the host
     if (R) G2V_CUDA(c, cudaMemcpyAsync(R, vb[7].p, 72 * static_cast<size_t>(n_pairs), cudaMemcpyDeviceToHost, s));

@@ -11,6 +11,7 @@
 #include <cfloat>
 
 #include "store.h"
+#include "verify_block.cuh"
 #include "verify_fivept.cuh"
 #include "verify_types.h"
 
@@ -316,27 +317,7 @@ __global__ void __launch_bounds__(256) score_kernel(VerifyBufs b, VerifyDims d, 
 
 // ---------------------------------------------------------------------------------------------------------------- K6/K7
 constexpr int kTopK = 8;            // candidates re-scored in fp64 (fp32 scoring only has to rank the best few)
-constexpr int kFinThreads = 128;
-
-// deterministic block sum of NV doubles per thread: warp shuffle tree, then warps added in order by thread 0
-template <int NV> __device__ void block_sum(double* v, double (*s_red)[24], double* s_out)
-{
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-#pragma unroll
-    for (int k = 0; k < NV; ++k) {
-        double x = v[k];
-#pragma unroll
-        for (int off = 16; off > 0; off >>= 1) x += __shfl_down_sync(0xffffffffu, x, off);
-        if (lane == 0) s_red[warp][k] = x;
-    }
-    __syncthreads();
-    if (threadIdx.x < NV) {
-        double s = 0;
-        for (int w = 0; w < kFinThreads / 32; ++w) s += s_red[w][threadIdx.x];
-        s_out[threadIdx.x] = s;
-    }
-    __syncthreads();
-}
+// kFinThreads, block_sum and recover_pose_block: verify_block.cuh
 
 __device__ inline void skew_times(const double* t, const double* R, double* E)   // E = [t]x R
 {
@@ -535,7 +516,7 @@ __global__ void __launch_bounds__(kFinThreads, 4) finalize_kernel(VerifyBufs b, 
     __shared__ double s_out[24];
     __shared__ double s_Ek[kTopK][9];
     __shared__ double s_R[9], s_t[3], s_E[9], s_dE[45];
-    __shared__ double s_R1[9], s_R2[9], s_tt[3];
+    __shared__ double s_pose[21];
     __shared__ int s_topi[kTopK];
     __shared__ int s_ctrl;
 
@@ -666,36 +647,7 @@ __global__ void __launch_bounds__(kFinThreads, 4) finalize_kernel(VerifyBufs b, 
     if (n_in == 0) { if (tid == 0) b.status[p] = 2; return; }
 
     // ---- (f) pose recovery (cv2.recoverPose): 4 candidates, cheirality vote over the inliers
-    if (tid == 0) vm::decompose_essential(E, s_R1, s_R2, s_tt);
-    __syncthreads();
-    {
-        double good[4] = {0, 0, 0, 0};
-        for (int i = tid; i < vp.M; i += kFinThreads) {
-            const double4 c = static_cast<const double4*>(b.corr_d)[vp.m0 + i];
-            if (!(vm::sampson_sq(E, c.x, c.y, c.z, c.w) < vp.thr2)) continue;
-#pragma unroll 1
-            for (int cand = 0; cand < 4; ++cand) {
-                const double* Rc = (cand & 1) ? s_R2 : s_R1;
-                const double sg = (cand & 2) ? -1.0 : 1.0;
-                double P1[12];
-                for (int r = 0; r < 3; ++r) { P1[4 * r] = Rc[3 * r]; P1[4 * r + 1] = Rc[3 * r + 1]; P1[4 * r + 2] = Rc[3 * r + 2]; P1[4 * r + 3] = sg * s_tt[r]; }
-                good[cand] += vm::cheirality_ok(P1, c.x, c.y, c.z, c.w) ? 1.0 : 0.0;
-            }
-        }
-        block_sum<4>(good, s_red, s_out);
-    }
-    if (tid == 0) {
-        const double g0 = s_out[0], g1 = s_out[1], g2 = s_out[2], g3 = s_out[3];
-        int best;
-        if (g0 >= g1 && g0 >= g2 && g0 >= g3) best = 0;
-        else if (g1 >= g0 && g1 >= g2 && g1 >= g3) best = 1;
-        else if (g2 >= g0 && g2 >= g1 && g2 >= g3) best = 2;
-        else best = 3;
-        const double* Rb = (best & 1) ? s_R2 : s_R1;
-        const double sg = (best & 2) ? -1.0 : 1.0;
-        for (int i = 0; i < 9; ++i) b.R[p * 9 + i] = Rb[i];
-        for (int i = 0; i < 3; ++i) b.t[p * 3 + i] = sg * s_tt[i];
-    }
+    recover_pose_block(b, vp, p, E, s_pose, s_red, s_out);
 }
 
 // ---------------------------------------------------------------------------------------------------------------- launch

@@ -31,12 +31,19 @@ struct VerifyBufs {
     int* topi;                 // [P][8] (this chunk) candidate ids (h * 10 + root) of the lowest fp32 costs, INT_MAX when absent
     double* Ek;                // [P][8][9] (this chunk) their essential matrices re-solved in fp64 (NaN when absent)
     unsigned int* best_cost;   // [P] (this chunk) bit pattern of the lowest complete fp32 MSAC cost seen so far
+    // ---- fundamental-matrix mode (verify_fmat.cu); corr_f then holds the float32 PIXEL coordinates cv2 works on
+    double* Fd;                // [P][H][3][9] fundamental matrices of the 7-point solves, slot r = r-th real root
+    unsigned char* nroot;      // [P][H] number of matrices of the hypothesis (0..3)
+    int* cnt;                  // [P][H][3] inlier count of every candidate, -1 when it left the race early
+    float* cmax;               // [P][4] max |x1|, |y1|, |x2|, |y2| over the pair's correspondences (error bound of the fp32 test)
+    int* best_cnt;             // [P] highest complete inlier count seen so far
 };
 
 struct VerifyDims {
     int H;                   // hypotheses per pair
     int lo_iters;
     unsigned long long seed;
+    double thr_px;           // fundamental-matrix mode: threshold in pixels (ransac.py:103-109)
 };
 
 #if defined(__CUDACC__)
@@ -54,14 +61,16 @@ G2V_HD inline uint64_t splitmix64(uint64_t x)
     return z ^ (z >> 31);
 }
 
-// Hypothesis h of pair `key`: five distinct match rows in [0, M), M >= 5.  Pure integer arithmetic, so the host copy
-// (gtsfm_ransac_samples) and the device copy agree bit for bit.
-G2V_HD inline void sample5(uint64_t seed, uint64_t key, uint32_t h, uint32_t M, int* out)
+// Hypothesis h of pair `key`: K distinct match rows in [0, M), M >= K (5 for the essential-matrix mode, 7 for the
+// fundamental-matrix mode).  Pure integer arithmetic, so the host copy (gtsfm_ransac_samples / _k) and the device copy
+// agree bit for bit.
+template <int K>
+G2V_HD inline void sample_k(uint64_t seed, uint64_t key, uint32_t h, uint32_t M, int* out)
 {
     const uint64_t state = splitmix64(splitmix64(seed) ^ splitmix64(key * 0xD1342543DE82EF95ull + h));
     int k = 0;
     uint64_t ctr = 0;
-    while (k < 5) {
+    while (k < K) {
         const uint64_t r = splitmix64(state + ctr++);
         const int idx = static_cast<int>(((r >> 32) * static_cast<uint64_t>(M)) >> 32);
         bool dup = false;
@@ -69,5 +78,6 @@ G2V_HD inline void sample5(uint64_t seed, uint64_t key, uint32_t h, uint32_t M, 
         if (!dup) out[k++] = idx;
     }
 }
+G2V_HD inline void sample5(uint64_t seed, uint64_t key, uint32_t h, uint32_t M, int* out) { sample_k<5>(seed, key, h, M, out); }
 
 }  // namespace g2v

@@ -1,8 +1,11 @@
-"""B200 Ransac verifier (essential-matrix mode): drop-in for the reference's gtsfm/frontend/verifier/ransac.py:25-111
-on top of OpencvVerifierBase.verify (opencv_verifier_base.py:45-109): same constructor kwargs, gates, outputs.
+"""B200 Ransac verifier: drop-in for the reference's gtsfm/frontend/verifier/ransac.py:25-111 on top of
+OpencvVerifierBase.verify (opencv_verifier_base.py:45-109): same constructor kwargs, gates, outputs.
 
-The whole estimate -- normalisation, 5-point hypotheses, Sampson/MSAC scoring, local optimisation, inlier mask and
-cv2.recoverPose-style pose recovery -- runs in libgtsfm_b200.so.  Hypothesis sample sets come from a counter-based
+use_intrinsics_in_verification=True: essential matrix (ransac.py:52-82) -- normalisation, 5-point hypotheses,
+Sampson/MSAC scoring, local optimisation, inlier mask and cv2.recoverPose-style pose recovery.
+use_intrinsics_in_verification=False: fundamental matrix (ransac.py:84-111) -- 7-point hypotheses on float32 pixel
+coordinates, cv2's FM_RANSAC error / inlier rule / model choice, E = K2^T F K1, the same pose recovery.
+Both run entirely in libgtsfm_b200.so.  Hypothesis sample sets come from a counter-based
 sampler (seed, pair key), exported by gtsfm_b200.ransac_samples so a CPU oracle can consume the identical set.
 """
 from typing import List, Optional, Sequence, Tuple
@@ -34,19 +37,16 @@ class Ransac(VerifierBase):
         p.seed = self._seed
         p.pair_keys = None if pair_keys is None else pair_keys.ctypes.data
         p.samples = None
+        p.estimate_fundamental = 0 if self._use_intrinsics_in_verification else 1
         return p
-
-    def _require_e_mode(self):
-        if not self._use_intrinsics_in_verification:
-            # the fundamental-matrix mode (ransac.py:84-111) is a "next" row; never fall back
-            raise NotImplementedError("Ransac(use_intrinsics_in_verification=False) is not implemented in the B200 verifier")
 
     def verify(self, keypoints_i1: Keypoints, keypoints_i2: Keypoints, match_indices: np.ndarray,
                camera_intrinsics_i1: Cal3Bundler, camera_intrinsics_i2: Cal3Bundler
                ) -> Tuple[Optional[Rot3], Optional[Unit3], np.ndarray, float]:
-        self._require_e_mode()
         match_indices = np.asarray(match_indices)
-        if match_indices.ndim != 2 or match_indices.shape[0] < 6:                  # opencv_verifier_base.py:69-78
+        # opencv_verifier_base.py:69-78: fewer than 5 (E) / 8 (F) matches, then fewer than 6 in the E mode
+        min_matches = 6 if self._use_intrinsics_in_verification else self._min_matches
+        if match_indices.ndim != 2 or match_indices.shape[0] < min_matches:
             return self._failure_result
         ctx = _native.default_context(self._device)
         out = ctx.verify_pair(keypoints_i1.coordinates, keypoints_i2.coordinates, match_indices.astype(np.uint32),
@@ -64,7 +64,6 @@ class Ransac(VerifierBase):
     def verify_batch(self, keypoints: Sequence[Keypoints], intrinsics: Sequence[Cal3Bundler], pairs: np.ndarray,
                      match_indices: Sequence[np.ndarray]) -> List[Tuple[Optional[Rot3], Optional[Unit3], np.ndarray, float]]:
         """All pairs in one device batch (replaces one Dask task per pair, two_view_estimator.py:569-584)."""
-        self._require_e_mode()
         pairs = np.ascontiguousarray(pairs, np.int32).reshape(-1, 2)
         ctx = _native.default_context(self._device)
         ctx.clear()

@@ -42,7 +42,7 @@ enum {
 /* per-pair verifier status (matches the oracle's VSTAT_* codes) */
 enum {
     GTSFM_V_OK = 0,
-    GTSFM_V_TOO_FEW = 1,     /* fewer than 6 putative matches -> failure tuple (opencv_verifier_base.py:69-78) */
+    GTSFM_V_TOO_FEW = 1,     /* fewer than 6 (F mode: 8) putative matches -> failure tuple (opencv_verifier_base.py:69-78) */
     GTSFM_V_NO_MODEL = 2     /* no essential matrix / no inliers */
 };
 
@@ -87,6 +87,8 @@ int gtsfm_match_fetch(gtsfm_ctx* ctx, uint32_t* out);
 /* Hypothesis h of pair-key k draws 5 distinct match rows in [0, M): the counter-based sampler used on the device,
  * exported so that a CPU oracle can consume the identical (H, 5) index set.  out: (n_hyp, 5) int32. */
 int gtsfm_ransac_samples(uint64_t seed, uint64_t pair_key, int n_matches, int n_hyp, int32_t* out);
+/* Same sampler with sample_size 5 or 7 (fundamental-matrix mode): out is (n_hyp, sample_size) int32. */
+int gtsfm_ransac_samples_k(uint64_t seed, uint64_t pair_key, int n_matches, int n_hyp, int sample_size, int32_t* out);
 
 typedef struct gtsfm_verify_params {
     double threshold_px;    /* Ransac(estimation_threshold_px) */
@@ -94,7 +96,14 @@ typedef struct gtsfm_verify_params {
     int lo_iters;           /* Levenberg-Marquardt local-optimisation iterations on the best model (0 = off) */
     uint64_t seed;          /* sampler seed; pair key = index of the pair in the call unless pair_keys is given */
     const uint64_t* pair_keys;   /* optional (P) sampler keys */
-    const int32_t* samples;      /* optional explicit samples (P, n_hypotheses, 5) int32, overrides the sampler */
+    const int32_t* samples;      /* optional explicit samples (P, n_hypotheses, 5) int32 -- (P, n_hypotheses, 7) in the
+                                    fundamental-matrix mode -- overrides the sampler */
+    int estimate_fundamental;    /* 0: Ransac(use_intrinsics_in_verification=True), essential matrix from 5 points
+                                    (ransac.py:52-82).  1: use_intrinsics_in_verification=False, Ransac.estimate_F =
+                                    cv2.findFundamentalMat(FM_RANSAC) on pixel coordinates (ransac.py:84-111): 7-point
+                                    samples, inlier <=> max squared epipolar-line distance <= threshold_px^2, the model with
+                                    the most inliers, fewer than 8 matches -> GTSFM_V_TOO_FEW, E = K2^T F K1
+                                    (utils/verification.py:97-110), then the same pose recovery.  lo_iters is ignored. */
 } gtsfm_verify_params;
 
 /* Verify the matches produced by the last gtsfm_match_batch (same pairs, same order; nothing is copied back to the
@@ -102,7 +111,8 @@ typedef struct gtsfm_verify_params {
  *   match_idx (total, 2) uint32, match_offsets (P + 1) int64 row offsets.
  * Outputs (any may be NULL): R (P, 9) row-major i2Ri1, t (P, 3) unit i2Ui1, n_inliers (P), status (P) GTSFM_V_*,
  * inlier_mask (total) uint8 aligned with the match rows (v_corr_idxs = match rows with mask 1,
- * inlier_ratio = n_inliers / M, opencv_verifier_base.py:98-101), E (P, 9) the final essential matrix. */
+ * inlier_ratio = n_inliers / M, opencv_verifier_base.py:98-101), E (P, 9) the final essential matrix (K2^T F K1 in the
+ * fundamental-matrix mode). */
 int gtsfm_verify_batch(gtsfm_ctx* ctx, const int32_t* pairs, int n_pairs, const uint32_t* match_idx,
                        const int64_t* match_offsets, const gtsfm_verify_params* params, double* R, double* t,
                        int32_t* n_inliers, int32_t* status, uint8_t* inlier_mask, double* E);

@@ -56,6 +56,28 @@ def _normalize(kp: np.ndarray, cal) -> np.ndarray:
     return (np.asarray(kp, np.float64) - [u0, v0]) / f
 
 
+def verify_pair_F(kp1: np.ndarray, kp2: np.ndarray, match_indices: np.ndarray, cal1, cal2, thr_px: float):
+    """Ransac(use_intrinsics_in_verification=False): ransac.py:84-111 + opencv_verifier_base.py:90-108."""
+    import cv2
+    fail = (None, None, np.array([], dtype=np.uint64), 0.0)
+    if match_indices.ndim != 2 or match_indices.shape[0] < 8:
+        return fail
+    F, mask = cv2.findFundamentalMat(np.asarray(kp1, np.float64)[match_indices[:, 0]], np.asarray(kp2, np.float64)[match_indices[:, 1]],
+                                     method=cv2.FM_RANSAC, ransacReprojThreshold=thr_px, confidence=0.999999, maxIters=1000000)
+    if F is None or mask is None:
+        return fail
+    K1 = np.array([[cal1[0], 0, cal1[3]], [0, cal1[0], cal1[4]], [0, 0, 1.0]])
+    K2 = np.array([[cal2[0], 0, cal2[3]], [0, cal2[0], cal2[4]], [0, 0, 1.0]])
+    E = K2.T @ F @ K1                                                          # utils/verification.py:110
+    inl = np.flatnonzero(mask.ravel() == 1)
+    v = match_indices[inl]
+    if len(inl) == 0:
+        return fail
+    uv1, uv2 = _normalize(kp1, cal1), _normalize(kp2, cal2)
+    _, R, t, _ = cv2.recoverPose(E, uv1[v[:, 0]], uv2[v[:, 1]])
+    return R, t.ravel(), v, float(mask.mean())
+
+
 def verify_pair(kp1: np.ndarray, kp2: np.ndarray, match_indices: np.ndarray, cal1, cal2, thr_px: float):
     """Returns (R, t, v_corr_idxs, inlier_ratio) or (None, None, empty, 0.0)."""
     import cv2
@@ -94,7 +116,8 @@ def _task(p: int):
     m = match_pair(s.descriptors[i], s.descriptors[j], s.ratio)
     if m.size == 0:
         return 0, 0
-    R, t, v, ratio = verify_pair(s.keypoints[i], s.keypoints[j], m, s.cal, s.cal, s.threshold_px)
+    fn = verify_pair_F if getattr(s, "fundamental", False) else verify_pair
+    R, t, v, ratio = fn(s.keypoints[i], s.keypoints[j], m, s.cal, s.cal, s.threshold_px)
     return len(m), len(v)
 
 

@@ -287,3 +287,106 @@ def test_full_size_properties_c2_pair(ctx):
     assert {(int(a), int(b)) for a, b in m01} == {(int(b), int(a)) for a, b in m10}
     # every ratio-test match is also a mutual nearest neighbour
     assert {(int(a), int(b)) for a, b in m} <= {(int(a), int(b)) for a, b in m01}
+
+
+# ------------------------------------------------------------------------------------------ fundamental-matrix mode
+def params_f(thr, H, seed=7, samples=None, keys=None):
+    p = params(thr, H, lo=0, seed=seed, samples=samples, keys=keys)
+    p.estimate_fundamental = 1
+    return p
+
+
+def check_against_oracle_F(got, kp1, kp2, mi, cal1, cal2, thr, samples):
+    """Ransac(use_intrinsics_in_verification=False): the inlier rule is cv2's float32 error <= thr^2 on integer-counted
+    inliers, so the bar is exact equality of the masks and of the winning model (E to 1e-9 relative); R, t within 0.1 deg."""
+    from oracle import oracle as O
+    ref = O.verify_pair_F(kp1, kp2, mi, cal1, cal2, thr, samples)
+    assert got["status"] == ref["status"]
+    if ref["status"] != 0:
+        return ref
+    np.testing.assert_array_equal(got["mask"], ref["mask"])
+    assert int(got["n_inliers"]) == ref["ninl"]
+    scale = np.abs(ref["E"]).max()
+    assert np.abs(got["E"] - ref["E"]).max() < 1e-9 * scale
+    assert rot_angle_deg(got["R"], ref["R"]) < ANGLE_TOL_DEG
+    assert dir_angle_deg(got["t"], ref["t"]) < ANGLE_TOL_DEG
+    return ref
+
+
+@pytest.mark.parametrize("n,out_frac,H", [(500, 0.4, 256), (3000, 0.5, 512), (64, 0.2, 128), (8, 0.0, 32), (5000, 0.3, 300)])
+def test_fundamental_mode_vs_oracle_same_samples(ctx, n, out_frac, H):
+    import gtsfm_b200
+    rng = np.random.default_rng(1000 + n)
+    kp1, kp2, R, t, cal = make_pixel_scene(rng, n, out_frac=out_frac)
+    mi = np.c_[np.arange(n), np.arange(n)].astype(np.uint32)
+    samples = gtsfm_b200.ransac_samples(7, 0, n, H, 7)
+    assert samples.shape == (H, 7) and all(len(set(r)) == 7 for r in samples.tolist())
+    g1 = ctx.verify_pair(kp1, kp2, mi, cal, cal, params_f(4.0, H, samples=samples))
+    g2 = ctx.verify_pair(kp1, kp2, mi, cal, cal, params_f(4.0, H))
+    np.testing.assert_array_equal(g1["mask"], g2["mask"])
+    np.testing.assert_array_equal(g1["R"], g2["R"])
+    ref = check_against_oracle_F(g1, kp1, kp2, mi, cal, cal, 4.0, samples)
+    if n >= 500:
+        assert ref["status"] == 0 and rot_angle_deg(g1["R"], R) < 3.0
+
+
+def test_fundamental_mode_golden_fixture(ctx):
+    """tests/golden/fmat_synth1500.npz (recorded output of the unmodified reference Ransac(False, 4).verify and of cv2,
+    oracle/gen_golden.py): oracle parity on the same samples, inlier-set IoU and pose agreement with the reference."""
+    import gtsfm_b200
+    g = np.load(os.path.join(GOLDEN, "fmat_synth1500.npz"))
+    kp1, kp2, mi, cal = g["kp1"].astype(np.float64), g["kp2"].astype(np.float64), g["mi"].astype(np.uint32), tuple(g["cal"])
+    M = mi.shape[0]
+    samples = gtsfm_b200.ransac_samples(11, 0, M, 1024, 7)
+    got = ctx.verify_pair(kp1, kp2, mi, cal, cal, params_f(4.0, 1024, seed=11))
+    check_against_oracle_F(got, kp1, kp2, mi, cal, cal, 4.0, samples)
+    mine = set(map(tuple, mi[got["mask"] == 1]))
+    ref = set(map(tuple, g["ref_idx"]))
+    assert len(mine & ref) / len(mine | ref) > 0.95
+    # no refit after the best minimal model (as cv2 FM_RANSAC): the translation direction is only good to a few degrees
+    assert rot_angle_deg(got["R"], g["R_gt"]) < 1.0 and dir_angle_deg(got["t"], g["t_gt"]) < 5.0
+
+
+def test_fundamental_mode_gates_and_batch(ctx):
+    """< 8 matches -> TOO_FEW (opencv_verifier_base.py:38-40,69); ragged batch over several chunks equals the oracle."""
+    import gtsfm_b200
+    rng = np.random.default_rng(6)
+    sizes = [300, 7, 1200, 40, 0, 9000, 8]
+    scenes = [make_pixel_scene(rng, max(n, 1)) for n in sizes]
+    ctx.clear()
+    for k, (kp1, kp2, _, _, cal) in enumerate(scenes):
+        ctx.upload_image(2 * k, None, kp1, cal)
+        ctx.upload_image(2 * k + 1, None, kp2, cal)
+    pairs = np.array([(2 * k, 2 * k + 1) for k in range(len(sizes))], np.int32)
+    mi = np.concatenate([np.c_[np.arange(n), np.arange(n)] for n in sizes]).astype(np.uint32)
+    off = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int64)
+    keys = np.arange(200, 200 + len(sizes), dtype=np.uint64)
+    ctx.set_workspace(64 << 20)
+    out = ctx.verify_batch(pairs, params_f(3.0, 200, seed=9, keys=keys), mi, off)
+    ctx.set_workspace(4 << 30)
+    for k, n in enumerate(sizes):
+        kp1, kp2, _, _, cal = scenes[k]
+        got = dict(status=out["status"][k], mask=out["mask"][off[k]:off[k + 1]], R=out["R"][k], t=out["t"][k],
+                   n_inliers=out["n_inliers"][k], E=out["E"][k])
+        if n < 8:
+            assert got["status"] == 1 and not got["mask"].any()
+            continue
+        samples = gtsfm_b200.ransac_samples(9, int(keys[k]), n, 200, 7)
+        check_against_oracle_F(got, kp1, kp2, mi[off[k]:off[k + 1]], cal, cal, 3.0, samples)
+    cand, hyps, evals, executed = ctx.verify_stats(reset=True)
+    assert hyps > 0 and 0 < executed <= evals and hyps <= cand <= 3 * hyps
+
+
+def test_fundamental_mode_plugin(ctx):
+    """Ransac(use_intrinsics_in_verification=False).verify through the plugin class (configs/verifier/ransac_8pt.yaml)."""
+    from gtsfm_b200.common.types import Cal3Bundler, Keypoints
+    from gtsfm_b200.frontend.verifier.ransac import Ransac
+    rng = np.random.default_rng(12)
+    n = 1500
+    kp1, kp2, R, t, cal = make_pixel_scene(rng, n, out_frac=0.3)
+    mi = np.c_[np.arange(n), np.arange(n)].astype(np.uint32)
+    v = Ransac(use_intrinsics_in_verification=False, estimation_threshold_px=2.0, num_hypotheses=512, seed=4)
+    c = Cal3Bundler(*cal)
+    i2Ri1, i2Ui1, v_corr, ratio = v.verify(Keypoints(kp1), Keypoints(kp2), mi, c, c)
+    assert i2Ri1 is not None and v_corr.dtype == mi.dtype and 0.5 < ratio <= 0.75
+    assert rot_angle_deg(i2Ri1.matrix(), R) < 2.0

@@ -104,8 +104,12 @@ def test_verifier_gates_and_failure_tuple():
     assert R is None and t is None and idx.size == 0 and ratio == 0.0
     R, t, idx, ratio = v.verify(kp, kp, np.array([]), cal, cal)
     assert R is None and idx.size == 0
-    with pytest.raises(NotImplementedError):                                         # F-matrix mode is a "next" row
-        Ransac(use_intrinsics_in_verification=False, estimation_threshold_px=4).verify(kp, kp, few, cal, cal)
+    # fundamental-matrix mode: fewer than 8 matches -> failure tuple (opencv_verifier_base.py:38-40,69), no GPU needed
+    vf = Ransac(use_intrinsics_in_verification=False, estimation_threshold_px=4)
+    seven = np.stack([np.arange(7), np.arange(7)], 1).astype(np.uint32)
+    R, t, idx, ratio = vf.verify(kp, kp, seven, cal, cal)
+    assert R is None and t is None and idx.size == 0 and ratio == 0.0
+    assert vf._params().estimate_fundamental == 1 and v._params().estimate_fundamental == 0
 
 
 def test_plugins_are_picklable_like_the_reference_requires():
