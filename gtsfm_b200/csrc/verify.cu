@@ -116,7 +116,10 @@ int gtsfm_verify_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, const ui
     G2V_CUDA(c, vb[14].reserve(4 * static_cast<size_t>(chunk), false, s));
     G2V_CUDA(c, vb[15].reserve(32 * static_cast<size_t>(chunk), false, s));
     G2V_CUDA(c, vb[16].reserve(576 * static_cast<size_t>(chunk), false, s));
-    if (fmode) G2V_CUDA(c, vb[17].reserve(16 * static_cast<size_t>(chunk), false, s));
+    if (fmode) {
+        G2V_CUDA(c, vb[17].reserve(16 * static_cast<size_t>(chunk), false, s));
+        G2V_CUDA(c, vb[18].reserve(static_cast<size_t>(chunk) * H * 144, false, s));
+    }
     G2V_CUDA(c, c->h_pairs.reserve(sizeof(VPair) * n_pairs));
     std::memcpy(c->h_pairs.p, vps.data(), sizeof(VPair) * n_pairs);
     G2V_CUDA(c, cudaMemcpyAsync(vb[0].p, c->h_pairs.p, sizeof(VPair) * n_pairs, cudaMemcpyHostToDevice, s));
@@ -141,7 +144,7 @@ int gtsfm_verify_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, const ui
         b.topi = vb[15].as<int>(); b.Ek = vb[16].as<double>();
         if (fmode) {
             b.Fd = vb[3].as<double>(); b.nroot = vb[4].as<unsigned char>(); b.cnt = vb[5].as<int>();
-            b.cmax = vb[17].as<float>(); b.best_cnt = vb[14].as<int>();
+            b.cmax = vb[17].as<float>(); b.best_cnt = vb[14].as<int>(); b.Ff = vb[18].as<float>();
             G2V_CUDA(c, cudaMemsetAsync(vb[14].p, 0, 4 * static_cast<size_t>(np), s));
             G2V_CUDA(c, cudaMemsetAsync(vb[17].p, 0, 16 * static_cast<size_t>(np), s));
         } else {

@@ -252,6 +252,31 @@ __global__ void __launch_bounds__(kF7Threads) solve7_kernel(VerifyBufs b, Verify
             x1[k] = c.x; y1[k] = c.y; x2[k] = c.z; y2[k] = c.w;
         }
         n = sevenpt_solve(x1, y1, x2, y2, Scr7{s_a + threadIdx.x}, b.Fd + g * (9 * kFMaxCand));
+        // fp32 copy of every matrix + the rounding-error band of its fp32 inlier test (count_kernel), u = 2^-24:
+        // |delta d| <= 6 u S, |delta n| <= 3.2 u max(A1 + B1, A2 + B2); thr * 1.2e-19 covers an argument of the approximate
+        // square root flushed to zero (< 2^-126).  S bounds every fp32 intermediate: when it is not far below the fp32
+        // overflow threshold of a square the band is infinite and the candidate is counted entirely in double.
+        const double X1 = b.cmax[4 * p], Y1 = b.cmax[4 * p + 1], X2 = b.cmax[4 * p + 2], Y2 = b.cmax[4 * p + 3];
+        for (int c = 0; c < n; ++c) {
+            const double* F = b.Fd + (g * kFMaxCand + c) * 9;
+            const double A1 = fabs(F[0]) * X1 + fabs(F[1]) * Y1 + fabs(F[2]);
+            const double B1 = fabs(F[3]) * X1 + fabs(F[4]) * Y1 + fabs(F[5]);
+            const double C1 = fabs(F[6]) * X1 + fabs(F[7]) * Y1 + fabs(F[8]);
+            const double A2 = fabs(F[0]) * X2 + fabs(F[3]) * Y2 + fabs(F[6]);
+            const double B2 = fabs(F[1]) * X2 + fabs(F[4]) * Y2 + fabs(F[7]);
+            const double S = X2 * A1 + Y2 * B1 + C1;
+            const double u = 5.9604644775390625e-8;
+            const double kb = (6.0 * u * S + d.thr_px * 3.2 * u * fmax(A1 + B1, A2 + B2)) * 1.01 + d.thr_px * 1.2e-19 + 1e-37;
+            float Kb = __double2float_ru(kb);
+            if (!(S < 1e15) || !(fmax(A1 + B1, A2 + B2) < 1e15) || !(Kb <= FLT_MAX)) Kb = __int_as_float(0x7f800000);
+            // half width of an interval [c - Wh, c + Wh], c = thr_lo sn - K + Wh, that contains the band
+            // [thr_lo sn - K, thr_hi sn + K] for every sn the kernel can compute (sn <= (A1 + B1) (1 + 1e-5))
+            const float Wh = __double2float_ru(static_cast<double>(Kb) + 2.1e-6 * d.thr_px * (A1 + B1) * (1.0 + 1e-5));
+            float4* o = reinterpret_cast<float4*>(b.Ff) + (g * kFMaxCand + c) * 3;
+            o[0] = make_float4(static_cast<float>(F[0]), static_cast<float>(F[1]), static_cast<float>(F[2]), static_cast<float>(F[3]));
+            o[1] = make_float4(static_cast<float>(F[4]), static_cast<float>(F[5]), static_cast<float>(F[6]), static_cast<float>(F[7]));
+            o[2] = make_float4(static_cast<float>(F[8]), Kb, Wh, 0.f);
+        }
     }
     b.nroot[g] = static_cast<unsigned char>(n);
     if (b.stats) {
@@ -287,17 +312,83 @@ __device__ __forceinline__ float fm_error_exact(const double* F, float fx1, floa
 
 constexpr int kCntHyp = 128;                         // hypotheses per CTA (the staged points are shared by their candidates)
 constexpr int kCntMaxCand = kCntHyp * kFMaxCand;
-constexpr int kCntTile = 4096;                       // correspondences per shared-memory tile (64 KB)
+constexpr int kCntTile = 4096;                       // correspondences per shared-memory tile (64 KB; three CTAs per SM)
 constexpr int kCntCheck = 512;                       // correspondences between two early-exit checks
 
-// fp32 classification of one correspondence against one candidate.  With d = x2^T F x1, n1 = |(F x1)_{0,1}|,
-// n2 = |(F^T x2)_{0,1}| the rule "max(d^2 / n1^2, d^2 / n2^2) <= thr^2" is |d| <= thr min(n1, n2).  All fp32 rounding
-// (the conversion of F, every FMA, the squares, the square root) is covered by the candidate's constant band K
-// (count_kernel) and the 2e-6 relative slack of thr_lo / thr_hi, so "in" and "out" are certain; anything else is decided
-// by fm_error_exact.
-__global__ void __launch_bounds__(256) count_kernel(VerifyBufs b, VerifyDims d, int n_pairs)
+// packed fp32x2 arithmetic (FFMA2 / FMUL2 on sm_100a): two correspondences per lane and instruction
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pk2(float a, float b) { f32x2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b)); return r; }
+__device__ __forceinline__ void upk2(f32x2 v, float& a, float& b) { asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); }
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) { f32x2 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) { f32x2 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ float sqrt_fast(float x) { float r; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+// -1 when a <= b, else 0 (also for NaN): one FSET, so that two tests are counted by a single three-input add
+__device__ __forceinline__ int set_le(float a, float b) { int r; asm("set.le.s32.f32 %0, %1, %2;" : "=r"(r) : "f"(a), "f"(b)); return r; }
+
+struct CandF32 {
+    f32x2 p[9];          // the candidate's matrix, each entry duplicated in both halves
+    f32x2 tl, th;        // thr (1 - 2e-6) rounded down, thr (1 + 2e-6) rounded up
+    f32x2 nk, pk;        // -K, +K: the candidate's absolute rounding-error band
+    f32x2 kc;            // Wh - K: centre offset of the fast test
+    float w_in, w_band;  // -Wh (1 + 1e-6): certain inlier below; Wh (1 + 2e-6): band suspected at or below (absolute value)
+};
+
+// fp32 classification of two correspondences (the packed pair at index k of the tile) against one candidate.  With
+// d = x2^T F x1, n1 = |(F x1)_{0,1}|, n2 = |(F^T x2)_{0,1}| the rule "max(d^2 / n1^2, d^2 / n2^2) <= thr^2" is
+// |d| <= thr min(n1, n2).  All fp32 rounding (the conversion of F, every FMA, the squares, the approximate square root
+// with relative error 2^-23, its flush of subnormal arguments) is covered by the candidate's constant band K
+// (solve7_kernel) and the 2e-6 relative slack of tl / th: |d| <= lo is a certain inlier, |d| > hi a certain outlier,
+// anything in between is decided by fm_error_exact.
+__device__ __forceinline__ void classify2(const CandF32& c, const float4* sA, const float4* sB, int k,
+                                          float& da, float& db, float& loa, float& lob, float& hia, float& hib)
 {
-    extern __shared__ float4 s_pts[];                  // [kCntTile] x1 y1 x2 y2 (float32 pixels)
+    const ulonglong2 A = *reinterpret_cast<const ulonglong2*>(sA + k);   // x1 pair, y1 pair
+    const ulonglong2 B = *reinterpret_cast<const ulonglong2*>(sB + k);   // x2 pair, y2 pair
+    const f32x2 a1 = fma2(c.p[0], A.x, fma2(c.p[1], A.y, c.p[2])), b1 = fma2(c.p[3], A.x, fma2(c.p[4], A.y, c.p[5])),
+                c1 = fma2(c.p[6], A.x, fma2(c.p[7], A.y, c.p[8]));
+    const f32x2 dd = fma2(B.x, a1, fma2(B.y, b1, c1));
+    const f32x2 a2 = fma2(c.p[0], B.x, fma2(c.p[3], B.y, c.p[6])), b2 = fma2(c.p[1], B.x, fma2(c.p[4], B.y, c.p[7]));
+    const f32x2 n1 = fma2(a1, a1, mul2(b1, b1)), n2 = fma2(a2, a2, mul2(b2, b2));
+    float n1a, n1b, n2a, n2b;
+    upk2(n1, n1a, n1b);
+    upk2(n2, n2a, n2b);
+    const f32x2 sn = pk2(sqrt_fast(fminf(n1a, n2a)), sqrt_fast(fminf(n1b, n2b)));
+    upk2(fma2(c.tl, sn, c.nk), loa, lob);
+    upk2(fma2(c.th, sn, c.pk), hia, hib);
+    upk2(dd, da, db);
+    da = fabsf(da); db = fabsf(db);
+}
+
+// Fast path of classify2: z = |d| - c with c the centre of an interval that contains the whole band.  z <= -Wh is a
+// certain inlier (|d| <= lo); |z| > Wh a certain inlier or outlier; the smallest |z| of a lane's share tells whether
+// any of its correspondences might be in the band, in which case the share is recounted with classify2.
+__device__ __forceinline__ void classify2_fast(const CandF32& c, const float4* sA, const float4* sB, int k, int& cnt, float& zmin)
+{
+    const ulonglong2 A = *reinterpret_cast<const ulonglong2*>(sA + k);   // x1 pair, y1 pair
+    const ulonglong2 B = *reinterpret_cast<const ulonglong2*>(sB + k);   // x2 pair, y2 pair
+    const f32x2 a1 = fma2(c.p[0], A.x, fma2(c.p[1], A.y, c.p[2])), b1 = fma2(c.p[3], A.x, fma2(c.p[4], A.y, c.p[5])),
+                c1 = fma2(c.p[6], A.x, fma2(c.p[7], A.y, c.p[8]));
+    const f32x2 dd = fma2(B.x, a1, fma2(B.y, b1, c1));
+    const f32x2 a2 = fma2(c.p[0], B.x, fma2(c.p[3], B.y, c.p[6])), b2 = fma2(c.p[1], B.x, fma2(c.p[4], B.y, c.p[7]));
+    const f32x2 n1 = fma2(a1, a1, mul2(b1, b1)), n2 = fma2(a2, a2, mul2(b2, b2));
+    float n1a, n1b, n2a, n2b, da, db, ca, cb;
+    upk2(n1, n1a, n1b);
+    upk2(n2, n2a, n2b);
+    const f32x2 sn = pk2(sqrt_fast(fminf(n1a, n2a)), sqrt_fast(fminf(n1b, n2b)));
+    upk2(fma2(c.tl, sn, c.kc), ca, cb);
+    upk2(dd, da, db);
+    const float za = fabsf(da) - ca, zb = fabsf(db) - cb;
+    cnt = cnt - set_le(za, c.w_in) - set_le(zb, c.w_in);
+    zmin = fminf(zmin, fminf(fabsf(za), fabsf(zb)));
+}
+
+constexpr int kCntPairs = kCntCheck / 2;             // packed pairs between two early-exit checks
+
+// Shared-memory tile: correspondences 2q and 2q + 1 are stored as A[q] = (x1a, x1b, y1a, y1b), B[q] = (x2a, x2b, y2a, y2b)
+// so that one LDS.128 yields two packed operands.
+__global__ void __launch_bounds__(256, 3) count_kernel(VerifyBufs b, VerifyDims d, int n_pairs)
+{
+    extern __shared__ float4 s_pts[];                  // [kCntTile / 2] A, then [kCntTile / 2] B
     __shared__ int s_cnt[kCntMaxCand];
     __shared__ unsigned short s_cand[kCntMaxCand];     // (local hypothesis << 2) | root
     __shared__ unsigned char s_dead[kCntMaxCand];
@@ -333,80 +424,121 @@ __global__ void __launch_bounds__(256) count_kernel(VerifyBufs b, VerifyDims d, 
     if (threadIdx.x == 0 && b.stats) atomicAdd(b.stats + 2, static_cast<unsigned long long>(n) * static_cast<unsigned long long>(vp.M));
     const double thr = d.thr_px, thr2 = thr * thr;
     const float thr_lo = __double2float_rd(thr * (1.0 - 2e-6)), thr_hi = __double2float_ru(thr * (1.0 + 2e-6));
-    const double X1 = b.cmax[4 * p], Y1 = b.cmax[4 * p + 1], X2 = b.cmax[4 * p + 2], Y2 = b.cmax[4 * p + 3];
     const double* Fbase = b.Fd + (static_cast<long long>(p) * d.H + h0) * (9 * kFMaxCand);
+    const float4* Ffbase = reinterpret_cast<const float4*>(b.Ff) + (static_cast<long long>(p) * d.H + h0) * (3 * kFMaxCand);
     const volatile int* best = reinterpret_cast<const volatile int*>(b.best_cnt + p);
+    float4* sA = s_pts;
+    float4* sB = s_pts + kCntTile / 2;
+    unsigned long long exec_w = 0;                     // correspondences this warp evaluated (lane 0)
     for (int t0 = 0; t0 < vp.M; t0 += kCntTile) {
         const int tn = min(kCntTile, vp.M - t0);
+        const int nq = tn >> 1;                        // complete pairs of correspondences
         const bool last_tile = t0 + kCntTile >= vp.M;
         __syncthreads();
-        for (int q = threadIdx.x; q < tn; q += blockDim.x) s_pts[q] = static_cast<const float4*>(b.corr_f)[vp.m0 + t0 + q];
+        for (int q = threadIdx.x; q < (tn + 1) >> 1; q += blockDim.x) {
+            const float4 ca = static_cast<const float4*>(b.corr_f)[vp.m0 + t0 + 2 * q];
+            const float4 cb = (2 * q + 1 < tn) ? static_cast<const float4*>(b.corr_f)[vp.m0 + t0 + 2 * q + 1] : ca;
+            sA[q] = make_float4(ca.x, cb.x, ca.y, cb.y);
+            sB[q] = make_float4(ca.z, cb.z, ca.w, cb.w);
+        }
         if (threadIdx.x == 0) s_next = 0;
         __syncthreads();
+        // candidates are handed out dynamically (early exits make their cost very uneven); the matrix of the next one is
+        // fetched while the current one is counted
+        auto grab = [&]() { int ci = 0; if (lane == 0) ci = atomicAdd(&s_next, 1); return __shfl_sync(0xffffffffu, ci, 0); };
+        auto fetch = [&](int ci, float4& q0, float4& q1, float4& q2) {
+            if (ci < n) {
+                const int code = s_cand[ci];
+                const float4* src = Ffbase + ((code >> 2) * kFMaxCand + (code & 3)) * 3;
+                q0 = __ldg(src); q1 = __ldg(src + 1); q2 = __ldg(src + 2);
+            }
+        };
+        int ci_next = grab();
+        float4 q0 = make_float4(0, 0, 0, 0), q1 = q0, q2 = q0;
+        fetch(ci_next, q0, q1, q2);
         for (;;) {
-            int ci = 0;
-            if (lane == 0) ci = atomicAdd(&s_next, 1);
-            ci = __shfl_sync(0xffffffffu, ci, 0);
+            const int ci = ci_next;
             if (ci >= n) break;
+            const float4 g0 = q0, g1 = q1, g2 = q2;
+            ci_next = grab();
+            fetch(ci_next, q0, q1, q2);
             if (s_dead[ci]) continue;
             const int code = s_cand[ci];
             const double* Fp = Fbase + ((code >> 2) * kFMaxCand + (code & 3)) * 9;
-            float f[9], Kb;
+            CandF32 c;
+            c.p[0] = pk2(g0.x, g0.x); c.p[1] = pk2(g0.y, g0.y); c.p[2] = pk2(g0.z, g0.z); c.p[3] = pk2(g0.w, g0.w);
+            c.p[4] = pk2(g1.x, g1.x); c.p[5] = pk2(g1.y, g1.y); c.p[6] = pk2(g1.z, g1.z); c.p[7] = pk2(g1.w, g1.w);
+            c.p[8] = pk2(g2.x, g2.x);
+            const float Kb = g2.y;
+            const bool all_exact = !(Kb <= FLT_MAX);       // fp32 could overflow on this candidate: count it in double
+            c.tl = pk2(thr_lo, thr_lo); c.th = pk2(thr_hi, thr_hi); c.nk = pk2(-Kb, -Kb); c.pk = pk2(Kb, Kb);
             {
+                const float Wh = g2.z, kc = __fsub_rn(Wh, Kb);
+                c.kc = pk2(kc, kc);
+                c.w_in = -__fmul_ru(Wh, 1.000001f);
+                c.w_band = __fmul_ru(Wh, 1.000002f);
+            }
+            // cv2's double-precision rule for the halves `bits` of the packed pair k
+            auto exact = [&](int k, unsigned bits) {
                 double Fd9[9];
 #pragma unroll
-                for (int e = 0; e < 9; ++e) { Fd9[e] = __ldg(Fp + e); f[e] = static_cast<float>(Fd9[e]); }
-                // rounding-error band of the fp32 test (u = 2^-24): |delta d| <= 6 u S, |delta n| <= 3.2 u max(A1 + B1, A2 + B2)
-                const double A1 = fabs(Fd9[0]) * X1 + fabs(Fd9[1]) * Y1 + fabs(Fd9[2]);
-                const double B1 = fabs(Fd9[3]) * X1 + fabs(Fd9[4]) * Y1 + fabs(Fd9[5]);
-                const double C1 = fabs(Fd9[6]) * X1 + fabs(Fd9[7]) * Y1 + fabs(Fd9[8]);
-                const double A2 = fabs(Fd9[0]) * X2 + fabs(Fd9[3]) * Y2 + fabs(Fd9[6]);
-                const double B2 = fabs(Fd9[1]) * X2 + fabs(Fd9[4]) * Y2 + fabs(Fd9[7]);
-                const double S = X2 * A1 + Y2 * B1 + C1;
-                const double u = 5.9604644775390625e-8;
-                const double kb = (6.0 * u * S + thr * 3.2 * u * fmax(A1 + B1, A2 + B2)) * 1.01 + 1e-37;
-                Kb = __double2float_ru(kb);
-                if (!(Kb <= FLT_MAX)) Kb = FLT_MAX;
-            }
+                for (int e = 0; e < 9; ++e) Fd9[e] = __ldg(Fp + e);
+                const float4 a4 = sA[k], b4 = sB[k];
+                int add = 0;
+                if ((bits & 1u) && fm_error_exact(Fd9, a4.x, a4.z, b4.x, b4.z) <= thr2) ++add;
+                if ((bits & 2u) && fm_error_exact(Fd9, a4.y, a4.w, b4.y, b4.w) <= thr2) ++add;
+                return add;
+            };
             const int before = s_cnt[ci];
             int mine = 0, done = 0, total_w = 0;
             bool dead = false;
-            for (int c0 = 0; c0 < tn; c0 += kCntCheck) {
-                const int c1 = min(tn, c0 + kCntCheck);
+            for (int c0 = 0; c0 < nq; c0 += kCntPairs) {
+                const int c1 = min(nq, c0 + kCntPairs);
                 const int bestv = *best;                   // issued here, consumed after the segment
-#pragma unroll 2
-                for (int k = c0 + lane; k < c1; k += 32) {
-                    const float4 c = s_pts[k];
-                    const float a1 = fmaf(f[0], c.x, fmaf(f[1], c.y, f[2])), b1 = fmaf(f[3], c.x, fmaf(f[4], c.y, f[5])),
-                                c1v = fmaf(f[6], c.x, fmaf(f[7], c.y, f[8]));
-                    const float dd = fabsf(fmaf(c.z, a1, fmaf(c.w, b1, c1v)));
-                    const float a2 = fmaf(f[0], c.z, fmaf(f[3], c.w, f[6])), b2 = fmaf(f[1], c.z, fmaf(f[4], c.w, f[7]));
-                    const float n1 = fmaf(a1, a1, b1 * b1), n2 = fmaf(a2, a2, b2 * b2);
-                    const float sn = sqrtf(fminf(n1, n2));
-                    const bool in = dd <= fmaf(thr_lo, sn, -Kb);
-                    const bool out = dd > fmaf(thr_hi, sn, Kb);
-                    if (in) ++mine;
-                    else if (!out) {                       // inside the band (or NaN): cv2's double-precision rule decides
-                        double Fd9[9];
-#pragma unroll
-                        for (int e = 0; e < 9; ++e) Fd9[e] = __ldg(Fp + e);
-                        if (fm_error_exact(Fd9, c.x, c.y, c.z, c.w) <= thr2) ++mine;
+                // certain inliers of the lane's share of the segment and its closest approach to the band; a correspondence
+                // that may be inside the band (a few per million) makes the lane recount its share, with the
+                // double-precision rule for the correspondences that are
+                int lo = 0;
+                float zmin = FLT_MAX;
+                if (!all_exact) {
+                    int k = c0 + lane;
+#pragma unroll 4
+                    for (; k < c1; k += 32) classify2_fast(c, sA, sB, k, lo, zmin);
+                }
+                if (zmin <= c.w_band || all_exact) {
+                    lo = 0;
+#pragma unroll 1
+                    for (int k = c0 + lane; k < c1; k += 32) {
+                        float da, db, loa, lob, hia, hib;
+                        unsigned bits = 3u;
+                        if (!all_exact) {
+                            classify2(c, sA, sB, k, da, db, loa, lob, hia, hib);
+                            const bool ina = da <= loa, inb = db <= lob;
+                            lo += (ina ? 1 : 0) + (inb ? 1 : 0);
+                            bits = ((ina || da > hia) ? 0u : 1u) | ((inb || db > hib) ? 0u : 2u);
+                        }
+                        if (bits) lo += exact(k, bits);
                     }
                 }
+                mine += lo;
                 done = c1;
                 // exact early exit: even if every remaining correspondence were an inlier the candidate would stay below
                 // the best complete count of the pair (equal counts are kept: the first found wins)
                 total_w = __reduce_add_sync(0xffffffffu, mine);
-                if (before + total_w + (vp.M - t0 - c1) < bestv) { dead = true; break; }
+                if (before + total_w + (vp.M - t0 - 2 * c1) < bestv) { dead = true; break; }
+            }
+            if (!dead && (tn & 1) && lane == 0) {      // odd tail: first half of the last (duplicated) pair, decided exactly
+                total_w += exact(nq, 1u);
             }
             if (lane == 0) {
                 s_cnt[ci] = before + total_w;
                 if (dead) s_dead[ci] = 1;
                 else if (last_tile) atomicMax(b.best_cnt + p, before + total_w);
-                atomicAdd(&s_exec, static_cast<unsigned long long>(done));
+                exec_w += static_cast<unsigned long long>(2 * done + (dead ? 0 : (tn & 1)));
             }
         }
     }
+    if (lane == 0) atomicAdd(&s_exec, exec_w);
     __syncthreads();
     for (int ci = threadIdx.x; ci < n; ci += blockDim.x) {
         const int code = s_cand[ci];

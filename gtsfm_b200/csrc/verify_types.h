@@ -33,6 +33,7 @@ struct VerifyBufs {
     unsigned int* best_cost;   // [P] (this chunk) bit pattern of the lowest complete fp32 MSAC cost seen so far
     // ---- fundamental-matrix mode (verify_fmat.cu); corr_f then holds the float32 PIXEL coordinates cv2 works on
     double* Fd;                // [P][H][3][9] fundamental matrices of the 7-point solves, slot r = r-th real root
+    float* Ff;                 // [P][H][3][12] fp32 copy of each matrix (9), its rounding-error band K (1), padding (2)
     unsigned char* nroot;      // [P][H] number of matrices of the hypothesis (0..3)
     int* cnt;                  // [P][H][3] inlier count of every candidate, -1 when it left the race early
     float* cmax;               // [P][4] max |x1|, |y1|, |x2|, |y2| over the pair's correspondences (error bound of the fp32 test)
