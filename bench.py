@@ -43,6 +43,8 @@ def parse_args():
     ap.add_argument("--verifier", default="essential", choices=["essential", "fundamental"],
                     help="essential = Ransac(use_intrinsics_in_verification=True) (BASELINE configs); fundamental = the "
                          "reference's F-matrix mode (ransac.py:84-111), a SURVEY 8(f) row measured with the same harness")
+    ap.add_argument("--float-screening", default="on", choices=["on", "off"],
+                    help="float descriptors, ratio test off (C4): fp16 tensor-core screening (default) or the exhaustive fp32 kernel")
     return ap.parse_args()
 
 
@@ -203,6 +205,7 @@ def run_b200(args):
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu = cpu_baseline_sample(scene, cfg)
     ctx = gtsfm_b200.Context(local)
+    ctx.set_float_screening(args.float_screening == "on")
 
     # pinned host copies of the step's inputs (the e2e leg uploads from these every step)
     desc_pin = [torch.from_numpy(d).pin_memory() for d in scene.descriptors]

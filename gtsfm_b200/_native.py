@@ -15,7 +15,7 @@ LIB_PATH = os.path.join(_HERE, "libgtsfm_b200.so")
 
 # every symbol include/gtsfm_b200.h declares
 EXPORTS = (
-    "gtsfm_ctx_create", "gtsfm_ctx_destroy", "gtsfm_last_error", "gtsfm_ctx_set_workspace", "gtsfm_kernel_launches",
+    "gtsfm_ctx_create", "gtsfm_ctx_destroy", "gtsfm_last_error", "gtsfm_ctx_set_workspace", "gtsfm_kernel_launches", "gtsfm_ctx_set_float_screening",
     "gtsfm_store_clear", "gtsfm_image_upload", "gtsfm_match_batch", "gtsfm_match_fetch", "gtsfm_ransac_samples", "gtsfm_ransac_samples_k",
     "gtsfm_verify_batch", "gtsfm_match_pair", "gtsfm_verify_pair", "gtsfm_debug_fetch",
     "gtsfm_profile_enable", "gtsfm_profile_get", "gtsfm_event_record", "gtsfm_event_elapsed_ms", "gtsfm_verify_stats",
@@ -65,6 +65,7 @@ def lib() -> ctypes.CDLL:
             L.gtsfm_ctx_destroy.argtypes = [ctypes.c_void_p]
             L.gtsfm_ctx_destroy.restype = None
             L.gtsfm_ctx_set_workspace.argtypes = [ctypes.c_void_p, ctypes.c_int64]
+            L.gtsfm_ctx_set_float_screening.argtypes = [ctypes.c_void_p, ctypes.c_int]
             L.gtsfm_store_clear.argtypes = [ctypes.c_void_p]
             L.gtsfm_host_alloc.argtypes = [ctypes.POINTER(ctypes.c_void_p), ctypes.c_int64]
             L.gtsfm_host_free.argtypes = [ctypes.c_void_p]
@@ -170,6 +171,10 @@ class Context:
         out = (ctypes.c_int64 * 4)()
         self._check(self._L.gtsfm_verify_stats(self._h, out, 1 if reset else 0))
         return int(out[0]), int(out[1]), int(out[2]), int(out[3])
+
+    def set_float_screening(self, on: bool):
+        """Float descriptors with the ratio test off: fp16 tensor-core screening (default) or the exhaustive fp32 kernel."""
+        self._check(self._L.gtsfm_ctx_set_float_screening(self._h, 1 if on else 0))
 
     def set_workspace(self, nbytes: int):
         self._check(self._L.gtsfm_ctx_set_workspace(self._h, int(nbytes)))

@@ -7,7 +7,7 @@ namespace g2v {
 
 struct PrepareArgs {
     const float* src; __nv_bfloat16* bf; uint8_t* u8; __nv_bfloat16* augq; __nv_bfloat16* augt; int* norm_i; uint8_t* valid;
-    int* img_flags; int n, n_pad, dim, kpad;
+    int* img_flags; __half* h16; __half* augq_h; __half* augt_h; float* norm_f; int n, n_pad, dim, kpad;
 };
 cudaError_t launch_prepare(const PrepareArgs& a, cudaStream_t s);
 
@@ -69,7 +69,8 @@ static EncodeTiledFn encode_tiled()
     }
     return fn;
 }
-static int make_map(gtsfm_ctx* c, CUtensorMap* m, void* base, int inner, long long rows, int box_inner, int box_rows, CUtensorMapSwizzle sw)
+static int make_map(gtsfm_ctx* c, CUtensorMap* m, void* base, int inner, long long rows, int box_inner, int box_rows, CUtensorMapSwizzle sw,
+                    CUtensorMapDataType dt = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16)
 {
     EncodeTiledFn fn = encode_tiled();
     if (!fn) return fail(c, GTSFM_E_CUDA, "cuTensorMapEncodeTiled entry point not found");
@@ -77,7 +78,7 @@ static int make_map(gtsfm_ctx* c, CUtensorMap* m, void* base, int inner, long lo
     cuuint64_t gstr[1] = {static_cast<cuuint64_t>(inner) * 2};
     cuuint32_t box[2] = {static_cast<cuuint32_t>(box_inner), static_cast<cuuint32_t>(box_rows)};
     cuuint32_t estr[2] = {1, 1};
-    CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
+    CUresult r = fn(m, dt, 2, base, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail(c, GTSFM_E_CUDA, "cuTensorMapEncodeTiled failed with code " + std::to_string(static_cast<int>(r)));
     return GTSFM_OK;
@@ -97,6 +98,10 @@ int store_reserve_rows(gtsfm_ctx* c, long long rows)
     G2V_CUDA(c, c->norm_i.reserve(static_cast<size_t>(ncap) * 4, true, s));
     G2V_CUDA(c, c->valid.reserve(static_cast<size_t>(ncap), true, s));
     G2V_CUDA(c, c->kps.reserve(static_cast<size_t>(ncap) * 16, true, s));
+    G2V_CUDA(c, c->desc_h16.reserve(static_cast<size_t>(ncap) * c->kpad * 2, true, s));
+    G2V_CUDA(c, c->augq_h.reserve(static_cast<size_t>(ncap) * kAugK * 2, true, s));
+    G2V_CUDA(c, c->augt_h.reserve(static_cast<size_t>(ncap) * kAugK * 2, true, s));
+    G2V_CUDA(c, c->norm_f.reserve(static_cast<size_t>(ncap) * 4, true, s));
     c->rows_cap = ncap;
     c->maps_valid = false;
     return GTSFM_OK;
@@ -109,6 +114,10 @@ static int ensure_maps(gtsfm_ctx* c)
     if ((r = make_map(c, &c->tm_desc, c->desc_bf16.p, c->kpad, c->rows_cap, 64, kTileQ, CU_TENSOR_MAP_SWIZZLE_128B))) return r;
     if ((r = make_map(c, &c->tm_augq, c->augq.p, kAugK, c->rows_cap, kAugK, kTileQ, CU_TENSOR_MAP_SWIZZLE_32B))) return r;
     if ((r = make_map(c, &c->tm_augt, c->augt.p, kAugK, c->rows_cap, kAugK, kTileQ, CU_TENSOR_MAP_SWIZZLE_32B))) return r;
+    const CUtensorMapDataType f16 = CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+    if ((r = make_map(c, &c->tm_desc_h, c->desc_h16.p, c->kpad, c->rows_cap, 64, kTileQ, CU_TENSOR_MAP_SWIZZLE_128B, f16))) return r;
+    if ((r = make_map(c, &c->tm_augq_h, c->augq_h.p, kAugK, c->rows_cap, kAugK, kTileQ, CU_TENSOR_MAP_SWIZZLE_32B, f16))) return r;
+    if ((r = make_map(c, &c->tm_augt_h, c->augt_h.p, kAugK, c->rows_cap, kAugK, kTileQ, CU_TENSOR_MAP_SWIZZLE_32B, f16))) return r;
     c->maps_valid = true;
     return GTSFM_OK;
 }
@@ -119,12 +128,14 @@ int store_sync_flags(gtsfm_ctx* c)
 {
     if (!c->flags_dirty) return GTSFM_OK;
     const size_t n = c->images.size();
-    std::vector<int> h(2 * n);
-    G2V_CUDA(c, cudaMemcpyAsync(h.data(), c->img_flags.p, 2 * n * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    std::vector<int> h(kImgFlagInts * n);
+    G2V_CUDA(c, cudaMemcpyAsync(h.data(), c->img_flags.p, kImgFlagInts * n * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
     G2V_CUDA(c, cudaStreamSynchronize(c->stream));
     for (size_t i = 0; i < n; ++i) {
-        c->images[i].path = (h[2 * i] & 1) ? 1 : 0;
-        c->images[i].n_valid = h[2 * i + 1];
+        c->images[i].path = (h[kImgFlagInts * i] & 1) ? 1 : 0;
+        c->images[i].f16_ok = (h[kImgFlagInts * i] & 2) ? 0 : 1;
+        c->images[i].n_valid = h[kImgFlagInts * i + 1];
+        std::memcpy(&c->images[i].max_norm2, &h[kImgFlagInts * i + 2], 4);
     }
     c->flags_dirty = false;
     return GTSFM_OK;
@@ -171,6 +182,7 @@ g2v::StoreView gtsfm_ctx::view() const
     v.desc_u8 = desc_u8.as<uint8_t>();
     v.desc_f32 = desc_f32.as<float>();
     v.norm_i = norm_i.as<int>();
+    v.norm_f = norm_f.as<float>();
     v.valid = valid.as<uint8_t>();
     v.kps = kps.as<double2>();
     v.dim = dim;
@@ -209,7 +221,7 @@ void gtsfm_ctx_destroy(gtsfm_ctx* c)
     if (!c) return;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
-    DevBuf* bufs[] = {&c->desc_bf16, &c->desc_u8, &c->desc_f32, &c->augq, &c->augt, &c->norm_i, &c->valid, &c->kps, &c->img_flags, &c->stage,
+    DevBuf* bufs[] = {&c->desc_h16, &c->augq_h, &c->augt_h, &c->norm_f, &c->desc_bf16, &c->desc_u8, &c->desc_f32, &c->augq, &c->augt, &c->norm_i, &c->valid, &c->kps, &c->img_flags, &c->stage,
                       &c->d_pairs, &c->rp_v1, &c->rp_v2, &c->rp_g, &c->colraw, &c->row_best, &c->row_d1, &c->row_d2, &c->col_best, &c->col_d1,
                       &c->col_d2, &c->flag_list, &c->n_flag, &c->keys_scratch, &c->match_slot, &c->match_count, &c->match_offsets,
                       &c->match_out, &c->d_total, &c->row_key, &c->col_key, &c->row_cnt, &c->col_cnt, &c->row_list, &c->col_list,
@@ -236,6 +248,13 @@ int gtsfm_ctx_set_workspace(gtsfm_ctx* c, int64_t bytes)
 }
 
 int64_t gtsfm_kernel_launches(const gtsfm_ctx* c) { return c ? c->launches : 0; }
+
+int gtsfm_ctx_set_float_screening(gtsfm_ctx* c, int on)
+{
+    if (!c) return GTSFM_E_ARG;
+    c->force_exact_float = on == 0;
+    return GTSFM_OK;
+}
 
 int gtsfm_profile_enable(gtsfm_ctx* c, int on)
 {
@@ -318,8 +337,8 @@ int gtsfm_image_upload(gtsfm_ctx* c, int image_id, const float* desc, int n, int
     if (c->dim == 0 && kps && n > 0) { c->dim = 1; c->kpad = 64; c->rows_cap = 0; }
     const int n_rows = ((rec.n > rec.n_kps ? rec.n : rec.n_kps) + kRowPad - 1) / kRowPad * kRowPad;
     rec.n_pad = n_rows;
-    G2V_CUDA(c, c->img_flags.reserve((c->images.size() + 1) * 2 * sizeof(int), true, c->stream));
-    G2V_CUDA(c, cudaMemsetAsync(c->img_flags.as<int>() + 2 * c->images.size(), 0, 2 * sizeof(int), c->stream));
+    G2V_CUDA(c, c->img_flags.reserve((c->images.size() + 1) * kImgFlagInts * sizeof(int), true, c->stream));
+    G2V_CUDA(c, cudaMemsetAsync(c->img_flags.as<int>() + kImgFlagInts * c->images.size(), 0, kImgFlagInts * sizeof(int), c->stream));
     if (n_rows > 0) {
         int r = store_reserve_rows(c, c->rows_used + n_rows);
         if (r) return r;
@@ -335,7 +354,11 @@ int gtsfm_image_upload(gtsfm_ctx* c, int image_id, const float* desc, int n, int
         a.augt = c->augt.as<__nv_bfloat16>() + static_cast<long long>(rec.row0) * kAugK;
         a.norm_i = c->norm_i.as<int>() + rec.row0;
         a.valid = c->valid.as<uint8_t>() + rec.row0;
-        a.img_flags = c->img_flags.as<int>() + 2 * c->images.size();
+        a.img_flags = c->img_flags.as<int>() + kImgFlagInts * c->images.size();
+        a.h16 = c->desc_h16.as<__half>() + static_cast<long long>(rec.row0) * c->kpad;
+        a.augq_h = c->augq_h.as<__half>() + static_cast<long long>(rec.row0) * kAugK;
+        a.augt_h = c->augt_h.as<__half>() + static_cast<long long>(rec.row0) * kAugK;
+        a.norm_f = c->norm_f.as<float>() + rec.row0;
         a.n = rec.n; a.n_pad = rec.n_pad; a.dim = c->dim; a.kpad = c->kpad;
         c->prof_begin(P_PREPARE);
         G2V_CUDA(c, launch_prepare(a, c->stream));

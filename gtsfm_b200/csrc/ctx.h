@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda.h>
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 
 #include <string>
@@ -47,8 +48,11 @@ struct gtsfm_ctx {
     std::vector<g2v::ImageRec> images;
     bool flags_dirty = false;
     g2v::DevBuf desc_bf16, desc_u8, desc_f32, augq, augt, norm_i, valid, kps, img_flags, stage;
+    g2v::DevBuf desc_h16, augq_h, augt_h, norm_f;     // float path: fp16 operands of the screening GEMM, float32 squared norms
     CUtensorMap tm_desc{}, tm_augq{}, tm_augt{};
+    CUtensorMap tm_desc_h{}, tm_augq_h{}, tm_augt_h{};
     bool maps_valid = false;
+    bool force_exact_float = false;     // diagnostics: float descriptors always take the exhaustive fp32 kernels
 
     // ---- matcher work buffers (one chunk of pairs) and batch outputs
     g2v::DevBuf d_pairs, rp_v1, rp_v2, rp_g, colraw, row_best, row_d1, row_d2, col_best, col_d1, col_d2, flag_list, n_flag, row_key, col_key, row_cnt, col_cnt, row_list, col_list, flag_scratch, col_cells;

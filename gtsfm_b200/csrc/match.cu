@@ -11,6 +11,10 @@ namespace g2v {
 cudaError_t launch_match_screen(const CUtensorMap& tm_desc, const CUtensorMap& tm_augq, const CUtensorMap& tm_augt,
                                 const PairDesc* pairs, int n_pairs, int n_items, float* rp_v1, float* rp_v2, uint8_t* rp_g,
                                 float* colraw, int kpad, int n_sm, cudaStream_t stream);
+cudaError_t launch_match_screen_f(const CUtensorMap& tm_desc, const CUtensorMap& tm_augq, const CUtensorMap& tm_augt,
+                                  const PairDesc* pairs, int n_pairs, int n_items, float* rp_v1, float* rp_v2, uint8_t* rp_g,
+                                  float* colraw, int kpad, int n_sm, cudaStream_t stream);
+cudaError_t launch_resolve_f(const StoreView& st, const MatchWork& w, long long total_rows, long long total_cols, cudaStream_t s);
 cudaError_t launch_resolve_int(const StoreView& st, const MatchWork& w, int which, long long total, int max_class_rows,
                                cudaStream_t s);
 cudaError_t launch_exact_scan(const StoreView& st, const MatchWork& w, int mode, int n_jobs, cudaStream_t s);
@@ -29,6 +33,7 @@ struct Chunk {
     int p0 = 0, p1 = 0;
     long long rp = 0, cr = 0, rows = 0, cols = 0;
     int items = 0, jobs = 0, max_class_rows = 0, max_hb = 0;
+    int fitems = 0;          // work items of the fp16 screening kernel (path-2 pairs)
 };
 }  // namespace g2v
 
@@ -58,6 +63,8 @@ int gtsfm_match_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, double ra
     Chunk cur;
     long long cur_bytes = 0, out_cap = 0;
     const bool screen_ok = c->kpad == 64 || c->kpad == 128;
+    // float descriptors: fp16 tensor-core screening when only the nearest neighbour is needed (ratio test off)
+    const bool screen_f_ok = !use_ratio && (c->kpad == 64 || c->kpad == 128 || c->kpad == 256) && (c->dim % 4) == 0 && !c->force_exact_float;
     for (int p = 0; p < n_pairs; ++p) {
         const int a = pairs[2 * p], b = pairs[2 * p + 1];
         if (a < 0 || b < 0 || a >= n_img || b >= n_img) return fail(c, GTSFM_E_ARG, "pair " + std::to_string(p) + " names an image that was not uploaded");
@@ -77,13 +84,17 @@ int gtsfm_match_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, double ra
         // the bucketed resolve kernels keep one lane class (nq_pad / 128 rows) in shared memory and use 13-bit half-block ids
         const bool fits = pd.nq_pad / kTileQ <= kMaxClassRows && pd.nt_pad / kHalfT < 8192;
         pd.path = (qa.path == 0 && tb.path == 0 && screen_ok && fits) ? 0 : 1;
-        const long long rp = pd.path == 0 ? static_cast<long long>(pd.nq_pad) * (pd.nt_pad / kHalfT) : 0;
-        const long long cr = pd.path == 0 ? static_cast<long long>(pd.nt_pad) * kTileQ : 0;
+        if (pd.path == 1 && !empty && qa.path == 1 && tb.path == 1 && qa.f16_ok && tb.f16_ok && screen_f_ok) pd.path = 2;
+        pd.q_maxn2 = qa.max_norm2; pd.t_maxn2 = tb.max_norm2;
+        const long long rp = pd.path != 1 ? static_cast<long long>(pd.nq_pad) * (pd.nt_pad / kHalfT) : 0;
+        const long long cr = pd.path != 1 ? static_cast<long long>(pd.nt_pad) * kTileQ : 0;
         const int items = pd.path == 0 && pd.nq > 0 ? pd.nt_pad / kBlockT : 0;
+        const int fitems = pd.path == 2 && pd.nq > 0 ? pd.nt_pad / kBlockT : 0;
         const int jobs = pd.path == 1 && pd.nq > 0 ? (pd.nq + 31) / 32 + (pd.nt + 31) / 32 : 0;
         const long long bytes = rp * 9 + cr * 4 + static_cast<long long>(pd.nq_pad) * (12 + 16 + 8 + 8 + 8) + static_cast<long long>(pd.nt_pad) * (12 + 8 + 8);
         if (cur.p1 > cur.p0 && (cur_bytes + bytes > c->workspace_bytes || cur.rows + cur.cols + pd.nq_pad + pd.nt_pad > kFlagScratchCap)) { chunks.push_back(cur); cur = Chunk{}; cur.p0 = cur.p1 = p; cur_bytes = 0; }
-        pd.rp_base = cur.rp; pd.cr_base = cur.cr; pd.out_base = cur.rows; pd.cb_base = cur.cols; pd.item0 = cur.items; pd.job0 = cur.jobs;
+        pd.rp_base = cur.rp; pd.cr_base = cur.cr; pd.out_base = cur.rows; pd.cb_base = cur.cols; pd.item0 = cur.items; pd.job0 = cur.jobs; pd.fitem0 = cur.fitems;
+        cur.fitems += fitems;
         cur.rp += rp; cur.cr += cr; cur.rows += pd.nq_pad; cur.cols += pd.nt_pad; cur.items += items; cur.jobs += jobs;
         cur.p1 = p + 1;
         if (items > 0) { cur.max_class_rows = std::max(cur.max_class_rows, pd.nq_pad / kTileQ); cur.max_hb = std::max(cur.max_hb, pd.nt_pad / kHalfT); }
@@ -164,10 +175,24 @@ int gtsfm_match_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, double ra
             c->prof_begin(P_RESOLVE_COLS);
             G2V_CUDA(c, launch_resolve_int(st, w, 1, k.cols, k.max_class_rows, s));
             c->prof_end();
+            c->launches += 9;
+        }
+        if (k.fitems > 0) {
+            c->prof_begin(P_SCREEN);
+            G2V_CUDA(c, launch_match_screen_f(c->tm_desc_h, c->tm_augq_h, c->tm_augt_h, w.pairs, w.n_pairs, k.fitems, c->rp_v1.as<float>(),
+                                              c->rp_v2.as<float>(), c->rp_g.as<uint8_t>(), c->colraw.as<float>(), c->kpad, c->n_sm, s));
+            c->prof_end();
+            c->prof_begin(P_RESOLVE_ROWS);
+            G2V_CUDA(c, launch_resolve_f(st, w, k.rows, k.cols, s));
+            c->prof_end();
+            c->launches += 3;
+        }
+        if (k.items > 0 || k.fitems > 0) {
+            // rows / columns the resolve kernels could not decide: exhaustive fp32 scan in cv2's summation order
             c->prof_begin(P_EXACT_SCAN);
             G2V_CUDA(c, launch_exact_scan(st, w, 1, w.flag_cap, s));
             c->prof_end();
-            c->launches += 10;
+            c->launches += 1;
         }
         if (k.jobs > 0) {
             c->prof_begin(P_EXACT_SCAN);

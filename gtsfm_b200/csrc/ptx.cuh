@@ -177,4 +177,10 @@ __host__ __device__ constexpr uint32_t idesc_bf16(int M, int N, bool negate_b)
            (static_cast<uint32_t>(M >> 4) << 24);
 }
 
+// Same with fp16 A/B (a_format = b_format = 0).
+__host__ __device__ constexpr uint32_t idesc_f16(int M, int N, bool negate_b)
+{
+    return (1u << 4) | ((negate_b ? 1u : 0u) << 14) | (static_cast<uint32_t>(N >> 3) << 17) | (static_cast<uint32_t>(M >> 4) << 24);
+}
+
 }  // namespace ptx

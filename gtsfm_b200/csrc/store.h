@@ -13,6 +13,7 @@ struct StoreView {
     const uint8_t* desc_u8;           // [rows][kpad]    exact integer copy for the resolve kernels (integer path)
     const float* desc_f32;            // [rows][dim]     the caller's float32 descriptors, untouched
     const int* norm_i;                // [rows]          integer squared norm (integer path)
+    const float* norm_f;              // [rows]          float32 squared norm (float path)
     const uint8_t* valid;             // [rows]          0 for rows containing NaN (twoway_matcher.py:75-76) and padding
     const double2* kps;               // [rows]          pixel coordinates (Keypoints.coordinates)
     int dim;                          // descriptor dimension as uploaded

@@ -52,6 +52,10 @@ void gtsfm_ctx_destroy(gtsfm_ctx* ctx);
 const char* gtsfm_last_error(const gtsfm_ctx* ctx);   /* ctx may be NULL: error of the last failed create */
 /* Work-buffer budget in bytes for one chunk of pairs (default 4 GiB). */
 int gtsfm_ctx_set_workspace(gtsfm_ctx* ctx, int64_t bytes);
+/* Float (non-integer) descriptors, ratio test off: on (default) = fp16 tensor-core screening + exact recompute of the
+ * winning candidates + exhaustive re-scan of ambiguous rows; off = every distance by the exhaustive fp32 kernel.  Both give
+ * the same matches (cv2's float32 arithmetic); the switch exists for tests and measurements. */
+int gtsfm_ctx_set_float_screening(gtsfm_ctx* ctx, int on);
 /* Number of hand-written kernels launched by this context since creation (bench.py's gpu_launches). */
 int64_t gtsfm_kernel_launches(const gtsfm_ctx* ctx);
 

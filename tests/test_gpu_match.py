@@ -148,3 +148,76 @@ def test_superpoint_like_batch_ratio_off(ctx):
         want = O.twoway_match(scene.descriptors[i], scene.descriptors[j], None).reshape(-1, 2)
         check(m[off[p]:off[p + 1]], want)
     assert off[-1] > 0
+
+
+# ------------------------------------------------------------------ float descriptors: fp16 tensor-core screening path
+def unit_float_descs(rng, n, dim, protos=None, noise=0.1):
+    p = rng.standard_normal((n, dim)) if protos is None else protos + noise * rng.standard_normal(protos.shape)
+    return (p / np.linalg.norm(p, axis=1, keepdims=True)).astype(np.float32)
+
+
+@pytest.mark.parametrize("n1,n2,dim", [(900, 1000, 256), (256, 256, 128), (300, 2049, 64), (2500, 130, 256), (5, 3, 128)])
+def test_float_screened_path_vs_oracle(ctx, n1, n2, dim):
+    """Unit-norm float descriptors, ratio test off: fp16 screening + exact recompute must reproduce cv2's float32 matches
+    bit for bit (indices and order), and equal the exhaustive kernel's result."""
+    from oracle import oracle as O
+    rng = np.random.default_rng(n1 * 3 + n2 + dim)
+    shared = min(n1, n2) // 2
+    protos = rng.standard_normal((shared, dim))
+    d1 = np.concatenate([unit_float_descs(rng, shared, dim, protos), unit_float_descs(rng, n1 - shared, dim)])[rng.permutation(n1)]
+    d2 = np.concatenate([unit_float_descs(rng, shared, dim, protos), unit_float_descs(rng, n2 - shared, dim)])[rng.permutation(n2)]
+    want = O.twoway_match(d1, d2, None).reshape(-1, 2)
+    got = ctx.match_pair(d1, d2, None)
+    check(got, want)
+    ctx.set_float_screening(False)
+    try:
+        check(ctx.match_pair(d1, d2, None), want)
+    finally:
+        ctx.set_float_screening(True)
+    # the ratio test needs the second-nearest neighbour: that stays on the exhaustive kernel
+    check(ctx.match_pair(d1, d2, 0.9), O.twoway_match(d1, d2, 0.9).reshape(-1, 2))
+
+
+def test_float_screened_ties_nan_and_scales(ctx):
+    """Duplicate rows (exact ties -> lowest index), NaN rows, rows of different norms inside the eligible range, and
+    descriptors outside it (|x|^2 > 1024 -> exhaustive kernel)."""
+    from oracle import oracle as O
+    rng = np.random.default_rng(77)
+    base = unit_float_descs(rng, 300, 128)
+    d1 = np.concatenate([base, base[:60], unit_float_descs(rng, 150, 128)])
+    d2 = np.concatenate([base[::-1], base[:40], unit_float_descs(rng, 90, 128)])
+    check(ctx.match_pair(d1, d2, None), O.twoway_match(d1, d2, None).reshape(-1, 2))
+    d1n, d2n = d1.copy(), d2.copy()
+    d1n[[3, 150, 400]] = np.nan
+    d2n[[0, 120]] = np.nan
+    check(ctx.match_pair(d1n, d2n, None), O.twoway_match(d1n, d2n, None).reshape(-1, 2))
+    s1 = (d1 * rng.uniform(0.05, 20.0, (d1.shape[0], 1))).astype(np.float32)
+    s2 = (d2 * rng.uniform(0.05, 20.0, (d2.shape[0], 1))).astype(np.float32)
+    check(ctx.match_pair(s1, s2, None), O.twoway_match(s1, s2, None).reshape(-1, 2))
+    b1, b2 = (d1 * 512).astype(np.float32), (d2 * 512).astype(np.float32)
+    check(ctx.match_pair(b1, b2, None), O.twoway_match(b1, b2, None).reshape(-1, 2))
+    z = np.zeros((40, 128), np.float32)                       # all-zero rows: every distance ties
+    check(ctx.match_pair(z, d2, None), O.twoway_match(z, d2, None).reshape(-1, 2))
+
+
+def test_float_screened_c4_size_flag_rate(ctx):
+    """C4-sized pair (2048 x 2048 x 256): screened == exhaustive, and only a small fraction of the rows and
+    columns needs the exhaustive re-scan."""
+    from gtsfm_b200 import synthetic
+    scene = synthetic.make_scene(n_images=3, n_kps=2048, dim=256, kind="superpoint", seed=20260004, ratio=None)
+    ctx.clear()
+    for i, d in enumerate(scene.descriptors):
+        ctx.upload_image(i, d)
+    m, off = ctx.match_batch(scene.pairs, None)
+    n_flag = int(ctx.debug_fetch(10, 1, np.int32)[0])
+    ctx.set_float_screening(False)
+    try:
+        m2, off2 = ctx.match_batch(scene.pairs, None)
+    finally:
+        ctx.set_float_screening(True)
+    np.testing.assert_array_equal(off, off2)
+    np.testing.assert_array_equal(m, m2)
+    assert off[-1] > 1000
+    total = sum(len(scene.descriptors[i]) + len(scene.descriptors[j]) for i, j in scene.pairs)
+    assert n_flag < 0.25 * total, (n_flag, total)
+    print("flagged rows+columns:", n_flag, "of", total)
