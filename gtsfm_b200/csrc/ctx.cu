@@ -229,6 +229,8 @@ void gtsfm_ctx_destroy(gtsfm_ctx* c)
     for (DevBuf* b : bufs) b->release();
     for (DevBuf& b : c->v_bufs) b.release();
     c->h_pairs.release();
+    c->h_blk_tab.release();
+    c->blk_tab.release();
     c->h_small.release();
     for (cudaEvent_t e : c->prof_pool) cudaEventDestroy(e);
     for (cudaEvent_t e : c->user_ev) if (e) cudaEventDestroy(e);

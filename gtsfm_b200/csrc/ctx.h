@@ -57,7 +57,8 @@ struct gtsfm_ctx {
     // ---- matcher work buffers (one chunk of pairs) and batch outputs
     g2v::DevBuf d_pairs, rp_v1, rp_v2, rp_g, colraw, row_best, row_d1, row_d2, col_best, col_d1, col_d2, flag_list, n_flag, row_key, col_key, row_cnt, col_cnt, row_list, col_list, flag_scratch, col_cells;
     g2v::DevBuf keys_scratch, match_slot, match_count, match_offsets, match_out, d_total;
-    g2v::PinnedBuf h_pairs, h_small;
+    g2v::PinnedBuf h_pairs, h_small, h_blk_tab;
+    g2v::DevBuf blk_tab;                        // float screening path: (row block -> pair) and (column block -> pair) tables
     std::vector<g2v::PairDesc> batch_pairs;     // PairDescs of the last match batch (chunk-relative bases)
     std::vector<int> batch_img;                 // (P, 2) image ids of the last match batch
     std::vector<int> batch_counts;              // matches per pair of the last match batch

@@ -34,6 +34,7 @@ struct Chunk {
     long long rp = 0, cr = 0, rows = 0, cols = 0;
     int items = 0, jobs = 0, max_class_rows = 0, max_hb = 0;
     int fitems = 0;          // work items of the fp16 screening kernel (path-2 pairs)
+    long long rtab = 0, ctab = 0;   // offsets of the chunk's block -> pair tables
 };
 }  // namespace g2v
 
@@ -87,7 +88,9 @@ int gtsfm_match_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, double ra
         if (pd.path == 1 && !empty && qa.path == 1 && tb.path == 1 && qa.f16_ok && tb.f16_ok && screen_f_ok) pd.path = 2;
         pd.q_maxn2 = qa.max_norm2; pd.t_maxn2 = tb.max_norm2;
         const long long rp = pd.path != 1 ? static_cast<long long>(pd.nq_pad) * (pd.nt_pad / kHalfT) : 0;
-        const long long cr = pd.path != 1 ? static_cast<long long>(pd.nt_pad) * kTileQ : 0;
+        const int n_tg = (pd.nq_pad / kTileQ + kFlushTiles - 1) / kFlushTiles;      // path 2: column minima per group of 4 query tiles
+        const long long cr = pd.path == 0 ? static_cast<long long>(pd.nt_pad) * kTileQ
+                                          : pd.path == 2 ? static_cast<long long>(pd.nt_pad) * n_tg * kTileQ : 0;
         const int items = pd.path == 0 && pd.nq > 0 ? pd.nt_pad / kBlockT : 0;
         const int fitems = pd.path == 2 && pd.nq > 0 ? pd.nt_pad / kBlockT : 0;
         const int jobs = pd.path == 1 && pd.nq > 0 ? (pd.nq + 31) / 32 + (pd.nt + 31) / 32 : 0;
@@ -146,6 +149,22 @@ int gtsfm_match_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, double ra
     G2V_CUDA(c, cudaMemcpyAsync(c->d_pairs.p, c->h_pairs.p, sizeof(PairDesc) * n_pairs, cudaMemcpyHostToDevice, s));
     G2V_CUDA(c, cudaMemsetAsync(c->d_total.p, 0, 8, s));
     if ((r = store_ensure_maps(c))) return r;
+    // block -> pair tables of the float screening path (one entry per kRowPad rows / columns, chunk-relative pair index)
+    bool any_screen_f = false;
+    for (const Chunk& k : chunks) any_screen_f |= k.fitems > 0;
+    if (any_screen_f) {
+        std::vector<int> tab;
+        for (Chunk& k : chunks) {
+            k.rtab = static_cast<long long>(tab.size());
+            for (int p = k.p0; p < k.p1; ++p) tab.insert(tab.end(), pds[p].nq_pad / kRowPad, p - k.p0);
+            k.ctab = static_cast<long long>(tab.size());
+            for (int p = k.p0; p < k.p1; ++p) tab.insert(tab.end(), pds[p].nt_pad / kRowPad, p - k.p0);
+        }
+        G2V_CUDA(c, c->blk_tab.reserve(4 * (tab.size() + 1), false, s));
+        G2V_CUDA(c, c->h_blk_tab.reserve(4 * (tab.size() + 1)));
+        std::memcpy(c->h_blk_tab.p, tab.data(), 4 * tab.size());
+        G2V_CUDA(c, cudaMemcpyAsync(c->blk_tab.p, c->h_blk_tab.p, 4 * tab.size(), cudaMemcpyHostToDevice, s));
+    }
 
     const StoreView st = c->view();
     for (const Chunk& k : chunks) {
@@ -158,6 +177,7 @@ int gtsfm_match_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, double ra
         w.row_key = c->row_key.as<unsigned int>(); w.col_key = c->col_key.as<unsigned int>();
         w.row_cnt = c->row_cnt.as<int>(); w.col_cnt = c->col_cnt.as<int>(); w.row_list = c->row_list.as<int>(); w.col_list = c->col_list.as<int>();
         w.max_hb = k.max_hb;
+        w.row_blk_pair = c->blk_tab.as<int>() + k.rtab; w.col_blk_pair = c->blk_tab.as<int>() + k.ctab;
         w.flag_list = c->flag_list.as<unsigned long long>(); w.n_flag = c->n_flag.as<int>();
         w.flag_scratch = c->flag_scratch.as<unsigned long long>();
         w.col_cells = c->col_cells.as<unsigned long long>();

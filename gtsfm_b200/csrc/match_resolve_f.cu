@@ -1,8 +1,8 @@
 // K2f -- exact resolve of the fp16-screened float path (ratio test off: only the nearest neighbour is needed).
 //
-// The screening kernel (match_screen_f.cu) leaves, per query row, the minimum of every group of 16 train columns (best /
+// The screening kernel (match_screen_f.cu) leaves, per query row, the minimum of every group of 4 train columns (best /
 // second-best group per 128-column half block) and, per train column, the minimum over every lane class
-// {q : q mod 128 == lane}.  Its values are d^2 / 2 up to the rounding of the fp16 operands and the fp32 accumulation:
+// {q = (4 tg + j) 128 + lane, j < 4} (at most four query rows).  Its values are d^2 / 2 up to the rounding of the fp16 operands and the fp32 accumulation:
 //     |s(q,t) - d^2(q,t) / 2|  <=  eps(q,t) = 1.1e-3 |q||t| + 1e-5 (|q|^2 + |t|^2) + 1e-6 (|q| + |t|)
 // (2^-10 |q||t| from the two 11-bit significands, the rest covers fp16 subnormals, the 3-term norm expansion, the float32
 // norms and the accumulation over K <= 272).
@@ -20,7 +20,7 @@
 
 namespace g2v {
 
-constexpr int kResF = 32;          // scan-side rows per CTA
+constexpr int kResF = 16;          // scan-side rows per CTA (one per half warp)
 constexpr int kStage2Budget = 1024; // candidates a row / column may recompute in the second stage before it is handed to
                                     // the exhaustive scan
 
@@ -53,6 +53,41 @@ __device__ __forceinline__ float cv2_l2_halfwarp(const float* a, const float* b,
     return sqrtf(d);
 }
 
+// NB distances at once (same arithmetic per distance): the scan-side element is loaded once for all of them and their
+// loads are independent.
+template <int NB>
+__device__ __forceinline__ void cv2_l2_halfwarp_n(const float* a, const float* const* b, int dim, int r16, float* out)
+{
+    const int nblk = dim >> 4;
+    float acc[NB];
+#pragma unroll
+    for (int u = 0; u < NB; ++u) acc[u] = 0.f;
+#pragma unroll 4
+    for (int k = 0; k < nblk; ++k) {
+        const float av = a[16 * k + r16];
+#pragma unroll
+        for (int u = 0; u < NB; ++u) {
+            const float d = __fsub_rn(av, __ldg(b[u] + 16 * k + r16));
+            acc[u] = __fadd_rn(acc[u], __fmul_rn(d, d));
+        }
+    }
+    const int l = r16 & 3;
+#pragma unroll
+    for (int u = 0; u < NB; ++u) {
+        const float a0 = __shfl_sync(0xffffffffu, acc[u], l, 16), a1 = __shfl_sync(0xffffffffu, acc[u], 4 + l, 16);
+        const float a2 = __shfl_sync(0xffffffffu, acc[u], 8 + l, 16), a3 = __shfl_sync(0xffffffffu, acc[u], 12 + l, 16);
+        const float s = __fadd_rn(__fadd_rn(__fadd_rn(a0, a1), a2), a3);
+        const float s0 = __shfl_sync(0xffffffffu, s, 0, 16), s1 = __shfl_sync(0xffffffffu, s, 1, 16);
+        const float s2 = __shfl_sync(0xffffffffu, s, 2, 16), s3 = __shfl_sync(0xffffffffu, s, 3, 16);
+        float d = __fadd_rn(__fadd_rn(s0, s2), __fadd_rn(s1, s3));
+        for (int e = 16 * nblk; e < dim; ++e) {
+            const float t = __fsub_rn(a[e], b[u][e]);
+            d = __fadd_rn(d, __fmul_rn(t, t));
+        }
+        out[u] = sqrtf(d);
+    }
+}
+
 __device__ __forceinline__ void push_flag_f(const MatchWork& w, int pair, int dir, int idx)
 {
     const int k = atomicAdd(w.n_flag, 1);
@@ -61,155 +96,177 @@ __device__ __forceinline__ void push_flag_f(const MatchWork& w, int pair, int di
                          static_cast<unsigned int>(idx);
 }
 
-// DIR 0: one CTA per 32 query rows (candidates: the 16 train columns of the winning group).
-// DIR 1: one CTA per 32 train columns (candidates: the nq_pad / 128 query rows of the winning lane class).
+// A half warp owns one scan-side row end to end (no shared memory, no block barrier), kResF rows per CTA:
+//   DIR 0: a query row; candidates = the 4 train columns of its winning group.
+//   DIR 1: a train column; candidates = the <= 4 query rows of its winning lane class.
 template <int DIR>
 __global__ void __launch_bounds__(256) resolve_f_kernel(StoreView st, MatchWork w)
 {
-    extern __shared__ float s_scan[];                 // [kResF][dim] the CTA's scan-side rows
-    __shared__ float s_r2[kResF];
-    __shared__ int s_c0[kResF];
     const long long base = static_cast<long long>(blockIdx.x) * kResF;
-    // pair of this block of rows / columns
-    int lo = 0, hi = w.n_pairs - 1;
-    while (lo < hi) {
-        const int mid = (lo + hi + 1) >> 1;
-        if ((DIR == 0 ? w.pairs[mid].out_base : w.pairs[mid].cb_base) <= base) lo = mid; else hi = mid - 1;
-    }
-    const int p = lo;
+    // pair of this block of rows / columns (table built by the host: a binary search over the pair list would put a chain
+    // of dependent global loads in front of every CTA)
+    const int p = (DIR == 0 ? w.row_blk_pair : w.col_blk_pair)[base / kRowPad];
     const PairDesc pd = w.pairs[p];
     if (pd.path != 2) return;
     const int i0 = static_cast<int>(base - (DIR == 0 ? pd.out_base : pd.cb_base));
-    const int n_scan = DIR == 0 ? pd.nq : pd.nt, n_scan_pad = DIR == 0 ? pd.nq_pad : pd.nt_pad;
-    if (i0 >= n_scan_pad || i0 >= n_scan) return;
+    const int n_scan = DIR == 0 ? pd.nq : pd.nt;
+    if (i0 >= n_scan) return;
     const int scan_row0 = (DIR == 0 ? pd.q_row0 : pd.t_row0) + i0;
     const int other_row0 = DIR == 0 ? pd.t_row0 : pd.q_row0;
     const int other_n = DIR == 0 ? pd.nt : pd.nq;
     const int dim = st.dim;
     const int cnt = min(kResF, n_scan - i0);
-    for (int k = threadIdx.x; k < cnt * dim; k += blockDim.x) s_scan[k] = st.desc_f32[static_cast<long long>(scan_row0) * dim + k];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-
-    // ---- phase 1: winning group / class and the smallest screened value outside it
-    if (DIR == 0) {
-        if (threadIdx.x < kResF) {
-            const int q = i0 + threadIdx.x;
-            const int nhb = pd.nt_pad / kHalfT;
-            float bv = FLT_MAX, r2 = FLT_MAX;
-            int bc = 0;
-            for (int hb = 0; hb < nhb; ++hb) {
-                const long long e = pd.rp_base + static_cast<long long>(hb) * pd.nq_pad + q;
-                const float v1 = w.rp_v1[e], v2 = w.rp_v2[e];
-                const int g = w.rp_g[e];
-                if (v1 < bv) { r2 = fminf(r2, bv); bv = v1; bc = hb * kHalfT + g * kGroup; }
-                else r2 = fminf(r2, v1);
-                r2 = fminf(r2, v2);
-            }
-            s_r2[threadIdx.x] = r2;
-            s_c0[threadIdx.x] = bc;
-        }
-    } else {
-#pragma unroll 1
-        for (int u = 0; u < 4; ++u) {
-            const int r = warp * 4 + u;
-            const int t = i0 + r;
-            const float4 v = *reinterpret_cast<const float4*>(w.colraw + pd.cr_base + static_cast<long long>(t) * kTileQ + 4 * lane);
-            float b = v.x, s2 = FLT_MAX;
-            int bi = 4 * lane;
-            const float vv[3] = {v.y, v.z, v.w};
-#pragma unroll
-            for (int k = 0; k < 3; ++k) {
-                if (vv[k] < b) { s2 = fminf(s2, b); b = vv[k]; bi = 4 * lane + 1 + k; } else s2 = fminf(s2, vv[k]);
-            }
-#pragma unroll
-            for (int off = 16; off > 0; off >>= 1) {
-                const float ob = __shfl_xor_sync(0xffffffffu, b, off), os = __shfl_xor_sync(0xffffffffu, s2, off);
-                const int oi = __shfl_xor_sync(0xffffffffu, bi, off);
-                const bool take = ob < b || (ob == b && oi < bi);
-                s2 = fminf(fminf(s2, os), take ? b : ob);
-                if (take) { b = ob; bi = oi; }
-            }
-            if (lane == 0) { s_r2[r] = s2; s_c0[r] = bi; }
-        }
-    }
-    __syncthreads();
-
-    // ---- phase 2: exact recompute of the candidates, a half warp per distance
     const int h = lane >> 4, r16 = lane & 15;
-    const int n_cand = DIR == 0 ? kGroup : pd.nq_pad / kTileQ;
+    // DIR 1: lane class cl = tg * 128 + lane holds the query rows (kFlushTiles tg + j) 128 + lane, j < kFlushTiles
+    const int n_qtiles = pd.nq_pad / kTileQ;
+    const int n_cls = (n_qtiles + kFlushTiles - 1) / kFlushTiles * kTileQ;
+    auto class_row0 = [&](int cl) { return (cl / kTileQ) * kFlushTiles * kTileQ + (cl % kTileQ); };
+    auto class_rows = [&](int cl) { return min(kFlushTiles, n_qtiles - (cl / kTileQ) * kFlushTiles); };
     const float other_maxn2 = DIR == 0 ? pd.t_maxn2 : pd.q_maxn2;
     int* o_best = DIR == 0 ? w.row_best : w.col_best;
     float* o_d1 = DIR == 0 ? w.row_d1 : w.col_d1;
     float* o_d2 = DIR == 0 ? w.row_d2 : w.col_d2;
     const long long out0 = (DIR == 0 ? pd.out_base : pd.cb_base) + i0;
-#pragma unroll 1
-    for (int u = 0; u < 4; ++u) {
-        const int r = warp * 4 + u;
-        if (r >= cnt) break;
-        if (!st.valid[scan_row0 + r]) {
-            if (lane == 0) { o_best[out0 + r] = -1; o_d1[out0 + r] = FLT_MAX; o_d2[out0 + r] = FLT_MAX; }
-            continue;
+
+    const int r = warp * 2 + h;                          // this half warp's row of the block
+    const bool in_range = r < cnt;
+    const int rs = in_range ? r : 0;
+    const bool active = in_range && st.valid[scan_row0 + rs];
+    const float* a = st.desc_f32 + static_cast<long long>(scan_row0 + rs) * dim;
+
+    // ---- phase 1: winning group / class (c0) and the smallest screened value outside it (r2)
+    float bv = FLT_MAX, r2 = FLT_MAX;
+    int c0 = 0;
+    if (DIR == 0) {
+        const int nhb = pd.nt_pad / kHalfT;
+        for (int hb = r16; hb < nhb; hb += 16) {                     // ascending half blocks per lane
+            const long long e = pd.rp_base + static_cast<long long>(hb) * pd.nq_pad + (i0 + rs);
+            const float v1 = w.rp_v1[e], v2 = w.rp_v2[e];
+            const int g = w.rp_g[e];
+            if (v1 < bv) { r2 = fminf(r2, bv); bv = v1; c0 = hb * kHalfT + g * kGroupF; }
+            else r2 = fminf(r2, v1);
+            r2 = fminf(r2, v2);
         }
-        const float* a = s_scan + r * dim;
-        float f1 = FLT_MAX;
-        int i1 = INT_MAX;
-        // exact distances to n candidates c0, c0 + stride, ...: the half warps alternate, both always run the same rounds
-        auto scan_cands = [&](int c0, int stride, int n) {
-            for (int j = h; j < n; j += 2) {
-                const int c = c0 + j * stride;
-                const bool ok = c < other_n && st.valid[other_row0 + c];
-                const float f = cv2_l2_halfwarp(a, st.desc_f32 + static_cast<long long>(other_row0 + (ok ? c : 0)) * dim, dim, r16);
-                if (ok && (f < f1 || (f == f1 && c < i1))) { f1 = f; i1 = c; }       // the lowest index wins ties
+    } else {
+        const float* crp = w.colraw + pd.cr_base + static_cast<long long>(i0 + rs) * n_cls;
+        for (int k0 = 4 * r16; k0 < n_cls; k0 += 64) {               // ascending class ids per lane
+            const float4 v = __ldg(reinterpret_cast<const float4*>(crp + k0));
+            const float vv[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                if (vv[k] < bv) { r2 = fminf(r2, bv); bv = vv[k]; c0 = k0 + k; } else r2 = fminf(r2, vv[k]);
+            }
+        }
+    }
+#pragma unroll
+    for (int off = 8; off > 0; off >>= 1) {                          // within the half warp
+        const float ob = __shfl_xor_sync(0xffffffffu, bv, off), os = __shfl_xor_sync(0xffffffffu, r2, off);
+        const int oc = __shfl_xor_sync(0xffffffffu, c0, off);
+        const bool take = ob < bv || (ob == bv && oc < c0);
+        r2 = fminf(fminf(r2, os), take ? bv : ob);
+        if (take) { bv = ob; c0 = oc; }
+    }
+
+    // ---- phase 2, fast pass: the (<= 4) candidates in one batch, so all their loads are in flight together
+    float f1 = FLT_MAX;
+    int i1 = INT_MAX;
+    bool done = false;
+    {
+        const int cbase = DIR == 0 ? c0 : class_row0(c0), cstride = DIR == 0 ? 1 : kTileQ;
+        const int cn = DIR == 0 ? kGroupF : class_rows(c0);
+        int c[4];
+        bool ok[4];
+        const float* bp[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            c[k] = cbase + k * cstride;
+            ok[k] = active && k < cn && c[k] < other_n && st.valid[other_row0 + (c[k] < other_n ? c[k] : 0)];
+            bp[k] = st.desc_f32 + static_cast<long long>(other_row0 + (ok[k] ? c[k] : 0)) * dim;
+        }
+        float f[4];
+        cv2_l2_halfwarp_n<4>(a, bp, dim, r16, f);
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+            if (ok[k] && f[k] < f1) { f1 = f[k]; i1 = c[k]; }                    // ascending index: the lowest wins ties
+    }
+    const float eps = screen_eps(st.norm_f[scan_row0 + rs], other_maxn2);
+    // every candidate whose screened value exceeds thr is farther than f1 in cv2's float32 arithmetic
+    const double thr_d = 0.5 * static_cast<double>(f1) * static_cast<double>(f1) * (1.0 + 1e-5) + static_cast<double>(eps) + 1e-30;
+    if (active && i1 != INT_MAX) done = static_cast<double>(r2) > thr_d;
+    if (r16 == 0 && in_range) {
+        if (!active) { o_best[out0 + r] = -1; o_d1[out0 + r] = FLT_MAX; o_d2[out0 + r] = FLT_MAX; }
+        else if (done) { o_best[out0 + r] = i1; o_d1[out0 + r] = f1; o_d2[out0 + r] = FLT_MAX; }
+    }
+    const unsigned need = __ballot_sync(0xffffffffu, active && !done);
+    if (need == 0) return;
+
+    // ---- second stage (about 1 % of the rows): the whole warp recomputes every other group / class the screening cannot
+    // rule out.  Rows: a half block whose second-best group is a suspect is recomputed whole (the screening keeps only the
+    // id of its best group).
+#pragma unroll 1
+    for (int u = 0; u < 2; ++u) {
+        if (!((need >> (16 * u)) & 1u)) continue;
+        const int ru = warp * 2 + u;
+        const float* au = st.desc_f32 + static_cast<long long>(scan_row0 + ru) * dim;
+        const int c0u = __shfl_sync(0xffffffffu, c0, 16 * u);
+        const float thr = __double2float_ru(__shfl_sync(0xffffffffu, thr_d, 16 * u));
+        float g1 = __shfl_sync(0xffffffffu, f1, 16 * u);
+        int j1 = __shfl_sync(0xffffffffu, i1, 16 * u);
+        if (j1 == INT_MAX) { if (lane == 0) push_flag_f(w, p, DIR, i0 + ru); continue; }   // no valid candidate: exhaustive scan
+        // exact distances to n candidates cb, cb + stride, ...: the half warps alternate, both always run the same rounds
+        auto scan_cands = [&](int cb, int stride, int n) {                       // n is even
+            constexpr int NB = 2;                                                // candidates per half warp and round
+            for (int m0 = 0; m0 < (n >> 1); m0 += NB) {
+                int c[NB];
+                bool ok[NB];
+                const float* bp[NB];
+#pragma unroll
+                for (int k = 0; k < NB; ++k) {
+                    c[k] = cb + (h + 2 * (m0 + k)) * stride;
+                    ok[k] = (m0 + k) < (n >> 1) && c[k] < other_n && st.valid[other_row0 + (c[k] < other_n ? c[k] : 0)];
+                    bp[k] = st.desc_f32 + static_cast<long long>(other_row0 + (ok[k] ? c[k] : 0)) * dim;
+                }
+                float f[NB];
+                cv2_l2_halfwarp_n<NB>(au, bp, dim, r16, f);
+#pragma unroll
+                for (int k = 0; k < NB; ++k)
+                    if (ok[k] && (f[k] < g1 || (f[k] == g1 && c[k] < j1))) { g1 = f[k]; j1 = c[k]; }   // the lowest index wins ties
             }
         };
-        const int c0 = s_c0[r];
-        scan_cands(c0, DIR == 0 ? 1 : kTileQ, n_cand);
-        {
-            const float of = __shfl_xor_sync(0xffffffffu, f1, 16);
-            const int oi = __shfl_xor_sync(0xffffffffu, i1, 16);
-            if (of < f1 || (of == f1 && oi < i1)) { f1 = of; i1 = oi; }
-        }
-        const float eps = screen_eps(st.norm_f[scan_row0 + r], other_maxn2);
-        // every candidate whose screened value exceeds thr is farther than f1 in cv2's float32 arithmetic
-        const double thr_d = 0.5 * static_cast<double>(f1) * static_cast<double>(f1) * (1.0 + 1e-5) + static_cast<double>(eps) + 1e-30;
-        bool done = i1 != INT_MAX && static_cast<double>(s_r2[r]) > thr_d;
-        if (!done && i1 != INT_MAX) {
-            // second stage: recompute every other group / class the screening cannot rule out.  Rows: a half block whose
-            // second-best group is a suspect is recomputed whole (the screening keeps only the id of its best group).
-            const float thr = __double2float_ru(thr_d);
-            int budget = kStage2Budget;                         // candidates this row may still recompute
-            if (DIR == 0) {
-                const int nhb = pd.nt_pad / kHalfT;
-                for (int hb = 0; hb < nhb && budget >= 0; ++hb) {
-                    const long long e = pd.rp_base + static_cast<long long>(hb) * pd.nq_pad + (i0 + r);
-                    const float v1 = w.rp_v1[e], v2 = w.rp_v2[e];
-                    const int g = w.rp_g[e];
-                    const int cg = hb * kHalfT + g * kGroup;
-                    if (v2 <= thr) {
-                        budget -= kHalfT;
-                        if (budget >= 0) scan_cands(hb * kHalfT, 1, kHalfT);        // includes the best group again: harmless
-                    } else if (v1 <= thr && cg != c0) {
-                        budget -= kGroup;
-                        if (budget >= 0) scan_cands(cg, 1, kGroup);
-                    }
-                }
-            } else {
-                const float* cr = w.colraw + pd.cr_base + static_cast<long long>(i0 + r) * kTileQ;
-                for (int cl = 0; cl < kTileQ && budget >= 0; ++cl) {
-                    if (cl != c0 && cr[cl] <= thr) {
-                        budget -= n_cand;
-                        if (budget >= 0) scan_cands(cl, kTileQ, n_cand);
-                    }
+        int budget = kStage2Budget;                             // candidates this row may still recompute
+        if (DIR == 0) {
+            const int nhb = pd.nt_pad / kHalfT;
+            for (int hb = 0; hb < nhb && budget >= 0; ++hb) {
+                const long long e = pd.rp_base + static_cast<long long>(hb) * pd.nq_pad + (i0 + ru);
+                const float v1 = w.rp_v1[e], v2 = w.rp_v2[e];
+                const int cg = hb * kHalfT + w.rp_g[e] * kGroupF;
+                if (v2 <= thr) {
+                    budget -= kHalfT;
+                    if (budget >= 0) scan_cands(hb * kHalfT, 1, kHalfT);        // includes the best group again: harmless
+                } else if (v1 <= thr && cg != c0u) {
+                    budget -= kGroupF;
+                    if (budget >= 0) scan_cands(cg, 1, kGroupF);
                 }
             }
-            const float of = __shfl_xor_sync(0xffffffffu, f1, 16);
-            const int oi = __shfl_xor_sync(0xffffffffu, i1, 16);
-            if (of < f1 || (of == f1 && oi < i1)) { f1 = of; i1 = oi; }
-            done = budget >= 0;
+        } else {
+            const float* cr = w.colraw + pd.cr_base + static_cast<long long>(i0 + ru) * n_cls;
+            for (int cl0 = 0; cl0 < n_cls && budget >= 0; cl0 += 32) {          // 32 classes per step, suspects by ballot
+                unsigned sus = __ballot_sync(0xffffffffu, (cl0 + lane) < n_cls && (cl0 + lane) != c0u && cr[cl0 + lane] <= thr);
+                while (sus && budget >= 0) {
+                    const int cl = cl0 + __ffs(sus) - 1;
+                    sus &= sus - 1;
+                    budget -= kFlushTiles;
+                    if (budget >= 0) scan_cands(class_row0(cl), kTileQ, class_rows(cl));
+                }
+            }
         }
+        const float of = __shfl_xor_sync(0xffffffffu, g1, 16);
+        const int oi = __shfl_xor_sync(0xffffffffu, j1, 16);
+        if (of < g1 || (of == g1 && oi < j1)) { g1 = of; j1 = oi; }
         if (lane == 0) {
-            if (done) { o_best[out0 + r] = i1; o_d1[out0 + r] = f1; o_d2[out0 + r] = FLT_MAX; }
-            else push_flag_f(w, p, DIR, i0 + r);                // too many suspects (or no valid candidate): exhaustive scan
+            if (budget >= 0) { o_best[out0 + ru] = j1; o_d1[out0 + ru] = g1; o_d2[out0 + ru] = FLT_MAX; }
+            else push_flag_f(w, p, DIR, i0 + ru);               // too many suspects: exhaustive scan
         }
     }
 }
@@ -217,17 +274,8 @@ __global__ void __launch_bounds__(256) resolve_f_kernel(StoreView st, MatchWork 
 // total_rows / total_cols: rows (columns) of the chunk over all pairs (multiples of 256).
 cudaError_t launch_resolve_f(const StoreView& st, const MatchWork& w, long long total_rows, long long total_cols, cudaStream_t s)
 {
-    const size_t smem = static_cast<size_t>(kResF) * st.dim * sizeof(float);
-    static size_t configured = 0;
-    if (smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(resolve_f_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
-        if (e != cudaSuccess) return e;
-        e = cudaFuncSetAttribute(resolve_f_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
-        if (e != cudaSuccess) return e;
-        configured = smem;
-    }
-    if (total_rows > 0) resolve_f_kernel<0><<<static_cast<unsigned>(total_rows / kResF), 256, smem, s>>>(st, w);
-    if (total_cols > 0) resolve_f_kernel<1><<<static_cast<unsigned>(total_cols / kResF), 256, smem, s>>>(st, w);
+    if (total_rows > 0) resolve_f_kernel<0><<<static_cast<unsigned>(total_rows / kResF), 256, 0, s>>>(st, w);
+    if (total_cols > 0) resolve_f_kernel<1><<<static_cast<unsigned>(total_cols / kResF), 256, 0, s>>>(st, w);
     return cudaGetLastError();
 }
 

@@ -16,6 +16,7 @@ namespace g2v {
 constexpr int kThreadsF = 384;          // warp 0 TMA, warp 1 MMA, warp 2 TMEM alloc, warp 3 idle, warps 4..11 epilogue
 constexpr int kEpiWarp0F = 4;
 constexpr uint32_t kTmemColsF = 512;    // two 128x256 fp32 accumulators
+// kGroupF (train columns per group of the row partials) and kFlushTiles (query tiles per column-minimum flush): types.h
 
 template <int KCH> struct ScreenSmemF {
     static constexpr int kSlots = KCH + 1;                  // ring of 64-wide K chunks of query tiles (see the aug hazard note)
@@ -188,6 +189,9 @@ match_screen_f_kernel(const __grid_constant__ CUtensorMap tm_desc, const __grid_
             long long e = args.pairs[p].rp_base + static_cast<long long>(blk * 2 + half) * nq_pad + m_local;
 #pragma unroll
             for (int i = 0; i < kHalfT; ++i) cmin[i] = kHuge * 4.0f;
+            const int n_tg = (ntiles + kFlushTiles - 1) / kFlushTiles;
+            float* cr = args.colraw + args.pairs[p].cr_base +
+                        (static_cast<long long>(blk) * kBlockT + half * kHalfT) * (static_cast<long long>(n_tg) * kTileQ) + m_local;
             for (int t = 0; t < ntiles; ++t, ++acnt) {
                 const uint32_t a = acnt & 1, aph = (acnt >> 1) & 1;
                 ptx::mbar_wait(&acc_full[a], aph);
@@ -195,19 +199,19 @@ match_screen_f_kernel(const __grid_constant__ CUtensorMap tm_desc, const __grid_
                 float v1 = kHuge * 4.0f, v2 = kHuge * 4.0f;
                 int g1 = 0;
 #pragma unroll
-                for (int c = 0; c < kHalfT / kGroup; ++c) {
-                    float v[kGroup];
-                    ptx::tmem_ld_32x32b_x16(t_lane + a * kBlockT + c * kGroup, v);
+                for (int c = 0; c < kHalfT / 16; ++c) {
+                    float v[16];
+                    ptx::tmem_ld_32x32b_x16(t_lane + a * kBlockT + c * 16, v);
 #pragma unroll
-                    for (int i = 0; i < kGroup; ++i) cmin[c * kGroup + i] = fminf(cmin[c * kGroup + i], v[i]);
-                    float m = fminf(fminf(v[0], v[1]), v[2]);
+                    for (int i = 0; i < 16; ++i) cmin[c * 16 + i] = fminf(cmin[c * 16 + i], v[i]);
 #pragma unroll
-                    for (int i = 3; i < 15; i += 2) m = fminf(fminf(m, v[i]), v[i + 1]);
-                    m = fminf(m, v[15]);
-                    const bool lt = m < v1;                      // strict: the lowest group id wins ties
-                    v2 = fminf(v2, fmaxf(v1, m));
-                    g1 = lt ? c : g1;
-                    v1 = fminf(v1, m);
+                    for (int sg = 0; sg < 16 / kGroupF; ++sg) {
+                        const float m = fminf(fminf(fminf(v[4 * sg], v[4 * sg + 1]), v[4 * sg + 2]), v[4 * sg + 3]);
+                        const bool lt = m < v1;                      // strict: the lowest group id wins ties
+                        v2 = fminf(v2, fmaxf(v1, m));
+                        g1 = lt ? c * (16 / kGroupF) + sg : g1;
+                        v1 = fminf(v1, m);
+                    }
                 }
                 ptx::tc_fence_before();
                 __syncwarp();
@@ -216,10 +220,17 @@ match_screen_f_kernel(const __grid_constant__ CUtensorMap tm_desc, const __grid_
                 args.rp_v2[e] = v2;
                 args.rp_g[e] = static_cast<uint8_t>(g1);
                 e += kTileQ;
-            }
-            float* cr = args.colraw + args.pairs[p].cr_base + (static_cast<long long>(blk) * kBlockT + half * kHalfT) * kTileQ + m_local;
+                // column minima leave the registers every kFlushTiles query tiles: a lane class then holds at most
+                // kFlushTiles rows {(kFlushTiles tg + j) 128 + lane}, which is what the resolve kernel recomputes exactly
+                if ((t % kFlushTiles) == kFlushTiles - 1 || t == ntiles - 1) {
+                    float* dst = cr + static_cast<long long>(t / kFlushTiles) * kTileQ;
 #pragma unroll
-            for (int i = 0; i < kHalfT; ++i) cr[static_cast<long long>(i) * kTileQ] = cmin[i];
+                    for (int i = 0; i < kHalfT; ++i) {
+                        dst[static_cast<long long>(i) * n_tg * kTileQ] = cmin[i];
+                        cmin[i] = kHuge * 4.0f;
+                    }
+                }
+            }
         }
     }
 

@@ -39,6 +39,8 @@ struct MatchWork {
     unsigned int* col_key;
     int* row_cnt;  int* col_cnt;
     int* row_list; int* col_list;
+    const int* row_blk_pair;            // float screening path: pair (chunk-relative) of every block of kRowPad query rows
+    const int* col_blk_pair;            //                       ... of every block of kRowPad train columns
     int max_hb;                         // largest number of 128-column half blocks of a pair of the chunk
     // rows / columns whose screening result was ambiguous: (pair << 33 | dir << 32 | index), counted by n_flag
     unsigned long long* col_cells;      // float path: 16 B per train column (0xff-filled): merge cell of exact_tile_kernel

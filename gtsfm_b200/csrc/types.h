@@ -16,6 +16,8 @@ constexpr float kHuge = 1.2676506e30f;   // 2^100: squared norm given to padding
 // below 2 kF16MaxNorm2 = 2048 < kF16Never / 2, the half squared norm given to padding / NaN / ineligible rows
 constexpr float kF16MaxNorm2 = 1024.0f;
 constexpr float kF16Never = 32768.0f;
+constexpr int kGroupF = 4;               // float path: train columns per group of the row partials (32 groups per half block)
+constexpr int kFlushTiles = 4;           // float path: query tiles per column-minimum flush (a lane class holds <= 4 rows)
 constexpr int kImgFlagInts = 4;          // ints per image in the flag array written by the prepare kernel
 
 // One image pair of a chunk.  Row indices are rows of the descriptor store.
@@ -27,7 +29,7 @@ struct PairDesc {
     int path;                // 0 = integer descriptors (tensor-core screening is exact), 1 = float (exact fp32 scan),
                              // 2 = float, fp16 tensor-core screening + exact recompute of the winning group (ratio test off)
     long long rp_base;       // entry offset into the row-partial arrays: [nt_pad / kHalfT][nq_pad]
-    long long cr_base;       // float offset into colraw: [nt_pad][kTileQ]
+    long long cr_base;       // float offset into colraw: [nt_pad][kTileQ]; path 2: [nt_pad][ceil(nq_pad / 512)][kTileQ]
     long long out_base;      // offset of this pair's slot in the per-query-row arrays and the match slot (capacity nq_pad)
     long long cb_base;       // offset of this pair's slot in the per-train-column arrays (capacity nt_pad)
     int img_q, img_t;        // image slots (for keypoints / calibration)
