@@ -281,6 +281,21 @@ def run_b200(args):
     step_ms = max(ms, wall * 1e3) / args.steps
     value = world * P / (step_ms / 1e3)
 
+    # ---- the stage after verify() in run_2view (GT metrics + InlierSupportProcessor), timed on its own:
+    # it is not part of BASELINE's metric, so it stays outside `value` / `e2e`
+    gt = [scene.relative_pose(int(a), int(b)) for a, b in pairs]
+    gt_R, gt_t = np.stack([g[0] for g in gt]), np.stack([g[1] for g in gt])
+    rep = ctx.two_view_report_batch(P, int(off[-1]), scene.threshold_px, 15, 0.1, gt_R, gt_t)
+    ctx.event_record(2)
+    rep = ctx.two_view_report_batch(P, int(off[-1]), scene.threshold_px, 15, 0.1, gt_R, gt_t)
+    ctx.event_record(3)
+    report_ms = ctx.event_elapsed_ms(2, 3)
+    ok_pairs = out["status"] == 0
+    report_extra = {"ms_per_pass_incl_result_copies": report_ms, "pairs_kept_by_inlier_support": int(rep["keep"].sum()),
+                    "median_R_error_deg": float(np.nanmedian(rep["R_error_deg"])) if ok_pairs.any() else None,
+                    "median_U_error_deg": float(np.nanmedian(rep["U_error_deg"])) if ok_pairs.any() else None,
+                    "gt_correct_fraction_of_verified": float(rep["num_inliers_gt"].sum() / max(int(out["n_inliers"][ok_pairs].sum()), 1))}
+
     # ---- end-to-end leg: pinned host buffers -> device -> results on the host, every step
     def e2e_step():
         upload()
@@ -330,7 +345,8 @@ def run_b200(args):
                            "parallelism": f"pairs sharded over {world} GPU(s), NCCL all_gather of result records" if world > 1 else "1 GPU"},
                 "roofline": roofline, "cpu_baseline": cpu,
                 "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": int(d2h_bytes)},
-                "gpu_launches": int(launches), "clocks": clk, "device_event_ms_per_step": ms / args.steps}
+                "gpu_launches": int(launches), "clocks": clk, "device_event_ms_per_step": ms / args.steps,
+                "two_view_report": report_extra}
         print(json.dumps(line), file=_REAL_STDOUT, flush=True)
     ctx.close()
     if world > 1:

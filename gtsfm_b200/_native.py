@@ -17,7 +17,7 @@ LIB_PATH = os.path.join(_HERE, "libgtsfm_b200.so")
 EXPORTS = (
     "gtsfm_ctx_create", "gtsfm_ctx_destroy", "gtsfm_last_error", "gtsfm_ctx_set_workspace", "gtsfm_kernel_launches", "gtsfm_ctx_set_float_screening",
     "gtsfm_store_clear", "gtsfm_image_upload", "gtsfm_match_batch", "gtsfm_match_fetch", "gtsfm_ransac_samples", "gtsfm_ransac_samples_k",
-    "gtsfm_verify_batch", "gtsfm_match_pair", "gtsfm_verify_pair", "gtsfm_debug_fetch",
+    "gtsfm_verify_batch", "gtsfm_two_view_report_batch", "gtsfm_match_pair", "gtsfm_verify_pair", "gtsfm_debug_fetch",
     "gtsfm_profile_enable", "gtsfm_profile_get", "gtsfm_event_record", "gtsfm_event_elapsed_ms", "gtsfm_verify_stats",
     "gtsfm_host_alloc", "gtsfm_host_free", "gtsfm_match_fetch_async", "gtsfm_sync",
 )
@@ -39,6 +39,14 @@ class VerifyParams(ctypes.Structure):
         ("pair_keys", ctypes.c_void_p),
         ("samples", ctypes.c_void_p),
         ("estimate_fundamental", ctypes.c_int),
+    ]
+
+
+class ReportParams(ctypes.Structure):
+    _fields_ = [
+        ("dist_threshold_px", ctypes.c_double),
+        ("min_num_inliers_est_model", ctypes.c_int),
+        ("min_inlier_ratio_est_model", ctypes.c_double),
     ]
 
 
@@ -83,6 +91,8 @@ def lib() -> ctypes.CDLL:
                                                  ctypes.c_void_p]
             L.gtsfm_verify_batch.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p,
                                              ctypes.POINTER(VerifyParams)] + [ctypes.c_void_p] * 6
+            L.gtsfm_two_view_report_batch.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p,
+                                                      ctypes.POINTER(ReportParams)] + [ctypes.c_void_p] * 8
             L.gtsfm_match_pair.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int,
                                            ctypes.c_int, ctypes.c_double, ctypes.c_void_p, ctypes.POINTER(ctypes.c_int32)]
             L.gtsfm_verify_pair.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int,
@@ -290,6 +300,24 @@ class Context:
         self._check(self._L.gtsfm_verify_batch(self._h, _ptr(pairs), P, _ptr(match_idx), _ptr(match_offsets), ctypes.byref(params),
                                                _ptr(R), _ptr(t), _ptr(ninl), _ptr(status), _ptr(mask), _ptr(E)))
         return dict(R=R.reshape(P, 3, 3), t=t, n_inliers=ninl, status=status, mask=mask[: int(total or 0)], E=E.reshape(P, 3, 3))
+
+    def two_view_report_batch(self, n_pairs: int, total: int, dist_threshold_px: float, min_num_inliers_est_model: int,
+                              min_inlier_ratio_est_model: float, gt_i2Ri1: Optional[np.ndarray] = None,
+                              gt_i2ti1: Optional[np.ndarray] = None):
+        """Post-verification report of the pairs of the last verify_batch (gtsfm_two_view_report_batch)."""
+        P = int(n_pairs)
+        prm = ReportParams(float(dist_threshold_px), int(min_num_inliers_est_model), float(min_inlier_ratio_est_model))
+        if gt_i2Ri1 is not None:
+            gt_i2Ri1 = np.ascontiguousarray(gt_i2Ri1, np.float64).reshape(P, 9)
+            gt_i2ti1 = np.ascontiguousarray(gt_i2ti1, np.float64).reshape(P, 3)
+        dist = np.full(max(int(total), 1), np.nan); gmask = np.zeros(max(int(total), 1), np.uint8)
+        n_gt = np.zeros(P, np.int32); keep = np.zeros(P, np.int32)
+        in_avg = np.zeros(P); out_avg = np.zeros(P); r_err = np.zeros(P); u_err = np.zeros(P)
+        self._check(self._L.gtsfm_two_view_report_batch(self._h, P, _ptr(gt_i2Ri1), _ptr(gt_i2ti1), ctypes.byref(prm), _ptr(dist),
+                                                        _ptr(gmask), _ptr(n_gt), _ptr(in_avg), _ptr(out_avg), _ptr(r_err),
+                                                        _ptr(u_err), _ptr(keep)))
+        return dict(dist_sq=dist[: int(total)], gt_mask=gmask[: int(total)], num_inliers_gt=n_gt, inlier_avg_err=in_avg,
+                    outlier_avg_err=out_avg, R_error_deg=r_err, U_error_deg=u_err, keep=keep)
 
     def verify_pair(self, kps1, kps2, match_idx, cal1, cal2, params: "VerifyParams"):
         kps1 = np.ascontiguousarray(kps1, np.float64).reshape(-1, 2)

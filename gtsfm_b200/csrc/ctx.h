@@ -79,8 +79,10 @@ struct gtsfm_ctx {
     void prof_end();
     int prof_collect();
 
-    // ---- verifier buffers
+    // ---- verifier buffers; state of the last gtsfm_verify_batch (read by gtsfm_two_view_report_batch)
     g2v::DevBuf v_bufs[24];
+    int verify_n = 0;
+    long long verify_total = 0;
 
     g2v::StoreView view() const;
 };

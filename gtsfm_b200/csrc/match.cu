@@ -51,6 +51,7 @@ int gtsfm_match_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, double ra
     if (r) return r;
     c->batch_n = 0;
     c->batch_total = 0;
+    c->verify_n = 0;          // the device match rows of the last verify batch are about to be overwritten
     if (total) *total = 0;
     G2V_CUDA(c, cudaStreamSynchronize(c->copy_stream));      // an asynchronous fetch of the previous batch may still read match_out
     if (n_pairs == 0) return GTSFM_OK;

@@ -38,6 +38,7 @@ int gtsfm_verify_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, const ui
 {
     if (!c || !prm || n_pairs < 0 || (n_pairs > 0 && !pairs)) return fail(c, GTSFM_E_ARG, "bad arguments");
     cudaSetDevice(c->device);
+    c->verify_n = 0;
     if (n_pairs == 0) return GTSFM_OK;
     if (prm->n_hypotheses <= 0 || prm->n_hypotheses > (1 << 20)) return fail(c, GTSFM_E_ARG, "n_hypotheses out of range");
     if (!(prm->threshold_px > 0)) return fail(c, GTSFM_E_ARG, "threshold_px must be positive");
@@ -168,6 +169,8 @@ int gtsfm_verify_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, const ui
     if (status) G2V_CUDA(c, cudaMemcpyAsync(status, vb[11].p, 4 * static_cast<size_t>(n_pairs), cudaMemcpyDeviceToHost, s));
     if (inlier_mask && total > 0) G2V_CUDA(c, cudaMemcpyAsync(inlier_mask, vb[12].p, static_cast<size_t>(total), cudaMemcpyDeviceToHost, s));
     G2V_CUDA(c, cudaStreamSynchronize(s));
+    c->verify_n = n_pairs;
+    c->verify_total = total;
     return GTSFM_OK;
 }
 

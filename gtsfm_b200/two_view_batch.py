@@ -49,6 +49,46 @@ class TwoViewBatchResult:
         return Rd, td, vd, rd
 
 
+def two_view_reports(result: TwoViewBatchResult, ctx: "_native.Context", corr_metric_dist_threshold: float,
+                     min_num_inliers_est_model: int, min_inlier_ratio_est_model: float,
+                     gt_i2Ri1: Optional[np.ndarray] = None, gt_i2ti1: Optional[np.ndarray] = None):
+    """The stage after verify() in TwoViewEstimator.run_2view (two_view_estimator.py:298-349) for every pair of the batch the
+    context verified last: GT correspondence metrics, relative-pose errors, report aggregates and the InlierSupportProcessor
+    decision, computed on the device in one launch.  Returns (reports, keep): a TwoViewEstimationReport per pair (the
+    pre-ISP report) and the boolean keep mask; a dropped pair gets (None, None, empty, report with 0 inliers) from
+    post_isp_results()."""
+    from gtsfm_b200.common.two_view_estimation_report import TwoViewEstimationReport
+    P = len(result.pairs)
+    o = result.match_offsets
+    rep = ctx.two_view_report_batch(P, int(o[-1]), corr_metric_dist_threshold, min_num_inliers_est_model,
+                                    min_inlier_ratio_est_model, gt_i2Ri1, gt_i2ti1)
+    have_gt = gt_i2Ri1 is not None
+    reports = []
+    for p in range(P):
+        m = result.matches[o[p]:o[p + 1]]
+        ok = result.status[p] == 0
+        mask = result.inlier_mask[o[p]:o[p + 1]] == 1 if ok else np.zeros(len(m), bool)
+        v = m[mask] if ok else np.array([], dtype=np.uint64)
+        ratio = float(mask.mean()) if (ok and mask.size) else 0.0
+        if have_gt and ok and len(v) > 0:
+            gm = rep["gt_mask"][o[p]:o[p + 1]][mask].astype(bool)
+            err = rep["dist_sq"][o[p]:o[p + 1]][mask]
+            n_gt = int(rep["num_inliers_gt"][p])
+            reports.append(TwoViewEstimationReport(
+                v_corr_idxs=v, num_inliers_est_model=len(v), inlier_ratio_est_model=ratio, num_inliers_gt_model=n_gt,
+                inlier_ratio_gt_model=n_gt / len(v), v_corr_idxs_inlier_mask_gt=gm, R_error_deg=float(rep["R_error_deg"][p]),
+                U_error_deg=float(rep["U_error_deg"][p]), reproj_error_gt_model=err,
+                inlier_avg_reproj_error_gt_model=float(rep["inlier_avg_err"][p]),
+                outlier_avg_reproj_error_gt_model=float(rep["outlier_avg_err"][p])))
+        else:
+            reports.append(TwoViewEstimationReport(
+                v_corr_idxs=v, num_inliers_est_model=len(v), inlier_ratio_est_model=ratio, num_inliers_gt_model=0,
+                inlier_ratio_gt_model=float("nan"), R_error_deg=float(rep["R_error_deg"][p]) if (have_gt and ok) else None,
+                U_error_deg=float(rep["U_error_deg"][p]) if (have_gt and ok) else None,
+                inlier_avg_reproj_error_gt_model=float("nan"), outlier_avg_reproj_error_gt_model=float("nan")))
+    return reports, rep["keep"].astype(bool), rep
+
+
 def shard_pairs(pairs: np.ndarray, n_shards: int, cost: Optional[np.ndarray] = None) -> List[np.ndarray]:
     """Contiguous, cost-balanced split of an i1-sorted pair list: returns index arrays per shard.
     Contiguity keeps each shard's image set compact, so only those images have to be placed on that GPU."""

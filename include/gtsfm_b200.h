@@ -121,6 +121,32 @@ int gtsfm_verify_batch(gtsfm_ctx* ctx, const int32_t* pairs, int n_pairs, const 
                        const int64_t* match_offsets, const gtsfm_verify_params* params, double* R, double* t,
                        int32_t* n_inliers, int32_t* status, uint8_t* inlier_mask, double* E);
 
+/* ---- post-verification report over a batch of pairs ----------------------------------------- */
+typedef struct gtsfm_report_params {
+    double dist_threshold_px;           /* TwoViewEstimator(corr_metric_dist_threshold): correct <=> sampson^2 < threshold^2 */
+    int min_num_inliers_est_model;      /* InlierSupportProcessor(min_num_inliers_est_model) */
+    double min_inlier_ratio_est_model;  /* InlierSupportProcessor(min_inlier_ratio_est_model) */
+} gtsfm_report_params;
+
+/* The stage that follows verify() in TwoViewEstimator.run_2view (gtsfm/two_view_estimator.py:298-349), for every pair of
+ * the last gtsfm_verify_batch (same order; its match rows, inlier mask and poses are still on the device):
+ *   - compute_correspondence_metrics / epipolar_inlier_correspondences (gtsfm/utils/metrics.py:38-128): squared Sampson
+ *     distance in pixels of every VERIFIED correspondence against F_gt = K2^-T [t]x R K1^-1 (utils/verification.py:113-126,
+ *     170-214), correct <=> distance^2 < dist_threshold_px^2;
+ *   - compute_relative_pose_metrics (utils/geometry_comparisons.py:266-309): rotation / translation-direction error in degrees;
+ *   - the aggregates of generate_two_view_report (two_view_estimator.py:354-393);
+ *   - InlierSupportProcessor.run_inlier_support (frontend/inlier_support_processor.py:39-95): keep[p] = 0 when the inlier
+ *     ratio or the inlier count is insufficient (or verification failed).
+ * gt_i2Ri1 (P, 9) row-major and gt_i2ti1 (P, 3) are the ground-truth relative poses, both NULL when there is none (then only
+ * keep[] is meaningful, the metrics are NaN / 0).  Outputs (any may be NULL): dist_sq (total) float64 aligned with the match
+ * rows (NaN for rows that were not verified), gt_mask (total) uint8, num_inliers_gt (P), inlier_avg_err / outlier_avg_err (P)
+ * mean squared distance of the correct / incorrect verified correspondences (NaN when there are none), R_error_deg /
+ * U_error_deg (P), keep (P). */
+int gtsfm_two_view_report_batch(gtsfm_ctx* ctx, int n_pairs, const double* gt_i2Ri1, const double* gt_i2ti1,
+                                const gtsfm_report_params* params, double* dist_sq, uint8_t* gt_mask, int32_t* num_inliers_gt,
+                                double* inlier_avg_err, double* outlier_avg_err, double* R_error_deg, double* U_error_deg,
+                                int32_t* keep);
+
 /* ---- single-pair conveniences used by the MatcherBase / VerifierBase plugin classes ---------------------------- */
 /* TwoWayMatcher.match for one pair from host arrays.  out capacity: min(n1, n2) rows of 2 uint32. */
 int gtsfm_match_pair(gtsfm_ctx* ctx, const float* desc1, int n1, const float* desc2, int n2, int dim, double ratio,

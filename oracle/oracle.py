@@ -216,3 +216,54 @@ def verify_pair_F(kp1: np.ndarray, kp2: np.ndarray, match_indices: np.ndarray, c
                                     _d(F), _d(E), mask.ctypes.data_as(_bp), _d(R), _d(t), info.ctypes.data_as(_ip))
     return dict(status=int(st), F=F.reshape(3, 3), E=E.reshape(3, 3), mask=mask[:M], R=R.reshape(3, 3), t=t,
                 ninl=int(info[0]), best_id=int(info[1]), ncand=int(info[2]))
+
+
+# ---------------------------------------------------------------- post-verification report
+def essential_to_fundamental(R: np.ndarray, t: np.ndarray, cal1, cal2) -> np.ndarray:
+    """essential_to_fundamental_matrix (utils/verification.py:113-126) with i2Ei1 = EssentialMatrix(R, Unit3(t)) = [t/|t|]x R."""
+    t = np.asarray(t, np.float64) / np.linalg.norm(t)
+    tx = np.array([[0, -t[2], t[1]], [t[2], 0, -t[0]], [-t[1], t[0], 0]])
+    K1 = np.array([[cal1[0], 0, cal1[3]], [0, cal1[0], cal1[4]], [0, 0, 1.0]])
+    K2 = np.array([[cal2[0], 0, cal2[3]], [0, cal2[0], cal2[4]], [0, 0, 1.0]])
+    return np.linalg.inv(K2.T) @ (tx @ np.asarray(R, np.float64)) @ np.linalg.inv(K1)
+
+
+def sampson_sq_numpy(c1: np.ndarray, c2: np.ndarray, F: np.ndarray) -> np.ndarray:
+    """compute_epipolar_distances_sq_sampson (utils/verification.py:170-214), line for line in numpy."""
+    h1 = np.c_[c1, np.ones(len(c1))]
+    h2 = np.c_[c2, np.ones(len(c2))]
+    lines_i2 = h1 @ F.T                      # F x1
+    lines_i1 = h2 @ F                        # F^T x2
+    num = np.square(np.sum(h1 * lines_i1, axis=1))
+    den = np.sum(np.square(lines_i1[:, :2]), axis=1) + np.sum(np.square(lines_i2[:, :2]), axis=1)
+    return num / den
+
+
+def two_view_report(kp1, kp2, v_corr_idxs, n_putative, R_est, t_est, cal1, cal2, gt_R, gt_t, dist_threshold,
+                    min_num_inliers, min_inlier_ratio) -> dict:
+    """epipolar_inlier_correspondences (utils/metrics.py:100-128) + compute_relative_pose_metrics
+    (utils/geometry_comparisons.py:266-309) + generate_two_view_report aggregates (two_view_estimator.py:354-393) +
+    InlierSupportProcessor.run_inlier_support (frontend/inlier_support_processor.py:39-95) for one pair."""
+    from scipy.spatial.transform import Rotation
+    v = np.asarray(v_corr_idxs).reshape(-1, 2)
+    n_est = len(v) if R_est is not None else 0
+    ratio = n_est / n_putative if (R_est is not None and n_putative) else 0.0
+    keep = not (ratio < min_inlier_ratio) and not (n_est > 0 and n_est < min_num_inliers) and R_est is not None
+    out = dict(keep=keep, dist_sq=None, gt_mask=None, num_inliers_gt=0, inlier_avg=float("nan"), outlier_avg=float("nan"),
+               R_error_deg=None, U_error_deg=None)
+    if gt_R is None or R_est is None:
+        return out
+    out["R_error_deg"] = float(np.rad2deg(np.linalg.norm(Rotation.from_matrix(np.asarray(R_est).T @ np.asarray(gt_R)).as_rotvec())))
+    u = np.asarray(gt_t, np.float64) / np.linalg.norm(gt_t)
+    out["U_error_deg"] = float(np.rad2deg(np.arccos(np.clip(np.dot(np.asarray(t_est), u), -1, 1))))
+    if n_est == 0:
+        return out
+    F = essential_to_fundamental(gt_R, gt_t, cal1, cal2)
+    d2 = sampson_sq_numpy(np.asarray(kp1, np.float64)[v[:, 0]], np.asarray(kp2, np.float64)[v[:, 1]], F)
+    gm = d2 < dist_threshold ** 2
+    out.update(dist_sq=d2, gt_mask=gm, num_inliers_gt=int(np.count_nonzero(gm)))
+    with np.errstate(all="ignore"):
+        out["inlier_avg"] = float(np.mean(d2[gm])) if gm.any() else float("nan")
+        rest = d2[~gm]
+        out["outlier_avg"] = float(np.nanmean(rest)) if np.any(~np.isnan(rest)) else float("nan")
+    return out

@@ -390,3 +390,78 @@ def test_fundamental_mode_plugin(ctx):
     i2Ri1, i2Ui1, v_corr, ratio = v.verify(Keypoints(kp1), Keypoints(kp2), mi, c, c)
     assert i2Ri1 is not None and v_corr.dtype == mi.dtype and 0.5 < ratio <= 0.75
     assert rot_angle_deg(i2Ri1.matrix(), R) < 2.0
+
+
+# ------------------------------------------------------------------------------ post-verification report (8(f) rank 2)
+def test_two_view_report_batch_vs_oracle(ctx):
+    """GT correspondence metrics, relative-pose errors, report aggregates and the InlierSupportProcessor decision of every
+    pair of a ragged batch (one pair fails verification, one has few inliers) against the numpy restatement."""
+    from oracle import oracle as O
+    rng = np.random.default_rng(31)
+    sizes = [400, 5, 1500, 30, 900]
+    out_fracs = [0.3, 0.0, 0.6, 0.0, 0.97]
+    scenes = [make_pixel_scene(rng, max(n, 1), out_frac=f) for n, f in zip(sizes, out_fracs)]
+    ctx.clear()
+    for k, (kp1, kp2, _, _, cal) in enumerate(scenes):
+        ctx.upload_image(2 * k, None, kp1, cal)
+        ctx.upload_image(2 * k + 1, None, kp2, cal)
+    P = len(sizes)
+    pairs = np.array([(2 * k, 2 * k + 1) for k in range(P)], np.int32)
+    mi = np.concatenate([np.c_[np.arange(n), np.arange(n)] for n in sizes]).astype(np.uint32)
+    off = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int64)
+    out = ctx.verify_batch(pairs, params(4.0, 256, seed=2), mi, off)
+    gt_R = np.stack([s[2] for s in scenes])
+    gt_t = np.stack([s[3] * 2.5 for s in scenes])             # any scale: Unit3 normalises
+    thr, min_inl, min_ratio = 1.5, 15, 0.1
+    rep = ctx.two_view_report_batch(P, int(off[-1]), thr, min_inl, min_ratio, gt_R, gt_t)
+    for k, n in enumerate(sizes):
+        kp1, kp2, _, _, cal = scenes[k]
+        ok = out["status"][k] == 0
+        mask = out["mask"][off[k]:off[k + 1]] == 1
+        v = mi[off[k]:off[k + 1]][mask] if ok else np.zeros((0, 2), np.uint32)
+        ref = O.two_view_report(kp1, kp2, v, n, out["R"][k] if ok else None, out["t"][k] if ok else None, cal, cal,
+                                gt_R[k], gt_t[k], thr, min_inl, min_ratio)
+        assert bool(rep["keep"][k]) == ref["keep"], k
+        d = rep["dist_sq"][off[k]:off[k + 1]]
+        g = rep["gt_mask"][off[k]:off[k + 1]]
+        if not ok or len(v) == 0:
+            assert np.isnan(d).all() and not g.any() and rep["num_inliers_gt"][k] == 0
+            continue
+        assert np.isnan(d[~mask]).all() and not g[~mask].any()
+        np.testing.assert_allclose(d[mask], ref["dist_sq"], rtol=1e-9, atol=1e-18)
+        band = np.abs(ref["dist_sq"] / thr ** 2 - 1.0) < 1e-9
+        assert ((g[mask] == 1) == ref["gt_mask"])[~band].all()
+        assert abs(int(rep["num_inliers_gt"][k]) - ref["num_inliers_gt"]) <= int(band.sum())
+        for a, b in ((rep["inlier_avg_err"][k], ref["inlier_avg"]), (rep["outlier_avg_err"][k], ref["outlier_avg"])):
+            assert (np.isnan(a) and np.isnan(b)) or abs(a - b) <= 1e-9 * max(abs(b), 1e-30)
+        assert abs(rep["R_error_deg"][k] - ref["R_error_deg"]) < 1e-7
+        assert abs(rep["U_error_deg"][k] - ref["U_error_deg"]) < 1e-6
+    assert not rep["keep"][1] and rep["keep"][0] and rep["keep"][2]          # too few matches fails, good pairs pass
+    # without ground truth only the InlierSupportProcessor decision is defined
+    rep2 = ctx.two_view_report_batch(P, int(off[-1]), thr, min_inl, min_ratio)
+    np.testing.assert_array_equal(rep2["keep"], rep["keep"])
+    assert np.isnan(rep2["dist_sq"]).all() and np.isnan(rep2["R_error_deg"]).all()
+
+
+def test_two_view_reports_python_layer(ctx):
+    """two_view_reports(): TwoViewEstimationReport objects + keep mask; agree with the per-pair reference-style classes."""
+    from gtsfm_b200 import synthetic
+    from gtsfm_b200.common.two_view_estimation_report import generate_two_view_report
+    from gtsfm_b200.frontend.inlier_support_processor import InlierSupportProcessor
+    from gtsfm_b200.two_view_batch import run_two_view_batch, two_view_reports
+    scene = synthetic.make_scene(n_images=4, n_kps=1024, seed=5)
+    res = run_two_view_batch(scene.descriptors, scene.keypoints, [scene.cal] * 4, scene.pairs, ratio_test_threshold=0.8,
+                             estimation_threshold_px=4.0, num_hypotheses=256, seed=1, ctx=ctx)
+    gt = [scene.relative_pose(int(a), int(b)) for a, b in scene.pairs]
+    reports, keep, _ = two_view_reports(res, ctx, 4.0, 15, 0.1, np.stack([g[0] for g in gt]), np.stack([g[1] for g in gt]))
+    isp = InlierSupportProcessor(15, 0.1)
+    Rd, td, vd, rd = res.two_view_dicts()
+    for p, (a, b) in enumerate(scene.pairs):
+        r = reports[p]
+        key = (int(a), int(b))
+        ref = generate_two_view_report(rd[key], vd[key], r.R_error_deg, r.U_error_deg, r.v_corr_idxs_inlier_mask_gt, r.reproj_error_gt_model)
+        assert ref.num_inliers_gt_model == r.num_inliers_gt_model and ref.num_inliers_est_model == r.num_inliers_est_model
+        assert abs(ref.inlier_avg_reproj_error_gt_model - r.inlier_avg_reproj_error_gt_model) < 1e-9
+        assert r.R_error_deg < 1.0 and r.num_inliers_gt_model > 0.9 * r.num_inliers_est_model
+        kept = isp.run_inlier_support(Rd[key], td[key], vd[key], r)[0] is not None
+        assert kept == bool(keep[p])

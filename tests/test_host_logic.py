@@ -161,3 +161,30 @@ def test_record_packing_round_trips_without_a_process_group():
     assert (table[:, 0:9] == res.R.reshape(-1, 9)).all() and (table[:, 9:12] == res.t).all()
     assert (table[:, 12] == res.n_inliers).all() and (table[:, 13] == res.status).all()
     assert (table[:, 14] == np.diff(res.match_offsets)).all()
+
+
+def test_inlier_support_processor_decisions():
+    """inlier_support_processor.py:39-95: ratio test first, then the count test for valid models."""
+    from gtsfm_b200.common.two_view_estimation_report import TwoViewEstimationReport, generate_two_view_report
+    from gtsfm_b200.frontend.inlier_support_processor import InlierSupportProcessor
+    isp = InlierSupportProcessor(min_num_inliers_est_model=15, min_inlier_ratio_est_model=0.1)
+    v = np.zeros((20, 2), np.uint32)
+    ok = isp.run_inlier_support("R", "U", v, TwoViewEstimationReport(v_corr_idxs=v, num_inliers_est_model=20, inlier_ratio_est_model=0.5))
+    assert ok[0] == "R" and ok[2] is v
+    low_ratio = isp.run_inlier_support("R", "U", v, TwoViewEstimationReport(v_corr_idxs=v, num_inliers_est_model=20, inlier_ratio_est_model=0.05))
+    assert low_ratio[0] is None and low_ratio[2].size == 0 and low_ratio[3].num_inliers_est_model == 0
+    few = isp.run_inlier_support("R", "U", v[:10], TwoViewEstimationReport(v_corr_idxs=v[:10], num_inliers_est_model=10, inlier_ratio_est_model=0.5))
+    assert few[0] is None
+    rep = generate_two_view_report(0.5, v, 1.0, 2.0, np.array([True] * 15 + [False] * 5), np.r_[np.full(15, 0.25), np.full(4, 9.0), np.nan])
+    assert rep.num_inliers_gt_model == 15 and rep.inlier_ratio_gt_model == 0.75
+    assert rep.inlier_avg_reproj_error_gt_model == 0.25 and rep.outlier_avg_reproj_error_gt_model == 9.0
+
+
+def test_report_oracle_matches_the_pinned_sampson_restatement():
+    """The numpy restatement of compute_epipolar_distances_sq_sampson used by the report oracle equals the C oracle's
+    sampson_sq (itself pinned against the reference's known answers, tests/test_oracle_verify.py)."""
+    from oracle import oracle as O
+    rng = np.random.default_rng(2)
+    F = rng.standard_normal((3, 3))
+    c1, c2 = rng.uniform(0, 1000, (50, 2)), rng.uniform(0, 1000, (50, 2))
+    np.testing.assert_allclose(O.sampson_sq_numpy(c1, c2, F), O.sampson_sq(F, c1, c2), rtol=1e-10)
