@@ -16,7 +16,7 @@ LIB_PATH = os.path.join(_HERE, "libgtsfm_b200.so")
 # every symbol include/gtsfm_b200.h declares
 EXPORTS = (
     "gtsfm_ctx_create", "gtsfm_ctx_destroy", "gtsfm_last_error", "gtsfm_ctx_set_workspace", "gtsfm_kernel_launches", "gtsfm_ctx_set_float_screening",
-    "gtsfm_store_clear", "gtsfm_image_upload", "gtsfm_match_batch", "gtsfm_match_fetch", "gtsfm_ransac_samples", "gtsfm_ransac_samples_k",
+    "gtsfm_store_clear", "gtsfm_image_upload", "gtsfm_image_upload_u8", "gtsfm_match_pair_u8", "gtsfm_match_batch", "gtsfm_match_fetch", "gtsfm_ransac_samples", "gtsfm_ransac_samples_k",
     "gtsfm_verify_batch", "gtsfm_two_view_report_batch", "gtsfm_match_pair", "gtsfm_verify_pair", "gtsfm_debug_fetch",
     "gtsfm_profile_enable", "gtsfm_profile_get", "gtsfm_event_record", "gtsfm_event_elapsed_ms", "gtsfm_verify_stats",
     "gtsfm_host_alloc", "gtsfm_host_free", "gtsfm_match_fetch_async", "gtsfm_sync",
@@ -83,6 +83,10 @@ def lib() -> ctypes.CDLL:
             L.gtsfm_verify_stats.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_int64), ctypes.c_int]
             L.gtsfm_image_upload.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_int,
                                              ctypes.c_void_p, ctypes.c_void_p]
+            L.gtsfm_image_upload_u8.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_int,
+                                                ctypes.c_void_p, ctypes.c_void_p]
+            L.gtsfm_match_pair_u8.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int,
+                                              ctypes.c_int, ctypes.c_double, ctypes.c_void_p, ctypes.POINTER(ctypes.c_int32)]
             L.gtsfm_match_batch.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_double, ctypes.c_void_p,
                                             ctypes.POINTER(ctypes.c_int64)]
             L.gtsfm_match_fetch.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
@@ -214,6 +218,20 @@ class Context:
         self._keep += [desc, kps, calv]
         self._check(self._L.gtsfm_image_upload(self._h, int(image_id), _ptr(desc), int(n), int(dim), _ptr(kps), _ptr(calv)))
 
+    def upload_image_u8(self, image_id: int, desc: np.ndarray, kps: Optional[np.ndarray] = None, cal=None):
+        """Binary descriptors (n, nbytes) uint8 for the HAMMING distance; kps / cal as in upload_image."""
+        desc = np.ascontiguousarray(desc, np.uint8)
+        if desc.ndim != 2:
+            raise ValueError("descriptors must be (n, nbytes)")
+        n, nbytes = desc.shape
+        if kps is not None:
+            kps = np.ascontiguousarray(kps, np.float64).reshape(-1, 2)
+            if kps.shape[0] != n:
+                raise ValueError("keypoints and descriptors disagree on n")
+        calv = None if cal is None else np.ascontiguousarray(cal, np.float64)
+        self._keep += [desc, kps, calv]
+        self._check(self._L.gtsfm_image_upload_u8(self._h, int(image_id), _ptr(desc), int(n), int(nbytes), _ptr(kps), _ptr(calv)))
+
     # ---- matcher
     def match_batch(self, pairs: np.ndarray, ratio: Optional[float], fetch=True, reuse_outputs: bool = False):
         """Returns (matches (total, 2) uint32, offsets (P + 1) int64); fetch=False leaves the matches on the device.
@@ -249,6 +267,20 @@ class Context:
         cnt = ctypes.c_int32(0)
         r = float("nan") if ratio is None else float(ratio)
         self._check(self._L.gtsfm_match_pair(self._h, _ptr(d1), n1, _ptr(d2), n2, dim, r, _ptr(out), ctypes.byref(cnt)))
+        return out[: cnt.value].copy()
+
+    def match_pair_u8(self, d1: np.ndarray, d2: np.ndarray, ratio: Optional[float]) -> np.ndarray:
+        """TwoWayMatcher(HAMMING).match for one pair of (n, nbytes) uint8 arrays."""
+        d1 = np.ascontiguousarray(d1, np.uint8)
+        d2 = np.ascontiguousarray(d2, np.uint8)
+        if d1.size == 0 or d2.size == 0:
+            return np.empty((0, 2), np.uint32)
+        n1, nbytes = d1.shape
+        n2 = d2.shape[0]
+        out = np.empty((min(n1, n2), 2), np.uint32)
+        cnt = ctypes.c_int32(0)
+        r = float("nan") if ratio is None else float(ratio)
+        self._check(self._L.gtsfm_match_pair_u8(self._h, _ptr(d1), n1, _ptr(d2), n2, nbytes, r, _ptr(out), ctypes.byref(cnt)))
         return out[: cnt.value].copy()
 
     PROFILE_SLOTS = ("prepare", "screen", "resolve_rows", "resolve_cols", "exact_scan", "match_finalize", "gather",

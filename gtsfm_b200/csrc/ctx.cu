@@ -132,7 +132,7 @@ int store_sync_flags(gtsfm_ctx* c)
     G2V_CUDA(c, cudaMemcpyAsync(h.data(), c->img_flags.p, kImgFlagInts * n * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
     G2V_CUDA(c, cudaStreamSynchronize(c->stream));
     for (size_t i = 0; i < n; ++i) {
-        c->images[i].path = (h[kImgFlagInts * i] & 1) ? 1 : 0;
+        c->images[i].path = (h[kImgFlagInts * i] & 4) ? 3 : (h[kImgFlagInts * i] & 1) ? 1 : 0;
         c->images[i].f16_ok = (h[kImgFlagInts * i] & 2) ? 0 : 1;
         c->images[i].n_valid = h[kImgFlagInts * i + 1];
         std::memcpy(&c->images[i].max_norm2, &h[kImgFlagInts * i + 2], 4);
@@ -305,6 +305,7 @@ int gtsfm_store_clear(gtsfm_ctx* c)
     c->rows_used = 0;
     c->dim = 0;
     c->kpad = 0;
+    c->binary = -1;
     c->flags_dirty = false;
     c->maps_valid = false;
     c->batch_n = 0;
@@ -319,6 +320,10 @@ int gtsfm_image_upload(gtsfm_ctx* c, int image_id, const float* desc, int n, int
     if (image_id != static_cast<int>(c->images.size())) return fail(c, GTSFM_E_ARG, "image ids must be dense and uploaded in order");
     if (n < 0 || dim < 0 || (n > 0 && dim > 0 && !desc)) return fail(c, GTSFM_E_ARG, "bad descriptor array");
     if (dim > 4096) return fail(c, GTSFM_E_UNSUPPORTED, "descriptor dimension above 4096");
+    if (dim > 0 && n > 0) {
+        if (c->binary == 1) return fail(c, GTSFM_E_ARG, "this store holds binary (HAMMING) descriptors");
+        c->binary = 0;
+    }
     if (c->dim == 0 && dim > 0) {
         if (c->rows_used != 0) return fail(c, GTSFM_E_ARG, "descriptor dimension changed inside one store");
         c->dim = dim;
@@ -372,6 +377,44 @@ int gtsfm_image_upload(gtsfm_ctx* c, int image_id, const float* desc, int n, int
         G2V_CUDA(c, cudaMemcpyAsync(c->kps.as<double2>() + rec.row0, kps, static_cast<size_t>(n) * 16, cudaMemcpyHostToDevice, c->stream));
     c->images.push_back(rec);
     c->rows_used += n_rows;
+    return GTSFM_OK;
+}
+
+int gtsfm_image_upload_u8(gtsfm_ctx* c, int image_id, const uint8_t* desc, int n, int nbytes, const double* kps, const double* cal)
+{
+    if (!c) return GTSFM_E_ARG;
+    cudaSetDevice(c->device);
+    if (image_id != static_cast<int>(c->images.size())) return fail(c, GTSFM_E_ARG, "image ids must be dense and uploaded in order");
+    if (n < 0 || nbytes <= 0 || (n > 0 && !desc)) return fail(c, GTSFM_E_ARG, "bad descriptor array");
+    if (nbytes > 64) return fail(c, GTSFM_E_UNSUPPORTED, "binary descriptors above 64 bytes");
+    if (c->binary == 0) return fail(c, GTSFM_E_ARG, "this store holds float32 (EUCLIDEAN) descriptors");
+    if (c->dim == 0) {
+        if (c->rows_used != 0) return fail(c, GTSFM_E_ARG, "descriptor dimension changed inside one store");
+        c->dim = nbytes; c->kpad = 64; c->rows_cap = 0;
+    }
+    if (nbytes != c->dim) return fail(c, GTSFM_E_ARG, "all images of a store must share the descriptor size");
+    c->binary = 1;
+    ImageRec rec{};
+    rec.row0 = static_cast<int>(c->rows_used);
+    rec.n = n; rec.n_kps = kps ? n : 0; rec.dim = nbytes; rec.path = 3; rec.n_valid = n; rec.has_kps = kps != nullptr;
+    if (cal) std::memcpy(rec.cal, cal, sizeof(rec.cal)); else { rec.cal[0] = 1; rec.cal[1] = rec.cal[2] = rec.cal[3] = rec.cal[4] = 0; }
+    rec.n_pad = (n + kRowPad - 1) / kRowPad * kRowPad;
+    G2V_CUDA(c, c->img_flags.reserve((c->images.size() + 1) * kImgFlagInts * sizeof(int), true, c->stream));
+    const int flags[kImgFlagInts] = {4, n, 0, 0};             // bit 2: binary image; number of valid rows (uint8 has no NaN)
+    G2V_CUDA(c, cudaMemcpyAsync(c->img_flags.as<int>() + kImgFlagInts * c->images.size(), flags, sizeof(flags), cudaMemcpyHostToDevice, c->stream));
+    if (rec.n_pad > 0) {
+        int r = store_reserve_rows(c, c->rows_used + rec.n_pad);
+        if (r) return r;
+        uint8_t* dst = c->desc_u8.as<uint8_t>() + static_cast<long long>(rec.row0) * c->kpad;
+        G2V_CUDA(c, cudaMemsetAsync(dst, 0, static_cast<size_t>(rec.n_pad) * c->kpad, c->stream));
+        G2V_CUDA(c, cudaMemcpy2DAsync(dst, c->kpad, desc, nbytes, nbytes, n, cudaMemcpyHostToDevice, c->stream));
+        G2V_CUDA(c, cudaMemsetAsync(c->valid.as<uint8_t>() + rec.row0, 0, rec.n_pad, c->stream));
+        G2V_CUDA(c, cudaMemsetAsync(c->valid.as<uint8_t>() + rec.row0, 1, n, c->stream));
+    }
+    if (kps && n > 0)
+        G2V_CUDA(c, cudaMemcpyAsync(c->kps.as<double2>() + rec.row0, kps, static_cast<size_t>(n) * 16, cudaMemcpyHostToDevice, c->stream));
+    c->images.push_back(rec);
+    c->rows_used += rec.n_pad;
     return GTSFM_OK;
 }
 

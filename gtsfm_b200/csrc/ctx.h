@@ -44,6 +44,7 @@ struct gtsfm_ctx {
 
     // ---- store
     int dim = 0, kpad = 0;
+    int binary = -1;                    // -1 no descriptors yet, 0 float32 descriptors (EUCLIDEAN), 1 uint8 rows (HAMMING)
     long long rows_used = 0, rows_cap = 0;
     std::vector<g2v::ImageRec> images;
     bool flags_dirty = false;

@@ -15,6 +15,7 @@ cudaError_t launch_match_screen_f(const CUtensorMap& tm_desc, const CUtensorMap&
                                   const PairDesc* pairs, int n_pairs, int n_items, float* rp_v1, float* rp_v2, uint8_t* rp_g,
                                   float* colraw, int kpad, int n_sm, cudaStream_t stream);
 cudaError_t launch_resolve_f(const StoreView& st, const MatchWork& w, long long total_rows, long long total_cols, cudaStream_t s);
+cudaError_t launch_hamming(const StoreView& st, const MatchWork& w, long long total_rows, long long total_cols, int words, cudaStream_t s);
 cudaError_t launch_resolve_int(const StoreView& st, const MatchWork& w, int which, long long total, int max_class_rows,
                                cudaStream_t s);
 cudaError_t launch_exact_scan(const StoreView& st, const MatchWork& w, int mode, int n_jobs, cudaStream_t s);
@@ -35,6 +36,7 @@ struct Chunk {
     int items = 0, jobs = 0, max_class_rows = 0, max_hb = 0;
     int fitems = 0;          // work items of the fp16 screening kernel (path-2 pairs)
     long long rtab = 0, ctab = 0;   // offsets of the chunk's block -> pair tables
+    int hpairs = 0;                 // binary (HAMMING) pairs
 };
 }  // namespace g2v
 
@@ -87,6 +89,7 @@ int gtsfm_match_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, double ra
         const bool fits = pd.nq_pad / kTileQ <= kMaxClassRows && pd.nt_pad / kHalfT < 8192;
         pd.path = (qa.path == 0 && tb.path == 0 && screen_ok && fits) ? 0 : 1;
         if (pd.path == 1 && !empty && qa.path == 1 && tb.path == 1 && qa.f16_ok && tb.f16_ok && screen_f_ok) pd.path = 2;
+        if (qa.path == 3 || tb.path == 3) pd.path = 3;          // a store holds either binary or float32 descriptors
         pd.q_maxn2 = qa.max_norm2; pd.t_maxn2 = tb.max_norm2;
         const long long rp = pd.path != 1 ? static_cast<long long>(pd.nq_pad) * (pd.nt_pad / kHalfT) : 0;
         const int n_tg = (pd.nq_pad / kTileQ + kFlushTiles - 1) / kFlushTiles;      // path 2: column minima per group of 4 query tiles
@@ -94,6 +97,7 @@ int gtsfm_match_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, double ra
                                           : pd.path == 2 ? static_cast<long long>(pd.nt_pad) * n_tg * kTileQ : 0;
         const int items = pd.path == 0 && pd.nq > 0 ? pd.nt_pad / kBlockT : 0;
         const int fitems = pd.path == 2 && pd.nq > 0 ? pd.nt_pad / kBlockT : 0;
+        if (pd.path == 3 && pd.nq > 0) cur.hpairs += 1;
         const int jobs = pd.path == 1 && pd.nq > 0 ? (pd.nq + 31) / 32 + (pd.nt + 31) / 32 : 0;
         const long long bytes = rp * 9 + cr * 4 + static_cast<long long>(pd.nq_pad) * (12 + 16 + 8 + 8 + 8) + static_cast<long long>(pd.nt_pad) * (12 + 8 + 8);
         if (cur.p1 > cur.p0 && (cur_bytes + bytes > c->workspace_bytes || cur.rows + cur.cols + pd.nq_pad + pd.nt_pad > kFlagScratchCap)) { chunks.push_back(cur); cur = Chunk{}; cur.p0 = cur.p1 = p; cur_bytes = 0; }
@@ -152,7 +156,7 @@ int gtsfm_match_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, double ra
     if ((r = store_ensure_maps(c))) return r;
     // block -> pair tables of the float screening path (one entry per kRowPad rows / columns, chunk-relative pair index)
     bool any_screen_f = false;
-    for (const Chunk& k : chunks) any_screen_f |= k.fitems > 0;
+    for (const Chunk& k : chunks) any_screen_f |= k.fitems > 0 || k.hpairs > 0;
     if (any_screen_f) {
         std::vector<int> tab;
         for (Chunk& k : chunks) {
@@ -214,6 +218,12 @@ int gtsfm_match_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, double ra
             G2V_CUDA(c, launch_exact_scan(st, w, 1, w.flag_cap, s));
             c->prof_end();
             c->launches += 1;
+        }
+        if (k.hpairs > 0) {
+            c->prof_begin(P_EXACT_SCAN);
+            G2V_CUDA(c, launch_hamming(st, w, k.rows, k.cols, c->dim <= 32 ? 8 : 16, s));
+            c->prof_end();
+            c->launches += 2;
         }
         if (k.jobs > 0) {
             c->prof_begin(P_EXACT_SCAN);
@@ -277,6 +287,22 @@ int gtsfm_debug_fetch(gtsfm_ctx* c, int what, void* dst, int64_t bytes)
     G2V_CUDA(c, cudaMemcpyAsync(dst, b[what]->p, bytes, cudaMemcpyDeviceToHost, c->stream));
     G2V_CUDA(c, cudaStreamSynchronize(c->stream));
     return GTSFM_OK;
+}
+
+int gtsfm_match_pair_u8(gtsfm_ctx* c, const uint8_t* desc1, int n1, const uint8_t* desc2, int n2, int nbytes, double ratio, uint32_t* out,
+                        int32_t* count)
+{
+    if (!c || !count) return fail(c, GTSFM_E_ARG, "bad arguments");
+    *count = 0;
+    int r;
+    if ((r = gtsfm_store_clear(c))) return r;
+    if (n1 <= 0 || n2 <= 0 || nbytes <= 0) return GTSFM_OK;                  // twoway_matcher.py:71-72
+    if ((r = gtsfm_image_upload_u8(c, 0, desc1, n1, nbytes, nullptr, nullptr))) return r;
+    if ((r = gtsfm_image_upload_u8(c, 1, desc2, n2, nbytes, nullptr, nullptr))) return r;
+    const int32_t pr[2] = {0, 1};
+    int64_t total = 0;
+    if ((r = gtsfm_match_batch(c, pr, 1, ratio, count, &total))) return r;
+    return gtsfm_match_fetch(c, out);
 }
 
 int gtsfm_match_pair(gtsfm_ctx* c, const float* desc1, int n1, const float* desc2, int n2, int dim, double ratio, uint32_t* out,

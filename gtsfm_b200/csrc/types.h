@@ -28,6 +28,7 @@ struct PairDesc {
     int item0;               // first screening work item of this pair (one item per kBlockT train rows)
     int path;                // 0 = integer descriptors (tensor-core screening is exact), 1 = float (exact fp32 scan),
                              // 2 = float, fp16 tensor-core screening + exact recompute of the winning group (ratio test off)
+                             // 3 = binary descriptors, HAMMING distance (match_hamming.cu)
     long long rp_base;       // entry offset into the row-partial arrays: [nt_pad / kHalfT][nq_pad]
     long long cr_base;       // float offset into colraw: [nt_pad][kTileQ]; path 2: [nt_pad][ceil(nq_pad / 512)][kTileQ]
     long long out_base;      // offset of this pair's slot in the per-query-row arrays and the match slot (capacity nq_pad)
@@ -44,7 +45,7 @@ struct ImageRec {
     int row0, n, n_pad, dim;  // n = descriptor rows (0 when the image was uploaded with keypoints only)
     int n_kps;               // keypoints uploaded (0 when none)
     int n_valid;             // rows without NaN
-    int path;                // 0 integer, 1 float
+    int path;                // 0 integer, 1 float, 3 binary (uint8 rows uploaded with gtsfm_image_upload_u8, HAMMING distance)
     int f16_ok;              // float image whose rows all qualify for the fp16 screening (|x|^2 <= kF16MaxNorm2)
     float max_norm2;         // max |x|^2 over the valid rows
     double cal[5];           // f, k1, k2, u0, v0

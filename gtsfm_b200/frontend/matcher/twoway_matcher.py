@@ -32,12 +32,13 @@ class TwoWayMatcher(MatcherBase):
         self._device = device
 
     def _check_distance_type(self):
-        if self._distance_type == MatchingDistanceType.EUCLIDEAN:
+        if self._distance_type in (MatchingDistanceType.EUCLIDEAN, MatchingDistanceType.HAMMING):
             return
-        if self._distance_type == MatchingDistanceType.HAMMING:
-            # binary descriptors are a "next" item; never fall back silently
-            raise NotImplementedError("HAMMING descriptors are not implemented in the B200 matcher")
         raise NotImplementedError("The distance type is not in MatchingDistanceType")     # twoway_matcher.py:100
+
+    @property
+    def _hamming(self) -> bool:
+        return self._distance_type == MatchingDistanceType.HAMMING
 
     def match(self, keypoints_i1: Keypoints, keypoints_i2: Keypoints, descriptors_i1: np.ndarray, descriptors_i2: np.ndarray,
               im_shape_i1: Tuple[int, int, int] = None, im_shape_i2: Tuple[int, int, int] = None) -> np.ndarray:
@@ -46,8 +47,11 @@ class TwoWayMatcher(MatcherBase):
             return np.array([])                                                            # twoway_matcher.py:71-72
         self._check_distance_type()
         ctx = _native.default_context(self._device)
-        m = ctx.match_pair(np.asarray(descriptors_i1, np.float32), np.asarray(descriptors_i2, np.float32),
-                           self._ratio_test_threshold)
+        if self._hamming:                                                                  # uint8 rows, cv2.NORM_HAMMING (twoway_matcher.py:97-98)
+            m = ctx.match_pair_u8(np.asarray(descriptors_i1, np.uint8), np.asarray(descriptors_i2, np.uint8), self._ratio_test_threshold)
+        else:
+            m = ctx.match_pair(np.asarray(descriptors_i1, np.float32), np.asarray(descriptors_i2, np.float32),
+                               self._ratio_test_threshold)
         return m if m.shape[0] else np.array([])                                           # twoway_matcher.py:80-81
 
     def match_batch(self, descriptors: Sequence[np.ndarray], pairs: np.ndarray) -> List[np.ndarray]:
@@ -57,6 +61,9 @@ class TwoWayMatcher(MatcherBase):
         ctx = _native.default_context(self._device)
         ctx.clear()
         for i, d in enumerate(descriptors):
-            ctx.upload_image(i, d)
+            if self._hamming:
+                ctx.upload_image_u8(i, d)
+            else:
+                ctx.upload_image(i, d)
         m, off = ctx.match_batch(pairs, self._ratio_test_threshold)
         return [m[off[p]:off[p + 1]] if off[p + 1] > off[p] else np.array([]) for p in range(len(off) - 1)]

@@ -78,6 +78,10 @@ int gtsfm_store_clear(gtsfm_ctx* ctx);
  *   cal   {f, k1, k2, u0, v0} of the image's Cal3Bundler or NULL */
 int gtsfm_image_upload(gtsfm_ctx* ctx, int image_id, const float* desc, int n, int dim, const double* kps, const double* cal);
 
+/* Binary descriptors for TwoWayMatcher(distance_type=HAMMING) (twoway_matcher.py:17-21,95-98): desc (n, nbytes) uint8 rows,
+ * nbytes <= 64.  A store holds either float32 or binary descriptors; gtsfm_match_batch picks the distance accordingly. */
+int gtsfm_image_upload_u8(gtsfm_ctx* ctx, int image_id, const uint8_t* desc, int n, int nbytes, const double* kps, const double* cal);
+
 /* ---- TwoWayMatcher over a batch of pairs ---------------------------------------------------------------------- */
 /* pairs: (P, 2) int32 image ids (i1, i2).  ratio: Lowe ratio threshold, NaN = ratio test off
  * (TwoWayMatcher(ratio_test_threshold=None)).  On return counts[p] = number of matches of pair p and *total their
@@ -151,6 +155,9 @@ int gtsfm_two_view_report_batch(gtsfm_ctx* ctx, int n_pairs, const double* gt_i2
 /* TwoWayMatcher.match for one pair from host arrays.  out capacity: min(n1, n2) rows of 2 uint32. */
 int gtsfm_match_pair(gtsfm_ctx* ctx, const float* desc1, int n1, const float* desc2, int n2, int dim, double ratio,
                      uint32_t* out, int32_t* count);
+/* TwoWayMatcher(distance_type=HAMMING).match for one pair of uint8 descriptor arrays. */
+int gtsfm_match_pair_u8(gtsfm_ctx* ctx, const uint8_t* desc1, int n1, const uint8_t* desc2, int n2, int nbytes, double ratio,
+                        uint32_t* out, int32_t* count);
 /* OpencvVerifierBase.verify for one pair from host arrays (kps in pixels, cal = {f,k1,k2,u0,v0}). */
 int gtsfm_verify_pair(gtsfm_ctx* ctx, const double* kps1, int n1, const double* kps2, int n2, const uint32_t* match_idx,
                       int n_matches, const double* cal1, const double* cal2, const gtsfm_verify_params* params, double* R,

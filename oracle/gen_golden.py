@@ -224,8 +224,36 @@ def gen_fmat():
     print("fmat_synth1500: ref verified", v.shape, "ratio", ratio, "7pt solutions", n7.sum())
 
 
+def gen_hamming():
+    """TwoWayMatcher(distance_type=HAMMING) of the unmodified reference on ORB-like 256-bit descriptors (uint8 rows)."""
+    from gtsfm.frontend.matcher.twoway_matcher import MatchingDistanceType
+    rng = np.random.default_rng(20260006)
+    kp = Keypoints(coordinates=np.zeros((0, 2)))
+    base = rng.integers(0, 256, (300, 32), dtype=np.uint8)
+
+    def noisy(d, flips):
+        d = np.unpackbits(d, axis=1)
+        for r in range(d.shape[0]):
+            d[r, rng.choice(256, flips, replace=False)] ^= 1
+        return np.packbits(d, axis=1)
+    d1 = np.concatenate([noisy(base, 20), rng.integers(0, 256, (150, 32), dtype=np.uint8), base[:25]])
+    d2 = np.concatenate([noisy(base[::-1], 25), rng.integers(0, 256, (100, 32), dtype=np.uint8), base[:25]])
+    out = dict(d1=d1, d2=d2)
+    for tag, ratio in (("none", None), ("r08", 0.8), ("r095", 0.95)):
+        m = TwoWayMatcher(distance_type=MatchingDistanceType.HAMMING, ratio_test_threshold=ratio).match(kp, kp, d1, d2, (1, 1), (1, 1))
+        out["m_" + tag] = np.asarray(m).reshape(-1, 2).astype(np.uint32)
+    np.savez_compressed(os.path.join(OUT, "hamming_orb256.npz"), **out)
+    print("hamming:", {k: v.shape for k, v in out.items()})
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
+    if sys.argv[1:] == ["hamming"]:
+        gen_hamming()
+        with open(os.path.join(OUT, "PROVENANCE.txt"), "a") as fh:
+            fh.write(f"hamming_*.npz: oracle/gen_golden.py hamming, /root/reference (commit bc04d78b), cv2 {cv2.__version__}, "
+                     f"numpy {np.__version__}, gtsam={GTSAM}\n")
+        sys.exit(0)
     if sys.argv[1:] == ["fmat"]:
         gen_fmat()
         with open(os.path.join(OUT, "PROVENANCE.txt"), "a") as fh:
@@ -239,6 +267,7 @@ if __name__ == "__main__":
     gen_verifier(rng)
     gen_sampson(rng)
     gen_fmat()
+    gen_hamming()
     with open(os.path.join(OUT, "PROVENANCE.txt"), "w") as fh:
         fh.write(f"generated by oracle/gen_golden.py from /root/reference (commit bc04d78b), cv2 {cv2.__version__}, "
                  f"numpy {np.__version__}, gtsam={GTSAM}\n")

@@ -85,6 +85,21 @@ def twoway_match(desc1: np.ndarray, desc2: np.ndarray, ratio: Optional[float] = 
     return out[:k].copy()
 
 
+def twoway_match_hamming(desc1: np.ndarray, desc2: np.ndarray, ratio: Optional[float] = None) -> np.ndarray:
+    """TwoWayMatcher(HAMMING, ratio).match on uint8 descriptors (twoway_matcher.py:42-144 with cv2.NORM_HAMMING)."""
+    if desc1.size == 0 or desc2.size == 0:
+        return np.array([])
+    a = np.ascontiguousarray(desc1, np.uint8)
+    b = np.ascontiguousarray(desc2, np.uint8)
+    out = np.empty((min(a.shape[0], b.shape[0]), 2), np.uint32)
+    k = lib().oracle_twoway_match_hamming(a.ctypes.data_as(_bp), a.shape[0], b.ctypes.data_as(_bp), b.shape[0], a.shape[1],
+                                          int(ratio is not None), ctypes.c_double(0.0 if ratio is None else ratio),
+                                          out.ctypes.data_as(_up))
+    if k < 0:
+        raise ValueError("not enough values to unpack (expected 2, got 1)")
+    return out[:k].copy() if k else np.array([])
+
+
 def sampson_sq(F: np.ndarray, c1: np.ndarray, c2: np.ndarray) -> np.ndarray:
     """gtsfm/utils/verification.py:170-214."""
     F = np.ascontiguousarray(F, np.float64)

@@ -221,3 +221,41 @@ def test_float_screened_c4_size_flag_rate(ctx):
     total = sum(len(scene.descriptors[i]) + len(scene.descriptors[j]) for i, j in scene.pairs)
     assert n_flag < 0.25 * total, (n_flag, total)
     print("flagged rows+columns:", n_flag, "of", total)
+
+
+# ------------------------------------------------------------------------------------------ HAMMING (binary descriptors)
+def test_hamming_golden_and_oracle(ctx):
+    """TwoWayMatcher(distance_type=HAMMING): the reference's recorded matches on ORB-like 256-bit descriptors, then random
+    32- and 61-byte descriptors (heavy ties: integer distances) against the oracle, ratio test on and off."""
+    from oracle import oracle as O
+    g = np.load(os.path.join(GOLDEN, "hamming_orb256.npz"))
+    for tag, ratio in TAGS:
+        check(ctx.match_pair_u8(g["d1"], g["d2"], ratio), g["m_" + tag])
+    rng = np.random.default_rng(8)
+    for n1, n2, nb in ((700, 900, 32), (300, 257, 61), (2, 5, 32), (1100, 64, 64)):
+        base = rng.integers(0, 256, (min(n1, n2), nb), dtype=np.uint8)
+        d1 = np.concatenate([base, rng.integers(0, 256, (n1 - len(base), nb), dtype=np.uint8)])[rng.permutation(n1)]
+        flip = (rng.random((len(base), nb)) < 0.05).astype(np.uint8) * rng.integers(1, 256, (len(base), nb), dtype=np.uint8)
+        d2 = np.concatenate([base ^ flip, rng.integers(0, 256, (n2 - len(base), nb), dtype=np.uint8)])[rng.permutation(n2)]
+        for ratio in (None, 0.8):
+            check(ctx.match_pair_u8(d1, d2, ratio), O.twoway_match_hamming(d1, d2, ratio).reshape(-1, 2))
+
+
+def test_hamming_plugin_and_batch(ctx):
+    from gtsfm_b200.frontend.matcher.twoway_matcher import MatchingDistanceType, TwoWayMatcher
+    from oracle import oracle as O
+    rng = np.random.default_rng(9)
+    imgs = [rng.integers(0, 256, (n, 32), dtype=np.uint8) for n in (500, 260, 900)]
+    imgs[1][:200] = imgs[0][100:300]
+    imgs[2][:300] = imgs[0][:300] ^ (rng.random((300, 32)) < 0.03).astype(np.uint8)
+    m = TwoWayMatcher(distance_type=MatchingDistanceType.HAMMING, ratio_test_threshold=0.8)
+    pairs = np.array([[0, 1], [0, 2], [1, 2]], np.int32)
+    out = m.match_batch(imgs, pairs)
+    for (i, j), got in zip(pairs, out):
+        want = O.twoway_match_hamming(imgs[i], imgs[j], 0.8).reshape(-1, 2)
+        check(np.asarray(got).reshape(-1, 2), want)
+        single = m.match(None, None, imgs[i], imgs[j])
+        check(np.asarray(single).reshape(-1, 2), want)
+    with pytest.raises(Exception):                       # one store cannot mix float32 and binary descriptors
+        ctx.clear(); ctx.upload_image_u8(0, imgs[0]); ctx.upload_image(1, np.ones((4, 32), np.float32))
+    ctx.clear()

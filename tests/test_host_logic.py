@@ -88,11 +88,12 @@ def test_matcher_empty_inputs_return_empty_array_without_touching_the_gpu():
         assert isinstance(out, np.ndarray) and out.size == 0 and out.ndim == 1       # twoway_matcher.py:72: np.array([])
 
 
-def test_matcher_rejects_unimplemented_distance_types_loudly():
-    m = TwoWayMatcher(distance_type=MatchingDistanceType.HAMMING)
+def test_matcher_rejects_unknown_distance_types_loudly():
+    m = TwoWayMatcher(distance_type="cosine")
     d = np.ones((5, 32), np.float32)
-    with pytest.raises(NotImplementedError):
+    with pytest.raises(NotImplementedError):                                           # twoway_matcher.py:100
         m.match(None, None, d, d)
+    assert TwoWayMatcher(distance_type=MatchingDistanceType.HAMMING)._hamming
 
 
 def test_verifier_gates_and_failure_tuple():

@@ -72,3 +72,11 @@ def test_empty_inputs():
     for a, b in ((e, d), (d, e), (e, e)):
         r = O.twoway_match(a, b, None)
         assert r.size == 0 and r.shape == (0,)
+
+
+def test_hamming_oracle_matches_reference_golden():
+    """TwoWayMatcher(distance_type=HAMMING) of the unmodified reference on ORB-like 256-bit descriptors (gen_golden.py hamming)."""
+    g = np.load(os.path.join(GOLDEN, "hamming_orb256.npz"))
+    for tag, ratio in (("none", None), ("r08", 0.8), ("r095", 0.95)):
+        got = O.twoway_match_hamming(g["d1"], g["d2"], ratio).reshape(-1, 2)
+        np.testing.assert_array_equal(got, g["m_" + tag])
