@@ -43,6 +43,7 @@ def parse_args():
     ap.add_argument("--verifier", default="essential", choices=["essential", "fundamental"],
                     help="essential = Ransac(use_intrinsics_in_verification=True) (BASELINE configs); fundamental = the "
                          "reference's F-matrix mode (ransac.py:84-111), a SURVEY 8(f) row measured with the same harness")
+    ap.add_argument("--workspace-gib", type=float, default=0.0, help="matcher / verifier work-buffer budget per chunk (0 = library default)")
     ap.add_argument("--float-screening", default="on", choices=["on", "off"],
                     help="float descriptors, ratio test off (C4): fp16 tensor-core screening (default) or the exhaustive fp32 kernel")
     return ap.parse_args()
@@ -206,6 +207,8 @@ def run_b200(args):
         cpu = cpu_baseline_sample(scene, cfg)
     ctx = gtsfm_b200.Context(local)
     ctx.set_float_screening(args.float_screening == "on")
+    if args.workspace_gib > 0:
+        ctx.set_workspace(int(args.workspace_gib * (1 << 30)))
 
     # pinned host copies of the step's inputs (the e2e leg uploads from these every step)
     desc_pin = [torch.from_numpy(d).pin_memory() for d in scene.descriptors]

@@ -40,7 +40,7 @@ struct gtsfm_ctx {
     cudaEvent_t match_done = nullptr;       // recorded on `stream` when the compacted matches of a batch are complete
     std::string err;
     int64_t launches = 0;
-    int64_t workspace_bytes = 4ll << 30;
+    int64_t workspace_bytes = 12ll << 30;
 
     // ---- store
     int dim = 0, kpad = 0;

@@ -50,7 +50,7 @@ enum {
 int gtsfm_ctx_create(int device, gtsfm_ctx** out);
 void gtsfm_ctx_destroy(gtsfm_ctx* ctx);
 const char* gtsfm_last_error(const gtsfm_ctx* ctx);   /* ctx may be NULL: error of the last failed create */
-/* Work-buffer budget in bytes for one chunk of pairs (default 4 GiB). */
+/* Work-buffer budget in bytes for one chunk of pairs (default 12 GiB). */
 int gtsfm_ctx_set_workspace(gtsfm_ctx* ctx, int64_t bytes);
 /* Float (non-integer) descriptors, ratio test off: on (default) = fp16 tensor-core screening + exact recompute of the
  * winning candidates + exhaustive re-scan of ambiguous rows; off = every distance by the exhaustive fp32 kernel.  Both give
