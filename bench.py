@@ -110,6 +110,10 @@ class ClockSampler:
 
 def make_scene(args, rank: int):
     from gtsfm_b200 import synthetic
+    if args.config == "C1":            # the reference's own CPU-runnable case: real SIFT features of its 12 Lund-door images
+        scene = synthetic.load_c1(os.path.join(os.path.dirname(os.path.abspath(__file__)), "tests", "golden", "c1_lund_door_12.npz"))
+        scene.fundamental = args.verifier == "fundamental"
+        return scene, dict(n_images=12, n_kps=5000, kind="lund-door-sift", dim=128, pairs="exhaustive", n_hyp=1024, ratio=0.8, seed=0)
     cfg = dict(synthetic.CONFIGS[args.config])
     if args.images:
         cfg["n_images"] = args.images
@@ -122,7 +126,7 @@ def make_scene(args, rank: int):
 
 
 def workload_name(args, cfg, n_pairs):
-    s = f"{args.config}: synthetic {cfg['n_images']} images x {cfg['n_kps']} {cfg['kind']}-{cfg['dim']} keypoints, {n_pairs} pairs ({cfg['pairs']})"
+    s = f"{args.config}: {'reference fixture' if args.config == 'C1' else 'synthetic'} {cfg['n_images']} images x {cfg['n_kps']} {cfg['kind']}-{cfg['dim']} keypoints, {n_pairs} pairs ({cfg['pairs']})"
     if args.verifier == "fundamental":
         s += " [verifier in fundamental-matrix mode - not the BASELINE configuration]"
     if args.images or args.kps:
@@ -160,7 +164,7 @@ def run_reference(args):
     sample = f"{per_step} random pairs per step, one task per pair on {cores} single-threaded cv2 workers"
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": 1e3 * secs / max(args.steps, 1), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-            "data": "synthetic", "config": {"workload": workload_name(args, cfg, n_pairs),
+            "data": "reference fixture (Lund door SIFT features)" if args.config == "C1" else "synthetic", "config": {"workload": workload_name(args, cfg, n_pairs),
                        "n_hypotheses": "cv2 FM_RANSAC (adaptive, maxIters 1e6)" if args.verifier == "fundamental" else "cv2 USAC_ACCURATE default (maxIters 1000)"},
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
@@ -340,7 +344,7 @@ def run_b200(args):
         n_match = int(off[-1])
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16 GEMM / f32 scoring / f64 finalize",
-                "data": "synthetic",
+                "data": "reference fixture (Lund door SIFT features)" if args.config == "C1" else "synthetic",
                 "config": {"workload": workload_name(args, cfg, P), "pairs_per_gpu": P, "ratio_test": scene.ratio, "n_hypotheses": scene.n_hyp,
                            "threshold_px": scene.threshold_px, "lo_iters": 20, "matches_per_pair": n_match / P,
                            "inliers_per_pair": float(out["n_inliers"].mean()), "verified_ok": int((out["status"] == 0).sum()),

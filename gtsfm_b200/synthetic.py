@@ -153,3 +153,18 @@ def make_config(name: str, n_images: Optional[int] = None, n_kps: Optional[int] 
     if max_pairs:
         cfg["max_pairs"] = max_pairs
     return make_scene(**cfg)
+
+
+def load_c1(path: str) -> Scene:
+    """BASELINE config C1 from the committed fixture (tests/golden/c1_lund_door_12.npz, written by oracle/gen_golden.py c1):
+    the reference's own 12 Lund-door images through its SIFT front end, intrinsics and GT poses as the Olsson loader
+    builds them (gtsfm/loader/olsson_loader.py:75-147), all 66 pairs (ExhaustiveRetriever)."""
+    g = np.load(path)
+    off = g["img_off"]
+    n = len(off) - 1
+    descs = [g["desc_u8"][off[i]:off[i + 1]].astype(np.float32) for i in range(n)]
+    kps = [g["kps"][off[i]:off[i + 1]].astype(np.float64) for i in range(n)]
+    Rs = [g["wRc"][i].T for i in range(n)]
+    ts = [-(g["wRc"][i].T @ g["wtc"][i]) for i in range(n)]
+    ids = [np.full(len(d), -1, np.int64) for d in descs]
+    return Scene(descs, kps, ids, Rs, ts, np.ascontiguousarray(g["pairs"], np.int32), tuple(float(v) for v in g["cal"][0]), 0.8, 1024)

@@ -129,6 +129,64 @@ def gen_lund():
     print("lund", {k: getattr(v, "shape", v) for k, v in out.items()})
 
 
+def gen_c1():
+    """BASELINE config C1: the 12 Lund-door images through the reference's own front end (loader resize to
+    --max_resolution 760: gtsfm/loader/loader_base.py:168-190, gtsfm/utils/images.py:101-201; SIFT top-5000:
+    gtsfm/frontend/detector_descriptor/sift.py:44-54) and the unmodified TwoWayMatcher(ratio 0.8) on all 66 pairs
+    (ExhaustiveRetriever).  Intrinsics / GT poses from data.mat as gtsfm/loader/olsson_loader.py:75-147 does
+    (RQ decomposition, gtsfm/utils/verification.py:20-49), intrinsics rescaled as loader_base.py:214-224."""
+    import glob
+    import hashlib
+    import scipy.io
+    import scipy.linalg
+    from PIL import Image as PILImage
+    import gtsfm.utils.images as img_utils
+    from gtsfm.common.image import Image
+    from gtsfm.frontend.detector_descriptor.sift import SIFTDetectorDescriptor
+    root = os.path.join(REF, "tests", "data", "set1_lund_door")
+    paths = sorted(glob.glob(os.path.join(root, "images", "*.JPG")))
+    P = scipy.io.loadmat(os.path.join(root, "data.mat"))["P"][0]
+    assert len(paths) == len(P) == 12
+    det = SIFTDetectorDescriptor(max_keypoints=5000)
+    descs, kps, cals, wRc, wtc, counts = [], [], [], [], [], []
+    for path, M in zip(paths, P):
+        pil = PILImage.open(path)
+        pil = pil.convert("RGB") if pil.mode != "RGB" else pil
+        img = Image(value_array=np.asarray(pil), file_name=os.path.basename(path))
+        su, sv, th, tw = img_utils.get_downsampling_factor_per_axis(img.height, img.width, 760)
+        if min(img.height, img.width) > 760:
+            img = img_utils.resize_image(img, new_height=th, new_width=tw)
+        k, d = det.detect_and_describe(img)
+        assert np.all(d == np.rint(d)) and d.max() <= 255 and d.min() >= 0
+        Q, m4 = M[:3, :3], M[:, 3]
+        K, cRw = scipy.linalg.rq(Q)
+        T = np.diag(np.sign(np.diag(K)))
+        K, cRw = K @ T, T @ cRw
+        if not cals:                       # olsson_loader.py:87,135-147: every image gets the FIRST camera's K
+            K0 = K / K[2, 2]
+        f = min(K0[0, 0], K0[1, 1])
+        cals.append([f * su, 0.0, 0.0, K0[0, 2] * su, K0[1, 2] * sv])
+        wRc.append(cRw.T)
+        wtc.append(np.linalg.inv(-Q) @ m4)
+        counts.append(len(k))
+        descs.append(d.astype(np.uint8))
+        kps.append(np.asarray(k.coordinates, np.float32))
+    off = np.concatenate([[0], np.cumsum(counts)]).astype(np.int64)
+    pairs = [(i, j) for i in range(12) for j in range(i + 1, 12)]
+    m_all, m_off, sha = [], [0], []
+    for i, j in pairs:
+        m = ref_match(descs[i].astype(np.float32), descs[j].astype(np.float32), 0.8).reshape(-1, 2).astype(np.uint32)
+        sha.append(hashlib.sha1(np.ascontiguousarray(m).tobytes()).hexdigest())
+        m_all.append(m.astype(np.uint16))
+        m_off.append(m_off[-1] + len(m))
+    out = {"desc_u8": np.concatenate(descs), "kps": np.concatenate(kps), "img_off": off, "cal": np.array(cals),
+           "wRc": np.array(wRc), "wtc": np.array(wtc), "pairs": np.array(pairs, np.int32),
+           "m_u16": np.concatenate(m_all), "m_off": np.array(m_off, np.int64), "m_sha1": np.array(sha)}
+    np.savez_compressed(os.path.join(OUT, "c1_lund_door_12.npz"), **out)
+    print("c1", counts, "matches/pair", np.diff(m_off).min(), np.diff(m_off).max(),
+          os.path.getsize(os.path.join(OUT, "c1_lund_door_12.npz")))
+
+
 def gen_verifier(rng):
     sys.path.insert(0, REF)
     import tests.frontend.verifier.test_verifier_base as tvb
@@ -254,6 +312,12 @@ if __name__ == "__main__":
             fh.write(f"hamming_*.npz: oracle/gen_golden.py hamming, /root/reference (commit bc04d78b), cv2 {cv2.__version__}, "
                      f"numpy {np.__version__}, gtsam={GTSAM}\n")
         sys.exit(0)
+    if sys.argv[1:] == ["c1"]:
+        gen_c1()
+        with open(os.path.join(OUT, "PROVENANCE.txt"), "a") as fh:
+            fh.write(f"c1_lund_door_12.npz: oracle/gen_golden.py c1, /root/reference (commit bc04d78b), cv2 {cv2.__version__}, "
+                     f"numpy {np.__version__}, gtsam={GTSAM}\n")
+        sys.exit(0)
     if sys.argv[1:] == ["fmat"]:
         gen_fmat()
         with open(os.path.join(OUT, "PROVENANCE.txt"), "a") as fh:
@@ -268,6 +332,7 @@ if __name__ == "__main__":
     gen_sampson(rng)
     gen_fmat()
     gen_hamming()
+    gen_c1()
     with open(os.path.join(OUT, "PROVENANCE.txt"), "w") as fh:
         fh.write(f"generated by oracle/gen_golden.py from /root/reference (commit bc04d78b), cv2 {cv2.__version__}, "
                  f"numpy {np.__version__}, gtsam={GTSAM}\n")

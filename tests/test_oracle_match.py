@@ -80,3 +80,16 @@ def test_hamming_oracle_matches_reference_golden():
     for tag, ratio in (("none", None), ("r08", 0.8), ("r095", 0.95)):
         got = O.twoway_match_hamming(g["d1"], g["d2"], ratio).reshape(-1, 2)
         np.testing.assert_array_equal(got, g["m_" + tag])
+
+
+def test_oracle_reproduces_reference_matches_on_c1_pairs(golden_dir):
+    """BASELINE config C1 (12 Lund-door images, reference SIFT + TwoWayMatcher(0.8), oracle/gen_golden.py c1): the
+    oracle's matches equal the recorded reference output on the first and the last of the 66 pairs."""
+    import os
+    from oracle import oracle as O
+    g = np.load(os.path.join(golden_dir, "c1_lund_door_12.npz"))
+    off, mo = g["img_off"], g["m_off"]
+    for k in (0, 65):
+        i, j = g["pairs"][k]
+        m = O.twoway_match(g["desc_u8"][off[i]:off[i + 1]].astype(np.float32), g["desc_u8"][off[j]:off[j + 1]].astype(np.float32), 0.8)
+        np.testing.assert_array_equal(m, g["m_u16"][mo[k]:mo[k + 1]].astype(np.uint32))
