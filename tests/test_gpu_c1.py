@@ -87,3 +87,32 @@ def test_c1_verifier_vs_oracle_and_ground_truth(c1):
     assert np.median(r_err) < 1.0 and np.median(t_err) < 3.0, (np.median(r_err), np.median(t_err))
     assert (r_err < 5.0).mean() > 0.9, np.sort(r_err)[-8:]
     assert np.median(ratio) > 0.5
+
+
+def test_c1_matcher_cacher_batch(c1, tmp_path):
+    """MatcherCacher over the device matcher: one batch for the misses, reference-compatible entries, second pass all hits."""
+    from gtsfm_b200.common.types import Keypoints
+    from gtsfm_b200.frontend.cacher.matcher_cacher import MatcherCacher
+    from gtsfm_b200.frontend.matcher.twoway_matcher import TwoWayMatcher
+    _, g = c1
+    off, mo = g["img_off"], g["m_off"]
+    kps = [Keypoints(coordinates=g["kps"][off[i]:off[i + 1]]) for i in range(12)]
+    descs = [g["desc_u8"][off[i]:off[i + 1]].astype(np.float32) for i in range(12)]
+    shapes = [(1135, 760, 3)] * 12
+    sel = [0, 5, 11, 40, 65]
+    pairs = g["pairs"][sel]
+    cacher = MatcherCacher(TwoWayMatcher(ratio_test_threshold=0.8), cache_root=tmp_path)
+    out = cacher.match_batch(kps, descs, shapes, pairs)
+    assert (cacher.hits, cacher.misses) == (0, 5)
+    for k, m in zip(sel, out):
+        np.testing.assert_array_equal(m, g["m_u16"][mo[k]:mo[k + 1]].astype(np.uint32))
+    assert len(os.listdir(tmp_path / "matcher")) == 5
+    assert all(f.startswith("TwoWayMatcher_") and f.endswith(".pbz2") for f in os.listdir(tmp_path / "matcher"))
+    out2 = cacher.match_batch(kps, descs, shapes, pairs)
+    assert (cacher.hits, cacher.misses) == (5, 5)
+    for a, b in zip(out, out2):
+        np.testing.assert_array_equal(a, b)
+    i, j = pairs[2]
+    single = cacher.match(kps[i], kps[j], descs[i], descs[j], shapes[i], shapes[j])
+    np.testing.assert_array_equal(single, out[2])
+    assert cacher.hits == 6
