@@ -376,14 +376,19 @@ def ransac_samples(seed: int, pair_key: int, n_matches: int, n_hyp: int, sample_
     return out
 
 
-_default_ctx = {}
-_default_lock = threading.Lock()
+_default_tls = threading.local()
 
 
 def default_context(device: int = 0) -> Context:
-    """Lazily created per-process, per-device context (plugin objects stay picklable: they never hold one)."""
+    """Lazily created context of the calling THREAD of this process for `device`.  Plugin objects never hold one, so they
+    stay picklable (det_desc_correspondence_generator.py:67 scatters them); a context is single-threaded, so every thread
+    of a Dask worker (--threads_per_worker > 1, gtsfm_runner_base.py:58-69) gets its own store, stream and work buffers:
+    match() / verify() are re-entrant like the reference's, which builds a fresh cv2 matcher per call
+    (twoway_matcher.py:133).  A context created before a fork is never reused in the child (key includes the pid)."""
+    table = getattr(_default_tls, "ctx", None)
+    if table is None:
+        table = _default_tls.ctx = {}
     key = (os.getpid(), int(device))
-    with _default_lock:
-        if key not in _default_ctx:
-            _default_ctx[key] = Context(device)
-        return _default_ctx[key]
+    if key not in table:
+        table[key] = Context(device)
+    return table[key]

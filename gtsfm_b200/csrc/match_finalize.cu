@@ -136,11 +136,12 @@ cudaError_t launch_match_finalize(const MatchWork& w, int use_ratio, double rati
                                   uint2* match_slot, int* match_count, long long* offsets, long long* running, uint2* compact_out, cudaStream_t s)
 {
     if (w.n_pairs <= 0) return cudaSuccess;
-    static bool configured = false;
+    static g2v::DeviceOnce once;
+    int& configured = once.cur();
     if (!configured) {
         cudaError_t e = cudaFuncSetAttribute(select_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSortSmem * 8);
         if (e != cudaSuccess) return e;
-        configured = true;
+        configured = 1;
     }
     select_sort_kernel<<<w.n_pairs, 512, kSortSmem * 8, s>>>(w, use_ratio, ratio, keys_scratch, match_slot, match_count);
     scan_counts_kernel<<<1, 1024, 0, s>>>(match_count, w.n_pairs, offsets, running);

@@ -426,7 +426,8 @@ __global__ void __launch_bounds__(128) bucket_cols_kernel(StoreView st, MatchWor
 
 template <int N16> static cudaError_t launch_bucket_cols(const StoreView& st, const MatchWork& w, int max_class_rows, cudaStream_t s)
 {
-    static int configured = 0;
+    static g2v::DeviceOnce once;
+    int& configured = once.cur();
     const int smem = ((max_class_rows + 7) & ~7) * (Staged<N16>::kStride * 16 + 5) + 16;
     if (smem > configured) {
         const int want = kMaxClassRows * (Staged<N16>::kStride * 16 + 5) + 16;

@@ -237,11 +237,12 @@ static cudaError_t launch_screen_t(const CUtensorMap& tm_desc, const CUtensorMap
                                    const ScreenArgs& args, int n_sm, cudaStream_t stream)
 {
     using L = ScreenSmem<KCH>;
-    static bool configured = false;
+    static g2v::DeviceOnce once;
+    int& configured = once.cur();
     if (!configured) {
         cudaError_t e = cudaFuncSetAttribute(match_screen_kernel<KCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal);
         if (e != cudaSuccess) return e;
-        configured = true;
+        configured = 1;
     }
     const int grid = args.n_items < n_sm ? args.n_items : n_sm;
     if (grid <= 0) return cudaSuccess;

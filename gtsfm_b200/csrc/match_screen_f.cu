@@ -244,11 +244,12 @@ static cudaError_t launch_screen_f_t(const CUtensorMap& tm_desc, const CUtensorM
                                      const ScreenArgsF& args, int n_sm, cudaStream_t stream)
 {
     using L = ScreenSmemF<KCH>;
-    static bool configured = false;
+    static g2v::DeviceOnce once;
+    int& configured = once.cur();
     if (!configured) {
         cudaError_t e = cudaFuncSetAttribute(match_screen_f_kernel<KCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal);
         if (e != cudaSuccess) return e;
-        configured = true;
+        configured = 1;
     }
     const int grid = args.n_items < n_sm ? args.n_items : n_sm;
     if (grid <= 0) return cudaSuccess;

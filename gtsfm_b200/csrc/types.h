@@ -2,6 +2,8 @@
 #pragma once
 #include <cstdint>
 
+#include <cuda_runtime.h>
+
 namespace g2v {
 
 constexpr int kRowPad = 256;   // every image occupies a multiple of 256 rows of the descriptor store
@@ -52,4 +54,13 @@ struct ImageRec {
     int has_kps;
 };
 
+}  // namespace g2v
+
+namespace g2v {
+// "This kernel's attributes are set" flag of the CURRENT device: cudaFuncSetAttribute applies to one device, and a process
+// may hold contexts on several devices and call in from several threads (a repeated set is harmless).
+struct DeviceOnce {
+    int v[64] = {0};
+    int& cur() { int dev = 0; cudaGetDevice(&dev); return v[dev & 63]; }
+};
 }  // namespace g2v

@@ -627,11 +627,12 @@ __global__ void __launch_bounds__(kFinThreads, 4) finalize_f_kernel(VerifyBufs b
 cudaError_t launch_verify_step_f(int step, const StoreView& st, const VerifyBufs& b, const VerifyDims& d, int n_pairs, int max_m, cudaStream_t s)
 {
     if (n_pairs <= 0) return cudaSuccess;
-    static bool configured = false;
+    static g2v::DeviceOnce once;
+    int& configured = once.cur();
     if (!configured) {
         cudaError_t e = cudaFuncSetAttribute(count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kCntTile * 16);
         if (e != cudaSuccess) return e;
-        configured = true;
+        configured = 1;
     }
     if (step == 0) {
         const int gx = max_m > 0 ? (max_m + 255) / 256 : 1;
