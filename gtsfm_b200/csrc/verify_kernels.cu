@@ -376,7 +376,7 @@ __device__ inline bool solve_lm5(const double* JtJ, const double* Jtr, double la
 // One pass over all correspondences at model (R, t) in shared memory: s_out = {cost, #inliers, Jtr[5], JtJ upper[15]}
 // of the signed Sampson residuals of the inliers; parameters: R <- R Exp(w), t <- normalize(t + b1 a + b2 b).
 __device__ void lo_pass(const VerifyBufs& b, const VPair& vp, const double* s_R, const double* s_t, double* s_E, double* s_dE,
-                        double (*s_red)[24], double* s_out)
+                        double (*s_red)[24], double* s_out, double4 (*s_q)[64])
 {
     if (threadIdx.x == 0) {
         double b1[3], b2[3];
@@ -395,17 +395,17 @@ __device__ void lo_pass(const VerifyBufs& b, const VPair& vp, const double* s_R,
     for (int i = 0; i < 9; ++i) E[i] = s_E[i];
     double acc[22];
     for (int i = 0; i < 22; ++i) acc[i] = 0;
-    for (int i = threadIdx.x; i < vp.M; i += kFinThreads) {
-        const double4 c = static_cast<const double4*>(b.corr_d)[vp.m0 + i];
+    // The Jacobian rows are only needed for the inliers (about half of the correspondences, scattered), and they are
+    // ~85 % of the fp64 work of a pass: every warp first classifies 32 correspondences (residual only), queues its inliers
+    // in shared memory and runs the Jacobian part whenever 32 of them are waiting, i.e. on full warps.
+    auto inlier_terms = [&](const double4& c) {
         const double a1 = c.x, c1 = c.y, a2 = c.z, c2 = c.w;
         const double l0 = E[0] * a1 + E[1] * c1 + E[2], l1 = E[3] * a1 + E[4] * c1 + E[5], l2 = E[6] * a1 + E[7] * c1 + E[8];
         const double m0 = E[0] * a2 + E[3] * c2 + E[6], m1 = E[1] * a2 + E[4] * c2 + E[7];
         const double num = a2 * l0 + c2 * l1 + l2, den = l0 * l0 + l1 * l1 + m0 * m0 + m1 * m1;
-        const double s = num * num / den;
-        if (!(s < vp.thr2)) { acc[0] += vp.thr2; continue; }
-        acc[0] += s;
-        acc[1] += 1.0;
         const double isd = 1.0 / sqrt(den), r = num * isd, q = r / den;
+        acc[0] += num * num / den;
+        acc[1] += 1.0;
         double J[5];
 #pragma unroll
         for (int pz = 0; pz < 5; ++pz) {
@@ -422,7 +422,31 @@ __device__ void lo_pass(const VerifyBufs& b, const VPair& vp, const double* s_R,
 #pragma unroll
             for (int u = pz; u < 5; ++u) acc[k++] += J[pz] * J[u];
         }
+    };
+    const int lane = threadIdx.x & 31;
+    double4* q = s_q[threadIdx.x >> 5];
+    int qn = 0;                                             // warp-uniform: inliers waiting in the queue (< 32 between rounds)
+    for (int i0 = threadIdx.x - lane; i0 < vp.M; i0 += kFinThreads) {
+        const int i = i0 + lane;
+        bool in = false;
+        double4 c = make_double4(0, 0, 0, 0);
+        if (i < vp.M) {
+            c = static_cast<const double4*>(b.corr_d)[vp.m0 + i];
+            in = vm::sampson_sq(E, c.x, c.y, c.z, c.w) < vp.thr2;
+            if (!in) acc[0] += vp.thr2;
+        }
+        const unsigned bal = __ballot_sync(0xffffffffu, in);
+        if (in) q[qn + __popc(bal & ((1u << lane) - 1u))] = c;
+        qn += __popc(bal);
+        __syncwarp();
+        if (qn >= 32) {
+            qn -= 32;
+            const double4 cc = q[qn + lane];
+            __syncwarp();
+            inlier_terms(cc);
+        }
     }
+    if (lane < qn) inlier_terms(q[lane]);
     block_sum<22>(acc, s_red, s_out);
 }
 
@@ -517,6 +541,7 @@ __global__ void __launch_bounds__(kFinThreads, 4) finalize_kernel(VerifyBufs b, 
     __shared__ double s_Ek[kTopK][9];
     __shared__ double s_R[9], s_t[3], s_E[9], s_dE[45];
     __shared__ double s_pose[21];
+    __shared__ double4 s_q[kFinThreads / 32][64];      // lo_pass: per-warp queue of inliers awaiting their Jacobian rows
     __shared__ int s_topi[kTopK];
     __shared__ int s_ctrl;
 
@@ -574,7 +599,7 @@ __global__ void __launch_bounds__(kFinThreads, 4) finalize_kernel(VerifyBufs b, 
             for (int i = 0; i < 3; ++i) s_t[i] = t[i];
         }
         __syncthreads();
-        lo_pass(b, vp, s_R, s_t, s_E, s_dE, s_red, s_out);
+        lo_pass(b, vp, s_R, s_t, s_E, s_dE, s_red, s_out, s_q);
         auto unpack = [&](double* jtj, double* jtr) {
             for (int i = 0; i < 5; ++i) jtr[i] = s_out[2 + i];
             int k = 7;
@@ -601,7 +626,7 @@ __global__ void __launch_bounds__(kFinThreads, 4) finalize_kernel(VerifyBufs b, 
             }
             __syncthreads();
             if (s_ctrl) break;
-            lo_pass(b, vp, s_R, s_t, s_E, s_dE, s_red, s_out);
+            lo_pass(b, vp, s_R, s_t, s_E, s_dE, s_red, s_out, s_q);
             if (tid == 0) {
                 const double cn = s_out[0];
                 if (cn < cst) {
