@@ -32,9 +32,9 @@ template <int NV> __device__ void block_sum(double* v, double (*s_red)[24], doub
 // triangulation of every inlier under each candidate, cheirality vote (0 < z < 50 in both views), first maximum in the
 // order (R1,t), (R2,t), (R1,-t), (R2,-t).  The inliers are the rows whose mask byte is 1; every thread reads the bytes it
 // wrote itself (same stride), so no barrier is needed between the mask pass and this one.
-// s_pose: 21 doubles of shared memory (R1, R2, t).
+// s_pose: 21 doubles of shared memory (R1, R2, t); s_q: a 64-entry queue per warp.
 __device__ inline void recover_pose_block(const VerifyBufs& b, const VPair& vp, int p, const double* E, double* s_pose,
-                                          double (*s_red)[24], double* s_out)
+                                          double (*s_red)[24], double* s_out, double4 (*s_q)[64])
 {
     const int tid = threadIdx.x;
     double* s_R1 = s_pose;
@@ -44,9 +44,7 @@ __device__ inline void recover_pose_block(const VerifyBufs& b, const VPair& vp, 
     __syncthreads();
     {
         double good[4] = {0, 0, 0, 0};
-        for (int i = tid; i < vp.M; i += kFinThreads) {
-            if (!b.mask[vp.m0 + i]) continue;
-            const double4 c = static_cast<const double4*>(b.corr_d)[vp.m0 + i];
+        auto vote = [&](const double4& c) {
 #pragma unroll 1
             for (int cand = 0; cand < 4; ++cand) {
                 const double* Rc = (cand & 1) ? s_R2 : s_R1;
@@ -55,7 +53,26 @@ __device__ inline void recover_pose_block(const VerifyBufs& b, const VPair& vp, 
                 for (int r = 0; r < 3; ++r) { P1[4 * r] = Rc[3 * r]; P1[4 * r + 1] = Rc[3 * r + 1]; P1[4 * r + 2] = Rc[3 * r + 2]; P1[4 * r + 3] = sg * s_tt[r]; }
                 good[cand] += vm::cheirality_ok(P1, c.x, c.y, c.z, c.w) ? 1.0 : 0.0;
             }
+        };
+        // the inliers are scattered: every warp queues the ones among its next 32 rows and triangulates on full warps
+        const int lane = tid & 31;
+        double4* q = s_q[tid >> 5];
+        int qn = 0;
+        for (int i0 = tid - lane; i0 < vp.M; i0 += kFinThreads) {
+            const int i = i0 + lane;
+            const bool in = i < vp.M && b.mask[vp.m0 + i];
+            const unsigned bal = __ballot_sync(0xffffffffu, in);
+            if (in) q[qn + __popc(bal & ((1u << lane) - 1u))] = static_cast<const double4*>(b.corr_d)[vp.m0 + i];
+            qn += __popc(bal);
+            __syncwarp();
+            if (qn >= 32) {
+                qn -= 32;
+                const double4 c = q[qn + lane];
+                __syncwarp();
+                vote(c);
+            }
         }
+        if (lane < qn) vote(q[lane]);
         block_sum<4>(good, s_red, s_out);
     }
     if (tid == 0) {

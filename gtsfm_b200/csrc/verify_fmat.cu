@@ -553,6 +553,7 @@ __global__ void __launch_bounds__(kFinThreads, 4) finalize_f_kernel(VerifyBufs b
     __shared__ double s_red[kFinThreads / 32][24];
     __shared__ double s_out[24];
     __shared__ double s_pose[21];
+    __shared__ double4 s_q[kFinThreads / 32][64];      // recover_pose_block: per-warp inlier queue
     __shared__ double s_E[9];
     __shared__ long long s_key[kFinThreads / 32];
     const int p = blockIdx.x;
@@ -619,7 +620,7 @@ __global__ void __launch_bounds__(kFinThreads, 4) finalize_f_kernel(VerifyBufs b
     double E[9];
 #pragma unroll
     for (int e = 0; e < 9; ++e) E[e] = s_E[e];
-    recover_pose_block(b, vp, p, E, s_pose, s_red, s_out);
+    recover_pose_block(b, vp, p, E, s_pose, s_red, s_out, s_q);
 }
 
 // ---------------------------------------------------------------------------------------------------------------- launch

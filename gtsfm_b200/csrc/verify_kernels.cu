@@ -672,7 +672,7 @@ __global__ void __launch_bounds__(kFinThreads, 4) finalize_kernel(VerifyBufs b, 
     if (n_in == 0) { if (tid == 0) b.status[p] = 2; return; }
 
     // ---- (f) pose recovery (cv2.recoverPose): 4 candidates, cheirality vote over the inliers
-    recover_pose_block(b, vp, p, E, s_pose, s_red, s_out);
+    recover_pose_block(b, vp, p, E, s_pose, s_red, s_out, s_q);
 }
 
 // ---------------------------------------------------------------------------------------------------------------- launch
