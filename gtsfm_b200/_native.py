@@ -20,6 +20,7 @@ EXPORTS = (
     "gtsfm_verify_batch", "gtsfm_two_view_report_batch", "gtsfm_match_pair", "gtsfm_verify_pair", "gtsfm_debug_fetch",
     "gtsfm_profile_enable", "gtsfm_profile_get", "gtsfm_event_record", "gtsfm_event_elapsed_ms", "gtsfm_verify_stats",
     "gtsfm_host_alloc", "gtsfm_host_free", "gtsfm_match_fetch_async", "gtsfm_sync",
+    "gtsfm_retriever_similarity", "gtsfm_retriever_topk",
 )
 
 OK, E_CUDA, E_ARG, E_NO_DEVICE, E_KNN_UNPACK, E_UNSUPPORTED = range(6)
@@ -95,6 +96,9 @@ def lib() -> ctypes.CDLL:
                                                  ctypes.c_void_p]
             L.gtsfm_verify_batch.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p,
                                              ctypes.POINTER(VerifyParams)] + [ctypes.c_void_p] * 6
+            L.gtsfm_retriever_similarity.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_void_p]
+            L.gtsfm_retriever_topk.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_double, ctypes.c_void_p,
+                                               ctypes.c_void_p]
             L.gtsfm_two_view_report_batch.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p,
                                                       ctypes.POINTER(ReportParams)] + [ctypes.c_void_p] * 8
             L.gtsfm_match_pair.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int,
@@ -332,6 +336,31 @@ class Context:
         self._check(self._L.gtsfm_verify_batch(self._h, _ptr(pairs), P, _ptr(match_idx), _ptr(match_offsets), ctypes.byref(params),
                                                _ptr(R), _ptr(t), _ptr(ninl), _ptr(status), _ptr(mask), _ptr(E)))
         return dict(R=R.reshape(P, 3, 3), t=t, n_inliers=ninl, status=status, mask=mask[: int(total or 0)], E=E.reshape(P, 3, 3))
+
+    def retriever_similarity(self, global_desc: np.ndarray, blocksize: int = 50, fetch: bool = True) -> Optional[np.ndarray]:
+        """sim = G G^T of (n_images, dim) float32 global descriptors (gtsfm_retriever_similarity); the matrix also stays on
+        the device for retriever_topk(None, ...)."""
+        g = np.ascontiguousarray(global_desc, np.float32)
+        if g.ndim != 2:
+            raise ValueError("global descriptors must be (n_images, dim)")
+        n, dim = g.shape
+        sim = np.empty((n, n), np.float32) if fetch else None
+        self._check(self._L.gtsfm_retriever_similarity(self._h, _ptr(g), n, dim, int(blocksize), _ptr(sim)))
+        return sim
+
+    def retriever_topk(self, sim: Optional[np.ndarray], n_images: int, num_select: int, min_score: Optional[float]):
+        """(idx (n, k) int32 with -1 for unused slots, score (n, k) float32), k = min(num_select, n) (gtsfm_retriever_topk)."""
+        n = int(n_images)
+        k = min(int(num_select), n)
+        if sim is not None:
+            sim = np.ascontiguousarray(sim, np.float32)
+            if sim.shape != (n, n):
+                raise ValueError("similarity matrix must be (n_images, n_images)")
+        idx = np.empty((n, k), np.int32)
+        score = np.empty((n, k), np.float32)
+        ms = float("nan") if min_score is None else float(min_score)
+        self._check(self._L.gtsfm_retriever_topk(self._h, _ptr(sim), n, k, ms, _ptr(idx), _ptr(score)))
+        return idx, score
 
     def two_view_report_batch(self, n_pairs: int, total: int, dist_threshold_px: float, min_num_inliers_est_model: int,
                               min_inlier_ratio_est_model: float, gt_i2Ri1: Optional[np.ndarray] = None,

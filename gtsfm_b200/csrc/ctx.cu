@@ -232,6 +232,7 @@ void gtsfm_ctx_destroy(gtsfm_ctx* c)
     c->h_blk_tab.release();
     c->blk_tab.release();
     c->h_small.release();
+    c->r_desc.release(); c->r_sim.release(); c->r_tiles.release(); c->r_out.release();
     for (cudaEvent_t e : c->prof_pool) cudaEventDestroy(e);
     for (cudaEvent_t e : c->user_ev) if (e) cudaEventDestroy(e);
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);

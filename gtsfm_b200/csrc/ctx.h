@@ -85,6 +85,10 @@ struct gtsfm_ctx {
     int verify_n = 0;
     long long verify_total = 0;
 
+    // ---- retriever (retrieve.cu): global descriptors, similarity matrix of the last gtsfm_retriever_similarity, top-K outputs
+    g2v::DevBuf r_desc, r_sim, r_tiles, r_out;
+    int r_n = 0;
+
     g2v::StoreView view() const;
 };
 

@@ -151,6 +151,23 @@ int gtsfm_two_view_report_batch(gtsfm_ctx* ctx, int n_pairs, const double* gt_i2
                                 double* inlier_avg_err, double* outlier_avg_err, double* R_error_deg, double* U_error_deg,
                                 int32_t* keep);
 
+/* ---- the retriever step in front of the matcher ---------------------------------------------------
+ * Replaces NetVLADRetriever.compute_similarity_matrix (gtsfm/retriever/netvlad_retriever.py:77-149: blocked
+ * torch.einsum("id,jd->ij") of the global descriptors) and pairs_from_score_matrix (:196-228: mask + min_score + torch.topk).
+ *
+ * gtsfm_retriever_similarity: global_desc (n_images, dim) float32 row-major on the host -> sim = G G^T, fp32 accumulation in
+ * ascending k (two levels: spans of 128, then the spans).  Like the reference only the blocks with block(j) >= block(i)
+ * (block = index / blocksize) are computed, all other entries are 0.  The matrix stays on the device for
+ * gtsfm_retriever_topk; sim_out (n_images^2 floats, may be NULL) receives a copy.  More than 10,000 images -> GTSFM_E_ARG
+ * (MAX_NUM_IMAGES, netvlad_retriever.py:21,91-92).
+ * gtsfm_retriever_topk: for every image i the num_select = min(num_select, n_images) best j > i (upper triangle, no
+ * self-matches, netvlad_retriever.py:166-168) with !(score < (float)min_score) and finite score, best first, ties by lower j.
+ * min_score NaN = no minimum.  sim_in NULL = the matrix of the last gtsfm_retriever_similarity call, else an (n_images,
+ * n_images) float32 host matrix.  out_idx / out_score: (n_images, num_select) row-major, unused slots -1 / -inf. */
+int gtsfm_retriever_similarity(gtsfm_ctx* ctx, const float* global_desc, int n_images, int dim, int blocksize, float* sim_out);
+int gtsfm_retriever_topk(gtsfm_ctx* ctx, const float* sim_in, int n_images, int num_select, double min_score, int32_t* out_idx,
+                         float* out_score);
+
 /* ---- single-pair conveniences used by the MatcherBase / VerifierBase plugin classes ---------------------------- */
 /* TwoWayMatcher.match for one pair from host arrays.  out capacity: min(n1, n2) rows of 2 uint32. */
 int gtsfm_match_pair(gtsfm_ctx* ctx, const float* desc1, int n1, const float* desc2, int n2, int dim, double ratio,
