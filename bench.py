@@ -303,6 +303,20 @@ def run_b200(args):
                     "median_U_error_deg": float(np.nanmedian(rep["U_error_deg"])) if ok_pairs.any() else None,
                     "gt_correct_fraction_of_verified": float(rep["num_inliers_gt"].sum() / max(int(out["n_inliers"][ok_pairs].sum()), 1))}
 
+    # ---- the retriever step in front of the path, outside the timed steps: similarity + top-50 of
+    # 2,000 images x 4,096-d global descriptors (C4's image count, NetVLAD's dimension), host arrays in, pair list out
+    retr_extra = None
+    if rank == 0:
+        rg = np.random.default_rng(5).standard_normal((2000, 4096)).astype(np.float32)
+        rg /= np.linalg.norm(rg, axis=1, keepdims=True)
+        ctx.retriever_similarity(rg, 50, fetch=False)
+        ctx.retriever_topk(None, 2000, 50, 0.0)
+        t0 = time.perf_counter()
+        ctx.retriever_similarity(rg, 50, fetch=False)
+        ridx, _ = ctx.retriever_topk(None, 2000, 50, 0.0)
+        retr_extra = {"workload": "2000 images x 4096-d, top-50, min_score 0", "ms_incl_copies": (time.perf_counter() - t0) * 1e3,
+                      "pairs": int((ridx >= 0).sum())}
+
     # ---- end-to-end leg: pinned host buffers -> device -> results on the host, every step
     def e2e_step():
         upload()
@@ -353,7 +367,7 @@ def run_b200(args):
                 "roofline": roofline, "cpu_baseline": cpu,
                 "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": int(d2h_bytes)},
                 "gpu_launches": int(launches), "clocks": clk, "device_event_ms_per_step": ms / args.steps,
-                "two_view_report": report_extra}
+                "two_view_report": report_extra, "retriever": retr_extra}
         print(json.dumps(line), file=_REAL_STDOUT, flush=True)
     ctx.close()
     if world > 1:

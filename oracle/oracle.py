@@ -282,3 +282,33 @@ def two_view_report(kp1, kp2, v_corr_idxs, n_putative, R_est, t_est, cal1, cal2,
         rest = d2[~gm]
         out["outlier_avg"] = float(np.nanmean(rest)) if np.any(~np.isnan(rest)) else float("nan")
     return out
+
+
+# ---------------------------------------------------------------------------------------------------- retriever (8(f) rank 4)
+def retriever_similarity(global_descriptors: np.ndarray, blocksize: int = 50) -> np.ndarray:
+    """gtsfm/retriever/netvlad_retriever.py:77-153: blocked G G^T, only blocks with block_j >= block_i, zeros elsewhere.
+    float64 accumulation here (the reference's einsum order is BLAS-defined), rounded to float32."""
+    g = np.asarray(global_descriptors, np.float64)
+    n = g.shape[0]
+    sim = g @ g.T
+    bi = np.arange(n) // blocksize
+    sim[bi[None, :] < bi[:, None]] = 0.0
+    return sim.astype(np.float32)
+
+
+def pairs_from_score_matrix(scores: np.ndarray, num_select: int, min_score: Optional[float] = None):
+    """gtsfm/retriever/netvlad_retriever.py:166-168,196-228 in numpy: upper triangle without the diagonal, scores below
+    min_score (compared in float32) dropped, the num_select best per row (ties: lower index), row-major pair list."""
+    s = np.array(scores, np.float32)
+    n = s.shape[0]
+    invalid = ~np.triu(np.ones((n, n), bool))
+    np.fill_diagonal(invalid, True)
+    if min_score is not None:
+        invalid |= s < np.float32(min_score)
+    s[invalid] = -np.inf
+    k = min(num_select, n)
+    pairs = []
+    for i in range(n):
+        order = np.lexsort((np.arange(n), -s[i]))[:k]
+        pairs += [(i, int(j)) for j in order if np.isfinite(s[i, j])]
+    return pairs
