@@ -15,10 +15,22 @@ import numpy as np
 
 from gtsfm_b200 import _native
 
+try:  # pragma: no cover - inside a GTSfM environment the class registers like the reference's (retriever_base.py:26-46)
+    from gtsfm.retriever.retriever_base import ImageMatchingRegime, RetrieverBase  # type: ignore
+except Exception:  # noqa: BLE001
+    class RetrieverBase:  # type: ignore[no-redef]
+        """Stand-in for gtsfm.retriever.retriever_base.RetrieverBase."""
+
+        def __init__(self, matching_regime) -> None:
+            self._matching_regime = matching_regime
+
+    class ImageMatchingRegime:  # type: ignore[no-redef]
+        RETRIEVAL = "retrieval"
+
 MAX_NUM_IMAGES = 10000
 
 
-class NetVLADRetriever:
+class NetVLADRetriever(RetrieverBase):
     def __init__(self, num_matched: int, min_score: float = 0.1, blocksize: int = 50, device: int = 0) -> None:
         """
         Args:
@@ -27,6 +39,7 @@ class NetVLADRetriever:
             blocksize: sub-block size of the reference's blocked similarity computation; only decides which entries of the
                 returned matrix are filled (blocks on or above the block diagonal), never the pairs.
         """
+        super().__init__(matching_regime=ImageMatchingRegime.RETRIEVAL)
         self._num_matched = num_matched
         self._blocksize = blocksize
         self._min_score = min_score
