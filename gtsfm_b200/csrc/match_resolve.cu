@@ -256,7 +256,7 @@ __device__ __forceinline__ float dist_or_max(int d2) { return d2 == INT_MAX ? FL
 // bucket, rows: one CTA per (pair, half block of 128 train columns).  The members of the half block are sorted by group;
 // a warp takes 16 members of one group at a time and multiplies them with the group's 16 staged train rows.
 template <int N16>
-__global__ void __launch_bounds__(128) bucket_rows_kernel(StoreView st, MatchWork w)
+__global__ void __launch_bounds__(128, 8) bucket_rows_kernel(StoreView st, MatchWork w)
 {
     constexpr int kStride = Staged<N16>::kStride;
     __shared__ uint4 s_t[kHalfT * kStride];
