@@ -43,6 +43,9 @@ def parse_args():
     ap.add_argument("--verifier", default="essential", choices=["essential", "fundamental"],
                     help="essential = Ransac(use_intrinsics_in_verification=True) (BASELINE configs); fundamental = the "
                          "reference's F-matrix mode (ransac.py:84-111), a SURVEY 8(f) row measured with the same harness")
+    ap.add_argument("--scaling", choices=("weak", "strong"), default="weak",
+                    help="N > 1: weak = every rank its own shard-sized scene (default, the driver's scaling run); strong = ONE scene, "
+                         "its pair list dealt over the ranks by shard_pairs, every rank uploads only the images its shard names")
     ap.add_argument("--workspace-gib", type=float, default=0.0, help="matcher / verifier work-buffer budget per chunk (0 = library default)")
     ap.add_argument("--float-screening", default="on", choices=["on", "off"],
                     help="float descriptors, ratio test off (C4): fp16 tensor-core screening (default) or the exhaustive fp32 kernel")
@@ -201,10 +204,24 @@ def run_b200(args):
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    scene, cfg = make_scene(args, rank)
-    pairs = scene.pairs
+    strong = args.scaling == "strong" and world > 1
+    scene, cfg = make_scene(args, 0 if strong else rank)
+    from gtsfm_b200.two_view_batch import shard_pairs
+    if strong:                                           # contiguous cost-balanced blocks of the i1-sorted pair list
+        mine = shard_pairs(scene.pairs, world)[rank]
+        pairs_g = np.ascontiguousarray(scene.pairs[mine])
+        used = np.unique(pairs_g)
+        remap = -np.ones(len(scene.descriptors), np.int64)
+        remap[used] = np.arange(len(used))
+        pairs = np.ascontiguousarray(remap[pairs_g].astype(np.int32))
+        P_total = len(scene.pairs)
+    else:
+        pairs_g = pairs = scene.pairs
+        used = np.arange(len(scene.descriptors))
+        mine = None
+        P_total = world * len(pairs)
     P = len(pairs)
-    n_img = len(scene.descriptors)
+    n_img = len(used)
     # CPU baseline first: the worker pool is forked before this process creates its CUDA context
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -215,13 +232,13 @@ def run_b200(args):
         ctx.set_workspace(int(args.workspace_gib * (1 << 30)))
 
     # pinned host copies of the step's inputs (the e2e leg uploads from these every step)
-    desc_pin = [torch.from_numpy(d).pin_memory() for d in scene.descriptors]
-    kps_pin = [torch.from_numpy(k).pin_memory() for k in scene.keypoints]
+    desc_pin = [torch.from_numpy(scene.descriptors[i]).pin_memory() for i in used]
+    kps_pin = [torch.from_numpy(scene.keypoints[i]).pin_memory() for i in used]
     h2d_bytes = sum(t.numel() * t.element_size() for t in desc_pin + kps_pin)
 
     prm = _native.VerifyParams()
     prm.threshold_px, prm.n_hypotheses, prm.lo_iters, prm.seed = scene.threshold_px, scene.n_hyp, 20, 20260002
-    keys = (pairs[:, 0].astype(np.uint64) << np.uint64(32)) | pairs[:, 1].astype(np.uint64)
+    keys = (pairs_g[:, 0].astype(np.uint64) << np.uint64(32)) | pairs_g[:, 1].astype(np.uint64)     # sampler keys = global pair ids
     prm.pair_keys, prm.samples = keys.ctypes.data, None
     prm.estimate_fundamental = 1 if args.verifier == "fundamental" else 0
 
@@ -231,7 +248,7 @@ def run_b200(args):
             ctx.upload_image(i, desc_pin[i].numpy(), kps_pin[i].numpy(), scene.cal)
 
     from gtsfm_b200.two_view_batch import TwoViewBatchResult, gather_records, pack_records
-    pair_ids = rank * P + np.arange(P)                                     # every rank owns P pairs of the weak-scaling job
+    pair_ids = mine if strong else rank * P + np.arange(P)                 # weak scaling: every rank owns P pairs of the job
 
     def compute(fetch: bool):
         # e2e leg: the match D2H is enqueued on the copy stream and overlaps the verifier; results land in pinned buffers
@@ -242,8 +259,8 @@ def run_b200(args):
         d2h = m.nbytes + out["mask"].nbytes + out["R"].nbytes + out["t"].nbytes + out["E"].nbytes + out["n_inliers"].nbytes + out["status"].nbytes + 4 * P
         if world > 1:                                                      # per-pair result records gathered via NCCL (north_star)
             res = TwoViewBatchResult(pairs, off, m, out["mask"], out["R"], out["t"], out["n_inliers"], out["status"])
-            table = gather_records(pack_records(res, pair_ids), world * P, dist, device="cuda")
-            assert table.shape[0] == world * P
+            table = gather_records(pack_records(res, pair_ids), P_total, dist, device="cuda")
+            assert table.shape[0] == P_total
         return off, out, d2h
 
     def sync_all():
@@ -286,11 +303,11 @@ def run_b200(args):
     n_cand, n_hyp_solved, n_evals, n_evals_exec = ctx.verify_stats(reset=True)
     # the device-event time excludes nothing but host gaps after the last kernel; use the larger of the two clocks
     step_ms = max(ms, wall * 1e3) / args.steps
-    value = world * P / (step_ms / 1e3)
+    value = P_total / (step_ms / 1e3)
 
     # ---- the stage after verify() in run_2view (GT metrics + InlierSupportProcessor), timed on its own:
     # it is not part of BASELINE's metric, so it stays outside `value` / `e2e`
-    gt = [scene.relative_pose(int(a), int(b)) for a, b in pairs]
+    gt = [scene.relative_pose(int(a), int(b)) for a, b in pairs_g]
     gt_R, gt_t = np.stack([g[0] for g in gt]), np.stack([g[1] for g in gt])
     rep = ctx.two_view_report_batch(P, int(off[-1]), scene.threshold_px, 15, 0.1, gt_R, gt_t)
     ctx.event_record(2)
@@ -325,7 +342,7 @@ def run_b200(args):
         e2e_step()
     ems, ewall, (_, _, d2h_bytes) = timed(e2e_step, args.steps)
     e2e_ms = max(ems, ewall * 1e3) / args.steps
-    e2e_value = world * P / (e2e_ms / 1e3)
+    e2e_value = P_total / (e2e_ms / 1e3)
 
     if rank == 0:
         peaks = load_peaks()
@@ -357,13 +374,15 @@ def run_b200(args):
         roofline["traffic"] = load_traffic(args, cfg)
         n_match = int(off[-1])
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-                "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16 GEMM / f32 scoring / f64 finalize",
+                "ms_per_step": step_ms, "higher_is_better": True, "scaling": "strong" if strong else "weak", "vs_baseline": None, "dtype": "bf16 GEMM / f32 scoring / f64 finalize",
                 "data": "reference fixture (Lund door SIFT features)" if args.config == "C1" else "synthetic",
-                "config": {"workload": workload_name(args, cfg, P), "pairs_per_gpu": P, "ratio_test": scene.ratio, "n_hypotheses": scene.n_hyp,
+                "config": {"workload": workload_name(args, cfg, P_total if strong else P), "pairs_per_gpu": P, "ratio_test": scene.ratio, "n_hypotheses": scene.n_hyp,
                            "threshold_px": scene.threshold_px, "lo_iters": 20, "matches_per_pair": n_match / P,
                            "inliers_per_pair": float(out["n_inliers"].mean()), "verified_ok": int((out["status"] == 0).sum()),
                            "l2": "inputs exceed L2 (descriptor store %.0f MB per GPU)" % (n_img * n_kps * (dim * 7 + 96) / 1e6),
-                           "parallelism": f"pairs sharded over {world} GPU(s), NCCL all_gather of result records" if world > 1 else "1 GPU"},
+                           "parallelism": (f"one pair list dealt over {world} GPU(s) (shard_pairs), {n_img} of {len(scene.descriptors)} images on rank 0, "
+                                           "NCCL all_gather of result records") if strong else
+                                          f"pairs sharded over {world} GPU(s), NCCL all_gather of result records" if world > 1 else "1 GPU"},
                 "roofline": roofline, "cpu_baseline": cpu,
                 "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": int(d2h_bytes)},
                 "gpu_launches": int(launches), "clocks": clk, "device_event_ms_per_step": ms / args.steps,
