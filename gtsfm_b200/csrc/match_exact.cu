@@ -29,6 +29,8 @@ __device__ __forceinline__ int find_by_job0(const PairDesc* pairs, int n, int jo
 }
 
 // mode 0: jobs enumerated from PairDesc::job0 (float-path pairs); mode 1: one job per flagged row / column.
+// NU = scan rows per warp: 4 in mode 0, 1 in mode 1 (a flagged job is ONE row; computing four cost 4x the arithmetic).
+template <int NU>
 __global__ void __launch_bounds__(256) exact_scan_kernel(StoreView st, MatchWork w, int mode, int n_range_jobs)
 {
     extern __shared__ float sm[];
@@ -75,10 +77,10 @@ __global__ void __launch_bounds__(256) exact_scan_kernel(StoreView st, MatchWork
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int h = lane >> 4, r16 = lane & 15;
     const int nblk = dim / 16;
-    float f1[4], f2[4];
-    int i1[4];
+    float f1[NU], f2[NU];
+    int i1[NU];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) { f1[u] = FLT_MAX; f2[u] = FLT_MAX; i1[u] = INT_MAX; }
+    for (int u = 0; u < NU; ++u) { f1[u] = FLT_MAX; f2[u] = FLT_MAX; i1[u] = INT_MAX; }
     const bool single = mode == 1;                     // one scan row: the 8 warps split each tile's rows
     const bool warp_active = single || warp * 4 < cnt;
     const int qrow0 = single ? 0 : warp * 4;
@@ -110,17 +112,19 @@ __global__ void __launch_bounds__(256) exact_scan_kernel(StoreView st, MatchWork
         for (int it = it0; it < it1; ++it) {
             const int jr = 2 * it + h;
             const float* trow = stile + jr * tstride;
-            float acc[4] = {0.f, 0.f, 0.f, 0.f};
+            float acc[NU];
+#pragma unroll
+            for (int u = 0; u < NU; ++u) acc[u] = 0.f;
             for (int b = 0; b < nblk; ++b) {
                 const float tv = trow[16 * b + r16];
 #pragma unroll
-                for (int u = 0; u < 4; ++u) {
+                for (int u = 0; u < NU; ++u) {
                     const float d = __fsub_rn(sq[(qrow0 + u) * dim + 16 * b + r16], tv);
                     acc[u] = __fadd_rn(acc[u], __fmul_rn(d, d));
                 }
             }
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
+            for (int u = 0; u < NU; ++u) {
                 const int l = r16 & 3;
                 const float a0 = __shfl_sync(0xffffffffu, acc[u], l, 16), a1 = __shfl_sync(0xffffffffu, acc[u], 4 + l, 16);
                 const float a2 = __shfl_sync(0xffffffffu, acc[u], 8 + l, 16), a3 = __shfl_sync(0xffffffffu, acc[u], 12 + l, 16);
@@ -143,7 +147,7 @@ __global__ void __launch_bounds__(256) exact_scan_kernel(StoreView st, MatchWork
     }
     if (!warp_active) continue;
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
+    for (int u = 0; u < NU; ++u) {
         const float o1 = __shfl_xor_sync(0xffffffffu, f1[u], 16), o2 = __shfl_xor_sync(0xffffffffu, f2[u], 16);
         const int oi = __shfl_xor_sync(0xffffffffu, i1[u], 16);
         const bool take = (o1 < f1[u]) || (o1 == f1[u] && oi < i1[u]);
@@ -208,15 +212,20 @@ cudaError_t launch_exact_scan(const StoreView& st, const MatchWork& w, int mode,
 {
     if (n_jobs <= 0) return cudaSuccess;
     const size_t smem = static_cast<size_t>(kScanRows * st.dim + kScanTile * (st.dim + 16)) * sizeof(float);
-    static size_t configured = 0;
+    static size_t configured_all[64][2] = {};             // per device (the attribute is per device) and per instantiation
+    int dev = 0;
+    cudaGetDevice(&dev);
+    size_t& configured = configured_all[dev & 63][mode == 1 ? 1 : 0];
     if (smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(exact_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+        cudaError_t e = mode == 1 ? cudaFuncSetAttribute(exact_scan_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem))
+                                  : cudaFuncSetAttribute(exact_scan_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
         if (e != cudaSuccess) return e;
         configured = smem;
     }
     const long long items = mode == 0 ? n_jobs : static_cast<long long>(n_jobs) * kScanSeg;
     const int grid = static_cast<int>(items < 1184 ? items : 1184);
-    exact_scan_kernel<<<grid, 256, smem, s>>>(st, w, mode, n_jobs);
+    if (mode == 1) exact_scan_kernel<1><<<grid, 256, smem, s>>>(st, w, mode, n_jobs);
+    else exact_scan_kernel<4><<<grid, 256, smem, s>>>(st, w, mode, n_jobs);
     return cudaGetLastError();
 }
 
