@@ -290,7 +290,7 @@ def run_b200(args):
     upload()
     for _ in range(args.warmup):
         compute(False)
-    ctx.profile_enable(True)
+    ctx.profile_enable(not os.environ.get("GTSFM_B200_BENCH_NOPROF"))      # diagnostics: how much the per-kernel events cost
     ctx.verify_stats(reset=True)
     launches0 = ctx.kernel_launches
     clocks = ClockSampler(local)
