@@ -253,7 +253,7 @@ def run_b200(args):
     def compute(fetch: bool):
         # e2e leg: the match D2H is enqueued on the copy stream and overlaps the verifier; results land in pinned buffers
         m, off = ctx.match_batch(pairs, scene.ratio, fetch="async" if fetch else False)
-        out = ctx.verify_batch(pairs, prm, total=int(off[-1]), reuse_outputs=fetch)
+        out = ctx.verify_batch(pairs, prm, total=int(off[-1]), reuse_outputs=True)      # results land in the pinned arena in both legs
         if fetch:
             ctx.sync()
         d2h = m.nbytes + out["mask"].nbytes + out["R"].nbytes + out["t"].nbytes + out["E"].nbytes + out["n_inliers"].nbytes + out["status"].nbytes + 4 * P
