@@ -309,9 +309,9 @@ def run_b200(args):
     # it is not part of BASELINE's metric, so it stays outside `value` / `e2e`
     gt = [scene.relative_pose(int(a), int(b)) for a, b in pairs_g]
     gt_R, gt_t = np.stack([g[0] for g in gt]), np.stack([g[1] for g in gt])
-    rep = ctx.two_view_report_batch(P, int(off[-1]), scene.threshold_px, 15, 0.1, gt_R, gt_t)
+    rep = ctx.two_view_report_batch(P, int(off[-1]), scene.threshold_px, 15, 0.1, gt_R, gt_t, reuse_outputs=True)
     ctx.event_record(2)
-    rep = ctx.two_view_report_batch(P, int(off[-1]), scene.threshold_px, 15, 0.1, gt_R, gt_t)
+    rep = ctx.two_view_report_batch(P, int(off[-1]), scene.threshold_px, 15, 0.1, gt_R, gt_t, reuse_outputs=True)
     ctx.event_record(3)
     report_ms = ctx.event_elapsed_ms(2, 3)
     ok_pairs = out["status"] == 0

@@ -364,14 +364,19 @@ class Context:
 
     def two_view_report_batch(self, n_pairs: int, total: int, dist_threshold_px: float, min_num_inliers_est_model: int,
                               min_inlier_ratio_est_model: float, gt_i2Ri1: Optional[np.ndarray] = None,
-                              gt_i2ti1: Optional[np.ndarray] = None):
-        """Post-verification report of the pairs of the last verify_batch (gtsfm_two_view_report_batch)."""
+                              gt_i2ti1: Optional[np.ndarray] = None, reuse_outputs: bool = False):
+        """Post-verification report of the pairs of the last verify_batch (gtsfm_two_view_report_batch).  With reuse_outputs the
+        per-correspondence arrays are views of the context's pinned arena (valid until the next report call)."""
         P = int(n_pairs)
         prm = ReportParams(float(dist_threshold_px), int(min_num_inliers_est_model), float(min_inlier_ratio_est_model))
         if gt_i2Ri1 is not None:
             gt_i2Ri1 = np.ascontiguousarray(gt_i2Ri1, np.float64).reshape(P, 9)
             gt_i2ti1 = np.ascontiguousarray(gt_i2ti1, np.float64).reshape(P, 3)
-        dist = np.full(max(int(total), 1), np.nan); gmask = np.zeros(max(int(total), 1), np.uint8)
+        nt = max(int(total), 1)                      # the kernel writes every row (NaN / 0 where nothing was verified)
+        dist = self._pinned("report_dist", (nt,), np.float64) if reuse_outputs else np.empty(nt, np.float64)
+        gmask = self._pinned("report_mask", (nt,), np.uint8) if reuse_outputs else np.empty(nt, np.uint8)
+        if int(total) == 0:
+            dist[:] = np.nan; gmask[:] = 0
         n_gt = np.zeros(P, np.int32); keep = np.zeros(P, np.int32)
         in_avg = np.zeros(P); out_avg = np.zeros(P); r_err = np.zeros(P); u_err = np.zeros(P)
         self._check(self._L.gtsfm_two_view_report_batch(self._h, P, _ptr(gt_i2Ri1), _ptr(gt_i2ti1), ctypes.byref(prm), _ptr(dist),
