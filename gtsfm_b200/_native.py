@@ -199,6 +199,8 @@ class Context:
 
     # ---- store
     def clear(self):
+        if self._keep:          # uploads nothing has waited for yet may still be reading these host arrays
+            self.sync()
         self._check(self._L.gtsfm_store_clear(self._h))
         self._keep.clear()
         self._n_images = 0

@@ -90,6 +90,8 @@ int store_reserve_rows(gtsfm_ctx* c, long long rows)
     long long ncap = c->rows_cap ? c->rows_cap : 4096;
     while (ncap < rows) ncap *= 2;
     cudaStream_t s = c->stream;
+    // a growing buffer is copied and freed on `s`: no upload copy (copy_stream) may still be writing into the old one
+    G2V_CUDA(c, cudaStreamSynchronize(c->copy_stream));
     G2V_CUDA(c, c->desc_bf16.reserve(static_cast<size_t>(ncap) * c->kpad * 2, true, s));
     G2V_CUDA(c, c->desc_u8.reserve(static_cast<size_t>(ncap) * c->kpad, true, s));
     G2V_CUDA(c, c->desc_f32.reserve(static_cast<size_t>(ncap) * c->dim * 4, true, s));
@@ -208,7 +210,8 @@ int gtsfm_ctx_create(int device, gtsfm_ctx** out)
     c->n_sm = prop.multiProcessorCount;
     if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return fail(nullptr, GTSFM_E_CUDA, "cudaStreamCreate failed"); }
     if (cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaEventCreateWithFlags(&c->match_done, cudaEventDisableTiming) != cudaSuccess) {
+        cudaEventCreateWithFlags(&c->match_done, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->upload_ev, cudaEventDisableTiming) != cudaSuccess) {
         delete c;
         return fail(nullptr, GTSFM_E_CUDA, "cudaStreamCreate failed");
     }
@@ -237,6 +240,7 @@ void gtsfm_ctx_destroy(gtsfm_ctx* c)
     for (cudaEvent_t e : c->user_ev) if (e) cudaEventDestroy(e);
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     if (c->match_done) cudaEventDestroy(c->match_done);
+    if (c->upload_ev) cudaEventDestroy(c->upload_ev);
     cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -311,6 +315,9 @@ int gtsfm_store_clear(gtsfm_ctx* c)
     c->maps_valid = false;
     c->batch_n = 0;
     c->batch_total = 0;
+    // the next uploads overwrite rows that kernels already enqueued on `stream` may still read
+    G2V_CUDA(c, cudaEventRecord(c->upload_ev, c->stream));
+    G2V_CUDA(c, cudaStreamWaitEvent(c->copy_stream, c->upload_ev, 0));
     return GTSFM_OK;
 }
 
@@ -353,7 +360,13 @@ int gtsfm_image_upload(gtsfm_ctx* c, int image_id, const float* desc, int n, int
     }
     if (rec.n > 0) {
         float* dst = c->desc_f32.as<float>() + static_cast<long long>(rec.row0) * c->dim;
-        G2V_CUDA(c, cudaMemcpyAsync(dst, desc, static_cast<size_t>(rec.n) * c->dim * 4, cudaMemcpyHostToDevice, c->stream));
+        // H2D on the copy stream, so that the copy of image i + 1 overlaps the prepare kernel of image i; `stream` waits for
+        // this image's copies only (one event, re-recorded per image: a wait refers to the record that precedes it)
+        G2V_CUDA(c, cudaMemcpyAsync(dst, desc, static_cast<size_t>(rec.n) * c->dim * 4, cudaMemcpyHostToDevice, c->copy_stream));
+        if (kps)
+            G2V_CUDA(c, cudaMemcpyAsync(c->kps.as<double2>() + rec.row0, kps, static_cast<size_t>(n) * 16, cudaMemcpyHostToDevice, c->copy_stream));
+        G2V_CUDA(c, cudaEventRecord(c->upload_ev, c->copy_stream));
+        G2V_CUDA(c, cudaStreamWaitEvent(c->stream, c->upload_ev, 0));
         PrepareArgs a;
         a.src = dst;
         a.bf = c->desc_bf16.as<__nv_bfloat16>() + static_cast<long long>(rec.row0) * c->kpad;
@@ -374,7 +387,7 @@ int gtsfm_image_upload(gtsfm_ctx* c, int image_id, const float* desc, int n, int
         ++c->launches;
         c->flags_dirty = true;
     }
-    if (kps && n > 0)
+    if (kps && n > 0 && rec.n == 0)         // keypoint-only image (the other case copied them above)
         G2V_CUDA(c, cudaMemcpyAsync(c->kps.as<double2>() + rec.row0, kps, static_cast<size_t>(n) * 16, cudaMemcpyHostToDevice, c->stream));
     c->images.push_back(rec);
     c->rows_used += n_rows;

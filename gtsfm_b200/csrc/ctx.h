@@ -38,6 +38,7 @@ struct gtsfm_ctx {
     cudaStream_t stream = nullptr;
     cudaStream_t copy_stream = nullptr;     // device -> host copies that overlap the next kernels (gtsfm_match_fetch_async)
     cudaEvent_t match_done = nullptr;       // recorded on `stream` when the compacted matches of a batch are complete
+    cudaEvent_t upload_ev = nullptr;        // image uploads: H2D copies run on copy_stream, `stream` waits for them per image
     std::string err;
     int64_t launches = 0;
     int64_t workspace_bytes = 12ll << 30;
