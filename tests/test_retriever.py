@@ -97,3 +97,21 @@ def test_device_retriever_errors():
         r.compute_similarity_matrix([np.zeros(4, np.float32)] * 10001)
     # one image: no pairs
     assert r.get_image_pairs([np.ones(8, np.float32)], ["a"]) == []
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,dim,k,blocksize", [(77, 100, 4, 50), (65, 7, 70, 3), (2, 513, 1, 50), (129, 130, 5, 64)])
+def test_device_retriever_odd_shapes_vs_oracle(n, dim, k, blocksize):
+    """Dimensions that are not multiples of the 16-wide K chunk, image counts around the 64-wide tile, tiny blocks."""
+    from oracle import oracle as O
+    from gtsfm_b200.retriever.netvlad_retriever import NetVLADRetriever
+    rng = np.random.default_rng(n * 1000 + dim)
+    G = rng.standard_normal((n, dim)).astype(np.float32)
+    G /= np.linalg.norm(G, axis=1, keepdims=True)
+    r = NetVLADRetriever(num_matched=k, min_score=-1.0, blocksize=blocksize)
+    sim = r.compute_similarity_matrix(list(G))
+    ref = O.retriever_similarity(G, blocksize)
+    np.testing.assert_allclose(sim, ref, atol=TOL, rtol=0)
+    assert ((sim == 0) == (ref == 0)).all() or np.abs(ref[(sim == 0) != (ref == 0)]).max() < TOL
+    pairs = r.get_image_pairs(list(G), [str(i) for i in range(n)])
+    assert [(int(i), int(j)) for i, j in pairs] == O.pairs_from_score_matrix(sim, k, -1.0)
