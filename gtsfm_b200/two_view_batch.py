@@ -107,10 +107,12 @@ def shard_pairs(pairs: np.ndarray, n_shards: int, cost: Optional[np.ndarray] = N
 def run_two_view_batch(descriptors: Sequence[np.ndarray], keypoints: Sequence[np.ndarray], intrinsics: Sequence, pairs: np.ndarray,
                        ratio_test_threshold: Optional[float] = 0.8, estimation_threshold_px: float = 4.0, num_hypotheses: int = 1024,
                        seed: int = 0, lo_iters: int = 20, device: int = 0, ctx: Optional[_native.Context] = None,
-                       upload: bool = True, fetch_matches: bool = True) -> TwoViewBatchResult:
+                       upload: bool = True, fetch_matches: bool = True, pinned_outputs: bool = False) -> TwoViewBatchResult:
     """Match + verify every pair of one shard on one GPU.  Only the images a shard's pairs name are uploaded; image
     indices in `pairs` refer to the caller's lists.  keypoints: (N, 2) pixel arrays; intrinsics: Cal3Bundler-likes or
-    (f, k1, k2, u0, v0) tuples."""
+    (f, k1, k2, u0, v0) tuples.  pinned_outputs: the result arrays are views of the context's page-locked arena (device -> host
+    copies at full PCIe rate instead of through pageable staging: ~55 ms less per 5,000 C2-sized pairs); they stay valid until
+    the next batch on the same context, so copy what must outlive it."""
     pairs = np.ascontiguousarray(pairs, np.int32).reshape(-1, 2)
     ctx = ctx or _native.default_context(device)
     if upload:
@@ -127,8 +129,8 @@ def run_two_view_batch(descriptors: Sequence[np.ndarray], keypoints: Sequence[np
     p.threshold_px, p.n_hypotheses, p.lo_iters, p.seed = float(estimation_threshold_px), int(num_hypotheses), int(lo_iters), int(seed)
     keys = (pairs[:, 0].astype(np.uint64) << np.uint64(32)) | pairs[:, 1].astype(np.uint64)   # sampler keys = global pair ids
     p.pair_keys, p.samples = keys.ctypes.data, None
-    matches, off = ctx.match_batch(local, ratio_test_threshold, fetch=fetch_matches)
-    out = ctx.verify_batch(local, p, total=int(off[-1]))
+    matches, off = ctx.match_batch(local, ratio_test_threshold, fetch=fetch_matches, reuse_outputs=pinned_outputs)
+    out = ctx.verify_batch(local, p, total=int(off[-1]), reuse_outputs=pinned_outputs)
     return TwoViewBatchResult(pairs, off, matches, out["mask"], out["R"], out["t"], out["n_inliers"], out["status"])
 
 

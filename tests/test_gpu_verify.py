@@ -465,3 +465,16 @@ def test_two_view_reports_python_layer(ctx):
         assert r.R_error_deg < 1.0 and r.num_inliers_gt_model > 0.9 * r.num_inliers_est_model
         kept = isp.run_inlier_support(Rd[key], td[key], vd[key], r)[0] is not None
         assert kept == bool(keep[p])
+
+
+def test_run_two_view_batch_pinned_outputs_equal_owned_outputs(ctx):
+    """pinned_outputs only changes where the results live (the context's page-locked arena), never what they are."""
+    from gtsfm_b200 import synthetic
+    from gtsfm_b200.two_view_batch import run_two_view_batch
+    scene = synthetic.make_scene(n_images=5, n_kps=1024, seed=11)
+    kw = dict(ratio_test_threshold=0.8, estimation_threshold_px=4.0, num_hypotheses=128, seed=2, ctx=ctx)
+    a = run_two_view_batch(scene.descriptors, scene.keypoints, [scene.cal] * 5, scene.pairs, **kw)
+    b = run_two_view_batch(scene.descriptors, scene.keypoints, [scene.cal] * 5, scene.pairs, pinned_outputs=True, **kw)
+    for name in ("match_offsets", "matches", "inlier_mask", "R", "t", "n_inliers", "status"):
+        np.testing.assert_array_equal(getattr(a, name), getattr(b, name))
+    assert not b.matches.flags.owndata and a.matches.flags.owndata
