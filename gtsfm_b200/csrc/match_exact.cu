@@ -90,9 +90,13 @@ __global__ void __launch_bounds__(256) exact_scan_kernel(StoreView st, MatchWork
     const int seg_len = single ? ((other_n + kScanSeg * kScanTile - 1) / (kScanSeg * kScanTile)) * kScanTile : other_n;
     const int t_begin = single ? min(other_n, seg * seg_len) : 0;
     const int t_end = single ? min(other_n, t_begin + seg_len) : other_n;
+    if constexpr (NU == 1) __syncthreads();           // the scan row in `sq` is complete
     for (int t0 = t_begin; t0 < t_end; t0 += kScanTile) {
-        __syncthreads();
         const int tn = min(kScanTile, t_end - t0);
+        // A flagged job uses every element of the other side once: its half warps stream the rows straight from global
+        // memory (same row -> half-warp assignment and arithmetic as the staged path, so the results are identical).
+        if constexpr (NU != 1) {
+        __syncthreads();
         if ((dim & 3) == 0) {
             const int d4 = dim >> 2;
             for (int k = threadIdx.x; k < tn * d4; k += blockDim.x) {
@@ -108,13 +112,16 @@ __global__ void __launch_bounds__(256) exact_scan_kernel(StoreView st, MatchWork
         }
         if (threadIdx.x < kScanTile) svalid[threadIdx.x] = threadIdx.x < tn ? st.valid[other_base + t0 + threadIdx.x] : 0;
         __syncthreads();
+        }
         if (!warp_active) continue;
         for (int it = it0; it < it1; ++it) {
             const int jr = 2 * it + h;
-            const float* trow = stile + jr * tstride;
+            const long long grow = static_cast<long long>(other_base) + t0 + (jr < tn ? jr : tn - 1);
+            const float* trow = NU == 1 ? st.desc_f32 + grow * dim : stile + jr * tstride;
             float acc[NU];
 #pragma unroll
             for (int u = 0; u < NU; ++u) acc[u] = 0.f;
+#pragma unroll(NU == 1 ? 8 : 1)
             for (int b = 0; b < nblk; ++b) {
                 const float tv = trow[16 * b + r16];
 #pragma unroll
@@ -137,7 +144,7 @@ __global__ void __launch_bounds__(256) exact_scan_kernel(StoreView st, MatchWork
                     d = __fadd_rn(d, __fmul_rn(t, t));
                 }
                 const float f = sqrtf(d);
-                const bool ok = jr < tn && svalid[jr];
+                const bool ok = jr < tn && (NU == 1 ? st.valid[grow] != 0 : svalid[jr] != 0);
                 // cv2's top-2 insertion: strict '<', so the lowest train index wins ties
                 if (ok && f < f2[u]) {
                     if (f < f1[u]) { f2[u] = f1[u]; f1[u] = f; i1[u] = t0 + jr; } else f2[u] = f;
