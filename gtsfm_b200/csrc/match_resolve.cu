@@ -272,21 +272,21 @@ __global__ void __launch_bounds__(128, 8) bucket_rows_kernel(StoreView st, Match
 #pragma unroll
     for (int g = 0; g <= kHalfT / kGroup; ++g) o[g] = off[g];
     if (o[kHalfT / kGroup] == o[0]) return;
-    const long long trow0 = static_cast<long long>(pd.t_row0) + hb * kHalfT;
-    const uint4* tsrc = reinterpret_cast<const uint4*>(st.desc_u8) + trow0 * N16;
-    for (int idx = tid; idx < kHalfT * N16; idx += 128) {
-        const int r = idx / N16, k = idx % N16;
-        s_t[r * kStride + k] = __ldg(tsrc + idx);
-    }
-    s_norm[tid] = st.norm_i[trow0 + tid];
-    s_valid[tid] = (hb * kHalfT + tid < pd.nt) ? st.valid[trow0 + tid] : 0;
-    __syncthreads();
-
     int tiles = 0;
 #pragma unroll
     for (int g = 0; g < kHalfT / kGroup; ++g) tiles += (o[g + 1] - o[g] + 15) >> 4;
-    for (int tile = warp; tile < tiles; tile += 4) {
-        int g = 0, local = tile, first = o[0], n_g = o[1] - o[0];
+
+    // Registers of one tile of 16 members: everything that comes from global memory.  The first tile of every warp is
+    // fetched BEFORE the train rows are staged, so its gather latency hides behind the staging loads and the barrier
+    // (both were ~28 % of the stall samples each).
+    int g = 0, n_g = 0, i_lo = 0, i_hi = 0, n_lo = 0, n_hi = 0;
+    bool act_lo = false, act_hi = false;
+    long long pos = 0;
+    float k1 = 0.f, k2 = 0.f;
+    uint4 L[N16 / 4], H[N16 / 4];
+    auto fetch = [&](int tile) {
+        int local = tile, first = o[0];
+        g = 0; n_g = o[1] - o[0];
 #pragma unroll
         for (int gg = 0; gg < kHalfT / kGroup; ++gg) {
             const int tg = (o[gg + 1] - o[gg] + 15) >> 4;
@@ -295,16 +295,32 @@ __global__ void __launch_bounds__(128, 8) bucket_rows_kernel(StoreView st, Match
             local -= here ? (1 << 30) : tg;
         }
         const int* list = w.row_list + pd.out_base + first;
-        const bool act_lo = gid < n_g, act_hi = gid + 8 < n_g;
-        const int i_lo = act_lo ? list[gid] : list[0], i_hi = act_hi ? list[gid + 8] : i_lo;
+        act_lo = gid < n_g; act_hi = gid + 8 < n_g;
+        i_lo = act_lo ? list[gid] : list[0]; i_hi = act_hi ? list[gid + 8] : i_lo;
         const uint4* r_lo = reinterpret_cast<const uint4*>(st.desc_u8) + static_cast<long long>(pd.q_row0 + i_lo) * N16 + q;
         const uint4* r_hi = reinterpret_cast<const uint4*>(st.desc_u8) + static_cast<long long>(pd.q_row0 + i_hi) * N16 + q;
-        uint4 L[N16 / 4], H[N16 / 4];
 #pragma unroll
         for (int k = 0; k < N16 / 4; ++k) { L[k] = __ldg(r_lo + 4 * k); H[k] = __ldg(r_hi + 4 * k); }
-        const int n_lo = st.norm_i[pd.q_row0 + i_lo], n_hi = st.norm_i[pd.q_row0 + i_hi];
-        const long long pos = pd.out_base + ((q & 1) ? i_hi : i_lo);      // lane q = 0 finishes row g, lane q = 1 row g + 8
-        const float k1 = w.row_d1[pos], k2 = w.row_d2[pos];              // screened values, in flight during the products
+        n_lo = st.norm_i[pd.q_row0 + i_lo]; n_hi = st.norm_i[pd.q_row0 + i_hi];
+        pos = pd.out_base + ((q & 1) ? i_hi : i_lo);                       // lane q = 0 finishes row g, lane q = 1 row g + 8
+        k1 = w.row_d1[pos]; k2 = w.row_d2[pos];                            // screened values
+    };
+    if (warp < tiles) fetch(warp);
+
+    const long long trow0 = static_cast<long long>(pd.t_row0) + hb * kHalfT;
+    const uint4* tsrc = reinterpret_cast<const uint4*>(st.desc_u8) + trow0 * N16;
+#pragma unroll
+    for (int it = 0; it < kHalfT * N16 / 128; ++it) {                       // all loads of the block in flight at once
+        const int idx = tid + it * 128;
+        const int r = idx / N16, k = idx % N16;
+        s_t[r * kStride + k] = __ldg(tsrc + idx);
+    }
+    s_norm[tid] = st.norm_i[trow0 + tid];
+    s_valid[tid] = (hb * kHalfT + tid < pd.nt) ? st.valid[trow0 + tid] : 0;
+    __syncthreads();
+
+    for (int tile = warp; tile < tiles; tile += 4) {
+        if (tile != warp) fetch(tile);
         Top2 tl{INT_MAX, INT_MAX, INT_MAX}, th{INT_MAX, INT_MAX, INT_MAX};
 #pragma unroll
         for (int nt = 0; nt < kGroup / 8; ++nt) {
