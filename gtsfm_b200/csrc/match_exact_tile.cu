@@ -209,7 +209,10 @@ cudaError_t launch_exact_tile(const StoreView& st, const MatchWork& w, int n_job
 {
     if (n_jobs <= 0) return cudaSuccess;
     const size_t smem = static_cast<size_t>(kTQ + kTT) * (st.dim + 4) * sizeof(float);
-    static size_t configured = 0;
+    static size_t configured_all[64] = {};             // per device: cudaFuncSetAttribute applies to the current device only
+    int dev = 0;
+    cudaGetDevice(&dev);
+    size_t& configured = configured_all[dev & 63];
     if (smem > configured) {
         cudaError_t e = cudaFuncSetAttribute(exact_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
         if (e != cudaSuccess) return e;
