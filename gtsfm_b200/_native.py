@@ -20,7 +20,7 @@ EXPORTS = (
     "gtsfm_verify_batch", "gtsfm_two_view_report_batch", "gtsfm_match_pair", "gtsfm_verify_pair", "gtsfm_debug_fetch",
     "gtsfm_profile_enable", "gtsfm_profile_get", "gtsfm_event_record", "gtsfm_event_elapsed_ms", "gtsfm_verify_stats",
     "gtsfm_host_alloc", "gtsfm_host_free", "gtsfm_match_fetch_async", "gtsfm_sync",
-    "gtsfm_retriever_similarity", "gtsfm_retriever_topk",
+    "gtsfm_retriever_similarity", "gtsfm_retriever_topk", "gtsfm_retriever_pairs_noalloc",
 )
 
 OK, E_CUDA, E_ARG, E_NO_DEVICE, E_KNN_UNPACK, E_UNSUPPORTED = range(6)
@@ -99,6 +99,8 @@ def lib() -> ctypes.CDLL:
             L.gtsfm_retriever_similarity.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_void_p]
             L.gtsfm_retriever_topk.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_double, ctypes.c_void_p,
                                                ctypes.c_void_p]
+            L.gtsfm_retriever_pairs_noalloc.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_double,
+                                                        ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
             L.gtsfm_two_view_report_batch.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p,
                                                       ctypes.POINTER(ReportParams)] + [ctypes.c_void_p] * 8
             L.gtsfm_match_pair.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int,

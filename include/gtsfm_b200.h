@@ -168,6 +168,23 @@ int gtsfm_retriever_similarity(gtsfm_ctx* ctx, const float* global_desc, int n_i
 int gtsfm_retriever_topk(gtsfm_ctx* ctx, const float* sim_in, int n_images, int num_select, double min_score, int32_t* out_idx,
                          float* out_score);
 
+/* ---- allocation-free retriever step ---------------------------------------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * gtsfm_retriever_similarity + gtsfm_retriever_topk in one call that allocates nothing: the (n_images, n_images) similarity
+ * matrix lives in a fixed __device__ array inside the library (GTSFM_RETRIEVER_NOALLOC_MAX_IMAGES^2 floats = 4 MiB, held by
+ * every GPU that loads the library until the process exits).  d_global_desc (n_images, dim) float32, d_out_idx / d_out_score
+ * (n_images, num_select) are DEVICE pointers of the current device, everything is enqueued on cuda_stream (a cudaStream_t,
+ * NULL = the legacy default stream) and the call returns without synchronising; results (same values as the two regular
+ * calls: unused slots -1 / -inf, min_score NaN = no minimum) are ready once the stream reaches that point.  n_images above the
+ * maximum, or num_select > n_images, -> GTSFM_E_ARG with the text in gtsfm_last_error(NULL).  No context is involved.  All
+ * calls on one device share the array, which keeps the previous call's contents (the part a call uses is cleared first):
+ * calls that overlap on the GPU -- different streams without an ordering between them -- race.  The first call on each
+ * device looks up the array's address (cudaGetSymbolAddress): make that call outside stream capture. */
+#define GTSFM_RETRIEVER_NOALLOC_MAX_IMAGES 1024
+int gtsfm_retriever_pairs_noalloc(const float* d_global_desc, int n_images, int dim, int blocksize, int num_select, double min_score,
+                                  int32_t* d_out_idx, float* d_out_score, void* cuda_stream);
+
 /* ---- single-pair conveniences used by the MatcherBase / VerifierBase plugin classes ---------------------------- */
 /* TwoWayMatcher.match for one pair from host arrays.  out capacity: min(n1, n2) rows of 2 uint32. */
 int gtsfm_match_pair(gtsfm_ctx* ctx, const float* desc1, int n1, const float* desc2, int n2, int dim, double ratio,
