@@ -21,6 +21,7 @@ EXPORTS = (
     "gtsfm_profile_enable", "gtsfm_profile_get", "gtsfm_event_record", "gtsfm_event_elapsed_ms", "gtsfm_verify_stats",
     "gtsfm_host_alloc", "gtsfm_host_free", "gtsfm_match_fetch_async", "gtsfm_sync",
     "gtsfm_retriever_similarity", "gtsfm_retriever_topk", "gtsfm_retriever_pairs_noalloc",
+    "gtsfm_verify_hypotheses_used",
 )
 
 OK, E_CUDA, E_ARG, E_NO_DEVICE, E_KNN_UNPACK, E_UNSUPPORTED = range(6)
@@ -40,6 +41,8 @@ class VerifyParams(ctypes.Structure):
         ("pair_keys", ctypes.c_void_p),
         ("samples", ctypes.c_void_p),
         ("estimate_fundamental", ctypes.c_int),
+        ("adaptive_max_hypotheses", ctypes.c_int),
+        ("confidence", ctypes.c_double),
     ]
 
 
@@ -81,6 +84,7 @@ def lib() -> ctypes.CDLL:
             L.gtsfm_host_free.restype = None
             L.gtsfm_match_fetch_async.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
             L.gtsfm_sync.argtypes = [ctypes.c_void_p]
+            L.gtsfm_verify_hypotheses_used.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
             L.gtsfm_verify_stats.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_int64), ctypes.c_int]
             L.gtsfm_image_upload.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_int,
                                              ctypes.c_void_p, ctypes.c_void_p]
@@ -133,13 +137,17 @@ class Context:
         self._h = h
         self._keep = []   # host arrays whose asynchronous upload may still be in flight
         self._arena = {}  # name -> (pinned pointer, capacity in bytes): result buffers of the reuse_outputs mode
+        self._retired = []  # outgrown arena blocks (views handed out earlier stay valid memory until close())
         self.device = int(device)
 
     def close(self):
         if getattr(self, "_h", None):
             for ptr, _ in self._arena.values():
                 self._L.gtsfm_host_free(ptr)
+            for ptr in self._retired:
+                self._L.gtsfm_host_free(ptr)
             self._arena = {}
+            self._retired = []
             self._L.gtsfm_ctx_destroy(self._h)
             self._h = None
 
@@ -152,7 +160,7 @@ class Context:
         ptr, cap = self._arena.get(name, (None, 0))
         if cap < nbytes:
             if ptr:
-                self._L.gtsfm_host_free(ptr)
+                self._retired.append(ptr)     # arrays handed out earlier may still view it: freed at close(), never before
             cap = int(nbytes * 1.25) + 4096
             p = ctypes.c_void_p()
             self._check(self._L.gtsfm_host_alloc(ctypes.byref(p), cap))
@@ -185,6 +193,12 @@ class Context:
     @property
     def kernel_launches(self) -> int:
         return int(self._L.gtsfm_kernel_launches(self._h))
+
+    def verify_hypotheses_used(self, n_pairs: int) -> np.ndarray:
+        """Hypotheses evaluated per pair by the last verify_batch (differs from n_hypotheses only under the adaptive F budget)."""
+        out = np.zeros(int(n_pairs), np.int32)
+        self._check(self._L.gtsfm_verify_hypotheses_used(self._h, _ptr(out), int(n_pairs)))
+        return out
 
     def verify_stats(self, reset: bool = False):
         """(candidates scored, hypotheses solved, algorithmic Sampson evaluations, executed evaluations) since the last reset."""
@@ -228,14 +242,19 @@ class Context:
 
     def upload_image_u8(self, image_id: int, desc: np.ndarray, kps: Optional[np.ndarray] = None, cal=None):
         """Binary descriptors (n, nbytes) uint8 for the HAMMING distance; kps / cal as in upload_image."""
-        desc = np.ascontiguousarray(desc, np.uint8)
-        if desc.ndim != 2:
-            raise ValueError("descriptors must be (n, nbytes)")
-        n, nbytes = desc.shape
+        if desc is None or np.size(desc) == 0:      # an image without features: its pairs yield np.array([]) (twoway_matcher.py:71-72)
+            desc, n, nbytes = None, 0, 0
+        else:
+            desc = np.ascontiguousarray(desc, np.uint8)
+            if desc.ndim != 2:
+                raise ValueError("descriptors must be (n, nbytes)")
+            n, nbytes = desc.shape
         if kps is not None:
             kps = np.ascontiguousarray(kps, np.float64).reshape(-1, 2)
             if kps.shape[0] != n:
                 raise ValueError("keypoints and descriptors disagree on n")
+            if n == 0:
+                kps = None
         calv = None if cal is None else np.ascontiguousarray(cal, np.float64)
         self._keep += [desc, kps, calv]
         self._check(self._L.gtsfm_image_upload_u8(self._h, int(image_id), _ptr(desc), int(n), int(nbytes), _ptr(kps), _ptr(calv)))

@@ -399,7 +399,20 @@ int gtsfm_image_upload_u8(gtsfm_ctx* c, int image_id, const uint8_t* desc, int n
     if (!c) return GTSFM_E_ARG;
     cudaSetDevice(c->device);
     if (image_id != static_cast<int>(c->images.size())) return fail(c, GTSFM_E_ARG, "image ids must be dense and uploaded in order");
-    if (n < 0 || nbytes <= 0 || (n > 0 && !desc)) return fail(c, GTSFM_E_ARG, "bad descriptor array");
+    if (n < 0 || (n > 0 && (nbytes <= 0 || !desc))) return fail(c, GTSFM_E_ARG, "bad descriptor array");
+    if (n == 0) {
+        // an image without features (np.array([]) in the reference, twoway_matcher.py:71-72): its pairs yield no matches; it
+        // occupies no rows and fixes neither the descriptor size nor the kind of the store
+        ImageRec rec{};
+        rec.row0 = static_cast<int>(c->rows_used);
+        rec.path = 3; rec.dim = nbytes > 0 ? nbytes : 0;
+        if (cal) std::memcpy(rec.cal, cal, sizeof(rec.cal)); else { rec.cal[0] = 1; rec.cal[1] = rec.cal[2] = rec.cal[3] = rec.cal[4] = 0; }
+        G2V_CUDA(c, c->img_flags.reserve((c->images.size() + 1) * kImgFlagInts * sizeof(int), true, c->stream));
+        const int flags0[kImgFlagInts] = {4, 0, 0, 0};
+        G2V_CUDA(c, cudaMemcpyAsync(c->img_flags.as<int>() + kImgFlagInts * c->images.size(), flags0, sizeof(flags0), cudaMemcpyHostToDevice, c->stream));
+        c->images.push_back(rec);
+        return GTSFM_OK;
+    }
     if (nbytes > 64) return fail(c, GTSFM_E_UNSUPPORTED, "binary descriptors above 64 bytes");
     if (c->binary == 0) return fail(c, GTSFM_E_ARG, "this store holds float32 (EUCLIDEAN) descriptors");
     if (c->dim == 0) {

@@ -84,6 +84,7 @@ struct gtsfm_ctx {
     // ---- verifier buffers; state of the last gtsfm_verify_batch (read by gtsfm_two_view_report_batch)
     g2v::DevBuf v_bufs[24];
     int verify_n = 0;
+    std::vector<int> verify_hyp;            // hypotheses evaluated per pair of the last verify batch (adaptive F mode)
     long long verify_total = 0;
 
     // ---- retriever (retrieve.cu): global descriptors, similarity matrix of the last gtsfm_retriever_similarity, top-K outputs

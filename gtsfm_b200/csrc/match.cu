@@ -91,18 +91,18 @@ int gtsfm_match_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, double ra
         if (pd.path == 1 && !empty && qa.path == 1 && tb.path == 1 && qa.f16_ok && tb.f16_ok && screen_f_ok) pd.path = 2;
         if (qa.path == 3 || tb.path == 3) pd.path = 3;          // a store holds either binary or float32 descriptors
         pd.q_maxn2 = qa.max_norm2; pd.t_maxn2 = tb.max_norm2;
-        const long long rp = pd.path != 1 ? static_cast<long long>(pd.nq_pad) * (pd.nt_pad / kHalfT) : 0;
+        const long long rp = (pd.path == 0 || pd.path == 2) ? static_cast<long long>(pd.nq_pad) * (pd.nt_pad / kHalfT) : 0;
         const int n_tg = (pd.nq_pad / kTileQ + kFlushTiles - 1) / kFlushTiles;      // path 2: column minima per group of 4 query tiles
         const long long cr = pd.path == 0 ? static_cast<long long>(pd.nt_pad) * kTileQ
                                           : pd.path == 2 ? static_cast<long long>(pd.nt_pad) * n_tg * kTileQ : 0;
         const int items = pd.path == 0 && pd.nq > 0 ? pd.nt_pad / kBlockT : 0;
         const int fitems = pd.path == 2 && pd.nq > 0 ? pd.nt_pad / kBlockT : 0;
-        if (pd.path == 3 && pd.nq > 0) cur.hpairs += 1;
         const int jobs = pd.path == 1 && pd.nq > 0 ? (pd.nq + 31) / 32 + (pd.nt + 31) / 32 : 0;
         const long long bytes = rp * 9 + cr * 4 + static_cast<long long>(pd.nq_pad) * (12 + 16 + 8 + 8 + 8) + static_cast<long long>(pd.nt_pad) * (12 + 8 + 8);
         if (cur.p1 > cur.p0 && (cur_bytes + bytes > c->workspace_bytes || cur.rows + cur.cols + pd.nq_pad + pd.nt_pad > kFlagScratchCap)) { chunks.push_back(cur); cur = Chunk{}; cur.p0 = cur.p1 = p; cur_bytes = 0; }
         pd.rp_base = cur.rp; pd.cr_base = cur.cr; pd.out_base = cur.rows; pd.cb_base = cur.cols; pd.item0 = cur.items; pd.job0 = cur.jobs; pd.fitem0 = cur.fitems;
         cur.fitems += fitems;
+        if (pd.path == 3 && pd.nq > 0) cur.hpairs += 1;       // after the split test: the pair belongs to the chunk it lands in
         cur.rp += rp; cur.cr += cr; cur.rows += pd.nq_pad; cur.cols += pd.nt_pad; cur.items += items; cur.jobs += jobs;
         cur.p1 = p + 1;
         if (items > 0) { cur.max_class_rows = std::max(cur.max_class_rows, pd.nq_pad / kTileQ); cur.max_hb = std::max(cur.max_hb, pd.nt_pad / kHalfT); }

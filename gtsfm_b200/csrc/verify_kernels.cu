@@ -593,8 +593,15 @@ __global__ void __launch_bounds__(kFinThreads, 4) finalize_kernel(VerifyBufs b, 
         double R[9], t[3], JtJ[25], Jtr[5], cst = 0, lambda = 1e-4;
         int ninl = 0, it = 0;
         if (tid == 0) {
-            double R2[9];
-            vm::decompose_essential(s_E, R, R2, t);
+            // canonical start (independent of the sign of the minimal model and of the order an SVD returns the twisted
+            // pair in): the rotation with the larger trace, t signed so that [t]x R reproduces the model
+            double R1[9], R2[9], Et[9], dot = 0;
+            vm::decompose_essential(s_E, R1, R2, t);
+            const bool first = R1[0] + R1[4] + R1[8] >= R2[0] + R2[4] + R2[8];
+            for (int i = 0; i < 9; ++i) R[i] = first ? R1[i] : R2[i];
+            skew_times(t, R, Et);
+            for (int i = 0; i < 9; ++i) dot += Et[i] * s_E[i];
+            if (dot < 0) { t[0] = -t[0]; t[1] = -t[1]; t[2] = -t[2]; }
             for (int i = 0; i < 9; ++i) s_R[i] = R[i];
             for (int i = 0; i < 3; ++i) s_t[i] = t[i];
         }

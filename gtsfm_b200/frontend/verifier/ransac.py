@@ -18,13 +18,19 @@ from gtsfm_b200.frontend.verifier.verifier_base import VerifierBase
 
 DEFAULT_NUM_HYPOTHESES = 1024      # the reference relies on cv2's default maxIters = 1000 (ransac.py:74-81)
 DEFAULT_LO_ITERS = 20
+# fundamental-matrix mode: the reference passes confidence 0.999999 and maxIters 1,000,000 to cv2.findFundamentalMat
+# (ransac.py:22-23,103-110), i.e. the budget adapts to the inlier ratio; here: rounds of power-of-two budgets up to 2^20
+RANSAC_SUCCESS_PROB = 0.999999
+RANSAC_MAX_ITERS = 1 << 20
 
 
 class Ransac(VerifierBase):
     def __init__(self, use_intrinsics_in_verification: bool, estimation_threshold_px: float,
-                 num_hypotheses: int = DEFAULT_NUM_HYPOTHESES, seed: int = 0, lo_iters: int = DEFAULT_LO_ITERS, device: int = 0) -> None:
+                 num_hypotheses: int = DEFAULT_NUM_HYPOTHESES, seed: int = 0, lo_iters: int = DEFAULT_LO_ITERS, device: int = 0,
+                 max_hypotheses: int = RANSAC_MAX_ITERS) -> None:
         super().__init__(use_intrinsics_in_verification, estimation_threshold_px)
         self._num_hypotheses = int(num_hypotheses)
+        self._max_hypotheses = int(max_hypotheses)       # F mode only: cap of the adaptive budget (0 = fixed num_hypotheses)
         self._seed = int(seed)
         self._lo_iters = int(lo_iters)
         self._device = device
@@ -38,6 +44,8 @@ class Ransac(VerifierBase):
         p.pair_keys = None if pair_keys is None else pair_keys.ctypes.data
         p.samples = None
         p.estimate_fundamental = 0 if self._use_intrinsics_in_verification else 1
+        p.adaptive_max_hypotheses = 0 if self._use_intrinsics_in_verification else self._max_hypotheses
+        p.confidence = RANSAC_SUCCESS_PROB
         return p
 
     def verify(self, keypoints_i1: Keypoints, keypoints_i2: Keypoints, match_indices: np.ndarray,

@@ -27,13 +27,22 @@ class TwoViewBatchResult:
     t: np.ndarray                         # (P, 3) i2Ui1
     n_inliers: np.ndarray                 # (P,)
     status: np.ndarray                    # (P,) 0 ok, 1 too few matches, 2 no model
+    # Lifetime: with pinned_outputs=True the arrays are views of the context's page-locked arena and are overwritten by the
+    # next batch on that context (the memory itself stays valid until the context is closed); copy what must outlive it.
+
+    def _need_matches(self):
+        if len(self.matches) != int(self.match_offsets[-1]):
+            raise ValueError("this result was produced with fetch_matches=False: the match rows stayed on the device, so the "
+                             "correspondence dictionaries / reports cannot be built from it")
 
     def putative_corr_idxs_dict(self) -> Dict[Tuple[int, int], np.ndarray]:
+        self._need_matches()
         o = self.match_offsets
         return {(int(a), int(b)): self.matches[o[p]:o[p + 1]] for p, (a, b) in enumerate(self.pairs)}
 
     def two_view_dicts(self):
         """(i2Ri1_dict, i2Ui1_dict, v_corr_idxs_dict, inlier_ratio_dict), built lazily from the structure-of-arrays."""
+        self._need_matches()
         o = self.match_offsets
         Rd, td, vd, rd = {}, {}, {}, {}
         for p, (a, b) in enumerate(self.pairs):
@@ -58,6 +67,7 @@ def two_view_reports(result: TwoViewBatchResult, ctx: "_native.Context", corr_me
     pre-ISP report) and the boolean keep mask; a dropped pair gets (None, None, empty, report with 0 inliers) from
     post_isp_results()."""
     from gtsfm_b200.common.two_view_estimation_report import TwoViewEstimationReport
+    result._need_matches()
     P = len(result.pairs)
     o = result.match_offsets
     rep = ctx.two_view_report_batch(P, int(o[-1]), corr_metric_dist_threshold, min_num_inliers_est_model,

@@ -112,6 +112,13 @@ typedef struct gtsfm_verify_params {
                                     samples, inlier <=> max squared epipolar-line distance <= threshold_px^2, the model with
                                     the most inliers, fewer than 8 matches -> GTSFM_V_TOO_FEW, E = K2^T F K1
                                     (utils/verification.py:97-110), then the same pose recovery.  lo_iters is ignored. */
+    int adaptive_max_hypotheses; /* fundamental-matrix mode only, ignored with explicit samples.  > n_hypotheses: cv2's stopping
+                                    rule -- findFundamentalMat(confidence = 0.999999, maxIters = 1000000), ransac.py:22-23,
+                                    103-110 -- in rounds: a pair whose best model has inlier ratio w is finished once
+                                    log(1 - confidence) / log(1 - w^7) hypotheses were evaluated; otherwise it is run again with
+                                    twice the budget, up to min(this, 2^20).  Hypothesis h
+                                    draws the same sample whatever the budget.  0: exactly n_hypotheses per pair. */
+    double confidence;           /* of that rule; <= 0 or >= 1 selects the reference's 0.999999 (RANSAC_SUCCESS_PROB) */
 } gtsfm_verify_params;
 
 /* Verify the matches produced by the last gtsfm_match_batch (same pairs, same order; nothing is copied back to the
@@ -124,6 +131,10 @@ typedef struct gtsfm_verify_params {
 int gtsfm_verify_batch(gtsfm_ctx* ctx, const int32_t* pairs, int n_pairs, const uint32_t* match_idx,
                        const int64_t* match_offsets, const gtsfm_verify_params* params, double* R, double* t,
                        int32_t* n_inliers, int32_t* status, uint8_t* inlier_mask, double* E);
+
+/* Hypotheses evaluated per pair by the last gtsfm_verify_batch (n_hypotheses unless the adaptive fundamental-matrix budget
+ * raised it): out (n_pairs) int32.  With it a CPU run can draw the identical sample set (gtsfm_ransac_samples_k). */
+int gtsfm_verify_hypotheses_used(gtsfm_ctx* ctx, int32_t* out, int n_pairs);
 
 /* ---- post-verification report over a batch of pairs ----------------------------------------- */
 typedef struct gtsfm_report_params {

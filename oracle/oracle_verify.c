@@ -676,6 +676,23 @@ static int solve_lm5(const double* JtJ, const double* Jtr, double lambda, double
 
 #define LO_MAX_ITERS 20
 
+/* Starting point of the local optimisation.  E_in = +-[t]x R has two equivalent decompositions, (Ra, ta) and its twisted
+ * pair (Rb, -ta), and the minimal solver fixes neither the sign of E_in nor which of them an SVD returns first.  The
+ * retraction R Exp(w) differs between the two (to second order in the step), so the start must not depend on those
+ * accidents: take the rotation with the larger trace (the smaller rotation angle; the other one is turned by 180 degrees
+ * about the baseline) and the sign of t that reproduces E_in.  Starting from -E_in then mirrors the whole trajectory
+ * (same R, opposite t), so the result is independent of the sign of the minimal model. */
+static void lo_canonical_start(const double* E_in, double* R, double* t)
+{
+    double R1[9], R2[9], Et[9], dot = 0;
+    oracle_decompose_essential(E_in, R1, R2, t);
+    const double tr1 = R1[0] + R1[4] + R1[8], tr2 = R2[0] + R2[4] + R2[8];
+    memcpy(R, tr1 >= tr2 ? R1 : R2, sizeof(double) * 9);
+    skew_times(t, R, Et);
+    for (int i = 0; i < 9; ++i) dot += Et[i] * E_in[i];
+    if (dot < 0) { t[0] = -t[0]; t[1] = -t[1]; t[2] = -t[2]; }
+}
+
 /* diagnostics: Levenberg-Marquardt trial steps taken by the last oracle_lo_refine call */
 int oracle_lo_trials_last = 0;
 
@@ -686,7 +703,8 @@ double oracle_lo_refine(const double* E_in, const double* x1, const double* y1, 
 {
     double R[9], R2[9], t[3], JtJ[25], Jtr[5];
     int ninl;
-    oracle_decompose_essential(E_in, R, R2, t);
+    lo_canonical_start(E_in, R, t);
+    (void)R2;
     double cost = lo_pass(R, t, x1, y1, x2, y2, n, thr2, &ninl, JtJ, Jtr);
     double lambda = 1e-4;
     oracle_lo_trials_last = 0;

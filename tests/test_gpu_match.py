@@ -259,3 +259,40 @@ def test_hamming_plugin_and_batch(ctx):
     with pytest.raises(Exception):                       # one store cannot mix float32 and binary descriptors
         ctx.clear(); ctx.upload_image_u8(0, imgs[0]); ctx.upload_image(1, np.ones((4, 32), np.float32))
     ctx.clear()
+
+
+def test_hamming_multi_chunk_batch_last_chunk_single_pair(ctx):
+    """A binary-descriptor batch that runs as several chunks (64 MiB of workspace: 8,192-row pairs take 80 B per row and
+    column, so 102 pairs fit and the 103rd opens a chunk of its own), plus an image without any features.  Every pair equals
+    the single-pair entry point; the last pair and two others also equal the oracle."""
+    from gtsfm_b200.frontend.matcher.twoway_matcher import MatchingDistanceType, TwoWayMatcher
+    from oracle import oracle as O
+    rng = np.random.default_rng(91)
+    n_img, n = 15, 8192
+    base = rng.integers(0, 256, (n, 32), dtype=np.uint8)
+    imgs = []
+    for i in range(n_img):
+        d = base ^ (rng.random((n, 32)) < 0.02).astype(np.uint8) * rng.integers(1, 256, (n, 32), dtype=np.uint8)
+        d[: n // 4] = rng.integers(0, 256, (n // 4, 32), dtype=np.uint8)
+        imgs.append(d[rng.permutation(n)])
+    imgs.append(np.array([]))                                       # image 15: no features (twoway_matcher.py:71-72)
+    all_pairs = [(i, j) for i in range(n_img) for j in range(i + 1, n_img)]
+    pairs = np.array(all_pairs[:102] + [(3, 15)] + all_pairs[102:103], np.int32)          # 104 pairs, 103 of them non-empty
+    m = TwoWayMatcher(distance_type=MatchingDistanceType.HAMMING, ratio_test_threshold=0.8)
+    from gtsfm_b200 import _native
+    dc = _native.default_context(0)                                 # the context the plugin's match_batch runs on
+    dc.set_workspace(64 << 20)
+    try:
+        out = m.match_batch(imgs, pairs)
+    finally:
+        dc.set_workspace(12 << 30)
+    assert len(out) == len(pairs) and np.asarray(out[102]).size == 0
+    for p, (i, j) in enumerate(pairs):
+        if j == 15:
+            continue
+        single = ctx.match_pair_u8(imgs[i], imgs[j], 0.8)
+        check(np.asarray(out[p]).reshape(-1, 2), single)
+        assert len(single) > 1000
+    for p in (0, 57, 103):
+        i, j = pairs[p]
+        check(np.asarray(out[p]).reshape(-1, 2), O.twoway_match_hamming(imgs[i], imgs[j], 0.8).reshape(-1, 2))

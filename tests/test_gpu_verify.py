@@ -254,8 +254,8 @@ def test_low_inlier_rate_many_hypotheses(ctx):
 
 
 def test_full_size_properties_c2_pair(ctx):
-    """Size-independent properties at the BASELINE size (8192 keypoints per image, 1024 hypotheses), where the oracle is
-    too slow to run inside the suite: the inlier mask IS sampson^2 < thr^2 of the returned E (fp64, strict), E = [t]x R
+    """Size-independent properties at the BASELINE size (8192 keypoints per image, 1024 hypotheses; the oracle comparison at
+    this size is tests/test_gpu_baseline_sizes.py): the inlier mask IS sampson^2 < thr^2 of the returned E (fp64, strict), E = [t]x R
     up to scale, R is a rotation, t a unit vector, the pose is the scene's, and matching is symmetric under swapping the
     images (mutual nearest neighbours with the ratio test off)."""
     from gtsfm_b200 import synthetic
@@ -392,6 +392,49 @@ def test_fundamental_mode_plugin(ctx):
     assert rot_angle_deg(i2Ri1.matrix(), R) < 2.0
 
 
+def test_fundamental_mode_adaptive_budget_low_inlier_pairs(ctx):
+    """cv2.findFundamentalMat(FM_RANSAC, confidence 0.999999, maxIters 1e6) adapts its iteration count to the inlier ratio
+    (ransac.py:22-23,103-110).  Pairs at 30 % and 70 % inliers in one batch: with adaptive_max_hypotheses the low-inlier pair
+    is re-run with the budget the stopping rule asks for (tens of thousands of 7-point samples), the other one is not;
+    each equals the oracle on the sample set of the budget it ended with, and the low-inlier pair recovers as many inliers
+    as cv2 itself finds, which 1,024 fixed hypotheses do not."""
+    import cv2
+    import gtsfm_b200
+    rng = np.random.default_rng(41)
+    n = 1200
+    scenes = [make_pixel_scene(rng, n, out_frac=0.70), make_pixel_scene(rng, n, out_frac=0.30)]
+    ctx.clear()
+    for k, (kp1, kp2, _, _, cal) in enumerate(scenes):
+        ctx.upload_image(2 * k, None, kp1, cal)
+        ctx.upload_image(2 * k + 1, None, kp2, cal)
+    pairs = np.array([[0, 1], [2, 3]], np.int32)
+    mi = np.concatenate([np.c_[np.arange(n), np.arange(n)]] * 2).astype(np.uint32)
+    off = np.array([0, n, 2 * n], np.int64)
+    keys = np.array([5, 6], np.uint64)
+    fixed = ctx.verify_batch(pairs, params_f(3.0, 1024, seed=13, keys=keys), mi, off)
+    assert (ctx.verify_hypotheses_used(2) == 1024).all()
+    prm = params_f(3.0, 1024, seed=13, keys=keys)
+    prm.adaptive_max_hypotheses = 1 << 20
+    prm.confidence = 0.999999
+    out = ctx.verify_batch(pairs, prm, mi, off)
+    used = ctx.verify_hypotheses_used(2)
+    assert used[1] == 1024 and 16384 <= used[0] <= (1 << 18), used
+    for k in range(2):
+        kp1, kp2, R, t, cal = scenes[k]
+        got = dict(status=out["status"][k], mask=out["mask"][off[k]:off[k + 1]], R=out["R"][k], t=out["t"][k],
+                   n_inliers=out["n_inliers"][k], E=out["E"][k])
+        samples = gtsfm_b200.ransac_samples(13, int(keys[k]), n, int(used[k]), 7)
+        check_against_oracle_F(got, kp1, kp2, mi[off[k]:off[k + 1]], cal, cal, 3.0, samples)
+        # the stopping rule holds for the returned model
+        w = got["n_inliers"] / n
+        assert np.log(1 - 0.999999) / np.log(1 - w ** 7) <= used[k]
+    assert out["n_inliers"][0] >= fixed["n_inliers"][0]
+    kp1, kp2, R, t, cal = scenes[0]
+    _, cmask = cv2.findFundamentalMat(kp1, kp2, method=cv2.FM_RANSAC, ransacReprojThreshold=3.0, confidence=0.999999, maxIters=1000000)
+    assert out["n_inliers"][0] >= 0.95 * int(cmask.sum())
+    assert rot_angle_deg(out["R"][0], R) < 2.0
+
+
 # ------------------------------------------------------------------------------ post-verification report (8(f) rank 2)
 def test_two_view_report_batch_vs_oracle(ctx):
     """GT correspondence metrics, relative-pose errors, report aggregates and the InlierSupportProcessor decision of every
@@ -478,3 +521,18 @@ def test_run_two_view_batch_pinned_outputs_equal_owned_outputs(ctx):
     for name in ("match_offsets", "matches", "inlier_mask", "R", "t", "n_inliers", "status"):
         np.testing.assert_array_equal(getattr(a, name), getattr(b, name))
     assert not b.matches.flags.owndata and a.matches.flags.owndata
+
+
+def test_verify_batch_rejects_out_of_range_match_rows(ctx):
+    """Caller-supplied match rows are checked against each image's keypoint count (the reference raises IndexError)."""
+    import gtsfm_b200
+    rng = np.random.default_rng(2)
+    kp1, kp2, _, _, cal = make_pixel_scene(rng, 50)
+    ctx.clear()
+    ctx.upload_image(0, None, kp1, cal)
+    ctx.upload_image(1, None, kp2[:40], cal)
+    mi = np.c_[np.arange(50), np.arange(50)].astype(np.uint32)
+    with pytest.raises(gtsfm_b200.GtsfmB200Error, match="does not have"):
+        ctx.verify_batch(np.array([[0, 1]], np.int32), params(4.0, 32), mi, np.array([0, 50], np.int64))
+    out = ctx.verify_batch(np.array([[0, 1]], np.int32), params(4.0, 32), mi[:40], np.array([0, 40], np.int64))
+    assert out["status"][0] == 0
