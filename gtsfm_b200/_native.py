@@ -51,6 +51,7 @@ class ReportParams(ctypes.Structure):
         ("dist_threshold_px", ctypes.c_double),
         ("min_num_inliers_est_model", ctypes.c_int),
         ("min_inlier_ratio_est_model", ctypes.c_double),
+        ("gt_cal", ctypes.c_void_p),
     ]
 
 
@@ -387,11 +388,14 @@ class Context:
 
     def two_view_report_batch(self, n_pairs: int, total: int, dist_threshold_px: float, min_num_inliers_est_model: int,
                               min_inlier_ratio_est_model: float, gt_i2Ri1: Optional[np.ndarray] = None,
-                              gt_i2ti1: Optional[np.ndarray] = None, reuse_outputs: bool = False):
+                              gt_i2ti1: Optional[np.ndarray] = None, reuse_outputs: bool = False, gt_cal: Optional[np.ndarray] = None):
         """Post-verification report of the pairs of the last verify_batch (gtsfm_two_view_report_batch).  With reuse_outputs the
         per-correspondence arrays are views of the context's pinned arena (valid until the next report call)."""
         P = int(n_pairs)
-        prm = ReportParams(float(dist_threshold_px), int(min_num_inliers_est_model), float(min_inlier_ratio_est_model))
+        if gt_cal is not None:
+            gt_cal = np.ascontiguousarray(gt_cal, np.float64).reshape(P, 10)
+        prm = ReportParams(float(dist_threshold_px), int(min_num_inliers_est_model), float(min_inlier_ratio_est_model),
+                           None if gt_cal is None else gt_cal.ctypes.data)
         if gt_i2Ri1 is not None:
             gt_i2Ri1 = np.ascontiguousarray(gt_i2Ri1, np.float64).reshape(P, 9)
             gt_i2ti1 = np.ascontiguousarray(gt_i2ti1, np.float64).reshape(P, 3)

@@ -21,6 +21,7 @@ namespace g2v {
 struct ReportBufs {
     const VPair* pairs; const void* match; const unsigned char* mask; const double* R; const double* t; const int* ninl; const int* status;
     const double* gt_R; const double* gt_t;         // [P][9], [P][3] ground-truth i2Ri1 / i2ti1 or nullptr
+    const double* gt_cal;                           // [P][10] calibrations of the ground-truth cameras or nullptr (-> VPair's)
     double* dist_sq; unsigned char* gt_mask;        // per match row (NaN / 0 for rows that were not verified)
     int* n_gt; double* in_avg; double* out_avg; double* R_err; double* U_err; int* keep;
     double thr2; int min_inl; double min_ratio;
@@ -37,7 +38,7 @@ __global__ void __launch_bounds__(kFinThreads) two_view_report_kernel(StoreView 
     const int tid = threadIdx.x;
     const int n_inl = b.ninl[p];
     const bool ok = b.status[p] == 0;
-    const bool have_gt = b.gt_R != nullptr && b.gt_t != nullptr;
+    const bool have_gt = b.gt_R != nullptr && b.gt_t != nullptr && b.gt_R[9 * p] == b.gt_R[9 * p];   // NaN row: no GT for this pair
     if (tid == 0) {
         // InlierSupportProcessor.run_inlier_support: the ratio test first, then the count test (only for valid models)
         const double ratio = (ok && vp.M > 0) ? static_cast<double>(n_inl) / vp.M : 0.0;
@@ -75,7 +76,9 @@ __global__ void __launch_bounds__(kFinThreads) two_view_report_kernel(StoreView 
                 E[3 + j] = tz * R[j] - tx * R[6 + j];
                 E[6 + j] = -ty * R[j] + tx * R[3 + j];
             }
-            const double f1 = vp.cal1[0], u1 = vp.cal1[3], v1 = vp.cal1[4], f2 = vp.cal2[0], u2 = vp.cal2[3], v2 = vp.cal2[4];
+            const double* c1 = b.gt_cal ? b.gt_cal + 10 * p : vp.cal1;
+            const double* c2 = b.gt_cal ? b.gt_cal + 10 * p + 5 : vp.cal2;
+            const double f1 = c1[0], u1 = c1[3], v1 = c1[4], f2 = c2[0], u2 = c2[3], v2 = c2[4];
             const double K1i[9] = {1.0 / f1, 0, -u1 / f1, 0, 1.0 / f1, -v1 / f1, 0, 0, 1};
             const double K2it[9] = {1.0 / f2, 0, 0, 0, 1.0 / f2, 0, -u2 / f2, -v2 / f2, 1};
             double T[9];
@@ -129,7 +132,7 @@ extern "C" int gtsfm_two_view_report_batch(gtsfm_ctx* c, int n_pairs, const doub
     cudaStream_t s = c->stream;
     DevBuf* vb = c->v_bufs;
     const size_t total = static_cast<size_t>(c->verify_total);
-    G2V_CUDA(c, vb[19].reserve(96 * static_cast<size_t>(n_pairs), false, s));          // gt R, t
+    G2V_CUDA(c, vb[19].reserve(176 * static_cast<size_t>(n_pairs), false, s));         // gt R, t, calibrations
     G2V_CUDA(c, vb[20].reserve(8 * (total + 1), false, s));                              // dist_sq
     G2V_CUDA(c, vb[21].reserve(total + 1, false, s));                                    // gt mask
     G2V_CUDA(c, vb[22].reserve(48 * static_cast<size_t>(n_pairs), false, s));            // n_gt, keep (int) + 4 doubles per pair
@@ -141,6 +144,10 @@ extern "C" int gtsfm_two_view_report_batch(gtsfm_ctx* c, int n_pairs, const doub
         G2V_CUDA(c, cudaMemcpyAsync(g, gt_i2Ri1, 72 * static_cast<size_t>(n_pairs), cudaMemcpyHostToDevice, s));
         G2V_CUDA(c, cudaMemcpyAsync(g + 9ll * n_pairs, gt_i2ti1, 24 * static_cast<size_t>(n_pairs), cudaMemcpyHostToDevice, s));
         b.gt_R = g; b.gt_t = g + 9ll * n_pairs;
+        if (prm->gt_cal) {
+            G2V_CUDA(c, cudaMemcpyAsync(g + 12ll * n_pairs, prm->gt_cal, 80 * static_cast<size_t>(n_pairs), cudaMemcpyHostToDevice, s));
+            b.gt_cal = g + 12ll * n_pairs;
+        }
     }
     b.dist_sq = vb[20].as<double>(); b.gt_mask = vb[21].as<unsigned char>();
     double* pd = vb[22].as<double>();

@@ -82,7 +82,7 @@ class MatcherCacher(MatcherBase):
         return match_indices
 
     def match_batch(self, keypoints: Sequence[Keypoints], descriptors: Sequence[np.ndarray], im_shapes: Sequence[Tuple[int, int, int]],
-                    pairs: np.ndarray) -> List[np.ndarray]:
+                    pairs: np.ndarray, device: Optional[int] = None) -> List[np.ndarray]:
         """Per-pair results for `pairs` (P, 2) over per-image inputs; one device batch for all cache misses."""
         pairs = np.asarray(pairs).reshape(-1, 2)
         parts = {}
@@ -103,7 +103,7 @@ class MatcherCacher(MatcherBase):
             used = np.unique(pairs[missing])
             remap = {int(g): k for k, g in enumerate(used)}
             sub_pairs = np.array([[remap[int(i)], remap[int(j)]] for i, j in pairs[missing]], np.int32)
-            fresh = self._matcher.match_batch([descriptors[int(g)] for g in used], sub_pairs)
+            fresh = self._matcher.match_batch([descriptors[int(g)] for g in used], sub_pairs, **({} if device is None else {"device": device}))
             for p, m in zip(missing, fresh):
                 cache_io.write_entry(m, paths[p])
                 results[p] = m

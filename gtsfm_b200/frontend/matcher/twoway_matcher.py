@@ -54,11 +54,12 @@ class TwoWayMatcher(MatcherBase):
                                self._ratio_test_threshold)
         return m if m.shape[0] else np.array([])                                           # twoway_matcher.py:80-81
 
-    def match_batch(self, descriptors: Sequence[np.ndarray], pairs: np.ndarray) -> List[np.ndarray]:
+    def match_batch(self, descriptors: Sequence[np.ndarray], pairs: np.ndarray, device: Optional[int] = None) -> List[np.ndarray]:
         """All pairs in one device batch (replaces one Dask task per pair,
-        det_desc_correspondence_generator.py:71-81).  descriptors: per-image arrays; pairs: (P, 2) image indices."""
+        det_desc_correspondence_generator.py:71-81).  descriptors: per-image arrays; pairs: (P, 2) image indices; device: the
+        GPU of this shard (default: the matcher's own)."""
         self._check_distance_type()
-        ctx = _native.default_context(self._device)
+        ctx = _native.default_context(self._device if device is None else device)
         ctx.clear()
         for i, d in enumerate(descriptors):
             if self._hamming:

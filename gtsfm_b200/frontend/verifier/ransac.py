@@ -69,19 +69,29 @@ class Ransac(VerifierBase):
         inlier_ratio = float(mask.mean()) if mask.size else 0.0                    # opencv_verifier_base.py:101
         return Rot3(np.array(R)), Unit3(np.array(t)), v_corr_idxs, inlier_ratio
 
-    def verify_batch(self, keypoints: Sequence[Keypoints], intrinsics: Sequence[Cal3Bundler], pairs: np.ndarray,
-                     match_indices: Sequence[np.ndarray]) -> List[Tuple[Optional[Rot3], Optional[Unit3], np.ndarray, float]]:
-        """All pairs in one device batch (replaces one Dask task per pair, two_view_estimator.py:569-584)."""
+    def verify_batch_raw(self, keypoints: Sequence[Keypoints], intrinsics: Sequence[Cal3Bundler], pairs: np.ndarray,
+                         match_indices: Sequence[np.ndarray], device: Optional[int] = None, pair_ids: Optional[np.ndarray] = None):
+        """All pairs in one device batch; returns (raw output arrays of gtsfm_verify_batch, row offsets, per-pair (M, 2) uint32
+        match arrays, the context that holds the batch -- for gtsfm_two_view_report_batch).  pairs index `keypoints`; pair_ids
+        (P, 2) are the caller's global image ids (sampler keys, so a pair draws the same hypotheses in any shard)."""
         pairs = np.ascontiguousarray(pairs, np.int32).reshape(-1, 2)
-        ctx = _native.default_context(self._device)
+        ctx = _native.default_context(self._device if device is None else device)
         ctx.clear()
         for i, (kp, cal) in enumerate(zip(keypoints, intrinsics)):
             ctx.upload_image(i, None, kp.coordinates, cal_to_tuple(cal))
-        ms = [np.asarray(m).reshape(-1, 2) if np.asarray(m).size else np.zeros((0, 2), np.uint32) for m in match_indices]
+        ms = [np.asarray(m).reshape(-1, 2).astype(np.uint32) if np.asarray(m).size else np.zeros((0, 2), np.uint32) for m in match_indices]
         off = np.zeros(len(ms) + 1, np.int64)
         np.cumsum([m.shape[0] for m in ms], out=off[1:])
-        allm = np.concatenate(ms).astype(np.uint32) if off[-1] else np.zeros((0, 2), np.uint32)
-        keys = (pairs[:, 0].astype(np.uint64) << np.uint64(32)) | pairs[:, 1].astype(np.uint64)
+        allm = np.concatenate(ms) if off[-1] else np.zeros((0, 2), np.uint32)
+        ids = pairs if pair_ids is None else np.asarray(pair_ids).reshape(-1, 2)
+        keys = (ids[:, 0].astype(np.uint64) << np.uint64(32)) | ids[:, 1].astype(np.uint64)
         out = ctx.verify_batch(pairs, self._params(keys), allm, off)
-        return [self._to_result(out["status"][p], out["R"][p], out["t"][p], out["mask"][off[p]:off[p + 1]], ms[p])
+        return out, off, ms, ctx
+
+    def verify_batch(self, keypoints: Sequence[Keypoints], intrinsics: Sequence[Cal3Bundler], pairs: np.ndarray,
+                     match_indices: Sequence[np.ndarray]) -> List[Tuple[Optional[Rot3], Optional[Unit3], np.ndarray, float]]:
+        """All pairs in one device batch (replaces one Dask task per pair, two_view_estimator.py:569-584)."""
+        out, off, ms, _ = self.verify_batch_raw(keypoints, intrinsics, pairs, match_indices)
+        src = [np.asarray(m).reshape(-1, 2) if np.asarray(m).size else np.zeros((0, 2), np.uint32) for m in match_indices]
+        return [self._to_result(out["status"][p], out["R"][p], out["t"][p], out["mask"][off[p]:off[p + 1]], src[p])
                 for p in range(len(ms))]

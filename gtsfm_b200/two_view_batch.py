@@ -60,21 +60,24 @@ class TwoViewBatchResult:
 
 def two_view_reports(result: TwoViewBatchResult, ctx: "_native.Context", corr_metric_dist_threshold: float,
                      min_num_inliers_est_model: int, min_inlier_ratio_est_model: float,
-                     gt_i2Ri1: Optional[np.ndarray] = None, gt_i2ti1: Optional[np.ndarray] = None):
+                     gt_i2Ri1: Optional[np.ndarray] = None, gt_i2ti1: Optional[np.ndarray] = None,
+                     gt_cal: Optional[np.ndarray] = None):
     """The stage after verify() in TwoViewEstimator.run_2view (two_view_estimator.py:298-349) for every pair of the batch the
     context verified last: GT correspondence metrics, relative-pose errors, report aggregates and the InlierSupportProcessor
     decision, computed on the device in one launch.  Returns (reports, keep): a TwoViewEstimationReport per pair (the
-    pre-ISP report) and the boolean keep mask; a dropped pair gets (None, None, empty, report with 0 inliers) from
-    post_isp_results()."""
+    pre-ISP report), the boolean keep mask and the raw arrays.  gt_i2Ri1 rows of NaN mark pairs without ground truth; gt_cal
+    (P, 10) are the GT cameras' calibrations when they differ from the ones the images were uploaded with."""
     from gtsfm_b200.common.two_view_estimation_report import TwoViewEstimationReport
     result._need_matches()
     P = len(result.pairs)
     o = result.match_offsets
     rep = ctx.two_view_report_batch(P, int(o[-1]), corr_metric_dist_threshold, min_num_inliers_est_model,
-                                    min_inlier_ratio_est_model, gt_i2Ri1, gt_i2ti1)
-    have_gt = gt_i2Ri1 is not None
+                                    min_inlier_ratio_est_model, gt_i2Ri1, gt_i2ti1, gt_cal=gt_cal)
+    # a pair without ground truth (one of its gt cameras is None, two_view_estimator.py:131) carries a NaN row
+    gt_rows = None if gt_i2Ri1 is None else ~np.isnan(np.asarray(gt_i2Ri1, np.float64).reshape(P, 9)[:, 0])
     reports = []
     for p in range(P):
+        have_gt = gt_rows is not None and bool(gt_rows[p])
         m = result.matches[o[p]:o[p + 1]]
         ok = result.status[p] == 0
         mask = result.inlier_mask[o[p]:o[p + 1]] == 1 if ok else np.zeros(len(m), bool)
@@ -97,6 +100,27 @@ def two_view_reports(result: TwoViewBatchResult, ctx: "_native.Context", corr_me
                 U_error_deg=float(rep["U_error_deg"][p]) if (have_gt and ok) else None,
                 inlier_avg_reproj_error_gt_model=float("nan"), outlier_avg_reproj_error_gt_model=float("nan")))
     return reports, rep["keep"].astype(bool), rep
+
+
+def num_gpu_shards() -> int:
+    """Shards a batched caller deals its pair list into: GTSFM_B200_NUM_SHARDS when set, else the visible CUDA devices."""
+    import os
+    env = os.environ.get("GTSFM_B200_NUM_SHARDS")
+    if env:
+        return max(1, int(env))
+    try:
+        import torch
+        return max(1, torch.cuda.device_count())
+    except Exception:  # noqa: BLE001 - torch is plumbing here; without it there is one shard
+        return 1
+
+
+def num_gpu_devices() -> int:
+    try:
+        import torch
+        return max(1, torch.cuda.device_count())
+    except Exception:  # noqa: BLE001
+        return 1
 
 
 def shard_pairs(pairs: np.ndarray, n_shards: int, cost: Optional[np.ndarray] = None) -> List[np.ndarray]:

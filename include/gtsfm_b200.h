@@ -141,6 +141,9 @@ typedef struct gtsfm_report_params {
     double dist_threshold_px;           /* TwoViewEstimator(corr_metric_dist_threshold): correct <=> sampson^2 < threshold^2 */
     int min_num_inliers_est_model;      /* InlierSupportProcessor(min_num_inliers_est_model) */
     double min_inlier_ratio_est_model;  /* InlierSupportProcessor(min_inlier_ratio_est_model) */
+    const double* gt_cal;               /* optional (P, 10): {f, k1, k2, u0, v0} of the GROUND-TRUTH cameras of image 1 and image 2
+                                           (gt_camera.calibration(), utils/metrics.py:90-97) for F_gt; NULL = the calibrations the
+                                           images were uploaded with */
 } gtsfm_report_params;
 
 /* The stage that follows verify() in TwoViewEstimator.run_2view (gtsfm/two_view_estimator.py:298-349), for every pair of
@@ -153,7 +156,8 @@ typedef struct gtsfm_report_params {
  *   - InlierSupportProcessor.run_inlier_support (frontend/inlier_support_processor.py:39-95): keep[p] = 0 when the inlier
  *     ratio or the inlier count is insufficient (or verification failed).
  * gt_i2Ri1 (P, 9) row-major and gt_i2ti1 (P, 3) are the ground-truth relative poses, both NULL when there is none (then only
- * keep[] is meaningful, the metrics are NaN / 0).  Outputs (any may be NULL): dist_sq (total) float64 aligned with the match
+ * keep[] is meaningful, the metrics are NaN / 0); a pair whose gt_i2Ri1 row starts with NaN has no ground truth either (one of
+ * its gt cameras is None, two_view_estimator.py:131).  Outputs (any may be NULL): dist_sq (total) float64 aligned with the match
  * rows (NaN for rows that were not verified), gt_mask (total) uint8, num_inliers_gt (P), inlier_avg_err / outlier_avg_err (P)
  * mean squared distance of the correct / incorrect verified correspondences (NaN when there are none), R_error_deg /
  * U_error_deg (P), keep (P). */
