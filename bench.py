@@ -4,11 +4,14 @@
   python bench.py --gpus N --steps K --warmup W            the B200 path (one rank per GPU under torchrun for N > 1)
   python bench.py --impl reference --gpus N --steps K ...  the reference's CPU path (cv2, one task per pair, all cores)
 
-Workload (BASELINE.json): config C2 = synthetic 100 images x 8192 SIFT-128 keypoints, exhaustive 4,950 pairs, ratio test
-0.8, 1,024 five-point hypotheses per pair, 4 px threshold.  A "step" is one pass over all pairs: match + verify.
-`value` times the pass with descriptors / keypoints already resident in HBM; `e2e` times it through the public batched
-API from pinned host buffers, uploads and result downloads included.  N > 1: every rank runs its own C2-sized shard
-(weak scaling, pairs are independent units) and the per-pair result records are gathered with one NCCL all_gather.
+Workload (BASELINE.json): config C3 = synthetic 1,000 images x 8192 SIFT-128 keypoints, retriever top-50 = 48,725 pairs, ratio
+test 0.8, 1,024 five-point hypotheses per pair, 4 px threshold -- the configuration BASELINE quotes "sharded 1/2/4/8 B200".  A
+"step" is one pass over ALL pairs of that one scene: match + verify + the result table (i2Ri1, i2Ui1, v_corr_idxs, inlier
+ratio of every pair) in pinned host memory of rank 0.  N = 1 runs the whole pair list on one GPU; N > 1 deals the SAME list
+over the ranks with shard_pairs (strong scaling), every rank uploads only the images its shard names, and the result records
+are packed on the device and moved with one NCCL all-gather per sub-batch (gtsfm_b200.two_view_batch.ResultExchange).
+`value` times the pass with descriptors / keypoints already resident in HBM; `e2e` times it from pinned host buffers, uploads
+included.  `--config C2` (100 images, 4,950 pairs, one GPU) and `--scaling weak` (every rank its own scene) remain available.
 """
 import argparse
 import json
@@ -35,7 +38,7 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--config", default="C2")
+    ap.add_argument("--config", default="C3")
     ap.add_argument("--images", type=int, default=0, help="shrink the config (debugging only; the line then says so)")
     ap.add_argument("--kps", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -43,9 +46,11 @@ def parse_args():
     ap.add_argument("--verifier", default="essential", choices=["essential", "fundamental"],
                     help="essential = Ransac(use_intrinsics_in_verification=True) (BASELINE configs); fundamental = the "
                          "reference's F-matrix mode (ransac.py:84-111), a SURVEY 8(f) row measured with the same harness")
-    ap.add_argument("--scaling", choices=("weak", "strong"), default="weak",
-                    help="N > 1: weak = every rank its own shard-sized scene (default, the driver's scaling run); strong = ONE scene, "
-                         "its pair list dealt over the ranks by shard_pairs, every rank uploads only the images its shard names")
+    ap.add_argument("--scaling", choices=("weak", "strong"), default="strong",
+                    help="N > 1: strong (default) = ONE scene, its pair list dealt over the ranks by shard_pairs, every rank uploads only "
+                         "the images its shard names; weak = every rank its own scene of the configured size")
+    ap.add_argument("--sub-batches", type=int, default=0,
+                    help="sub-batches per step whose result exchange overlaps the next sub-batch's kernels (0 = 1 on one GPU, 4 otherwise)")
     ap.add_argument("--workspace-gib", type=float, default=0.0, help="matcher / verifier work-buffer budget per chunk (0 = library default)")
     ap.add_argument("--float-screening", default="on", choices=["on", "off"],
                     help="float descriptors, ratio test off (C4): fp16 tensor-core screening (default) or the exhaustive fp32 kernel")
@@ -111,7 +116,9 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
-def make_scene(args, rank: int):
+def make_scene(args, rank: int, shard=None):
+    """shard = (rank, world) of a strong-scaled run: only the images that rank's pairs name are generated (the scene's cameras
+    and pair list are always complete, and an image's features do not depend on which other images are generated)."""
     from gtsfm_b200 import synthetic
     if args.config == "C1":            # the reference's own CPU-runnable case: real SIFT features of its 12 Lund-door images
         scene = synthetic.load_c1(os.path.join(os.path.dirname(os.path.abspath(__file__)), "tests", "golden", "c1_lund_door_12.npz"))
@@ -122,8 +129,13 @@ def make_scene(args, rank: int):
         cfg["n_images"] = args.images
     if args.kps:
         cfg["n_kps"] = args.kps
-    cfg["seed"] = cfg["seed"] + 1000 * rank          # every rank its own shard of the same shape (weak scaling)
-    scene = synthetic.make_scene(**cfg)
+    cfg["seed"] = cfg["seed"] + 1000 * rank          # weak scaling: every rank its own scene of the same shape
+    only = None
+    if shard is not None and shard[1] > 1:
+        from gtsfm_b200.two_view_batch import shard_pairs
+        all_pairs = synthetic.config_pairs(cfg)
+        only = np.unique(all_pairs[shard_pairs(all_pairs, shard[1])[shard[0]]])
+    scene = synthetic.make_scene(**cfg, only_images=only)
     scene.fundamental = args.verifier == "fundamental"
     return scene, cfg
 
@@ -204,9 +216,9 @@ def run_b200(args):
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    strong = args.scaling == "strong" and world > 1
-    scene, cfg = make_scene(args, 0 if strong else rank)
-    from gtsfm_b200.two_view_batch import shard_pairs
+    strong = args.scaling == "strong" or world == 1
+    scene, cfg = make_scene(args, 0 if strong else rank, shard=(rank, world) if strong else None)
+    from gtsfm_b200.two_view_batch import ResultExchange, merge_gathered, shard_pairs
     if strong:                                           # contiguous cost-balanced blocks of the i1-sorted pair list
         mine = shard_pairs(scene.pairs, world)[rank]
         pairs_g = np.ascontiguousarray(scene.pairs[mine])
@@ -215,11 +227,12 @@ def run_b200(args):
         remap[used] = np.arange(len(used))
         pairs = np.ascontiguousarray(remap[pairs_g].astype(np.int32))
         P_total = len(scene.pairs)
+        pair_ids = np.ascontiguousarray(mine, np.int64)                    # positions in the global pair list
     else:
         pairs_g = pairs = scene.pairs
         used = np.arange(len(scene.descriptors))
-        mine = None
         P_total = world * len(pairs)
+        pair_ids = rank * len(pairs) + np.arange(len(pairs), dtype=np.int64)   # weak scaling: every rank owns P pairs of the job
     P = len(pairs)
     n_img = len(used)
     # CPU baseline first: the worker pool is forked before this process creates its CUDA context
@@ -239,7 +252,7 @@ def run_b200(args):
     prm = _native.VerifyParams()
     prm.threshold_px, prm.n_hypotheses, prm.lo_iters, prm.seed = scene.threshold_px, scene.n_hyp, 20, 20260002
     keys = (pairs_g[:, 0].astype(np.uint64) << np.uint64(32)) | pairs_g[:, 1].astype(np.uint64)     # sampler keys = global pair ids
-    prm.pair_keys, prm.samples = keys.ctypes.data, None
+    prm.samples = None
     prm.estimate_fundamental = 1 if args.verifier == "fundamental" else 0
 
     def upload():
@@ -247,21 +260,27 @@ def run_b200(args):
         for i in range(n_img):
             ctx.upload_image(i, desc_pin[i].numpy(), kps_pin[i].numpy(), scene.cal)
 
-    from gtsfm_b200.two_view_batch import TwoViewBatchResult, gather_records, pack_records
-    pair_ids = mine if strong else rank * P + np.arange(P)                 # weak scaling: every rank owns P pairs of the job
+    # sub-batches of the rank's pair list (contiguous, equal pair counts): the exchange of sub-batch k -- device pack, NCCL
+    # all-gather, copy to rank 0's pinned memory -- runs on torch's stream while the library's stream computes sub-batch k + 1
+    n_sub = args.sub_batches or (1 if world == 1 else 4)
+    n_sub = max(1, min(n_sub, P))
+    bounds = np.linspace(0, P, n_sub + 1).astype(np.int64)
+    exchange = ResultExchange(dist, root=0)
+    last_total = [0]
 
-    def compute(fetch: bool):
-        # e2e leg: the match D2H is enqueued on the copy stream and overlaps the verifier; results land in pinned buffers
-        m, off = ctx.match_batch(pairs, scene.ratio, fetch="async" if fetch else False)
-        out = ctx.verify_batch(pairs, prm, total=int(off[-1]), reuse_outputs=True)      # results land in the pinned arena in both legs
-        if fetch:
-            ctx.sync()
-        d2h = m.nbytes + out["mask"].nbytes + out["R"].nbytes + out["t"].nbytes + out["E"].nbytes + out["n_inliers"].nbytes + out["status"].nbytes + 4 * P
-        if world > 1:                                                      # per-pair result records gathered via NCCL (north_star)
-            res = TwoViewBatchResult(pairs, off, m, out["mask"], out["R"], out["t"], out["n_inliers"], out["status"])
-            table = gather_records(pack_records(res, pair_ids), P_total, dist, device="cuda")
-            assert table.shape[0] == P_total
-        return off, out, d2h
+    def compute():
+        handles = []
+        for k in range(n_sub):
+            a, b = int(bounds[k]), int(bounds[k + 1])
+            sub_keys = np.ascontiguousarray(keys[a:b])
+            prm.pair_keys = sub_keys.ctypes.data
+            _, off = ctx.match_batch(pairs[a:b], scene.ratio, fetch=False)               # putative matches stay on the device
+            ctx.verify_batch(pairs[a:b], prm, total=int(off[-1]), fetch=False)           # so do masks and poses
+            handles.append(exchange.start_device(ctx, b - a, pair_ids[a:b], slot=k))
+            last_total[0] = int(off[-1])
+        parts = [exchange.finish(h, P_total) for h in handles]                           # rank 0: the job's result table on the host
+        table = merge_gathered(parts) if parts[0] is not None else None
+        return table, sum(h["d2h_bytes"] for h in handles)
 
     def sync_all():
         if world > 1:
@@ -289,13 +308,13 @@ def run_b200(args):
     # ---- resident leg: inputs already in HBM
     upload()
     for _ in range(args.warmup):
-        compute(False)
-    ctx.profile_enable(not os.environ.get("GTSFM_B200_BENCH_NOPROF"))      # diagnostics: how much the per-kernel events cost
+        compute()
+    ctx.profile_enable(not os.environ.get("GTSFM_B200_BENCH_NOPROF"))      # per-kernel CUDA events (their cost stays inside `value`)
     ctx.verify_stats(reset=True)
     launches0 = ctx.kernel_launches
     clocks = ClockSampler(local)
     clocks.start()
-    ms, wall, (off, out, _) = timed(lambda: compute(False), args.steps)
+    ms, wall, (table, _) = timed(compute, args.steps)
     clk = clocks.stop()
     launches = ctx.kernel_launches - launches0
     prof = ctx.profile_get()
@@ -304,21 +323,31 @@ def run_b200(args):
     # the device-event time excludes nothing but host gaps after the last kernel; use the larger of the two clocks
     step_ms = max(ms, wall * 1e3) / args.steps
     value = P_total / (step_ms / 1e3)
+    stats = None
+    if rank == 0:
+        h = table.headers
+        assert (h["pair_id"] == np.arange(P_total)).all(), "the gathered table misses pairs"
+        okp = h["status"] == 0
+        stats = dict(matches_per_pair=float(h["n_matches"].mean()), inliers_per_pair=float(h["n_inliers"].mean()), verified_ok=int(okp.sum()),
+                     payload_rows=int(h["n_inliers"].sum()))
+        # spot check of the exchange: the verified correspondences of a few pairs are rows of plausible keypoint indices
+        for g in (0, P_total // 2, P_total - 1):
+            v = table.v_corr_idxs(g)
+            assert len(v) == h["n_inliers"][g] and (len(v) == 0 or int(v.max()) < cfg["n_kps"])
 
-    # ---- the stage after verify() in run_2view (GT metrics + InlierSupportProcessor), timed on its own:
-    # it is not part of BASELINE's metric, so it stays outside `value` / `e2e`
-    gt = [scene.relative_pose(int(a), int(b)) for a, b in pairs_g]
+    # ---- the stage after verify() in run_2view (GT metrics + InlierSupportProcessor), timed on its own
+    # over the pairs of the last sub-batch: it is not part of BASELINE's metric, so it stays outside `value` / `e2e`
+    a, b = int(bounds[n_sub - 1]), int(bounds[n_sub])
+    gt = [scene.relative_pose(int(i), int(j)) for i, j in pairs_g[a:b]]
     gt_R, gt_t = np.stack([g[0] for g in gt]), np.stack([g[1] for g in gt])
-    rep = ctx.two_view_report_batch(P, int(off[-1]), scene.threshold_px, 15, 0.1, gt_R, gt_t, reuse_outputs=True)
+    rep = ctx.two_view_report_batch(b - a, last_total[0], scene.threshold_px, 15, 0.1, gt_R, gt_t, reuse_outputs=True)
     ctx.event_record(2)
-    rep = ctx.two_view_report_batch(P, int(off[-1]), scene.threshold_px, 15, 0.1, gt_R, gt_t, reuse_outputs=True)
+    rep = ctx.two_view_report_batch(b - a, last_total[0], scene.threshold_px, 15, 0.1, gt_R, gt_t, reuse_outputs=True)
     ctx.event_record(3)
     report_ms = ctx.event_elapsed_ms(2, 3)
-    ok_pairs = out["status"] == 0
-    report_extra = {"ms_per_pass_incl_result_copies": report_ms, "pairs_kept_by_inlier_support": int(rep["keep"].sum()),
-                    "median_R_error_deg": float(np.nanmedian(rep["R_error_deg"])) if ok_pairs.any() else None,
-                    "median_U_error_deg": float(np.nanmedian(rep["U_error_deg"])) if ok_pairs.any() else None,
-                    "gt_correct_fraction_of_verified": float(rep["num_inliers_gt"].sum() / max(int(out["n_inliers"][ok_pairs].sum()), 1))}
+    report_extra = {"pairs": b - a, "ms_per_pass_incl_result_copies": report_ms, "pairs_kept_by_inlier_support": int(rep["keep"].sum()),
+                    "median_R_error_deg": float(np.nanmedian(rep["R_error_deg"])) if np.isfinite(rep["R_error_deg"]).any() else None,
+                    "median_U_error_deg": float(np.nanmedian(rep["U_error_deg"])) if np.isfinite(rep["U_error_deg"]).any() else None}
 
     # ---- the retriever step in front of the path, outside the timed steps: similarity + top-50 of
     # 2,000 images x 4,096-d global descriptors (C4's image count, NetVLAD's dimension), host arrays in, pair list out
@@ -337,10 +366,14 @@ def run_b200(args):
     # ---- end-to-end leg: pinned host buffers -> device -> results on the host, every step
     def e2e_step():
         upload()
-        return compute(True)
+        return compute()
     for _ in range(min(args.warmup, 1)):
         e2e_step()
-    ems, ewall, (_, _, d2h_bytes) = timed(e2e_step, args.steps)
+    ems, ewall, (_, d2h_bytes) = timed(e2e_step, args.steps)
+    if world > 1:                                          # whole-job copy volumes: uploads of every rank, downloads on rank 0
+        t = torch.tensor([float(h2d_bytes)], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t)
+        h2d_bytes = int(t[0])
     e2e_ms = max(ems, ewall * 1e3) / args.steps
     e2e_value = P_total / (e2e_ms / 1e3)
 
@@ -372,17 +405,19 @@ def run_b200(args):
                                "executed_tflops": 34.0 * n_evals_exec / (sc_ms * 1e-3) / 1e12 if sc_ms > 0 else 0.0, "candidates_per_hypothesis": n_cand / max(n_hyp_solved, 1),
                                "share_of_step": sc_ms / total_kernel_ms if total_kernel_ms else None}
         roofline["traffic"] = load_traffic(args, cfg)
-        n_match = int(off[-1])
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": step_ms, "higher_is_better": True, "scaling": "strong" if strong else "weak", "vs_baseline": None, "dtype": "bf16 GEMM / f32 scoring / f64 finalize",
                 "data": "reference fixture (Lund door SIFT features)" if args.config == "C1" else "synthetic",
                 "config": {"workload": workload_name(args, cfg, P_total if strong else P), "pairs_per_gpu": P, "ratio_test": scene.ratio, "n_hypotheses": scene.n_hyp,
-                           "threshold_px": scene.threshold_px, "lo_iters": 20, "matches_per_pair": n_match / P,
-                           "inliers_per_pair": float(out["n_inliers"].mean()), "verified_ok": int((out["status"] == 0).sum()),
-                           "l2": "inputs exceed L2 (descriptor store %.0f MB per GPU)" % (n_img * n_kps * (dim * 7 + 96) / 1e6),
-                           "parallelism": (f"one pair list dealt over {world} GPU(s) (shard_pairs), {n_img} of {len(scene.descriptors)} images on rank 0, "
-                                           "NCCL all_gather of result records") if strong else
-                                          f"pairs sharded over {world} GPU(s), NCCL all_gather of result records" if world > 1 else "1 GPU"},
+                           "threshold_px": scene.threshold_px, "lo_iters": 20, "matches_per_pair": stats["matches_per_pair"],
+                           "inliers_per_pair": stats["inliers_per_pair"], "verified_ok": stats["verified_ok"],
+                           "l2": "inputs exceed L2 (descriptor store %.0f MB on rank 0)" % (n_img * n_kps * (dim * 7 + 96) / 1e6),
+                           "result": "per pair a 128-byte header (R, t, counts, ratio) + v_corr_idxs, %d rows per step, in pinned host memory of rank 0"
+                                     % stats["payload_rows"],
+                           "sub_batches_per_step": n_sub,
+                           "parallelism": ((f"one pair list dealt over {world} GPUs (shard_pairs), {n_img} of {len(scene.descriptors)} images on rank 0, "
+                                            "device-packed result records, one NCCL all-gather per sub-batch") if world > 1 else "1 GPU") if strong else
+                                          f"every rank its own scene ({world} GPUs), device-packed result records, one NCCL all-gather per sub-batch"},
                 "roofline": roofline, "cpu_baseline": cpu,
                 "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": int(d2h_bytes)},
                 "gpu_launches": int(launches), "clocks": clk, "device_event_ms_per_step": ms / args.steps,

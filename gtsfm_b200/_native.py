@@ -21,7 +21,7 @@ EXPORTS = (
     "gtsfm_profile_enable", "gtsfm_profile_get", "gtsfm_event_record", "gtsfm_event_elapsed_ms", "gtsfm_verify_stats",
     "gtsfm_host_alloc", "gtsfm_host_free", "gtsfm_match_fetch_async", "gtsfm_sync",
     "gtsfm_retriever_similarity", "gtsfm_retriever_topk", "gtsfm_retriever_pairs_noalloc",
-    "gtsfm_verify_hypotheses_used",
+    "gtsfm_verify_hypotheses_used", "gtsfm_result_pack", "gtsfm_result_pack_copy", "gtsfm_stream_wait",
 )
 
 OK, E_CUDA, E_ARG, E_NO_DEVICE, E_KNN_UNPACK, E_UNSUPPORTED = range(6)
@@ -85,6 +85,9 @@ def lib() -> ctypes.CDLL:
             L.gtsfm_host_free.restype = None
             L.gtsfm_match_fetch_async.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
             L.gtsfm_sync.argtypes = [ctypes.c_void_p]
+            L.gtsfm_result_pack.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.POINTER(ctypes.c_int64)]
+            L.gtsfm_result_pack_copy.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int64]
+            L.gtsfm_stream_wait.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
             L.gtsfm_verify_hypotheses_used.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
             L.gtsfm_verify_stats.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_int64), ctypes.c_int]
             L.gtsfm_image_upload.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_int,
@@ -194,6 +197,22 @@ class Context:
     @property
     def kernel_launches(self) -> int:
         return int(self._L.gtsfm_kernel_launches(self._h))
+
+    def result_pack(self, n_pairs: int, pair_ids: Optional[np.ndarray] = None) -> int:
+        """Build the 128-byte result headers and the payload offset table of the last verify_batch on the device
+        (gtsfm_result_pack); returns the number of payload rows (verified correspondences of all pairs)."""
+        ids = None if pair_ids is None else np.ascontiguousarray(pair_ids, np.int64)
+        rows = ctypes.c_int64(0)
+        self._check(self._L.gtsfm_result_pack(self._h, int(n_pairs), _ptr(ids), ctypes.byref(rows)))
+        return int(rows.value)
+
+    def result_pack_copy(self, d_dst: int, dst_bytes: int, payload_offset_bytes: int):
+        """Write [headers | payload] into a caller-owned DEVICE buffer (address d_dst), on the context's stream."""
+        self._check(self._L.gtsfm_result_pack_copy(self._h, ctypes.c_void_p(int(d_dst)), int(dst_bytes), int(payload_offset_bytes)))
+
+    def stream_wait(self, cuda_stream: int, context_waits: bool = False):
+        """Order the context's stream against another CUDA stream (a torch stream's .cuda_stream) without a host sync."""
+        self._check(self._L.gtsfm_stream_wait(self._h, ctypes.c_void_p(int(cuda_stream)), 1 if context_waits else 0))
 
     def verify_hypotheses_used(self, n_pairs: int) -> np.ndarray:
         """Hypotheses evaluated per pair by the last verify_batch (differs from n_hypotheses only under the adaptive F budget)."""
@@ -340,15 +359,21 @@ class Context:
 
     # ---- verifier
     def verify_batch(self, pairs: np.ndarray, params: "VerifyParams", match_idx: Optional[np.ndarray] = None,
-                     match_offsets: Optional[np.ndarray] = None, total: Optional[int] = None, reuse_outputs: bool = False):
+                     match_offsets: Optional[np.ndarray] = None, total: Optional[int] = None, reuse_outputs: bool = False,
+                     fetch: bool = True):
         """Verify the last match batch (match_idx None) or caller-supplied matches.  Returns a dict of arrays; with
-        reuse_outputs they are views of the context's pinned arena, valid until the next verify_batch."""
+        reuse_outputs they are views of the context's pinned arena, valid until the next verify_batch.  fetch=False leaves
+        every result on the device (for result_pack / two_view_report_batch) and returns None."""
         pairs = np.ascontiguousarray(pairs, np.int32).reshape(-1, 2)
         P = pairs.shape[0]
         if match_idx is not None:
             match_idx = np.ascontiguousarray(match_idx, np.uint32).reshape(-1, 2)
             match_offsets = np.ascontiguousarray(match_offsets, np.int64)
             total = int(match_offsets[-1])
+        if not fetch:
+            self._check(self._L.gtsfm_verify_batch(self._h, _ptr(pairs), P, _ptr(match_idx), _ptr(match_offsets), ctypes.byref(params),
+                                                   None, None, None, None, None, None))
+            return None
         if reuse_outputs:
             R = self._pinned("R", (P, 9), np.float64); t = self._pinned("t", (P, 3), np.float64); E = self._pinned("E", (P, 9), np.float64)
             ninl = self._pinned("ninl", (P,), np.int32); status = self._pinned("status", (P,), np.int32)

@@ -241,6 +241,7 @@ void gtsfm_ctx_destroy(gtsfm_ctx* c)
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     if (c->match_done) cudaEventDestroy(c->match_done);
     if (c->upload_ev) cudaEventDestroy(c->upload_ev);
+    if (c->xs_ev) cudaEventDestroy(c->xs_ev);
     cudaStreamDestroy(c->stream);
     delete c;
 }

@@ -82,8 +82,11 @@ struct gtsfm_ctx {
     int prof_collect();
 
     // ---- verifier buffers; state of the last gtsfm_verify_batch (read by gtsfm_two_view_report_batch)
-    g2v::DevBuf v_bufs[24];
+    g2v::DevBuf v_bufs[32];
     int verify_n = 0;
+    int pack_n = 0;                          // pairs / payload rows of the last gtsfm_result_pack
+    long long pack_rows = 0;
+    cudaEvent_t xs_ev = nullptr;             // gtsfm_stream_wait: ordering against a caller's stream
     std::vector<int> verify_hyp;            // hypotheses evaluated per pair of the last verify batch (adaptive F mode)
     long long verify_total = 0;
 

@@ -4,7 +4,7 @@ keypoint noise and clutter, projected to SIFT-like 128-d (integer-valued, norm ~
 tests see identical inputs.  Pure numpy: used by bench.py, tests and tools; not part of the device path.
 """
 from dataclasses import dataclass
-from typing import List, Optional, Tuple
+from typing import List, Optional, Sequence, Tuple
 
 import numpy as np
 
@@ -98,7 +98,11 @@ def make_pairs(n_images: int, rule: str, top_k: int = 50, angles: Optional[np.nd
 
 def make_scene(n_images: int, n_kps: int, dim: int = 128, kind: str = "sift", visible: float = 0.7, pairs: str = "exhaustive",
                top_k: int = 50, n_hyp: int = 1024, ratio: Optional[float] = 0.8, seed: int = 0, max_pairs: Optional[int] = None,
-               noise_px: float = 0.5, arc: Optional[float] = None, clutter_hidden: float = 0.75) -> Scene:
+               noise_px: float = 0.5, arc: Optional[float] = None, clutter_hidden: float = 0.75,
+               only_images: Optional[Sequence[int]] = None) -> Scene:
+    """only_images: generate the features of these images only (a rank of a sharded job needs just the images its pairs
+    name); every image draws from its own generator (seed, image index), so the subset equals the full scene's entries and the
+    other entries are None.  Cameras and the pair list are always complete."""
     rng = np.random.default_rng(seed)
     n_pts = n_kps
     X = np.c_[rng.uniform(-4, 4, (n_pts, 2)), rng.uniform(-1, 1, n_pts)]
@@ -111,8 +115,16 @@ def make_scene(n_images: int, n_kps: int, dim: int = 128, kind: str = "sift", vi
     angles = np.sort(rng.uniform(0, arc, n_images))
     n_vis = int(round(visible * n_kps))
     descs, kps, ids, Rs, ts = [], [], [], [], []
+    cams = [_look_at_origin(rng, angles[i]) for i in range(n_images)]
+    wanted = None if only_images is None else set(int(i) for i in only_images)
     for i in range(n_images):
-        R, t = _look_at_origin(rng, angles[i])
+        R, t = cams[i]
+        Rs.append(R)
+        ts.append(t)
+        if wanted is not None and i not in wanted:
+            descs.append(None); kps.append(None); ids.append(None)
+            continue
+        rng = np.random.default_rng([seed, i])           # per-image stream: an image does not depend on which others are generated
         Xc = X @ R.T + t
         uv = Xc[:, :2] / Xc[:, 2:] * F + [U0, V0]
         ok = np.flatnonzero((Xc[:, 2] > 0.1) & (uv[:, 0] >= 0) & (uv[:, 0] < W) & (uv[:, 1] >= 0) & (uv[:, 1] < H))
@@ -137,10 +149,13 @@ def make_scene(n_images: int, n_kps: int, dim: int = 128, kind: str = "sift", vi
         descs.append(np.ascontiguousarray(d_i[perm]))
         kps.append(np.ascontiguousarray(uv_i[perm]))
         ids.append(id_i[perm])
-        Rs.append(R)
-        ts.append(t)
     pr = make_pairs(n_images, pairs, top_k, angles, max_pairs)
     return Scene(descs, kps, ids, Rs, ts, pr, CAL, ratio, n_hyp)
+
+
+def config_pairs(cfg: dict) -> np.ndarray:
+    """The pair list of a config without generating any features (cameras are drawn first from the scene's generator)."""
+    return make_scene(**cfg, only_images=[]).pairs
 
 
 def make_config(name: str, n_images: Optional[int] = None, n_kps: Optional[int] = None, max_pairs: Optional[int] = None) -> Scene:

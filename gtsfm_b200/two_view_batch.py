@@ -169,42 +169,200 @@ def run_two_view_batch(descriptors: Sequence[np.ndarray], keypoints: Sequence[np
 
 
 # ------------------------------------------------------------------------------------------------ multi-GPU result exchange
-RECORD_WIDTH = 16   # R (9) | t (3) | n_inliers | status | n_matches | global pair id
+# one process per GPU, no data-path collective; the only exchange is the result of every pair -- "per-pair
+# fixed header {n_matches, n_inliers, status, R[9], t[3], ratio} plus variable-length index payloads packed with a prefix-sum
+# offset table (two-phase: gather counts -> gather payload)".  The block is built on the device (csrc/result_pack.cu), moved
+# with one NCCL all-gather from the library's buffers and lands in pinned host memory with one copy; nothing is bounced
+# through the host in between.  What travels is what unzip_two_view_results hands to the back end
+# (gtsfm/runner/gtsfm_runner_base.py:415-440): i2Ri1, i2Ui1, v_corr_idxs, inlier ratio.
+HEADER_DTYPE = np.dtype([("pair_id", "<i8"), ("n_matches", "<i4"), ("n_inliers", "<i4"), ("status", "<i4"), ("pad", "<i4"),
+                         ("R", "<f8", (9,)), ("t", "<f8", (3,)), ("inlier_ratio", "<f8")])
+HEADER_BYTES = 128
+assert HEADER_DTYPE.itemsize == HEADER_BYTES
 
 
-def pack_records(result: TwoViewBatchResult, pair_ids: np.ndarray) -> np.ndarray:
-    """Fixed-width per-pair header: the only data that crosses GPUs.  pair_ids are the positions of the
-    shard's pairs in the global pair list, so the receiver can put every record back in place."""
+def block_layout(max_pairs: int, max_rows: int) -> Tuple[int, int]:
+    """(payload offset, block size) in bytes of a rank's [headers | payload] block, padded to the largest rank."""
+    payload_offset = HEADER_BYTES * int(max_pairs)
+    return payload_offset, payload_offset + 8 * int(max_rows) + 16
+
+
+def pack_block(result: TwoViewBatchResult, pair_ids: np.ndarray) -> Tuple[np.ndarray, np.ndarray]:
+    """Host mirror of the device pack (gtsfm_result_pack / gtsfm_result_pack_copy): (headers (P,) HEADER_DTYPE, payload
+    (rows, 2) uint32).  Used by the CPU (gloo) tests and to check the device kernels; the GPU path never calls it."""
+    result._need_matches()
     P = len(result.pairs)
-    rec = np.zeros((P, RECORD_WIDTH), np.float64)
-    rec[:, 0:9] = result.R.reshape(P, 9)
-    rec[:, 9:12] = result.t
-    rec[:, 12] = result.n_inliers
-    rec[:, 13] = result.status
-    rec[:, 14] = np.diff(result.match_offsets)
-    rec[:, 15] = pair_ids
-    return rec
+    o = result.match_offsets
+    hdr = np.zeros(P, HEADER_DTYPE)
+    ok = np.asarray(result.status) == 0
+    hdr["pair_id"] = pair_ids
+    hdr["n_matches"] = np.diff(o)
+    hdr["status"] = result.status
+    hdr["n_inliers"] = np.where(ok, result.n_inliers, 0)
+    hdr["R"] = np.where(ok[:, None], np.asarray(result.R, np.float64).reshape(P, 9), 0.0)
+    hdr["t"] = np.where(ok[:, None], np.asarray(result.t, np.float64).reshape(P, 3), 0.0)
+    with np.errstate(all="ignore"):
+        hdr["inlier_ratio"] = np.where(ok & (hdr["n_matches"] > 0), hdr["n_inliers"] / np.maximum(hdr["n_matches"], 1), 0.0)
+    keep = np.zeros(int(o[-1]), bool)
+    for p in np.flatnonzero(ok):
+        keep[o[p]:o[p + 1]] = result.inlier_mask[o[p]:o[p + 1]] == 1
+    return hdr, np.ascontiguousarray(result.matches[keep], np.uint32).reshape(-1, 2)
 
 
-def gather_records(rec, n_global: int, dist=None, device=None) -> np.ndarray:
-    """All-gather the shards' record blocks (NCCL over NVLink on the GPU box, gloo in the CPU tests) and scatter them
-    into global pair order.  Shards may differ in length: blocks are padded to the longest one, padding rows carry id -1."""
+def block_bytes(hdr: np.ndarray, payload: np.ndarray, max_pairs: int, max_rows: int) -> np.ndarray:
+    """One rank's block as bytes, in the layout of block_layout (host mirror of gtsfm_result_pack_copy)."""
+    off, size = block_layout(max_pairs, max_rows)
+    buf = np.zeros(size, np.uint8)
+    buf[: hdr.nbytes] = hdr.view(np.uint8)
+    buf[off: off + payload.nbytes] = payload.reshape(-1).view(np.uint8)
+    return buf
+
+
+@dataclass
+class GatheredTwoViewResults:
+    """The result table of a whole job after the exchange: headers in GLOBAL pair order, payload kept per rank (views into
+    the receive buffer: no second copy of up to gigabytes of indices)."""
+    headers: np.ndarray                   # (P_total,) HEADER_DTYPE, row = global pair id; pairs nobody reported have pair_id -1
+    _payload: List[np.ndarray]            # per rank (rows_r, 2) uint32
+    _where: np.ndarray                    # (P_total, 2) int64: rank and first payload row of every pair
+
+    def v_corr_idxs(self, pair_id: int) -> np.ndarray:
+        h = self.headers[pair_id]
+        r, o = self._where[pair_id]
+        return self._payload[int(r)][int(o): int(o) + int(h["n_inliers"])]
+
+    def two_view_dicts(self, pairs: np.ndarray):
+        """(i2Ri1_dict, i2Ui1_dict, v_corr_idxs_dict, inlier_ratio_dict) in the reference's conventions; failed pairs carry
+        (None, None, empty uint64, 0.0) like VerifierBase's failure tuple (verifier_base.py:56)."""
+        Rd, td, vd, rd = {}, {}, {}, {}
+        for g, (a, b) in enumerate(np.asarray(pairs).reshape(-1, 2)):
+            key, h = (int(a), int(b)), self.headers[g]
+            if h["pair_id"] < 0 or h["status"] != 0:
+                Rd[key], td[key], vd[key], rd[key] = None, None, np.array([], dtype=np.uint64), 0.0
+                continue
+            Rd[key], td[key] = Rot3(h["R"].reshape(3, 3).copy()), Unit3(h["t"].copy())
+            vd[key], rd[key] = self.v_corr_idxs(g), float(h["inlier_ratio"])
+        return Rd, td, vd, rd
+
+
+def unpack_blocks(buf: np.ndarray, counts: np.ndarray, n_global: int) -> GatheredTwoViewResults:
+    """buf: (world, block size) uint8 as received; counts: (world, 2) [pairs, payload rows] per rank."""
+    world = buf.shape[0]
+    off, _ = block_layout(counts[:, 0].max(), counts[:, 1].max())
+    headers = np.zeros(n_global, HEADER_DTYPE)
+    headers["pair_id"] = -1
+    where = np.zeros((n_global, 2), np.int64)
+    payloads = []
+    for r in range(world):
+        n, rows = int(counts[r, 0]), int(counts[r, 1])
+        h = buf[r, : HEADER_BYTES * n].view(HEADER_DTYPE)
+        payloads.append(buf[r, off: off + 8 * rows].view(np.uint32).reshape(-1, 2))
+        ids = h["pair_id"]
+        headers[ids] = h
+        where[ids, 0] = r
+        where[ids, 1] = np.concatenate([[0], np.cumsum(h["n_inliers"][:-1], dtype=np.int64)]) if n else np.zeros(0, np.int64)
+    return GatheredTwoViewResults(headers, payloads, where)
+
+
+def _all_gather_bytes(block, dist, world: int):
+    """All-gather equal-sized uint8 tensors: NCCL moves them as one collective straight between the GPUs' buffers; gloo (CPU
+    tests) goes through the list form."""
     import torch
-    if dist is None or not dist.is_initialized() or dist.get_world_size() == 1:
-        blocks = [np.asarray(rec)]
+    out = torch.empty((world, block.numel()), dtype=torch.uint8, device=block.device)
+    if block.is_cuda:
+        dist.all_gather_into_tensor(out.view(-1), block)
     else:
-        world = dist.get_world_size()
-        n = torch.tensor([len(rec)], dtype=torch.int64, device=device)
-        ns = [torch.zeros_like(n) for _ in range(world)]
-        dist.all_gather(ns, n)
-        longest = max(int(x) for x in ns)
-        pad = torch.full((longest, RECORD_WIDTH), -1.0, dtype=torch.float64, device=device)
-        pad[:len(rec)] = torch.as_tensor(rec, dtype=torch.float64, device=device)
-        out = [torch.zeros_like(pad) for _ in range(world)]
-        dist.all_gather(out, pad)
-        blocks = [o[:int(k)].cpu().numpy() for o, k in zip(out, ns)]
-    table = np.full((n_global, RECORD_WIDTH), np.nan)
-    for blk in blocks:
-        ids = blk[:, 15].astype(np.int64)
-        table[ids] = blk
-    return table
+        parts = [torch.empty_like(block) for _ in range(world)]
+        dist.all_gather(parts, block)
+        for r, p in enumerate(parts):
+            out[r] = p
+    return out
+
+
+class ResultExchange:
+    """Two-phase exchange of one (sub-)batch: phase 1 announces [pairs, payload rows] per rank, phase 2 all-gathers the
+    [headers | payload] blocks.  On the GPU the block is written by the library straight into a torch tensor, the collective is
+    enqueued behind it without a host synchronisation, and the gathered table is copied once into pinned host memory on
+    `root` (all ranks when root is None); `finish()` waits for that copy.  With one process there is no collective."""
+
+    def __init__(self, dist=None, root: Optional[int] = 0):
+        self.dist = dist if (dist is not None and dist.is_initialized() and dist.get_world_size() > 1) else None
+        self.world = self.dist.get_world_size() if self.dist else 1
+        self.rank = self.dist.get_rank() if self.dist else 0
+        self.root = root
+        self._pinned = {}
+
+    def _counts(self, n_pairs: int, rows: int, device):
+        import torch
+        mine = torch.tensor([n_pairs, rows], dtype=torch.int64, device=device)
+        if not self.dist:
+            return mine.cpu().numpy().reshape(1, 2)
+        if mine.is_cuda:
+            out = torch.empty(2 * self.world, dtype=torch.int64, device=device)
+            self.dist.all_gather_into_tensor(out, mine)
+        else:
+            parts = [torch.empty_like(mine) for _ in range(self.world)]
+            self.dist.all_gather(parts, mine)
+            out = torch.cat(parts)
+        return out.cpu().numpy().reshape(self.world, 2)
+
+    def start_device(self, ctx: "_native.Context", n_pairs: int, pair_ids: np.ndarray, slot: int = 0):
+        """Pack the last verify batch of `ctx` on its device and start the exchange; returns a handle for finish()."""
+        import torch
+        rows = ctx.result_pack(n_pairs, pair_ids)
+        dev = torch.device("cuda", ctx.device)
+        counts = self._counts(n_pairs, rows, dev)
+        off, size = block_layout(counts[:, 0].max(), counts[:, 1].max())
+        block = torch.empty(size, dtype=torch.uint8, device=dev)
+        ctx.result_pack_copy(block.data_ptr(), size, off)
+        stream = torch.cuda.current_stream(dev)
+        ctx.stream_wait(stream.cuda_stream)                       # the collective is ordered behind the pack kernels, no host sync
+        block.record_stream(stream)
+        gathered = _all_gather_bytes(block, self.dist, self.world) if self.dist else block.view(1, -1)
+        host = None
+        if self.root is None or self.rank == self.root:
+            host = self._host_buffer(slot, gathered.numel()).view(self.world, size)
+            host.copy_(gathered, non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record(stream)
+        return dict(counts=counts, host=host, event=ev, keep=(block, gathered), d2h_bytes=0 if host is None else gathered.numel())
+
+    def start_host(self, result: TwoViewBatchResult, pair_ids: np.ndarray):
+        """The same exchange from host arrays (CPU / gloo tests): the block is built by the host mirror of the device pack."""
+        import torch
+        hdr, payload = pack_block(result, pair_ids)
+        counts = self._counts(len(hdr), len(payload), torch.device("cpu"))
+        block = torch.from_numpy(block_bytes(hdr, payload, counts[:, 0].max(), counts[:, 1].max()))
+        gathered = _all_gather_bytes(block, self.dist, self.world) if self.dist else block.view(1, -1)
+        return dict(counts=counts, host=gathered, event=None, keep=None, d2h_bytes=0)
+
+    def _host_buffer(self, slot: int, nbytes: int):
+        import torch
+        buf = self._pinned.get(slot)
+        if buf is None or buf.numel() < nbytes:
+            buf = self._pinned[slot] = torch.empty(int(nbytes * 1.25) + 4096, dtype=torch.uint8, pin_memory=True)
+        return buf[:nbytes]
+
+    @staticmethod
+    def finish(handle, n_global: int) -> Optional[GatheredTwoViewResults]:
+        """Wait for the exchange; the gathered table on the root (None elsewhere).  The arrays are views of the exchange's
+        pinned buffer (slot), valid until that slot is used again."""
+        if handle["event"] is not None:
+            handle["event"].synchronize()
+        if handle["host"] is None:
+            return None
+        return unpack_blocks(handle["host"].numpy(), handle["counts"], n_global)
+
+
+def merge_gathered(parts: Sequence[GatheredTwoViewResults]) -> GatheredTwoViewResults:
+    """Sub-batches of one job (disjoint pair ids) -> one table."""
+    headers = parts[0].headers.copy()
+    where = parts[0]._where.copy()
+    payloads = list(parts[0]._payload)
+    for part in parts[1:]:
+        have = part.headers["pair_id"] >= 0
+        headers[have] = part.headers[have]
+        where[have, 0] = part._where[have, 0] + len(payloads)
+        where[have, 1] = part._where[have, 1]
+        payloads += list(part._payload)
+    return GatheredTwoViewResults(headers, payloads, where)

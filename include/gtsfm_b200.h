@@ -166,6 +166,26 @@ int gtsfm_two_view_report_batch(gtsfm_ctx* ctx, int n_pairs, const double* gt_i2
                                 double* inlier_avg_err, double* outlier_avg_err, double* R_error_deg, double* U_error_deg,
                                 int32_t* keep);
 
+/* ---- device-resident result records for the multi-GPU exchange ------------------------------------------
+ * What unzip_two_view_results hands to the back end (gtsfm/runner/gtsfm_runner_base.py:415-440) for every pair of the last
+ * gtsfm_verify_batch, packed ON THE DEVICE as one block [headers | payload] that a rank contributes to an NCCL all-gather:
+ *   header (128 bytes per pair, little endian): int64 pair_id; int32 n_matches, n_inliers, status, pad; double R[9] (i2Ri1,
+ *     row-major); double t[3] (i2Ui1); double inlier_ratio (opencv_verifier_base.py:101).  Failed pairs: n_inliers 0, R = t = 0.
+ *   payload: the verified correspondences v_corr_idxs (match rows with inlier mask 1, input order, opencv_verifier_base.py:
+ *     98-100) of pair 0, pair 1, ... back to back as (i1, i2) uint32 rows; pair p's rows start at the exclusive prefix sum of
+ *     n_inliers (the offset table is rebuilt from the headers).
+ * gtsfm_result_pack: builds the headers and the offset table; pair_ids (n_pairs) are the caller's global pair ids or NULL
+ *   (= 0..n_pairs-1); *n_payload_rows = total number of payload rows (the one number a rank has to announce before the
+ *   exchange).
+ * gtsfm_result_pack_copy: writes the headers at d_dst and the payload at d_dst + payload_offset_bytes (>= 128 * n_pairs, a
+ *   multiple of 8) into a DEVICE buffer of dst_bytes owned by the caller (e.g. a torch tensor); enqueued on the context's
+ *   stream, returns without synchronising.
+ * gtsfm_stream_wait: orders the context's stream against a caller's CUDA stream without a host synchronisation: direction 0 =
+ *   the caller's stream waits for everything the context has enqueued, 1 = the context's stream waits for the caller's. */
+int gtsfm_result_pack(gtsfm_ctx* ctx, int n_pairs, const int64_t* pair_ids, int64_t* n_payload_rows);
+int gtsfm_result_pack_copy(gtsfm_ctx* ctx, void* d_dst, int64_t dst_bytes, int64_t payload_offset_bytes);
+int gtsfm_stream_wait(gtsfm_ctx* ctx, void* cuda_stream, int direction);
+
 /* ---- the retriever step in front of the matcher ---------------------------------------------------
  * Replaces NetVLADRetriever.compute_similarity_matrix (gtsfm/retriever/netvlad_retriever.py:77-149: blocked
  * torch.einsum("id,jd->ij") of the global descriptors) and pairs_from_score_matrix (:196-228: mask + min_score + torch.topk).
