@@ -10,7 +10,8 @@ from gtsfm_b200 import synthetic
 from gtsfm_b200.common.types import Cal3Bundler, Keypoints
 from gtsfm_b200.frontend.matcher.twoway_matcher import MatchingDistanceType, TwoWayMatcher
 from gtsfm_b200.frontend.verifier.ransac import Ransac
-from gtsfm_b200.two_view_batch import RECORD_WIDTH, TwoViewBatchResult, gather_records, pack_records, shard_pairs
+from gtsfm_b200.two_view_batch import (HEADER_BYTES, ResultExchange, TwoViewBatchResult, block_bytes, block_layout, pack_block, shard_pairs,
+                                       unpack_blocks)
 
 
 # ---------------------------------------------------------------------------------------------------- sharding
@@ -153,15 +154,35 @@ def test_two_view_dicts_follow_the_reference_conventions():
             assert np.allclose(Rd[key].matrix(), res.R[p])
 
 
-def test_record_packing_round_trips_without_a_process_group():
+def test_result_blocks_round_trip_without_a_process_group():
+    """[headers | payload] blocks: pack on the host mirror, pad like an uneven all-gather, unpack."""
     pairs = synthetic.make_pairs(7, "exhaustive")
     res = _fake_result(pairs, 2)
-    rec = pack_records(res, np.arange(len(pairs)))
-    assert rec.shape == (len(pairs), RECORD_WIDTH)
-    table = gather_records(rec, len(pairs))
-    assert (table[:, 0:9] == res.R.reshape(-1, 9)).all() and (table[:, 9:12] == res.t).all()
-    assert (table[:, 12] == res.n_inliers).all() and (table[:, 13] == res.status).all()
-    assert (table[:, 14] == np.diff(res.match_offsets)).all()
+    hdr, payload = pack_block(res, np.arange(len(pairs)))
+    assert hdr.dtype.itemsize == HEADER_BYTES == 128 and payload.dtype == np.uint32
+    ok = res.status == 0
+    assert (hdr["n_matches"] == np.diff(res.match_offsets)).all() and (hdr["status"] == res.status).all()
+    assert (hdr["n_inliers"][ok] == res.n_inliers[ok]).all() and (hdr["n_inliers"][~ok] == 0).all()
+    assert (hdr["R"][ok] == res.R.reshape(-1, 9)[ok]).all() and (hdr["t"][ok] == res.t[ok]).all()
+    assert len(payload) == hdr["n_inliers"].sum()
+    # two "ranks" with different sizes: the second block is padded to the first one's layout
+    half = len(pairs) // 3
+    parts = [_fake_result(pairs[:half], 5), _fake_result(pairs[half:], 6)]
+    blocks = [pack_block(parts[0], np.arange(half)), pack_block(parts[1], np.arange(half, len(pairs)))]
+    counts = np.array([[len(h), len(p)] for h, p in blocks])
+    off, size = block_layout(counts[:, 0].max(), counts[:, 1].max())
+    buf = np.stack([block_bytes(h, p, counts[:, 0].max(), counts[:, 1].max()) for h, p in blocks])
+    assert buf.shape == (2, size) and off == 128 * counts[:, 0].max()
+    table = unpack_blocks(buf, counts, len(pairs))
+    assert (table.headers["pair_id"] == np.arange(len(pairs))).all()
+    for r, (h, p) in enumerate(blocks):
+        o = np.concatenate([[0], np.cumsum(h["n_inliers"])])
+        for k, g in enumerate(h["pair_id"]):
+            assert (table.v_corr_idxs(int(g)) == p[o[k]:o[k + 1]]).all()
+    # the single-process exchange is the identity
+    ex = ResultExchange(None)
+    t1 = ex.finish(ex.start_host(res, np.arange(len(pairs))), len(pairs))
+    assert (t1.headers == hdr).all()
 
 
 def test_inlier_support_processor_decisions():
