@@ -228,6 +228,11 @@ def run_b200(args):
         pairs = np.ascontiguousarray(remap[pairs_g].astype(np.int32))
         P_total = len(scene.pairs)
         pair_ids = np.ascontiguousarray(mine, np.int64)                    # positions in the global pair list
+        # the rank works through its pairs in the order of the LAST image a pair names: sub-batch 0 then needs a prefix of the
+        # (in-order) image uploads only and starts while the rest is still arriving.  Results go to pair_ids, sampler keys are
+        # global pair ids, so the order changes nothing but the schedule.
+        order = np.argsort(pairs.max(axis=1), kind="stable")
+        pairs, pairs_g, pair_ids = np.ascontiguousarray(pairs[order]), np.ascontiguousarray(pairs_g[order]), np.ascontiguousarray(pair_ids[order])
     else:
         pairs_g = pairs = scene.pairs
         used = np.arange(len(scene.descriptors))
@@ -255,31 +260,51 @@ def run_b200(args):
     prm.samples = None
     prm.estimate_fundamental = 1 if args.verifier == "fundamental" else 0
 
+    desc_np, kps_np, cal_np = [t.numpy() for t in desc_pin], [t.numpy() for t in kps_pin], np.tile(np.asarray(scene.cal, np.float64), (n_img, 1))
+
     def upload():
         ctx.clear()
-        for i in range(n_img):
-            ctx.upload_image(i, desc_pin[i].numpy(), kps_pin[i].numpy(), scene.cal)
+        ctx.upload_images(0, desc_np, kps_np, cal_np)           # one library call: copies + prepare kernels enqueued on the copy stream
 
     # sub-batches of the rank's pair list (contiguous, equal pair counts): the exchange of sub-batch k -- device pack, NCCL
     # all-gather, copy to rank 0's pinned memory -- runs on torch's stream while the library's stream computes sub-batch k + 1
-    n_sub = args.sub_batches or (1 if world == 1 else 4)
-    n_sub = max(1, min(n_sub, P))
-    bounds = np.linspace(0, P, n_sub + 1).astype(np.int64)
+    # (the e2e leg always pipelines: sub-batch 0 starts as soon as ITS images are on the device, the rest of the upload runs
+    # on the copy stream behind it)
+    n_sub = max(1, min(args.sub_batches or 4, P))
+    n_sub_e2e = max(1, min(args.sub_batches or (4 if world == 1 else 6), P))
+
+    def sub_bounds(n):
+        # equal sub-batches except a last one of half the size: its exchange is the only one nothing overlaps
+        w = np.ones(n)
+        if n > 1:
+            w[-1] = 0.5
+        return np.concatenate([[0], np.round(np.cumsum(w) / w.sum() * P)]).astype(np.int64)
     exchange = ResultExchange(dist, root=0)
     last_total = [0]
 
-    def compute():
+    trace = [] if os.environ.get("GTSFM_B200_BENCH_TRACE") else None      # host timestamps per sub-batch (diagnostics)
+
+    def compute(n_sub=n_sub):
+        bounds = sub_bounds(n_sub)
         handles = []
         for k in range(n_sub):
             a, b = int(bounds[k]), int(bounds[k + 1])
             sub_keys = np.ascontiguousarray(keys[a:b])
             prm.pair_keys = sub_keys.ctypes.data
+            t0 = time.perf_counter()
             _, off = ctx.match_batch(pairs[a:b], scene.ratio, fetch=False)               # putative matches stay on the device
+            t1 = time.perf_counter()
             ctx.verify_batch(pairs[a:b], prm, total=int(off[-1]), fetch=False)           # so do masks and poses
+            t2 = time.perf_counter()
             handles.append(exchange.start_device(ctx, b - a, pair_ids[a:b], slot=k))
+            if trace is not None:
+                trace.append((k, t1 - t0, t2 - t1, time.perf_counter() - t2))
             last_total[0] = int(off[-1])
+        t3 = time.perf_counter()
         parts = [exchange.finish(h, P_total) for h in handles]                           # rank 0: the job's result table on the host
         table = merge_gathered(parts) if parts[0] is not None else None
+        if trace is not None:
+            trace.append((-1, time.perf_counter() - t3, 0.0, 0.0))
         return table, sum(h["d2h_bytes"] for h in handles)
 
     def sync_all():
@@ -317,12 +342,23 @@ def run_b200(args):
     ms, wall, (table, _) = timed(compute, args.steps)
     clk = clocks.stop()
     launches = ctx.kernel_launches - launches0
+    if trace is not None:
+        print(f"[trace rank {rank}] (sub-batch, match s, verify s, exchange-start s) of the timed resident steps; -1 = finish:",
+              [(k, round(a * 1e3, 2), round(b * 1e3, 2), round(c * 1e3, 2)) for k, a, b, c in trace[-(n_sub + 1) * args.steps:]], file=sys.stderr)
     prof = ctx.profile_get()
     ctx.profile_enable(False)
     n_cand, n_hyp_solved, n_evals, n_evals_exec = ctx.verify_stats(reset=True)
     # the device-event time excludes nothing but host gaps after the last kernel; use the larger of the two clocks
     step_ms = max(ms, wall * 1e3) / args.steps
     value = P_total / (step_ms / 1e3)
+    # per-rank kernel time of the timed steps (load balance of the static split; clocks differ between GPUs under the power cap)
+    kern_ms = sum(v[0] for v in prof.values()) / args.steps
+    per_rank_kernel_ms = [kern_ms]
+    if world > 1:
+        t = torch.tensor([kern_ms], dtype=torch.float64, device="cuda")
+        allk = torch.empty(world, dtype=torch.float64, device="cuda")
+        dist.all_gather_into_tensor(allk, t)
+        per_rank_kernel_ms = [float(x) for x in allk.cpu()]
     stats = None
     if rank == 0:
         h = table.headers
@@ -337,6 +373,7 @@ def run_b200(args):
 
     # ---- the stage after verify() in run_2view (GT metrics + InlierSupportProcessor), timed on its own
     # over the pairs of the last sub-batch: it is not part of BASELINE's metric, so it stays outside `value` / `e2e`
+    bounds = sub_bounds(n_sub)
     a, b = int(bounds[n_sub - 1]), int(bounds[n_sub])
     gt = [scene.relative_pose(int(i), int(j)) for i, j in pairs_g[a:b]]
     gt_R, gt_t = np.stack([g[0] for g in gt]), np.stack([g[1] for g in gt])
@@ -366,7 +403,7 @@ def run_b200(args):
     # ---- end-to-end leg: pinned host buffers -> device -> results on the host, every step
     def e2e_step():
         upload()
-        return compute()
+        return compute(n_sub_e2e)
     for _ in range(min(args.warmup, 1)):
         e2e_step()
     ems, ewall, (_, d2h_bytes) = timed(e2e_step, args.steps)
@@ -414,14 +451,14 @@ def run_b200(args):
                            "l2": "inputs exceed L2 (descriptor store %.0f MB on rank 0)" % (n_img * n_kps * (dim * 7 + 96) / 1e6),
                            "result": "per pair a 128-byte header (R, t, counts, ratio) + v_corr_idxs, %d rows per step, in pinned host memory of rank 0"
                                      % stats["payload_rows"],
-                           "sub_batches_per_step": n_sub,
+                           "sub_batches_per_step": {"resident": n_sub, "e2e": n_sub_e2e},
                            "parallelism": ((f"one pair list dealt over {world} GPUs (shard_pairs), {n_img} of {len(scene.descriptors)} images on rank 0, "
                                             "device-packed result records, one NCCL all-gather per sub-batch") if world > 1 else "1 GPU") if strong else
                                           f"every rank its own scene ({world} GPUs), device-packed result records, one NCCL all-gather per sub-batch"},
                 "roofline": roofline, "cpu_baseline": cpu,
                 "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": int(d2h_bytes)},
                 "gpu_launches": int(launches), "clocks": clk, "device_event_ms_per_step": ms / args.steps,
-                "two_view_report": report_extra, "retriever": retr_extra}
+                "per_rank_kernel_ms_per_step": per_rank_kernel_ms, "two_view_report": report_extra, "retriever": retr_extra}
         print(json.dumps(line), file=_REAL_STDOUT, flush=True)
     ctx.close()
     if world > 1:

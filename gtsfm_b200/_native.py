@@ -22,6 +22,7 @@ EXPORTS = (
     "gtsfm_host_alloc", "gtsfm_host_free", "gtsfm_match_fetch_async", "gtsfm_sync",
     "gtsfm_retriever_similarity", "gtsfm_retriever_topk", "gtsfm_retriever_pairs_noalloc",
     "gtsfm_verify_hypotheses_used", "gtsfm_result_pack", "gtsfm_result_pack_copy", "gtsfm_stream_wait",
+    "gtsfm_images_upload",
 )
 
 OK, E_CUDA, E_ARG, E_NO_DEVICE, E_KNN_UNPACK, E_UNSUPPORTED = range(6)
@@ -92,6 +93,8 @@ def lib() -> ctypes.CDLL:
             L.gtsfm_verify_stats.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_int64), ctypes.c_int]
             L.gtsfm_image_upload.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_int,
                                              ctypes.c_void_p, ctypes.c_void_p]
+            L.gtsfm_images_upload.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int,
+                                              ctypes.c_void_p, ctypes.c_void_p]
             L.gtsfm_image_upload_u8.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_int,
                                                 ctypes.c_void_p, ctypes.c_void_p]
             L.gtsfm_match_pair_u8.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int,
@@ -260,6 +263,29 @@ class Context:
         self._keep += [desc, kps, calv]
         self._check(self._L.gtsfm_image_upload(self._h, int(image_id), _ptr(desc), int(n), int(dim), _ptr(kps), _ptr(calv)))
 
+    def upload_images(self, first_image_id: int, descs, kps=None, cals=None):
+        """A list of float32 descriptor arrays (n_i, dim) [+ (n_i, 2) float64 keypoints, + (f, k1, k2, u0, v0) per image] in one
+        library call (gtsfm_images_upload).  The copies are enqueued on the context's copy stream; the arrays are kept alive
+        until clear()."""
+        descs = [np.ascontiguousarray(d, np.float32) for d in descs]
+        m = len(descs)
+        if m == 0:
+            return
+        dim = int(descs[0].shape[1])
+        if any(d.ndim != 2 or d.shape[1] != dim for d in descs):
+            raise ValueError("descriptors must be (n, dim) arrays of one dimension")
+        n = np.array([d.shape[0] for d in descs], np.int32)
+        dptr = (ctypes.c_void_p * m)(*[d.ctypes.data for d in descs])
+        kptr = None
+        if kps is not None:
+            kps = [np.ascontiguousarray(k, np.float64).reshape(-1, 2) for k in kps]
+            if any(k.shape[0] != d.shape[0] for k, d in zip(kps, descs)):
+                raise ValueError("keypoints and descriptors disagree on n")
+            kptr = (ctypes.c_void_p * m)(*[k.ctypes.data for k in kps])
+        calv = None if cals is None else np.ascontiguousarray(cals, np.float64).reshape(m, 5)
+        self._keep += [descs, kps, calv, n]
+        self._check(self._L.gtsfm_images_upload(self._h, int(first_image_id), m, dptr, _ptr(n), dim, kptr, _ptr(calv)))
+
     def upload_image_u8(self, image_id: int, desc: np.ndarray, kps: Optional[np.ndarray] = None, cal=None):
         """Binary descriptors (n, nbytes) uint8 for the HAMMING distance; kps / cal as in upload_image."""
         if desc is None or np.size(desc) == 0:      # an image without features: its pairs yield np.array([]) (twoway_matcher.py:71-72)
@@ -290,7 +316,7 @@ class Context:
         total = ctypes.c_int64(0)
         r = float("nan") if ratio is None else float(ratio)
         self._check(self._L.gtsfm_match_batch(self._h, _ptr(pairs), P, r, _ptr(counts), ctypes.byref(total)))
-        self._keep.clear()
+        # uploads of images this batch does not name may still be in flight: their host arrays stay referenced until clear()
         if fetch == "async":
             out = self._pinned("matches", (total.value, 2), np.uint32)
             self._check(self._L.gtsfm_match_fetch_async(self._h, _ptr(out)))

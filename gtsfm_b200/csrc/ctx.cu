@@ -1,6 +1,7 @@
 // Context, descriptor store and image upload (C ABI: gtsfm_ctx_*, gtsfm_store_clear, gtsfm_image_upload).
 #include "ctx.h"
 
+#include <algorithm>
 #include <cstring>
 
 namespace g2v {
@@ -125,27 +126,52 @@ static int ensure_maps(gtsfm_ctx* c)
 }
 int store_ensure_maps(gtsfm_ctx* c) { return ensure_maps(c); }
 
-// Read back the per-image flags written by the prepare kernel (integer-valued? number of valid rows).
-int store_sync_flags(gtsfm_ctx* c)
+// Read back the per-image flags written by the prepare kernel (integer-valued? number of valid rows) of images
+// 0..max_image (-1: all): waits for the uploads of those images only.
+int store_sync_flags(gtsfm_ctx* c, int max_image)
 {
-    if (!c->flags_dirty) return GTSFM_OK;
-    const size_t n = c->images.size();
-    std::vector<int> h(kImgFlagInts * n);
-    G2V_CUDA(c, cudaMemcpyAsync(h.data(), c->img_flags.p, kImgFlagInts * n * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    const int n_all = static_cast<int>(c->images.size());
+    const int n = (max_image < 0 || max_image >= n_all) ? n_all : max_image + 1;
+    if (c->flags_synced >= n) return GTSFM_OK;
+    int r = c->wait_images(n - 1, false);
+    if (r) return r;
+    const int first = c->flags_synced;
+    std::vector<int> h(static_cast<size_t>(kImgFlagInts) * (n - first));
+    G2V_CUDA(c, cudaMemcpyAsync(h.data(), c->img_flags.as<int>() + static_cast<size_t>(kImgFlagInts) * first, h.size() * sizeof(int),
+                                cudaMemcpyDeviceToHost, c->stream));
     G2V_CUDA(c, cudaStreamSynchronize(c->stream));
-    for (size_t i = 0; i < n; ++i) {
-        c->images[i].path = (h[kImgFlagInts * i] & 4) ? 3 : (h[kImgFlagInts * i] & 1) ? 1 : 0;
-        c->images[i].f16_ok = (h[kImgFlagInts * i] & 2) ? 0 : 1;
-        c->images[i].n_valid = h[kImgFlagInts * i + 1];
-        std::memcpy(&c->images[i].max_norm2, &h[kImgFlagInts * i + 2], 4);
+    for (int i = first; i < n; ++i) {
+        const int* f = h.data() + static_cast<size_t>(kImgFlagInts) * (i - first);
+        c->images[i].path = (f[0] & 4) ? 3 : (f[0] & 1) ? 1 : 0;
+        c->images[i].f16_ok = (f[0] & 2) ? 0 : 1;
+        c->images[i].n_valid = f[1];
+        std::memcpy(&c->images[i].max_norm2, &f[2], 4);
     }
-    c->flags_dirty = false;
+    c->flags_synced = n;
     return GTSFM_OK;
 }
 
 }  // namespace g2v
 
 using namespace g2v;
+
+int gtsfm_ctx::wait_images(int max_image, bool host)
+{
+    if (max_image < 0 || img_ev.empty()) return GTSFM_OK;
+    if (max_image >= static_cast<int>(images.size())) max_image = static_cast<int>(images.size()) - 1;
+    cudaEvent_t ev = img_ev[max_image];
+    G2V_CUDA(this, cudaStreamWaitEvent(stream, ev, 0));
+    if (host) G2V_CUDA(this, cudaEventSynchronize(ev));
+    return GTSFM_OK;
+}
+
+int gtsfm_ctx::wait_fetch()
+{
+    if (!fetch_pending) return GTSFM_OK;
+    G2V_CUDA(this, cudaEventSynchronize(fetch_ev));
+    fetch_pending = false;
+    return GTSFM_OK;
+}
 
 cudaEvent_t gtsfm_ctx::prof_event()
 {
@@ -190,6 +216,29 @@ g2v::StoreView gtsfm_ctx::view() const
     v.dim = dim;
     v.kpad = kpad;
     return v;
+}
+
+// The flag array grows rarely; growth copies it on `stream`, so nothing may be writing it on the copy stream meanwhile.
+static int reserve_img_flags(gtsfm_ctx* c)
+{
+    const size_t need = (c->images.size() + 1) * kImgFlagInts * sizeof(int);
+    if (need <= c->img_flags.cap) return GTSFM_OK;
+    G2V_CUDA(c, cudaStreamSynchronize(c->copy_stream));
+    G2V_CUDA(c, c->img_flags.reserve(std::max<size_t>(need, 4 * c->img_flags.cap), true, c->stream));
+    return GTSFM_OK;
+}
+
+// img_ev[image] is recorded behind everything the upload of the newest image enqueued on `s`.
+static int record_image_event(gtsfm_ctx* c, cudaStream_t s)
+{
+    const size_t i = c->images.size() - 1;
+    while (c->img_ev.size() <= i) {
+        cudaEvent_t e = nullptr;
+        G2V_CUDA(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        c->img_ev.push_back(e);
+    }
+    G2V_CUDA(c, cudaEventRecord(c->img_ev[i], s));
+    return GTSFM_OK;
 }
 
 extern "C" {
@@ -242,6 +291,8 @@ void gtsfm_ctx_destroy(gtsfm_ctx* c)
     if (c->match_done) cudaEventDestroy(c->match_done);
     if (c->upload_ev) cudaEventDestroy(c->upload_ev);
     if (c->xs_ev) cudaEventDestroy(c->xs_ev);
+    if (c->fetch_ev) cudaEventDestroy(c->fetch_ev);
+    for (cudaEvent_t e : c->img_ev) cudaEventDestroy(e);
     cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -313,6 +364,7 @@ int gtsfm_store_clear(gtsfm_ctx* c)
     c->kpad = 0;
     c->binary = -1;
     c->flags_dirty = false;
+    c->flags_synced = 0;
     c->maps_valid = false;
     c->batch_n = 0;
     c->batch_total = 0;
@@ -353,21 +405,21 @@ int gtsfm_image_upload(gtsfm_ctx* c, int image_id, const float* desc, int n, int
     if (c->dim == 0 && kps && n > 0) { c->dim = 1; c->kpad = 64; c->rows_cap = 0; }
     const int n_rows = ((rec.n > rec.n_kps ? rec.n : rec.n_kps) + kRowPad - 1) / kRowPad * kRowPad;
     rec.n_pad = n_rows;
-    G2V_CUDA(c, c->img_flags.reserve((c->images.size() + 1) * kImgFlagInts * sizeof(int), true, c->stream));
-    G2V_CUDA(c, cudaMemsetAsync(c->img_flags.as<int>() + kImgFlagInts * c->images.size(), 0, kImgFlagInts * sizeof(int), c->stream));
+    int rr = reserve_img_flags(c);
+    if (rr) return rr;
+    G2V_CUDA(c, cudaMemsetAsync(c->img_flags.as<int>() + kImgFlagInts * c->images.size(), 0, kImgFlagInts * sizeof(int), c->copy_stream));
     if (n_rows > 0) {
         int r = store_reserve_rows(c, c->rows_used + n_rows);
         if (r) return r;
     }
     if (rec.n > 0) {
         float* dst = c->desc_f32.as<float>() + static_cast<long long>(rec.row0) * c->dim;
-        // H2D on the copy stream, so that the copy of image i + 1 overlaps the prepare kernel of image i; `stream` waits for
-        // this image's copies only (one event, re-recorded per image: a wait refers to the record that precedes it)
+        // H2D copy AND the prepare kernel on the copy stream: `stream` is not involved, so the kernels of a batch that does not
+        // name this image run while it is still arriving (gtsfm_match_batch / gtsfm_verify_batch wait for the event of the
+        // last image they name)
         G2V_CUDA(c, cudaMemcpyAsync(dst, desc, static_cast<size_t>(rec.n) * c->dim * 4, cudaMemcpyHostToDevice, c->copy_stream));
         if (kps)
             G2V_CUDA(c, cudaMemcpyAsync(c->kps.as<double2>() + rec.row0, kps, static_cast<size_t>(n) * 16, cudaMemcpyHostToDevice, c->copy_stream));
-        G2V_CUDA(c, cudaEventRecord(c->upload_ev, c->copy_stream));
-        G2V_CUDA(c, cudaStreamWaitEvent(c->stream, c->upload_ev, 0));
         PrepareArgs a;
         a.src = dst;
         a.bf = c->desc_bf16.as<__nv_bfloat16>() + static_cast<long long>(rec.row0) * c->kpad;
@@ -382,16 +434,33 @@ int gtsfm_image_upload(gtsfm_ctx* c, int image_id, const float* desc, int n, int
         a.augt_h = c->augt_h.as<__half>() + static_cast<long long>(rec.row0) * kAugK;
         a.norm_f = c->norm_f.as<float>() + rec.row0;
         a.n = rec.n; a.n_pad = rec.n_pad; a.dim = c->dim; a.kpad = c->kpad;
-        c->prof_begin(P_PREPARE);
-        G2V_CUDA(c, launch_prepare(a, c->stream));
-        c->prof_end();
+        G2V_CUDA(c, launch_prepare(a, c->copy_stream));
         ++c->launches;
         c->flags_dirty = true;
     }
     if (kps && n > 0 && rec.n == 0)         // keypoint-only image (the other case copied them above)
-        G2V_CUDA(c, cudaMemcpyAsync(c->kps.as<double2>() + rec.row0, kps, static_cast<size_t>(n) * 16, cudaMemcpyHostToDevice, c->stream));
+        G2V_CUDA(c, cudaMemcpyAsync(c->kps.as<double2>() + rec.row0, kps, static_cast<size_t>(n) * 16, cudaMemcpyHostToDevice, c->copy_stream));
     c->images.push_back(rec);
     c->rows_used += n_rows;
+    return record_image_event(c, c->copy_stream);
+}
+
+int gtsfm_images_upload(gtsfm_ctx* c, int first_image_id, int n_images, const float* const* desc, const int32_t* n, int dim,
+                        const double* const* kps, const double* cal)
+{
+    if (!c || n_images < 0 || (n_images > 0 && (!desc || !n))) return fail(c, GTSFM_E_ARG, "bad arguments");
+    cudaSetDevice(c->device);
+    // one growth of the store for the whole list instead of a doubling (copy + synchronise) every few images
+    if (dim > 0 && (c->dim == 0 || c->dim == dim) && c->binary != 1 && dim <= 4096) {
+        long long rows = c->rows_used;
+        for (int i = 0; i < n_images; ++i) rows += (static_cast<long long>(n[i] > 0 ? n[i] : 0) + kRowPad - 1) / kRowPad * kRowPad;
+        if (c->dim == 0) { if (c->rows_used == 0) { c->dim = dim; c->kpad = (dim + 63) / 64 * 64; c->rows_cap = 0; } }
+        if (c->dim == dim) { int r = store_reserve_rows(c, rows); if (r) return r; }
+    }
+    for (int i = 0; i < n_images; ++i) {
+        int r = gtsfm_image_upload(c, first_image_id + i, desc[i], n[i], dim, kps ? kps[i] : nullptr, cal ? cal + 5 * i : nullptr);
+        if (r) return r;
+    }
     return GTSFM_OK;
 }
 
@@ -408,11 +477,11 @@ int gtsfm_image_upload_u8(gtsfm_ctx* c, int image_id, const uint8_t* desc, int n
         rec.row0 = static_cast<int>(c->rows_used);
         rec.path = 3; rec.dim = nbytes > 0 ? nbytes : 0;
         if (cal) std::memcpy(rec.cal, cal, sizeof(rec.cal)); else { rec.cal[0] = 1; rec.cal[1] = rec.cal[2] = rec.cal[3] = rec.cal[4] = 0; }
-        G2V_CUDA(c, c->img_flags.reserve((c->images.size() + 1) * kImgFlagInts * sizeof(int), true, c->stream));
+        { int rr = reserve_img_flags(c); if (rr) return rr; }
         const int flags0[kImgFlagInts] = {4, 0, 0, 0};
         G2V_CUDA(c, cudaMemcpyAsync(c->img_flags.as<int>() + kImgFlagInts * c->images.size(), flags0, sizeof(flags0), cudaMemcpyHostToDevice, c->stream));
         c->images.push_back(rec);
-        return GTSFM_OK;
+        return record_image_event(c, c->stream);
     }
     if (nbytes > 64) return fail(c, GTSFM_E_UNSUPPORTED, "binary descriptors above 64 bytes");
     if (c->binary == 0) return fail(c, GTSFM_E_ARG, "this store holds float32 (EUCLIDEAN) descriptors");
@@ -427,7 +496,7 @@ int gtsfm_image_upload_u8(gtsfm_ctx* c, int image_id, const uint8_t* desc, int n
     rec.n = n; rec.n_kps = kps ? n : 0; rec.dim = nbytes; rec.path = 3; rec.n_valid = n; rec.has_kps = kps != nullptr;
     if (cal) std::memcpy(rec.cal, cal, sizeof(rec.cal)); else { rec.cal[0] = 1; rec.cal[1] = rec.cal[2] = rec.cal[3] = rec.cal[4] = 0; }
     rec.n_pad = (n + kRowPad - 1) / kRowPad * kRowPad;
-    G2V_CUDA(c, c->img_flags.reserve((c->images.size() + 1) * kImgFlagInts * sizeof(int), true, c->stream));
+    { int rr = reserve_img_flags(c); if (rr) return rr; }
     const int flags[kImgFlagInts] = {4, n, 0, 0};             // bit 2: binary image; number of valid rows (uint8 has no NaN)
     G2V_CUDA(c, cudaMemcpyAsync(c->img_flags.as<int>() + kImgFlagInts * c->images.size(), flags, sizeof(flags), cudaMemcpyHostToDevice, c->stream));
     if (rec.n_pad > 0) {
@@ -443,7 +512,7 @@ int gtsfm_image_upload_u8(gtsfm_ctx* c, int image_id, const uint8_t* desc, int n
         G2V_CUDA(c, cudaMemcpyAsync(c->kps.as<double2>() + rec.row0, kps, static_cast<size_t>(n) * 16, cudaMemcpyHostToDevice, c->stream));
     c->images.push_back(rec);
     c->rows_used += rec.n_pad;
-    return GTSFM_OK;
+    return record_image_event(c, c->stream);
 }
 
 int gtsfm_host_alloc(void** p, int64_t bytes)

@@ -38,7 +38,11 @@ struct gtsfm_ctx {
     cudaStream_t stream = nullptr;
     cudaStream_t copy_stream = nullptr;     // device -> host copies that overlap the next kernels (gtsfm_match_fetch_async)
     cudaEvent_t match_done = nullptr;       // recorded on `stream` when the compacted matches of a batch are complete
-    cudaEvent_t upload_ev = nullptr;        // image uploads: H2D copies run on copy_stream, `stream` waits for them per image
+    cudaEvent_t upload_ev = nullptr;        // store_clear: copy_stream waits for the kernels that may still read the old rows
+    // Image uploads (H2D copy + prepare kernel) run on copy_stream; img_ev[i] is recorded behind image i.  copy_stream is in
+    // order, so a batch waits for the event of the LAST image it names and starts while later images are still arriving.
+    std::vector<cudaEvent_t> img_ev;
+    int wait_images(int max_image, bool host);   // `stream` (and the host) wait for the uploads of images 0..max_image
     std::string err;
     int64_t launches = 0;
     int64_t workspace_bytes = 12ll << 30;
@@ -49,6 +53,7 @@ struct gtsfm_ctx {
     long long rows_used = 0, rows_cap = 0;
     std::vector<g2v::ImageRec> images;
     bool flags_dirty = false;
+    int flags_synced = 0;               // images whose prepare-kernel flags have been read back
     g2v::DevBuf desc_bf16, desc_u8, desc_f32, augq, augt, norm_i, valid, kps, img_flags, stage;
     g2v::DevBuf desc_h16, augq_h, augt_h, norm_f;     // float path: fp16 operands of the screening GEMM, float32 squared norms
     CUtensorMap tm_desc{}, tm_augq{}, tm_augt{};
@@ -86,6 +91,9 @@ struct gtsfm_ctx {
     int verify_n = 0;
     int pack_n = 0;                          // pairs / payload rows of the last gtsfm_result_pack
     long long pack_rows = 0;
+    cudaEvent_t fetch_ev = nullptr;          // recorded behind the copy of gtsfm_match_fetch_async (which reads match_out)
+    bool fetch_pending = false;
+    int wait_fetch();                        // host waits for that copy only (not for the uploads queued behind it)
     cudaEvent_t xs_ev = nullptr;             // gtsfm_stream_wait: ordering against a caller's stream
     std::vector<int> verify_hyp;            // hypotheses evaluated per pair of the last verify batch (adaptive F mode)
     long long verify_total = 0;
@@ -107,6 +115,6 @@ int cuda_fail(gtsfm_ctx* c, cudaError_t e, const char* what);
     } while (0)
 
 int store_reserve_rows(gtsfm_ctx* c, long long rows);
-int store_sync_flags(gtsfm_ctx* c);
+int store_sync_flags(gtsfm_ctx* c, int max_image = -1);
 enum ProfSlot { P_PREPARE = 0, P_SCREEN, P_RESOLVE_ROWS, P_RESOLVE_COLS, P_EXACT_SCAN, P_MATCH_FINALIZE, P_GATHER, P_SOLVE, P_SCORE, P_VFINALIZE, P_NSLOTS };
 }  // namespace g2v

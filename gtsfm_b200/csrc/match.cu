@@ -2,6 +2,7 @@
 // Replaces the one-Dask-task-per-pair loop of
 // gtsfm/frontend/correspondence_generator/det_desc_correspondence_generator.py:71-81 with chunks of pairs that run as
 // a handful of kernels on one stream; nothing returns to the host between the kernels of a chunk.
+#include <algorithm>
 #include <cmath>
 #include <cstring>
 
@@ -49,13 +50,22 @@ int gtsfm_match_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, double ra
     if (!c || n_pairs < 0 || (n_pairs > 0 && !pairs)) return fail(c, GTSFM_E_ARG, "bad pair list");
     cudaSetDevice(c->device);
     const int use_ratio = std::isnan(ratio) ? 0 : 1;
-    int r = store_sync_flags(c);
+    const int n_img_all = static_cast<int>(c->images.size());
+    int max_image = -1;
+    for (int p = 0; p < n_pairs; ++p) {
+        const int a = pairs[2 * p], b = pairs[2 * p + 1];
+        if (a < 0 || b < 0 || a >= n_img_all || b >= n_img_all) return fail(c, GTSFM_E_ARG, "pair " + std::to_string(p) + " names an image that was not uploaded");
+        max_image = std::max(max_image, std::max(a, b));
+    }
+    // uploads run on the copy stream: wait (stream and host) for the last image this batch names, not for later ones
+    int r = store_sync_flags(c, max_image);
     if (r) return r;
+    if ((r = c->wait_images(max_image, false))) return r;
     c->batch_n = 0;
     c->batch_total = 0;
     c->verify_n = 0;          // the device match rows of the last verify batch are about to be overwritten
     if (total) *total = 0;
-    G2V_CUDA(c, cudaStreamSynchronize(c->copy_stream));      // an asynchronous fetch of the previous batch may still read match_out
+    if ((r = c->wait_fetch())) return r;                     // an asynchronous fetch of the previous batch may still read match_out
     if (n_pairs == 0) return GTSFM_OK;
     const int n_img = static_cast<int>(c->images.size());
 
@@ -273,6 +283,9 @@ int gtsfm_match_fetch_async(gtsfm_ctx* c, uint32_t* out)
     if (!out) return fail(c, GTSFM_E_ARG, "out is NULL");
     G2V_CUDA(c, cudaStreamWaitEvent(c->copy_stream, c->match_done, 0));
     G2V_CUDA(c, cudaMemcpyAsync(out, c->match_out.p, 8 * static_cast<size_t>(c->batch_total), cudaMemcpyDeviceToHost, c->copy_stream));
+    if (!c->fetch_ev) G2V_CUDA(c, cudaEventCreateWithFlags(&c->fetch_ev, cudaEventDisableTiming));
+    G2V_CUDA(c, cudaEventRecord(c->fetch_ev, c->copy_stream));
+    c->fetch_pending = true;
     return GTSFM_OK;
 }
 

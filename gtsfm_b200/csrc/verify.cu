@@ -146,7 +146,7 @@ int gtsfm_verify_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, const ui
         }
     } else {
         if (!match_offsets) return fail(c, GTSFM_E_ARG, "match_offsets is NULL");
-        G2V_CUDA(c, cudaStreamSynchronize(c->copy_stream));
+        if ((r = c->wait_fetch())) return r;                 // match_out is about to be overwritten
         for (int p = 0; p <= n_pairs; ++p) off[p] = match_offsets[p];
         for (int p = 0; p < n_pairs; ++p) if (off[p + 1] < off[p]) return fail(c, GTSFM_E_ARG, "match_offsets must be non-decreasing");
         if (off[n_pairs] > 0 && !match_idx) return fail(c, GTSFM_E_ARG, "match_idx is NULL");
@@ -160,6 +160,11 @@ int gtsfm_verify_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, const ui
     // ---- per-pair records
     std::vector<VPair> vps(n_pairs);
     int max_m = 0;
+    {
+        int max_image = -1;
+        for (int p = 0; p < n_pairs; ++p) max_image = std::max(max_image, std::max(pairs[2 * p], pairs[2 * p + 1]));
+        if ((r = c->wait_images(max_image, false))) return r;        // keypoint uploads run on the copy stream
+    }
     for (int p = 0; p < n_pairs; ++p) {
         const int a = pairs[2 * p], b = pairs[2 * p + 1];
         if (a < 0 || b < 0 || a >= n_img || b >= n_img) return fail(c, GTSFM_E_ARG, "pair names an image that was not uploaded");

@@ -218,25 +218,50 @@ def block_bytes(hdr: np.ndarray, payload: np.ndarray, max_pairs: int, max_rows: 
     return buf
 
 
-@dataclass
 class GatheredTwoViewResults:
-    """The result table of a whole job after the exchange: headers in GLOBAL pair order, payload kept per rank (views into
-    the receive buffer: no second copy of up to gigabytes of indices)."""
-    headers: np.ndarray                   # (P_total,) HEADER_DTYPE, row = global pair id; pairs nobody reported have pair_id -1
-    _payload: List[np.ndarray]            # per rank (rows_r, 2) uint32
-    _where: np.ndarray                    # (P_total, 2) int64: rank and first payload row of every pair
+    """The result table of a whole job after the exchange.  It keeps the received blocks as they are -- per (sub-batch, rank)
+    a header view and a payload view into the pinned receive buffer, no copy of up to gigabytes of indices -- and builds the
+    global-order header table and the pair -> (block, first payload row) index on first use, so that finishing an exchange
+    costs no host work proportional to the job."""
+
+    def __init__(self, blocks: List[Tuple[np.ndarray, np.ndarray]], n_global: int):
+        self._blocks = blocks                 # [(headers (n,) HEADER_DTYPE, payload (rows, 2) uint32)]
+        self.n_global = int(n_global)
+        self._headers = None
+        self._where = None
+
+    def _index(self):
+        if self._headers is None:
+            headers = np.zeros(self.n_global, HEADER_DTYPE)
+            headers["pair_id"] = -1                     # pairs nobody reported
+            where = np.zeros((self.n_global, 2), np.int64)
+            for k, (h, _) in enumerate(self._blocks):
+                if len(h) == 0:
+                    continue
+                ids = h["pair_id"]
+                headers[ids] = h
+                where[ids, 0] = k
+                where[ids, 1] = np.concatenate([[0], np.cumsum(h["n_inliers"][:-1], dtype=np.int64)])
+            self._headers, self._where = headers, where
+        return self._headers, self._where
+
+    @property
+    def headers(self) -> np.ndarray:
+        """(P_total,) HEADER_DTYPE, row = global pair id; pair_id -1 where no rank reported the pair."""
+        return self._index()[0]
 
     def v_corr_idxs(self, pair_id: int) -> np.ndarray:
-        h = self.headers[pair_id]
-        r, o = self._where[pair_id]
-        return self._payload[int(r)][int(o): int(o) + int(h["n_inliers"])]
+        headers, where = self._index()
+        k, o = where[pair_id]
+        return self._blocks[int(k)][1][int(o): int(o) + int(headers[pair_id]["n_inliers"])]
 
     def two_view_dicts(self, pairs: np.ndarray):
         """(i2Ri1_dict, i2Ui1_dict, v_corr_idxs_dict, inlier_ratio_dict) in the reference's conventions; failed pairs carry
         (None, None, empty uint64, 0.0) like VerifierBase's failure tuple (verifier_base.py:56)."""
+        headers, _ = self._index()
         Rd, td, vd, rd = {}, {}, {}, {}
         for g, (a, b) in enumerate(np.asarray(pairs).reshape(-1, 2)):
-            key, h = (int(a), int(b)), self.headers[g]
+            key, h = (int(a), int(b)), headers[g]
             if h["pair_id"] < 0 or h["status"] != 0:
                 Rd[key], td[key], vd[key], rd[key] = None, None, np.array([], dtype=np.uint64), 0.0
                 continue
@@ -246,22 +271,13 @@ class GatheredTwoViewResults:
 
 
 def unpack_blocks(buf: np.ndarray, counts: np.ndarray, n_global: int) -> GatheredTwoViewResults:
-    """buf: (world, block size) uint8 as received; counts: (world, 2) [pairs, payload rows] per rank."""
-    world = buf.shape[0]
+    """buf: (world, block size) uint8 as received; counts: (world, 2) [pairs, payload rows] per rank.  Views only."""
     off, _ = block_layout(counts[:, 0].max(), counts[:, 1].max())
-    headers = np.zeros(n_global, HEADER_DTYPE)
-    headers["pair_id"] = -1
-    where = np.zeros((n_global, 2), np.int64)
-    payloads = []
-    for r in range(world):
+    blocks = []
+    for r in range(buf.shape[0]):
         n, rows = int(counts[r, 0]), int(counts[r, 1])
-        h = buf[r, : HEADER_BYTES * n].view(HEADER_DTYPE)
-        payloads.append(buf[r, off: off + 8 * rows].view(np.uint32).reshape(-1, 2))
-        ids = h["pair_id"]
-        headers[ids] = h
-        where[ids, 0] = r
-        where[ids, 1] = np.concatenate([[0], np.cumsum(h["n_inliers"][:-1], dtype=np.int64)]) if n else np.zeros(0, np.int64)
-    return GatheredTwoViewResults(headers, payloads, where)
+        blocks.append((buf[r, : HEADER_BYTES * n].view(HEADER_DTYPE), buf[r, off: off + 8 * rows].view(np.uint32).reshape(-1, 2)))
+    return GatheredTwoViewResults(blocks, n_global)
 
 
 def _all_gather_bytes(block, dist, world: int):
@@ -355,14 +371,5 @@ class ResultExchange:
 
 
 def merge_gathered(parts: Sequence[GatheredTwoViewResults]) -> GatheredTwoViewResults:
-    """Sub-batches of one job (disjoint pair ids) -> one table."""
-    headers = parts[0].headers.copy()
-    where = parts[0]._where.copy()
-    payloads = list(parts[0]._payload)
-    for part in parts[1:]:
-        have = part.headers["pair_id"] >= 0
-        headers[have] = part.headers[have]
-        where[have, 0] = part._where[have, 0] + len(payloads)
-        where[have, 1] = part._where[have, 1]
-        payloads += list(part._payload)
-    return GatheredTwoViewResults(headers, payloads, where)
+    """Sub-batches of one job (disjoint pair ids) -> one table (the blocks are shared, nothing is copied)."""
+    return GatheredTwoViewResults([b for part in parts for b in part._blocks], parts[0].n_global)

@@ -78,6 +78,13 @@ int gtsfm_store_clear(gtsfm_ctx* ctx);
  *   cal   {f, k1, k2, u0, v0} of the image's Cal3Bundler or NULL */
 int gtsfm_image_upload(gtsfm_ctx* ctx, int image_id, const float* desc, int n, int dim, const double* kps, const double* cal);
 
+/* A list of images in one call (ids first_image_id, first_image_id + 1, ...): desc[i] (n[i], dim) float32, kps[i] (n[i], 2)
+ * float64 (kps NULL, or kps[i] NULL: no keypoints), cal (n_images, 5) or NULL.  Same as n_images calls of gtsfm_image_upload
+ * without their per-call overhead; the copies are only ENQUEUED (on the context's copy stream), so the host arrays must stay
+ * valid until the next synchronising call (gtsfm_sync, or the batch calls for the images they name). */
+int gtsfm_images_upload(gtsfm_ctx* ctx, int first_image_id, int n_images, const float* const* desc, const int32_t* n, int dim,
+                        const double* const* kps, const double* cal);
+
 /* Binary descriptors for TwoWayMatcher(distance_type=HAMMING) (twoway_matcher.py:17-21,95-98): desc (n, nbytes) uint8 rows,
  * nbytes <= 64.  A store holds either float32 or binary descriptors; gtsfm_match_batch picks the distance accordingly. */
 int gtsfm_image_upload_u8(gtsfm_ctx* ctx, int image_id, const uint8_t* desc, int n, int nbytes, const double* kps, const double* cal);
