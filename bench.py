@@ -192,15 +192,48 @@ def cpu_baseline_sample(scene, cfg):
     from oracle import ref_cv2
     cores = len(os.sched_getaffinity(0))
     n = min(len(scene.pairs), 2 * cores)
-    pool = ref_cv2.PairPool(scene, cores)
+    pool = ref_cv2.PairPool(scene, cores, keep_poses=True)
     ids = np.random.default_rng(1).choice(len(scene.pairs), n, replace=False)
     pool.run(ids[:cores])                      # warm the workers (fork, cv2 import)
     t0 = time.perf_counter()
-    pool.run(ids)
+    res = pool.run(ids)
     dt = time.perf_counter() - t0
     pool.close()
     return {"value": n / dt, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": f"{n} random pairs of the same workload, one task per pair on {cores} single-threaded cv2 workers ({dt:.1f} s)"}
+            "sample": f"{n} random pairs of the same workload, one task per pair on {cores} single-threaded cv2 workers ({dt:.1f} s)"}, (ids, res)
+
+
+def agreement_vs_cv2(table, sample, scene=None):
+    """agreement of the device verifier with black-box cv2 (USAC_ACCURATE / FM_RANSAC) on the sampled pairs, as
+    a distribution: rotation / translation-direction angle between the two poses, IoU of the two verified-correspondence sets."""
+    ids, res = sample
+    r_deg, t_deg, iou = [], [], []
+    gt = {"device_R": [], "device_t": [], "cv2_R": [], "cv2_t": []}
+    ang = lambda A, B: float(np.degrees(np.arccos(np.clip((np.trace(A.T @ B) - 1) / 2, -1, 1))))
+    dirang = lambda a, b: float(np.degrees(np.arccos(np.clip(a @ b / np.linalg.norm(a) / np.linalg.norm(b), -1, 1))))
+    for g, out in zip(ids, res):
+        if len(out) < 5 or out[2] is None:
+            continue
+        h = table.headers[int(g)]
+        if h["status"] != 0:
+            continue
+        R, t = h["R"].reshape(3, 3), h["t"]
+        r_deg.append(float(np.degrees(np.arccos(np.clip((np.trace(R.T @ out[2]) - 1) / 2, -1, 1)))))
+        t_deg.append(float(np.degrees(np.arccos(np.clip(t @ out[3] / np.linalg.norm(out[3]), -1, 1)))))
+        a = set(map(tuple, table.v_corr_idxs(int(g)).tolist()))
+        b = set(map(tuple, out[4].tolist()))
+        iou.append(len(a & b) / max(len(a | b), 1))
+        if scene is not None:          # both against the synthetic scene's ground truth: which of the two is off when they disagree
+            Rg, tg = scene.relative_pose(int(scene.pairs[int(g)][0]), int(scene.pairs[int(g)][1]))
+            gt["device_R"].append(ang(R, Rg)); gt["device_t"].append(dirang(t, tg))
+            gt["cv2_R"].append(ang(out[2], Rg)); gt["cv2_t"].append(dirang(out[3], tg))
+    if not r_deg:
+        return None
+    q = lambda v, p: float(np.percentile(v, p))
+    return {"pairs": len(r_deg), "R_deg": {"median": q(r_deg, 50), "p95": q(r_deg, 95), "max": max(r_deg)},
+            "t_deg": {"median": q(t_deg, 50), "p95": q(t_deg, 95), "max": max(t_deg)},
+            "inlier_set_iou": {"median": q(iou, 50), "p5": q(iou, 5), "min": min(iou)},
+            "vs_ground_truth_deg": {k: {"median": q(v, 50), "p95": q(v, 95)} for k, v in gt.items() if v}}
 
 
 def run_b200(args):
@@ -241,9 +274,9 @@ def run_b200(args):
     P = len(pairs)
     n_img = len(used)
     # CPU baseline first: the worker pool is forked before this process creates its CUDA context
-    cpu = None
+    cpu, cpu_sample = None, None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        cpu = cpu_baseline_sample(scene, cfg)
+        cpu, cpu_sample = cpu_baseline_sample(scene, cfg)
     ctx = gtsfm_b200.Context(local)
     ctx.set_float_screening(args.float_screening == "on")
     if args.workspace_gib > 0:
@@ -370,6 +403,8 @@ def run_b200(args):
         for g in (0, P_total // 2, P_total - 1):
             v = table.v_corr_idxs(g)
             assert len(v) == h["n_inliers"][g] and (len(v) == 0 or int(v.max()) < cfg["n_kps"])
+        if cpu_sample is not None:
+            stats["agreement_vs_cv2"] = agreement_vs_cv2(table, cpu_sample, scene)
 
     # ---- the stage after verify() in run_2view (GT metrics + InlierSupportProcessor), timed on its own
     # over the pairs of the last sub-batch: it is not part of BASELINE's metric, so it stays outside `value` / `e2e`
@@ -458,7 +493,7 @@ def run_b200(args):
                 "roofline": roofline, "cpu_baseline": cpu,
                 "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": int(d2h_bytes)},
                 "gpu_launches": int(launches), "clocks": clk, "device_event_ms_per_step": ms / args.steps,
-                "per_rank_kernel_ms_per_step": per_rank_kernel_ms, "two_view_report": report_extra, "retriever": retr_extra}
+                "agreement_vs_cv2": stats.get("agreement_vs_cv2"), "per_rank_kernel_ms_per_step": per_rank_kernel_ms, "two_view_report": report_extra, "retriever": retr_extra}
         print(json.dumps(line), file=_REAL_STDOUT, flush=True)
     ctx.close()
     if world > 1:

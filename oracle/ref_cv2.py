@@ -101,13 +101,15 @@ def verify_pair(kp1: np.ndarray, kp2: np.ndarray, match_indices: np.ndarray, cal
 
 
 _SCENE = None
+_KEEP_POSES = False
 
 
-def _init_worker(scene):
-    global _SCENE
+def _init_worker(scene, keep_poses=False):
+    global _SCENE, _KEEP_POSES
     import cv2
     cv2.setNumThreads(1)
     _SCENE = scene
+    _KEEP_POSES = keep_poses
 
 
 def _task(p: int):
@@ -118,16 +120,19 @@ def _task(p: int):
         return 0, 0
     fn = verify_pair_F if getattr(s, "fundamental", False) else verify_pair
     R, t, v, ratio = fn(s.keypoints[i], s.keypoints[j], m, s.cal, s.cal, s.threshold_px)
+    if _KEEP_POSES:                    # bench.py's agreement report: cv2's pose and inlier set of the sampled pair
+        return len(m), len(v), R, t, np.asarray(v, np.uint32).reshape(-1, 2)
     return len(m), len(v)
 
 
 class PairPool:
     """One task per pair on n_workers single-threaded processes (the reference's Dask LocalCluster granularity)."""
 
-    def __init__(self, scene, n_workers: Optional[int] = None):
+    def __init__(self, scene, n_workers: Optional[int] = None, keep_poses: bool = False):
         self.n_workers = n_workers or len(os.sched_getaffinity(0))
         import multiprocessing as mp
-        self._ex = ProcessPoolExecutor(self.n_workers, mp_context=mp.get_context("fork"), initializer=_init_worker, initargs=(scene,))
+        self._ex = ProcessPoolExecutor(self.n_workers, mp_context=mp.get_context("fork"), initializer=_init_worker,
+                                       initargs=(scene, keep_poses))
 
     def run(self, pair_ids):
         return list(self._ex.map(_task, [int(p) for p in pair_ids]))
