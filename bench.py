@@ -58,14 +58,16 @@ def parse_args():
 
 
 def load_traffic(args, cfg):
-    """dram__bytes_read.sum + dram__bytes_write.sum of one match_screen_kernel launch, from the committed
-    `ncu --set full` capture of this same workload (profiles/r1_screen_ncu.json); None for any other workload."""
-    path = os.path.join(ROOT, "profiles", "r1_screen_ncu.json")
-    if args.images or args.kps or args.config != "C2" or not os.path.exists(path):
-        return None
-    with open(path) as f:
+    """dram__bytes_read.sum + dram__bytes_write.sum of one match_screen_kernel launch (one full workspace chunk), from the committed
+    `ncu --set full` capture of this same workload: profiles/r2_screen_ncu.json (C3, 512 pairs per launch) or
+    profiles/r1_screen_ncu.json (C2, 450 pairs); None for any other workload.  Returns (bytes, provenance)."""
+    name = {"C3": "r2_screen_ncu.json", "C2": "r1_screen_ncu.json"}.get(args.config)
+    if args.images or args.kps or name is None or not os.path.exists(os.path.join(ROOT, "profiles", name)):
+        return None, None
+    with open(os.path.join(ROOT, "profiles", name)) as f:
         rec = json.load(f)
-    return rec.get("dram_bytes_per_launch")
+    src = f"profiles/{name}: {rec.get('pairs_per_launch', 450)} pairs per launch, captured at commit {rec.get('commit', 'baca470 (round 1)')}"
+    return rec.get("dram_bytes_per_launch"), src
 
 
 def load_peaks():
@@ -476,7 +478,7 @@ def run_b200(args):
                                "executed_evaluations_per_step": n_evals_exec / args.steps,
                                "executed_tflops": 34.0 * n_evals_exec / (sc_ms * 1e-3) / 1e12 if sc_ms > 0 else 0.0, "candidates_per_hypothesis": n_cand / max(n_hyp_solved, 1),
                                "share_of_step": sc_ms / total_kernel_ms if total_kernel_ms else None}
-        roofline["traffic"] = load_traffic(args, cfg)
+        roofline["traffic"], roofline["traffic_source"] = load_traffic(args, cfg)
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": step_ms, "higher_is_better": True, "scaling": "strong" if strong else "weak", "vs_baseline": None, "dtype": "bf16 GEMM / f32 scoring / f64 finalize",
                 "data": "reference fixture (Lund door SIFT features)" if args.config == "C1" else "synthetic",
