@@ -51,6 +51,7 @@ def parse_args():
                          "the images its shard names; weak = every rank its own scene of the configured size")
     ap.add_argument("--sub-batches", type=int, default=0,
                     help="sub-batches per step whose result exchange overlaps the next sub-batch's kernels (0 = 1 on one GPU, 4 otherwise)")
+    ap.add_argument("--ratio", type=float, default=None, help="override the config's ratio-test threshold (e.g. C4 with the ratio test on)")
     ap.add_argument("--workspace-gib", type=float, default=0.0, help="matcher / verifier work-buffer budget per chunk (0 = library default)")
     ap.add_argument("--float-screening", default="on", choices=["on", "off"],
                     help="float descriptors, ratio test off (C4): fp16 tensor-core screening (default) or the exhaustive fp32 kernel")
@@ -139,6 +140,8 @@ def make_scene(args, rank: int, shard=None):
         only = np.unique(all_pairs[shard_pairs(all_pairs, shard[1])[shard[0]]])
     scene = synthetic.make_scene(**cfg, only_images=only)
     scene.fundamental = args.verifier == "fundamental"
+    if args.ratio is not None:
+        scene.ratio = args.ratio
     return scene, cfg
 
 
@@ -146,6 +149,8 @@ def workload_name(args, cfg, n_pairs):
     s = f"{args.config}: {'reference fixture' if args.config == 'C1' else 'synthetic'} {cfg['n_images']} images x {cfg['n_kps']} {cfg['kind']}-{cfg['dim']} keypoints, {n_pairs} pairs ({cfg['pairs']})"
     if args.verifier == "fundamental":
         s += " [verifier in fundamental-matrix mode - not the BASELINE configuration]"
+    if args.ratio is not None:
+        s += f" [ratio test {args.ratio} - not the BASELINE configuration]"
     if args.images or args.kps:
         s += " [SHRUNK - not the BASELINE configuration]"
     return s

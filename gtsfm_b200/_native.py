@@ -488,6 +488,7 @@ def ransac_samples(seed: int, pair_key: int, n_matches: int, n_hyp: int, sample_
     return out
 
 
+DEFAULT_PLUGIN_WORKSPACE_GIB = 4.0
 _default_tls = threading.local()
 
 
@@ -502,5 +503,10 @@ def default_context(device: int = 0) -> Context:
         table = _default_tls.ctx = {}
     key = (os.getpid(), int(device))
     if key not in table:
-        table[key] = Context(device)
+        ctx = Context(device)
+        # The library sizes its per-chunk work buffers by this budget (they grow on demand up to it and are kept).  Contexts of
+        # this kind exist once per worker THREAD, so the plugin default is 4 GiB instead of the library's 12 GiB; a smaller
+        # budget only means more, smaller chunks.  GTSFM_B200_WORKSPACE_GIB overrides it.
+        ctx.set_workspace(int(float(os.environ.get("GTSFM_B200_WORKSPACE_GIB", DEFAULT_PLUGIN_WORKSPACE_GIB)) * (1 << 30)))
+        table[key] = ctx
     return table[key]

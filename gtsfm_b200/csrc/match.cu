@@ -15,7 +15,8 @@ cudaError_t launch_match_screen(const CUtensorMap& tm_desc, const CUtensorMap& t
 cudaError_t launch_match_screen_f(const CUtensorMap& tm_desc, const CUtensorMap& tm_augq, const CUtensorMap& tm_augt,
                                   const PairDesc* pairs, int n_pairs, int n_items, float* rp_v1, float* rp_v2, uint8_t* rp_g,
                                   float* colraw, int kpad, int n_sm, cudaStream_t stream);
-cudaError_t launch_resolve_f(const StoreView& st, const MatchWork& w, long long total_rows, long long total_cols, cudaStream_t s);
+cudaError_t launch_resolve_f(const StoreView& st, const MatchWork& w, long long total_rows, long long total_cols, int use_ratio, double ratio,
+                             cudaStream_t s);
 cudaError_t launch_hamming(const StoreView& st, const MatchWork& w, long long total_rows, long long total_cols, int words, cudaStream_t s);
 cudaError_t launch_resolve_int(const StoreView& st, const MatchWork& w, int which, long long total, int max_class_rows,
                                cudaStream_t s);
@@ -77,8 +78,10 @@ int gtsfm_match_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, double ra
     Chunk cur;
     long long cur_bytes = 0, out_cap = 0;
     const bool screen_ok = c->kpad == 64 || c->kpad == 128;
-    // float descriptors: fp16 tensor-core screening when only the nearest neighbour is needed (ratio test off)
-    const bool screen_f_ok = !use_ratio && (c->kpad == 64 || c->kpad == 128 || c->kpad == 256) && (c->dim % 4) == 0 && !c->force_exact_float;
+    // float descriptors: fp16 tensor-core screening, with or without the ratio test (the resolve step certifies or recomputes
+    // the second-nearest distance); a non-positive ratio keeps nothing worth screening for and takes the exhaustive route
+    const bool screen_f_ok = (!use_ratio || ratio > 0) && (c->kpad == 64 || c->kpad == 128 || c->kpad == 256) && (c->dim % 4) == 0 &&
+                             !c->force_exact_float;
     for (int p = 0; p < n_pairs; ++p) {
         const int a = pairs[2 * p], b = pairs[2 * p + 1];
         if (a < 0 || b < 0 || a >= n_img || b >= n_img) return fail(c, GTSFM_E_ARG, "pair " + std::to_string(p) + " names an image that was not uploaded");
@@ -218,7 +221,7 @@ int gtsfm_match_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, double ra
                                               c->rp_v2.as<float>(), c->rp_g.as<uint8_t>(), c->colraw.as<float>(), c->kpad, c->n_sm, s));
             c->prof_end();
             c->prof_begin(P_RESOLVE_ROWS);
-            G2V_CUDA(c, launch_resolve_f(st, w, k.rows, k.cols, s));
+            G2V_CUDA(c, launch_resolve_f(st, w, k.rows, k.cols, use_ratio, ratio, s));
             c->prof_end();
             c->launches += 3;
         }

@@ -1,4 +1,5 @@
-// K2f -- exact resolve of the fp16-screened float path (ratio test off: only the nearest neighbour is needed).
+// K2f -- exact resolve of the fp16-screened float path: the nearest neighbour, and with the ratio test on the decision
+// d1 <= ratio * d2 (twoway_matcher.py:137) as well.
 //
 // The screening kernel (match_screen_f.cu) leaves, per query row, the minimum of every group of 4 train columns (best /
 // second-best group per 128-column half block) and, per train column, the minimum over every lane class
@@ -14,6 +15,16 @@
 // (about 1 % of the rows of SuperPoint-like inputs) a second stage recomputes every group / class whose screened minimum
 // is not above that threshold; only rows with more than kStage2Budget such candidates (degenerate inputs: many equal
 // rows) are appended to the flag list for the exhaustive scan (exact_scan_kernel, mode 1).
+//
+// Ratio test on (TwoWayMatcher(ratio_test_threshold=r) on float descriptors: configs/correspondence/kaze.yaml,
+// d2net.yaml).  The second-nearest distance d2 is either inside the winning group (exact, it was recomputed) or outside it,
+// where the screening brackets it: the smallest screened value outside the group, r2, gives
+//     sqrt(2 (r2 - eps)) (1 - 2e-6)  <=  d_out  <=  sqrt(2 (r2 + eps)) (1 + 2e-6)
+// for the nearest outside candidate in cv2's float32 arithmetic.  The test is CERTAIN when both ends of the bracket of
+// d2 = min(d2_inside, d_out) give the same answer; the row then carries d2 = FLT_MAX (keep) or -1 (drop) for the finalize
+// kernel, or the exact d2 when it is the inside one.  Otherwise (a fraction of a percent of the rows) the second stage
+// recomputes every group that can hold one of the two nearest neighbours -- screened minimum not above the level of an
+// upper bound of d2 -- and writes the exact pair (d1, d2).
 #include <cfloat>
 
 #include "store.h"
@@ -100,7 +111,7 @@ __device__ __forceinline__ void push_flag_f(const MatchWork& w, int pair, int di
 //   DIR 0: a query row; candidates = the 4 train columns of its winning group.
 //   DIR 1: a train column; candidates = the <= 4 query rows of its winning lane class.
 template <int DIR>
-__global__ void __launch_bounds__(256) resolve_f_kernel(StoreView st, MatchWork w)
+__global__ void __launch_bounds__(256) resolve_f_kernel(StoreView st, MatchWork w, int use_ratio, double ratio)
 {
     const long long base = static_cast<long long>(blockIdx.x) * kResF;
     // pair of this block of rows / columns (table built by the host: a binary search over the pair list would put a chain
@@ -169,7 +180,7 @@ __global__ void __launch_bounds__(256) resolve_f_kernel(StoreView st, MatchWork 
     }
 
     // ---- phase 2, fast pass: the (<= 4) candidates in one batch, so all their loads are in flight together
-    float f1 = FLT_MAX;
+    float f1 = FLT_MAX, f2in = FLT_MAX;                  // nearest and second nearest inside the winning group (exact)
     int i1 = INT_MAX;
     bool done = false;
     {
@@ -188,15 +199,42 @@ __global__ void __launch_bounds__(256) resolve_f_kernel(StoreView st, MatchWork 
         cv2_l2_halfwarp_n<4>(a, bp, dim, r16, f);
 #pragma unroll
         for (int k = 0; k < 4; ++k)
-            if (ok[k] && f[k] < f1) { f1 = f[k]; i1 = c[k]; }                    // ascending index: the lowest wins ties
+            if (ok[k]) {                                                         // ascending index: the lowest wins ties
+                if (f[k] < f1) { f2in = f1; f1 = f[k]; i1 = c[k]; }
+                else f2in = fminf(f2in, f[k]);
+            }
     }
     const float eps = screen_eps(st.norm_f[scan_row0 + rs], other_maxn2);
     // every candidate whose screened value exceeds thr is farther than f1 in cv2's float32 arithmetic
-    const double thr_d = 0.5 * static_cast<double>(f1) * static_cast<double>(f1) * (1.0 + 1e-5) + static_cast<double>(eps) + 1e-30;
+    double thr_d = 0.5 * static_cast<double>(f1) * static_cast<double>(f1) * (1.0 + 1e-5) + static_cast<double>(eps) + 1e-30;
     if (active && i1 != INT_MAX) done = static_cast<double>(r2) > thr_d;
+    float d2_out = FLT_MAX;                              // what the finalize kernel sees as the second-nearest distance
+    if (use_ratio && active && i1 != INT_MAX) {
+        // bracket of the nearest candidate OUTSIDE the group in cv2's float32 arithmetic (r2 = FLT_MAX: there is none)
+        double lo_out = 1e300, up_out = 1e300;
+        if (r2 < 1e37f) {
+            const double a0 = static_cast<double>(r2) - static_cast<double>(eps), a1 = static_cast<double>(r2) + static_cast<double>(eps);
+            lo_out = a0 > 0 ? sqrt(2.0 * a0) * (1.0 - 2e-6) : 0.0;
+            up_out = sqrt(2.0 * a1) * (1.0 + 2e-6);
+        }
+        const double d1 = f1, d2i = f2in < FLT_MAX ? static_cast<double>(f2in) : 1e300;
+        const double d2_lo = fmin(d2i, lo_out), d2_up = fmin(d2i, up_out);
+        if (done) {
+            if (d2i <= lo_out) d2_out = f2in;                                    // the second nearest is inside the group: exact
+            else if (d1 <= ratio * d2_lo && d1 <= ratio * d2_up) d2_out = FLT_MAX;   // certainly kept
+            else if (!(d1 <= ratio * d2_lo) && !(d1 <= ratio * d2_up)) d2_out = -1.0f;   // certainly dropped
+            else done = false;                                                   // undecided: exact second stage
+        }
+        if (!done) {
+            // the second stage must see every candidate that can be one of the two nearest: an upper bound of d2 is
+            // max(f1, min(f2in, up_out)) (two candidates are known to lie at or below it)
+            const double U = fmax(d1, d2_up);
+            thr_d = fmax(thr_d, 0.5 * U * U * (1.0 + 1e-5) + static_cast<double>(eps) + 1e-30);
+        }
+    }
     if (r16 == 0 && in_range) {
         if (!active) { o_best[out0 + r] = -1; o_d1[out0 + r] = FLT_MAX; o_d2[out0 + r] = FLT_MAX; }
-        else if (done) { o_best[out0 + r] = i1; o_d1[out0 + r] = f1; o_d2[out0 + r] = FLT_MAX; }
+        else if (done) { o_best[out0 + r] = i1; o_d1[out0 + r] = f1; o_d2[out0 + r] = d2_out; }
     }
     const unsigned need = __ballot_sync(0xffffffffu, active && !done);
     if (need == 0) return;
@@ -211,9 +249,16 @@ __global__ void __launch_bounds__(256) resolve_f_kernel(StoreView st, MatchWork 
         const float* au = st.desc_f32 + static_cast<long long>(scan_row0 + ru) * dim;
         const int c0u = __shfl_sync(0xffffffffu, c0, 16 * u);
         const float thr = __double2float_ru(__shfl_sync(0xffffffffu, thr_d, 16 * u));
-        float g1 = __shfl_sync(0xffffffffu, f1, 16 * u);
-        int j1 = __shfl_sync(0xffffffffu, i1, 16 * u);
-        if (j1 == INT_MAX) { if (lane == 0) push_flag_f(w, p, DIR, i0 + ru); continue; }   // no valid candidate: exhaustive scan
+        // result of the fast pass (the winning group, exact); each half warp collects what IT finds beyond that group in
+        // (g1 at j1, g2), the three disjoint sets are merged at the end
+        const float s1 = __shfl_sync(0xffffffffu, f1, 16 * u), s2 = __shfl_sync(0xffffffffu, f2in, 16 * u);
+        const int si = __shfl_sync(0xffffffffu, i1, 16 * u);
+        float g1 = FLT_MAX, g2 = FLT_MAX;
+        int j1 = INT_MAX;
+        if (si == INT_MAX) { if (lane == 0) push_flag_f(w, p, DIR, i0 + ru); continue; }   // no valid candidate: exhaustive scan
+        // index range of the winning group's candidates (rows: 4 consecutive columns; columns: rows 128 apart)
+        const int g0lo = DIR == 0 ? c0u : class_row0(c0u), g0step = DIR == 0 ? 1 : kTileQ;
+        const int g0hi = g0lo + (DIR == 0 ? kGroupF : class_rows(c0u)) * g0step - (g0step - 1);
         // exact distances to n candidates cb, cb + stride, ...: the half warps alternate, both always run the same rounds
         auto scan_cands = [&](int cb, int stride, int n) {                       // n is even
             constexpr int NB = 2;                                                // candidates per half warp and round
@@ -230,8 +275,12 @@ __global__ void __launch_bounds__(256) resolve_f_kernel(StoreView st, MatchWork 
                 float f[NB];
                 cv2_l2_halfwarp_n<NB>(au, bp, dim, r16, f);
 #pragma unroll
-                for (int k = 0; k < NB; ++k)
-                    if (ok[k] && (f[k] < g1 || (f[k] == g1 && c[k] < j1))) { g1 = f[k]; j1 = c[k]; }   // the lowest index wins ties
+                for (int k = 0; k < NB; ++k) {
+                    // the winning group was recomputed in the fast pass: its four candidates are in (g1, g2) already
+                    if (!ok[k] || (c[k] >= g0lo && c[k] < g0hi && ((c[k] - g0lo) % g0step) == 0)) continue;
+                    if (f[k] < g1 || (f[k] == g1 && c[k] < j1)) { g2 = g1; g1 = f[k]; j1 = c[k]; }   // the lowest index wins ties
+                    else g2 = fminf(g2, f[k]);
+                }
             }
         };
         int budget = kStage2Budget;                             // candidates this row may still recompute
@@ -261,21 +310,33 @@ __global__ void __launch_bounds__(256) resolve_f_kernel(StoreView st, MatchWork 
                 }
             }
         }
-        const float of = __shfl_xor_sync(0xffffffffu, g1, 16);
+        // merge: winning group (s1 at si, s2), this half (g1 at j1, g2), the other half
+        const float of = __shfl_xor_sync(0xffffffffu, g1, 16), of2 = __shfl_xor_sync(0xffffffffu, g2, 16);
         const int oi = __shfl_xor_sync(0xffffffffu, j1, 16);
-        if (of < g1 || (of == g1 && oi < j1)) { g1 = of; j1 = oi; }
+        {
+            float b1 = s1, b2 = s2;
+            int bi = si;
+            auto add_best = [&](float v, int idx) {            // a candidate with its index: the lowest index wins ties
+                if (idx == INT_MAX) return;
+                if (v < b1 || (v == b1 && idx < bi)) { b2 = b1; b1 = v; bi = idx; } else b2 = fminf(b2, v);
+            };
+            add_best(g1, j1); b2 = fminf(b2, g2);
+            add_best(of, oi); b2 = fminf(b2, of2);
+            g1 = b1; g2 = b2; j1 = bi;
+        }
         if (lane == 0) {
-            if (budget >= 0) { o_best[out0 + ru] = j1; o_d1[out0 + ru] = g1; o_d2[out0 + ru] = FLT_MAX; }
+            if (budget >= 0) { o_best[out0 + ru] = j1; o_d1[out0 + ru] = g1; o_d2[out0 + ru] = use_ratio ? g2 : FLT_MAX; }
             else push_flag_f(w, p, DIR, i0 + ru);               // too many suspects: exhaustive scan
         }
     }
 }
 
 // total_rows / total_cols: rows (columns) of the chunk over all pairs (multiples of 256).
-cudaError_t launch_resolve_f(const StoreView& st, const MatchWork& w, long long total_rows, long long total_cols, cudaStream_t s)
+cudaError_t launch_resolve_f(const StoreView& st, const MatchWork& w, long long total_rows, long long total_cols, int use_ratio, double ratio,
+                             cudaStream_t s)
 {
-    if (total_rows > 0) resolve_f_kernel<0><<<static_cast<unsigned>(total_rows / kResF), 256, 0, s>>>(st, w);
-    if (total_cols > 0) resolve_f_kernel<1><<<static_cast<unsigned>(total_cols / kResF), 256, 0, s>>>(st, w);
+    if (total_rows > 0) resolve_f_kernel<0><<<static_cast<unsigned>(total_rows / kResF), 256, 0, s>>>(st, w, use_ratio, ratio);
+    if (total_cols > 0) resolve_f_kernel<1><<<static_cast<unsigned>(total_cols / kResF), 256, 0, s>>>(st, w, use_ratio, ratio);
     return cudaGetLastError();
 }
 

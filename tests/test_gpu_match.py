@@ -174,8 +174,15 @@ def test_float_screened_path_vs_oracle(ctx, n1, n2, dim):
         check(ctx.match_pair(d1, d2, None), want)
     finally:
         ctx.set_float_screening(True)
-    # the ratio test needs the second-nearest neighbour: that stays on the exhaustive kernel
-    check(ctx.match_pair(d1, d2, 0.9), O.twoway_match(d1, d2, 0.9).reshape(-1, 2))
+    # ratio test on: the screened route certifies d1 <= ratio * d2 from the screening bounds or recomputes d2 exactly
+    for ratio in (0.9, 0.8, 0.6, 1.0):
+        want_r = O.twoway_match(d1, d2, ratio).reshape(-1, 2)
+        check(ctx.match_pair(d1, d2, ratio), want_r)
+    ctx.set_float_screening(False)
+    try:
+        check(ctx.match_pair(d1, d2, 0.8), O.twoway_match(d1, d2, 0.8).reshape(-1, 2))
+    finally:
+        ctx.set_float_screening(True)
 
 
 def test_float_screened_ties_nan_and_scales(ctx):
@@ -198,6 +205,40 @@ def test_float_screened_ties_nan_and_scales(ctx):
     check(ctx.match_pair(b1, b2, None), O.twoway_match(b1, b2, None).reshape(-1, 2))
     z = np.zeros((40, 128), np.float32)                       # all-zero rows: every distance ties
     check(ctx.match_pair(z, d2, None), O.twoway_match(z, d2, None).reshape(-1, 2))
+    # the same inputs with the ratio test on: exact duplicates make d1 == d2 (kept only when ratio >= 1), NaN rows, scales
+    for ratio in (0.8, 1.0, 0.99):
+        check(ctx.match_pair(d1, d2, ratio), O.twoway_match(d1, d2, ratio).reshape(-1, 2))
+        check(ctx.match_pair(d1n, d2n, ratio), O.twoway_match(d1n, d2n, ratio).reshape(-1, 2))
+        check(ctx.match_pair(s1, s2, ratio), O.twoway_match(s1, s2, ratio).reshape(-1, 2))
+        check(ctx.match_pair(z, d2, ratio), O.twoway_match(z, d2, ratio).reshape(-1, 2))
+
+
+def test_float_screened_ratio_on_c4_size_vs_oracle(ctx):
+    """TwoWayMatcher(ratio_test_threshold=0.8) on float descriptors (the reference's kaze.yaml / d2net.yaml correspondence
+    configs) at C4's pair size, 2048 x 2048 x 256, batched: the tensor-core route against the ORACLE for every pair, with
+    descriptors whose nearest / second-nearest ratios straddle the threshold (noise levels 0.1 .. 1.4 of the prototype amplitude)."""
+    from oracle import oracle as O
+    rng = np.random.default_rng(4242)
+    n, dim = 2048, 256
+    protos = rng.standard_normal((n, dim))
+    imgs = []
+    for noise in (0.1, 0.6, 1.0, 1.4):
+        d = unit_float_descs(rng, n, dim, protos, noise=noise)
+        d[: n // 4] = unit_float_descs(rng, n // 4, dim)
+        imgs.append(d[rng.permutation(n)])
+    pairs = np.array([(i, j) for i in range(4) for j in range(i + 1, 4)], np.int32)
+    ctx.clear()
+    for i, d in enumerate(imgs):
+        ctx.upload_image(i, d)
+    for ratio in (0.8, 0.95):
+        m, off = ctx.match_batch(pairs, ratio)
+        n_flag = int(ctx.debug_fetch(10, 1, np.int32)[0])
+        kept = []
+        for p, (i, j) in enumerate(pairs):
+            want = O.twoway_match(imgs[i], imgs[j], ratio).reshape(-1, 2)
+            check(m[off[p]:off[p + 1]], want)
+            kept.append(len(want))
+        assert min(kept) > 50 and n_flag < 0.25 * 2 * n * len(pairs), (kept, n_flag)
 
 
 def test_float_screened_c4_size_flag_rate(ctx):
