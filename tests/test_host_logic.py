@@ -210,3 +210,25 @@ def test_report_oracle_matches_the_pinned_sampson_restatement():
     F = rng.standard_normal((3, 3))
     c1, c2 = rng.uniform(0, 1000, (50, 2)), rng.uniform(0, 1000, (50, 2))
     np.testing.assert_allclose(O.sampson_sq_numpy(c1, c2, F), O.sampson_sq(F, c1, c2), rtol=1e-10)
+
+
+def test_plugin_contexts_cap_their_workspace(monkeypatch):
+    """default_context() (one per worker thread) sets a 4 GiB work-buffer budget instead of the library's 12 GiB;
+    GTSFM_B200_WORKSPACE_GIB overrides it.  No GPU: the Context class is replaced by a recorder."""
+    from gtsfm_b200 import _native
+    seen = []
+
+    class FakeCtx:
+        def __init__(self, device):
+            self.device = device
+
+        def set_workspace(self, nbytes):
+            seen.append(nbytes)
+
+    monkeypatch.setattr(_native, "Context", FakeCtx)
+    monkeypatch.setattr(_native, "_default_tls", __import__("threading").local())
+    _native.default_context(0)
+    monkeypatch.setenv("GTSFM_B200_WORKSPACE_GIB", "1.5")
+    _native.default_context(1)
+    assert seen == [4 << 30, int(1.5 * (1 << 30))]
+    assert _native.default_context(0) is _native.default_context(0) and len(seen) == 2
