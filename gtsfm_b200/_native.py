@@ -22,7 +22,7 @@ EXPORTS = (
     "gtsfm_host_alloc", "gtsfm_host_free", "gtsfm_match_fetch_async", "gtsfm_sync",
     "gtsfm_retriever_similarity", "gtsfm_retriever_topk", "gtsfm_retriever_pairs_noalloc",
     "gtsfm_verify_hypotheses_used", "gtsfm_result_pack", "gtsfm_result_pack_copy", "gtsfm_stream_wait",
-    "gtsfm_images_upload",
+    "gtsfm_images_upload", "gtsfm_two_view_ba_batch",
 )
 
 OK, E_CUDA, E_ARG, E_NO_DEVICE, E_KNN_UNPACK, E_UNSUPPORTED = range(6)
@@ -53,6 +53,18 @@ class ReportParams(ctypes.Structure):
         ("min_num_inliers_est_model", ctypes.c_int),
         ("min_inlier_ratio_est_model", ctypes.c_double),
         ("gt_cal", ctypes.c_void_p),
+        ("after_ba", ctypes.c_int),
+    ]
+
+
+class TwoViewBaParams(ctypes.Structure):
+    _fields_ = [
+        ("min_num_inliers", ctypes.c_int),
+        ("max_iterations", ctypes.c_int),
+        ("triangulation_reproj_error_thresh", ctypes.c_double),
+        ("ba_reproj_error_thresh", ctypes.c_double),
+        ("huber_k", ctypes.c_double),
+        ("min_triangulation_angle_deg", ctypes.c_double),
     ]
 
 
@@ -114,6 +126,7 @@ def lib() -> ctypes.CDLL:
                                                         ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
             L.gtsfm_two_view_report_batch.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p,
                                                       ctypes.POINTER(ReportParams)] + [ctypes.c_void_p] * 8
+            L.gtsfm_two_view_ba_batch.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.POINTER(TwoViewBaParams)] + [ctypes.c_void_p] * 6
             L.gtsfm_match_pair.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int,
                                            ctypes.c_int, ctypes.c_double, ctypes.c_void_p, ctypes.POINTER(ctypes.c_int32)]
             L.gtsfm_verify_pair.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int,
@@ -439,14 +452,16 @@ class Context:
 
     def two_view_report_batch(self, n_pairs: int, total: int, dist_threshold_px: float, min_num_inliers_est_model: int,
                               min_inlier_ratio_est_model: float, gt_i2Ri1: Optional[np.ndarray] = None,
-                              gt_i2ti1: Optional[np.ndarray] = None, reuse_outputs: bool = False, gt_cal: Optional[np.ndarray] = None):
+                              gt_i2ti1: Optional[np.ndarray] = None, reuse_outputs: bool = False, gt_cal: Optional[np.ndarray] = None,
+                              after_ba: bool = False):
         """Post-verification report of the pairs of the last verify_batch (gtsfm_two_view_report_batch).  With reuse_outputs the
-        per-correspondence arrays are views of the context's pinned arena (valid until the next report call)."""
+        per-correspondence arrays are views of the context's pinned arena (valid until the next report call).  after_ba: the
+        report of the results two_view_ba_batch left on the device (the post-BA report)."""
         P = int(n_pairs)
         if gt_cal is not None:
             gt_cal = np.ascontiguousarray(gt_cal, np.float64).reshape(P, 10)
         prm = ReportParams(float(dist_threshold_px), int(min_num_inliers_est_model), float(min_inlier_ratio_est_model),
-                           None if gt_cal is None else gt_cal.ctypes.data)
+                           None if gt_cal is None else gt_cal.ctypes.data, 1 if after_ba else 0)
         if gt_i2Ri1 is not None:
             gt_i2Ri1 = np.ascontiguousarray(gt_i2Ri1, np.float64).reshape(P, 9)
             gt_i2ti1 = np.ascontiguousarray(gt_i2ti1, np.float64).reshape(P, 3)
@@ -462,6 +477,22 @@ class Context:
                                                         _ptr(u_err), _ptr(keep)))
         return dict(dist_sq=dist[: int(total)], gt_mask=gmask[: int(total)], num_inliers_gt=n_gt, inlier_avg_err=in_avg,
                     outlier_avg_err=out_avg, R_error_deg=r_err, U_error_deg=u_err, keep=keep)
+
+    def two_view_ba_batch(self, n_pairs: int, total: int, min_num_inliers: int, max_iterations: int = 100,
+                          triangulation_reproj_error_thresh: float = 100.0, ba_reproj_error_thresh: float = 0.5, huber_k: float = 1.345,
+                          min_triangulation_angle_deg: float = 0.0):
+        """Triangulation + two-view bundle adjustment of the pairs of the last verify_batch (gtsfm_two_view_ba_batch).  Returns
+        R (P, 3, 3), t (P, 3) unit, valid_mask (total,) uint8 over the match rows, num_valid, status (0 ran / 1 skipped / 2
+        nothing triangulated), iterations."""
+        P = int(n_pairs)
+        prm = TwoViewBaParams(int(min_num_inliers), int(max_iterations), float(triangulation_reproj_error_thresh),
+                              float(ba_reproj_error_thresh), float(huber_k), float(min_triangulation_angle_deg))
+        R = np.zeros((P, 3, 3)); t = np.zeros((P, 3))
+        mask = np.zeros(max(int(total), 1), np.uint8)
+        n = np.zeros(P, np.int32); status = np.zeros(P, np.int32); iters = np.zeros(P, np.int32)
+        self._check(self._L.gtsfm_two_view_ba_batch(self._h, P, ctypes.byref(prm), _ptr(R), _ptr(t), _ptr(mask), _ptr(n), _ptr(status),
+                                                    _ptr(iters)))
+        return dict(R=R, t=t, valid_mask=mask[: int(total)], num_valid=n, status=status, iterations=iters)
 
     def verify_pair(self, kps1, kps2, match_idx, cal1, cal2, params: "VerifyParams"):
         kps1 = np.ascontiguousarray(kps1, np.float64).reshape(-1, 2)

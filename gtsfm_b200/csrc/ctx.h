@@ -89,6 +89,7 @@ struct gtsfm_ctx {
     // ---- verifier buffers; state of the last gtsfm_verify_batch (read by gtsfm_two_view_report_batch)
     g2v::DevBuf v_bufs[32];
     int verify_n = 0;
+    int ba_n = 0;                     // pairs of the last two_view_ba_batch (0 = none for the current verify batch)
     int pack_n = 0;                          // pairs / payload rows of the last gtsfm_result_pack
     long long pack_rows = 0;
     cudaEvent_t fetch_ev = nullptr;          // recorded behind the copy of gtsfm_match_fetch_async (which reads match_out)

@@ -64,7 +64,7 @@ int gtsfm_match_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, double ra
     if ((r = c->wait_images(max_image, false))) return r;
     c->batch_n = 0;
     c->batch_total = 0;
-    c->verify_n = 0;          // the device match rows of the last verify batch are about to be overwritten
+    c->verify_n = 0; c->ba_n = 0;          // the device match rows of the last verify batch are about to be overwritten
     if (total) *total = 0;
     if ((r = c->wait_fetch())) return r;                     // an asynchronous fetch of the previous batch may still read match_out
     if (n_pairs == 0) return GTSFM_OK;

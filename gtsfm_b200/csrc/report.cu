@@ -20,6 +20,7 @@ namespace g2v {
 
 struct ReportBufs {
     const VPair* pairs; const void* match; const unsigned char* mask; const double* R; const double* t; const int* ninl; const int* status;
+    const int* ninl_ratio;                          // verified count the inlier ratio is quoted on (= ninl before BA)
     const double* gt_R; const double* gt_t;         // [P][9], [P][3] ground-truth i2Ri1 / i2ti1 or nullptr
     const double* gt_cal;                           // [P][10] calibrations of the ground-truth cameras or nullptr (-> VPair's)
     double* dist_sq; unsigned char* gt_mask;        // per match row (NaN / 0 for rows that were not verified)
@@ -41,7 +42,8 @@ __global__ void __launch_bounds__(kFinThreads) two_view_report_kernel(StoreView 
     const bool have_gt = b.gt_R != nullptr && b.gt_t != nullptr && b.gt_R[9 * p] == b.gt_R[9 * p];   // NaN row: no GT for this pair
     if (tid == 0) {
         // InlierSupportProcessor.run_inlier_support: the ratio test first, then the count test (only for valid models)
-        const double ratio = (ok && vp.M > 0) ? static_cast<double>(n_inl) / vp.M : 0.0;
+        // after BA the ratio stays the verifier's (two_view_estimator.py:328-329), the count is the tracks BA kept
+        const double ratio = (ok && vp.M > 0) ? static_cast<double>(b.ninl_ratio[p]) / vp.M : 0.0;
         const int n_est = ok ? n_inl : 0;
         bool keep = !(ratio < b.min_ratio);
         if (keep && n_est > 0 && n_est < b.min_inl) keep = false;
@@ -139,6 +141,15 @@ extern "C" int gtsfm_two_view_report_batch(gtsfm_ctx* c, int n_pairs, const doub
     ReportBufs b{};
     b.pairs = vb[0].as<VPair>(); b.match = c->match_out.p; b.mask = vb[12].as<unsigned char>();
     b.R = vb[7].as<double>(); b.t = vb[8].as<double>(); b.ninl = vb[10].as<int>(); b.status = vb[11].as<int>();
+    b.ninl_ratio = b.ninl;
+    if (prm->after_ba) {
+        // the post-BA report (two_view_estimator.py:319-333): poses, valid tracks and their count from gtsfm_two_view_ba_batch
+        if (c->ba_n != n_pairs) return fail(c, GTSFM_E_ARG, "two_view_report_batch(after_ba) needs a preceding two_view_ba_batch");
+        const size_t P = static_cast<size_t>(n_pairs);
+        b.mask = vb[28].as<unsigned char>() + (total + 1);
+        b.R = vb[29].as<double>(); b.t = b.R + 9 * P;
+        b.ninl = reinterpret_cast<const int*>(b.t + 3 * P);
+    }
     if (gt_i2Ri1) {
         double* g = vb[19].as<double>();
         G2V_CUDA(c, cudaMemcpyAsync(g, gt_i2Ri1, 72 * static_cast<size_t>(n_pairs), cudaMemcpyHostToDevice, s));

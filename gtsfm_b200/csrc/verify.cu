@@ -123,7 +123,7 @@ int gtsfm_verify_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, const ui
 {
     if (!c || !prm || n_pairs < 0 || (n_pairs > 0 && !pairs)) return fail(c, GTSFM_E_ARG, "bad arguments");
     cudaSetDevice(c->device);
-    c->verify_n = 0;
+    c->verify_n = 0; c->ba_n = 0;
     if (n_pairs == 0) return GTSFM_OK;
     if (prm->n_hypotheses <= 0 || prm->n_hypotheses > (1 << 20)) return fail(c, GTSFM_E_ARG, "n_hypotheses out of range");
     if (!(prm->threshold_px > 0)) return fail(c, GTSFM_E_ARG, "threshold_px must be positive");

@@ -61,18 +61,20 @@ class TwoViewBatchResult:
 def two_view_reports(result: TwoViewBatchResult, ctx: "_native.Context", corr_metric_dist_threshold: float,
                      min_num_inliers_est_model: int, min_inlier_ratio_est_model: float,
                      gt_i2Ri1: Optional[np.ndarray] = None, gt_i2ti1: Optional[np.ndarray] = None,
-                     gt_cal: Optional[np.ndarray] = None):
+                     gt_cal: Optional[np.ndarray] = None, after_ba: bool = False, inlier_ratios: Optional[np.ndarray] = None):
     """The stage after verify() in TwoViewEstimator.run_2view (two_view_estimator.py:298-349) for every pair of the batch the
     context verified last: GT correspondence metrics, relative-pose errors, report aggregates and the InlierSupportProcessor
     decision, computed on the device in one launch.  Returns (reports, keep): a TwoViewEstimationReport per pair (the
     pre-ISP report), the boolean keep mask and the raw arrays.  gt_i2Ri1 rows of NaN mark pairs without ground truth; gt_cal
-    (P, 10) are the GT cameras' calibrations when they differ from the ones the images were uploaded with."""
+    (P, 10) are the GT cameras' calibrations when they differ from the ones the images were uploaded with.  after_ba: `result`
+    holds the outputs of two_view_ba_batch (post-BA report); inlier_ratios then carries the pre-BA ratios the reference keeps
+    (two_view_estimator.py:325-329)."""
     from gtsfm_b200.common.two_view_estimation_report import TwoViewEstimationReport
     result._need_matches()
     P = len(result.pairs)
     o = result.match_offsets
     rep = ctx.two_view_report_batch(P, int(o[-1]), corr_metric_dist_threshold, min_num_inliers_est_model,
-                                    min_inlier_ratio_est_model, gt_i2Ri1, gt_i2ti1, gt_cal=gt_cal)
+                                    min_inlier_ratio_est_model, gt_i2Ri1, gt_i2ti1, gt_cal=gt_cal, after_ba=after_ba)
     # a pair without ground truth (one of its gt cameras is None, two_view_estimator.py:131) carries a NaN row
     gt_rows = None if gt_i2Ri1 is None else ~np.isnan(np.asarray(gt_i2Ri1, np.float64).reshape(P, 9)[:, 0])
     reports = []
@@ -83,6 +85,8 @@ def two_view_reports(result: TwoViewBatchResult, ctx: "_native.Context", corr_me
         mask = result.inlier_mask[o[p]:o[p + 1]] == 1 if ok else np.zeros(len(m), bool)
         v = m[mask] if ok else np.array([], dtype=np.uint64)
         ratio = float(mask.mean()) if (ok and mask.size) else 0.0
+        if inlier_ratios is not None:
+            ratio = float(inlier_ratios[p])
         if have_gt and ok and len(v) > 0:
             gm = rep["gt_mask"][o[p]:o[p + 1]][mask].astype(bool)
             err = rep["dist_sq"][o[p]:o[p + 1]][mask]

@@ -4,13 +4,14 @@ TWO_VIEW_OUTPUT 6-tuples -- with the per-pair Dask submission loop (two_view_est
 GPU shard of the pair list.
 
 A shard task uploads the keypoints of the images its pairs name, verifies all pairs in one device batch
-(gtsfm_verify_batch), computes the ground-truth metrics, the report aggregates and the InlierSupportProcessor decision of
-every pair in one more launch (gtsfm_two_view_report_batch) and assembles the reference's structures on the host.
-run_2view is a batch of one through the same code.
+(gtsfm_verify_batch), triangulates and bundle-adjusts every pair with enough verified correspondences in one launch when
+bundle_adjust_2view is True (gtsfm_two_view_ba_batch), computes the ground-truth metrics, the report aggregates and the
+InlierSupportProcessor decision of every pair in one more launch per report (gtsfm_two_view_report_batch, pre- and post-BA)
+and assembles the reference's structures on the host.  run_2view is a batch of one through the same code.
 
-Not offered (loud errors, no CPU fallback): two-view bundle adjustment (`bundle_adjust_2view=True`,
-two_view_estimator.py:101-208: a GTSAM solve per pair -- SURVEY.md 8(f) rank 4) and mesh-based correspondence metrics
-(`gt_scene_mesh`, utils/metrics.py:75-83: ray casting against a trimesh).
+Not offered (loud errors, no CPU fallback): relative pose priors together with bundle adjustment (two_view_estimator.py:
+165-167,189: the prior as the initial pose and a BetweenFactor), triangulation modes other than NO_RANSAC, and mesh-based
+correspondence metrics (`gt_scene_mesh`, utils/metrics.py:75-83: ray casting against a trimesh).
 """
 import dataclasses
 from typing import Any, Dict, List, Optional, Sequence, Tuple
@@ -84,8 +85,13 @@ class TwoViewEstimator:
         """run_2view for every pair of the dictionary, in one device batch.  keypoints / camera_intrinsics / gt_cameras are
         indexable by image id (lists, or dicts holding only the images this shard names)."""
         if self._bundle_adjust_2view:
-            raise NotImplementedError("two-view bundle adjustment (two_view_estimator.py:101-208) is not part of the B200 two-view path; "
-                                      "configure bundle_adjust_2view: False")
+            mode = getattr(self._triangulation_options, "mode", None)
+            if self._triangulation_options is None or getattr(mode, "value", mode) != "NO_RANSAC":
+                raise NotImplementedError("two-view bundle adjustment on the B200 path triangulates with TriangulationSamplingMode.NO_RANSAC "
+                                          "(configs/sift_front_end.yaml:50-55); pass such TriangulationOptions")
+            if relative_pose_priors is not None and any(relative_pose_priors.get(k) is not None for k in putative_corr_idxs_dict):
+                raise NotImplementedError("relative pose priors in two-view bundle adjustment (two_view_estimator.py:165-167,189) are not "
+                                          "part of the B200 two-view path")
         if gt_scene_mesh is not None:
             raise NotImplementedError("mesh-based correspondence metrics (utils/metrics.py:75-83) are not part of the B200 two-view path")
         if not hasattr(self._verifier, "verify_batch_raw"):
@@ -117,19 +123,46 @@ class TwoViewEstimator:
         result = TwoViewBatchResult(pairs.astype(np.int32), off, allm, raw["mask"], raw["R"], raw["t"], raw["n_inliers"], raw["status"])
         reports, keep, _ = two_view_reports(result, ctx, self._corr_metric_dist_threshold, self.processor._min_num_inliers_est_model,
                                             self.processor._min_inlier_ratio_est_model, gt_R, gt_t, gt_cal)
+        total = int(off[-1])
+        post_reports, post_keep, ba = reports, keep, None
+        if self._bundle_adjust_2view:
+            # two_view_estimator.py:316-333: BA where enough correspondences were verified, then the post-BA report on its results
+            thr = self._ba_reproj_error_thresholds[-1] if self._ba_reproj_error_thresholds else None     # every stage restarts from
+            ba = ctx.two_view_ba_batch(P, total, self.processor._min_num_inliers_est_model,              # the initial data
+                                       self._bundle_adjust_2view_maxiters,                                # (bundle_adjustment.py:381-390)
+                                       float(self._triangulation_options.reproj_error_threshold),
+                                       float("inf") if thr is None else float(thr), 1.345,
+                                       float(self._triangulation_options.min_triangulation_angle))
+            ba_result = TwoViewBatchResult(result.pairs, off, allm, ba["valid_mask"], ba["R"].reshape(P, 9), ba["t"], ba["num_valid"],
+                                           raw["status"])
+            pre_ratio = np.array([r.inlier_ratio_est_model for r in reports])
+            post_reports, post_keep, _ = two_view_reports(ba_result, ctx, self._corr_metric_dist_threshold,
+                                                          self.processor._min_num_inliers_est_model,
+                                                          self.processor._min_inlier_ratio_est_model, gt_R, gt_t, gt_cal, after_ba=True,
+                                                          inlier_ratios=pre_ratio)
         out: Dict[Tuple[int, int], TWO_VIEW_OUTPUT] = {}
         for p, key in enumerate(keys):
             pre_ba_report = reports[p]
             ok = raw["status"][p] == _native.V_OK
             # v_corr_idxs keep the caller's dtype and row order (opencv_verifier_base.py:98-100); failure -> empty uint64
-            src = np.asarray(putative_corr_idxs_dict[key])
-            v = src.reshape(-1, 2)[raw["mask"][off[p]:off[p + 1]] == 1] if ok else np.array([], dtype=np.uint64)
+            src = np.asarray(putative_corr_idxs_dict[key]).reshape(-1, 2)
+            v = src[raw["mask"][off[p]:off[p + 1]] == 1] if ok else np.array([], dtype=np.uint64)
             pre_ba_report.v_corr_idxs = v
-            post_ba_report = dataclasses.replace(pre_ba_report)                      # two_view_estimator.py:338
-            if keep[p]:
-                post = (Rot3(raw["R"][p].copy()), Unit3(raw["t"][p].copy()), v, dataclasses.replace(post_ba_report))
-            else:                                                                    # inlier_support_processor.py:69-74
-                post = (None, None, np.array([], dtype=np.uint64), TwoViewEstimationReport(v_corr_idxs=v, num_inliers_est_model=0))
+            if ba is not None and ba["status"][p] != 1:
+                post_ba_report = post_reports[p]
+                post_v = src[ba["valid_mask"][off[p]:off[p + 1]] == 1]
+                if len(post_v) == 0:
+                    post_v = np.zeros((0, 2), np.int32)                                # two_view_estimator.py:180 / an empty selection
+                post_ba_report.v_corr_idxs = post_v
+                post_R, post_t = ba["R"][p], ba["t"][p]
+            else:
+                post_ba_report = dataclasses.replace(pre_ba_report)                  # two_view_estimator.py:338
+                post_v, post_R, post_t = v, raw["R"][p], raw["t"][p]
+            if post_keep[p]:
+                post = (Rot3(np.array(post_R, np.float64).reshape(3, 3)), Unit3(np.array(post_t, np.float64)), post_v,
+                        dataclasses.replace(post_ba_report))
+            else:                                                                    # inlier_support_processor.py:63-68
+                post = (None, None, np.array([], dtype=np.uint64), TwoViewEstimationReport(v_corr_idxs=post_v, num_inliers_est_model=0))
             out[(int(key[0]), int(key[1]))] = (post[0], post[1], post[2], pre_ba_report, post_ba_report, post[3])
         return out
 

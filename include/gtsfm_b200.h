@@ -151,6 +151,9 @@ typedef struct gtsfm_report_params {
     const double* gt_cal;               /* optional (P, 10): {f, k1, k2, u0, v0} of the GROUND-TRUTH cameras of image 1 and image 2
                                            (gt_camera.calibration(), utils/metrics.py:90-97) for F_gt; NULL = the calibrations the
                                            images were uploaded with */
+    int after_ba;                       /* 0 = the verifier's results (pre-BA report); 1 = the results of the last
+                                           gtsfm_two_view_ba_batch (post-BA report: its poses and valid tracks, the inlier RATIO
+                                           stays the verifier's, two_view_estimator.py:325-329) */
 } gtsfm_report_params;
 
 /* The stage that follows verify() in TwoViewEstimator.run_2view (gtsfm/two_view_estimator.py:298-349), for every pair of
@@ -172,6 +175,34 @@ int gtsfm_two_view_report_batch(gtsfm_ctx* ctx, int n_pairs, const double* gt_i2
                                 const gtsfm_report_params* params, double* dist_sq, uint8_t* gt_mask, int32_t* num_inliers_gt,
                                 double* inlier_avg_err, double* outlier_avg_err, double* R_error_deg, double* U_error_deg,
                                 int32_t* keep);
+
+/* ---- two-view triangulation + bundle adjustment over a batch of pairs ---------------------------
+ * TwoViewEstimator.bundle_adjust (gtsfm/two_view_estimator.py:137-208), run when bundle_adjust_2view is True -- the default of
+ * configs/sift_front_end.yaml:40 -- for every pair of the last gtsfm_verify_batch whose verified correspondences number at least
+ * min_num_inliers (two_view_estimator.py:316).  The arithmetic of the reference lives in the un-vendored gtsam==4.2
+ * (triangulatePoint3, GeneralSFMFactor2, LevenbergMarquardtOptimizer): PARITY UNPINNED, see DESIGN.md. */
+typedef struct gtsfm_two_view_ba_params {
+    int min_num_inliers;                       /* processor._min_num_inliers_est_model: fewer verified rows -> the pair is skipped */
+    int max_iterations;                        /* TwoViewEstimator(bundle_adjust_2view_maxiters), default 100 */
+    double triangulation_reproj_error_thresh;  /* TriangulationOptions.reproj_error_threshold (point3d_initializer.py:54), pixels */
+    double ba_reproj_error_thresh;             /* ba_reproj_error_thresholds[-1] (bundle_adjustment.py:335-357), pixels */
+    double huber_k;                            /* gtsam.noiseModel.mEstimator.Huber(1.345) (bundle_adjustment.py:137-141) */
+    double min_triangulation_angle_deg;        /* TriangulationOptions.min_triangulation_angle (point3d_initializer.py:287-291), 0 = off */
+} gtsfm_two_view_ba_params;
+
+/* Per pair: cameras (I, K1) and (i2Ti1 from the verifier, K2); every verified correspondence is triangulated (DLT + three
+ * Gauss-Newton steps on the pixel error, cheirality, both reprojection errors < triangulation_reproj_error_thresh); the pose and
+ * the points are refined by Levenberg-Marquardt on the Huber-robust reprojection cost (lambda 1e-5, factor 10, upper bound 1e5,
+ * relative / absolute error tolerance 1e-5, at most max_iterations accepted steps; camera 1 fixed, translation on the unit
+ * sphere, intrinsics fixed); a track stays valid when both reprojection errors are < ba_reproj_error_thresh.
+ * Outputs (any may be NULL), aligned with the last gtsfm_verify_batch: i2Ri1 (P, 9) row-major, i2Ui1 (P, 3) unit vectors,
+ * valid_mask (total match rows) uint8 = post_ba_v_corr_idxs as a mask, num_valid (P), ba_status (P): 0 = BA ran, 1 = skipped
+ * (verification failed or too few verified rows: pose / mask / count are the verifier's, two_view_estimator.py:334-338), 2 =
+ * nothing could be triangulated (the verifier's pose, no correspondences, two_view_estimator.py:179-180), 3 = BA ran and no
+ * track passed the filter (the verifier's pose, no correspondences, two_view_estimator.py:199-202); iterations (P) accepted LM
+ * steps.  The results stay on the device for gtsfm_two_view_report_batch(after_ba = 1). */
+int gtsfm_two_view_ba_batch(gtsfm_ctx* ctx, int n_pairs, const gtsfm_two_view_ba_params* params, double* i2Ri1, double* i2Ui1,
+                            uint8_t* valid_mask, int32_t* num_valid, int32_t* ba_status, int32_t* iterations);
 
 /* ---- device-resident result records for the multi-GPU exchange ------------------------------------------
  * What unzip_two_view_results hands to the back end (gtsfm/runner/gtsfm_runner_base.py:415-440) for every pair of the last

@@ -135,6 +135,13 @@ def test_unsupported_stages_fail_loudly():
     isp = InlierSupportProcessor(15, 0.1)
     with pytest.raises(NotImplementedError):
         TwoViewEstimator(Ransac(True, 4.0), isp, True, 4.0).run_2view_batch(kps, put, [None, None])
+    from gtsfm_b200.data_association.point3d_initializer import TriangulationOptions, TriangulationSamplingMode
+    with pytest.raises(NotImplementedError):                 # BA triangulates with NO_RANSAC only
+        TwoViewEstimator(Ransac(True, 4.0), isp, True, 4.0, TriangulationOptions(TriangulationSamplingMode.RANSAC_SAMPLE_UNIFORM)) \
+            .run_2view_batch(kps, put, [None, None])
+    with pytest.raises(NotImplementedError):                 # BA with a relative pose prior
+        TwoViewEstimator(Ransac(True, 4.0), isp, True, 4.0, TriangulationOptions(TriangulationSamplingMode.NO_RANSAC)) \
+            .run_2view_batch(kps, put, [None, None], {(0, 1): object()})
     with pytest.raises(NotImplementedError):
         TwoViewEstimator(Ransac(True, 4.0), isp, False, 4.0).run_2view_batch(kps, put, [None, None], gt_scene_mesh=object())
     with pytest.raises(NotImplementedError):
