@@ -428,6 +428,21 @@ def run_b200(args):
                     "median_R_error_deg": float(np.nanmedian(rep["R_error_deg"])) if np.isfinite(rep["R_error_deg"]).any() else None,
                     "median_U_error_deg": float(np.nanmedian(rep["U_error_deg"])) if np.isfinite(rep["U_error_deg"]).any() else None}
 
+    # ---- two-view triangulation + bundle adjustment of the same pairs (the default configuration's step
+    # between verify() and the inlier-support decision), timed on its own for the same reason; then the post-BA report
+    n_verified = ctx.two_view_ba_batch(b - a, last_total[0], 1 << 30)["num_valid"].copy()    # floor above every pair: the verifier's counts
+    ba = ctx.two_view_ba_batch(b - a, last_total[0], 15, 100, 100.0, 0.5, 1.345)
+    ctx.event_record(2)
+    ba = ctx.two_view_ba_batch(b - a, last_total[0], 15, 100, 100.0, 0.5, 1.345)
+    ctx.event_record(3)
+    rep_ba = ctx.two_view_report_batch(b - a, last_total[0], scene.threshold_px, 15, 0.1, gt_R, gt_t, reuse_outputs=True, after_ba=True)
+    ran = ba["status"] == 0
+    ba_extra = {"pairs": b - a, "pairs_adjusted": int(ran.sum()), "ms_per_pass_incl_result_copies": ctx.event_elapsed_ms(2, 3),
+                "median_lm_iterations": float(np.median(ba["iterations"][ran])) if ran.any() else None,
+                "tracks_kept_fraction": float(ba["num_valid"][ran].sum() / max(1, int(n_verified[ran].sum()))) if ran.any() else None,
+                "median_R_error_deg_post_ba": float(np.nanmedian(rep_ba["R_error_deg"])) if np.isfinite(rep_ba["R_error_deg"]).any() else None,
+                "median_U_error_deg_post_ba": float(np.nanmedian(rep_ba["U_error_deg"])) if np.isfinite(rep_ba["U_error_deg"]).any() else None}
+
     # ---- the retriever step in front of the path, outside the timed steps: similarity + top-50 of
     # 2,000 images x 4,096-d global descriptors (C4's image count, NetVLAD's dimension), host arrays in, pair list out
     retr_extra = None
@@ -500,7 +515,7 @@ def run_b200(args):
                 "roofline": roofline, "cpu_baseline": cpu,
                 "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": int(d2h_bytes)},
                 "gpu_launches": int(launches), "clocks": clk, "device_event_ms_per_step": ms / args.steps,
-                "agreement_vs_cv2": stats.get("agreement_vs_cv2"), "per_rank_kernel_ms_per_step": per_rank_kernel_ms, "two_view_report": report_extra, "retriever": retr_extra}
+                "agreement_vs_cv2": stats.get("agreement_vs_cv2"), "per_rank_kernel_ms_per_step": per_rank_kernel_ms, "two_view_report": report_extra, "two_view_ba": ba_extra, "retriever": retr_extra}
         print(json.dumps(line), file=_REAL_STDOUT, flush=True)
     ctx.close()
     if world > 1:
