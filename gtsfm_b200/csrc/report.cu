@@ -146,7 +146,7 @@ extern "C" int gtsfm_two_view_report_batch(gtsfm_ctx* c, int n_pairs, const doub
         // the post-BA report (two_view_estimator.py:319-333): poses, valid tracks and their count from gtsfm_two_view_ba_batch
         if (c->ba_n != n_pairs) return fail(c, GTSFM_E_ARG, "two_view_report_batch(after_ba) needs a preceding two_view_ba_batch");
         const size_t P = static_cast<size_t>(n_pairs);
-        b.mask = vb[28].as<unsigned char>() + (total + 1);
+        b.mask = vb[28].as<unsigned char>() + 4 * (total + 1);
         b.R = vb[29].as<double>(); b.t = b.R + 9 * P;
         b.ninl = reinterpret_cast<const int*>(b.t + 3 * P);
     }

@@ -32,8 +32,8 @@ namespace g2v {
 
 struct BaBufs {
     const VPair* pairs; const void* match; const unsigned char* mask; const double* R; const double* t; const int* ninl; const int* status;
-    double* X; double* Xn;          // [total][3] current / trial points, indexed by match row
-    unsigned char* tri;             // [total] 1 = triangulated track (a verified correspondence that passed the triangulation checks)
+    double* X; double* Xn;          // [total][3] point buffers (current / trial, swapped on acceptance), DENSE per pair: entry m0 + j
+    int* idx;                       // [total] match row (pair-relative) of dense track j at m0 + j: the triangulated tracks in row order
     unsigned char* ba_mask;         // [total] 1 = track valid after BA (verified, triangulated, reprojection errors below the threshold)
     double* out_R; double* out_t;   // [P][9], [P][3]
     int* out_n; int* out_status;    // [P] valid tracks; 0 = BA ran, 1 = skipped (too few verified / failed pair), 2 = nothing triangulated,
@@ -154,6 +154,7 @@ __global__ void __launch_bounds__(kBaThreads) two_view_ba_kernel(StoreView st, B
     __shared__ BaPose s_pose, s_trial;
     __shared__ double s_dc[5];
     __shared__ int s_ctrl;
+    __shared__ int s_wcnt[kBaThreads / 32];
     const int p = blockIdx.x;
     if (p >= n_pairs) return;
     const VPair& vp = b.pairs[p];
@@ -161,7 +162,7 @@ __global__ void __launch_bounds__(kBaThreads) two_view_ba_kernel(StoreView st, B
     const bool ok = b.status[p] == 0;
     const int n_ver = ok ? b.ninl[p] : 0;
     // ---- outputs default to the verifier's (two_view_estimator.py:334-338: without BA post_ba = pre_ba)
-    for (int i = tid; i < vp.M; i += kBaThreads) { b.ba_mask[vp.m0 + i] = ok ? b.mask[vp.m0 + i] : 0; b.tri[vp.m0 + i] = 0; }
+    for (int i = tid; i < vp.M; i += kBaThreads) b.ba_mask[vp.m0 + i] = ok ? b.mask[vp.m0 + i] : 0;
     if (tid < 9) b.out_R[9 * p + tid] = ok ? b.R[9 * p + tid] : 0.0;
     if (tid < 3) b.out_t[3 * p + tid] = ok ? b.t[3 * p + tid] : 0.0;
     if (tid == 0) { b.out_n[p] = n_ver; b.out_status[p] = 1; b.out_iters[p] = 0; }
@@ -179,72 +180,86 @@ __global__ void __launch_bounds__(kBaThreads) two_view_ba_kernel(StoreView st, B
     // ---- triangulation of every verified correspondence: DLT on the calibrated rays, three Gauss-Newton steps on the pixel
     // reprojection error (gtsam.triangulatePoint3(optimize=True)), cheirality in both cameras, reprojection errors below
     // triangulation_options.reproj_error_threshold (point3d_initializer.py:262-281)
+    // The tracks that pass are appended to the pair's DENSE list in row order (ballot + prefix over the CTA, deterministic), so
+    // the LM passes below run with full warps whatever the inlier ratio is.
     double acc[21];
-    for (int k = 0; k < 21; ++k) acc[k] = 0.0;
-    for (int i = tid; i < vp.M; i += kBaThreads) {
-        if (!b.mask[vp.m0 + i]) { b.ba_mask[vp.m0 + i] = 0; continue; }
-        const uint2 m = match[i];
-        const double2 m1 = kp1[m.x], m2 = kp2[m.y];
-        double x1, y1, x2, y2;
-        vm::calibrate(m1.x, m1.y, vp.cal1, &x1, &y1);
-        vm::calibrate(m2.x, m2.y, vp.cal2, &x2, &y2);
-        const double* R = s_pose.R;
-        const double* t = s_pose.t;
-        // rows of the DLT matrix: x P_3 - P_1, y P_3 - P_2 for P = [I | 0] and [R | t]
-        double A[16] = {-1, 0, x1, 0, 0, -1, y1, 0,
-                        x2 * R[6] - R[0], x2 * R[7] - R[1], x2 * R[8] - R[2], x2 * t[2] - t[0],
-                        y2 * R[6] - R[3], y2 * R[7] - R[4], y2 * R[8] - R[5], y2 * t[2] - t[1]};
-        double Q[4];
-        vm::dlt_null4(A, Q);
-        bool good = fabs(Q[3]) > 1e-300;
+    int n_tri = 0;                                       // same value in every thread
+    int* didx = b.idx + vp.m0;
+    double* Xcur = b.X + 3 * vp.m0;
+    double* Xtry = b.Xn + 3 * vp.m0;
+    const int warp = tid >> 5, lane = tid & 31;
+    for (int base = 0; base < vp.M; base += kBaThreads) {
+        const int i = base + tid;
+        bool good = false;
         double X[3] = {0, 0, 1};
-        if (good) {
-            X[0] = Q[0] / Q[3]; X[1] = Q[1] / Q[3]; X[2] = Q[2] / Q[3];
-            for (int it = 0; it < 3; ++it) {
-                BaLin L;
-                ba_linearise(s_pose, vp.cal1, vp.cal2, X, m1, m2, 1e300, true, L);        // no robust weight in the triangulation
-                double V[6] = {0, 0, 0, 0, 0, 0}, g[3] = {0, 0, 0};
-                for (int r = 0; r < 2; ++r) {
-                    const double* a0 = L.A0 + 3 * r;
-                    const double* a1 = L.A1 + 3 * r;
-                    const double w0 = L.w0 > 0 ? 1.0 : 0.0, w1 = L.w1 > 0 ? 1.0 : 0.0;
-                    V[0] += w0 * a0[0] * a0[0] + w1 * a1[0] * a1[0]; V[1] += w0 * a0[0] * a0[1] + w1 * a1[0] * a1[1];
-                    V[2] += w0 * a0[0] * a0[2] + w1 * a1[0] * a1[2]; V[3] += w0 * a0[1] * a0[1] + w1 * a1[1] * a1[1];
-                    V[4] += w0 * a0[1] * a0[2] + w1 * a1[1] * a1[2]; V[5] += w0 * a0[2] * a0[2] + w1 * a1[2] * a1[2];
-                    for (int c = 0; c < 3; ++c) g[c] += w0 * a0[c] * L.e0[r] + w1 * a1[c] * L.e1[r];
-                }
-                double Vi[6];
-                if (!inv_sym3(V, Vi)) break;
-                X[0] -= Vi[0] * g[0] + Vi[1] * g[1] + Vi[2] * g[2];
-                X[1] -= Vi[1] * g[0] + Vi[3] * g[1] + Vi[4] * g[2];
-                X[2] -= Vi[2] * g[0] + Vi[4] * g[1] + Vi[5] * g[2];
-            }
-            double u, v;
-            const double rx = R[0] * X[0] + R[1] * X[1] + R[2] * X[2] + t[0], ry = R[3] * X[0] + R[4] * X[1] + R[5] * X[2] + t[1],
-                         rz = R[6] * X[0] + R[7] * X[1] + R[8] * X[2] + t[2];
-            good = X[2] > 0 && rz > 0 && isfinite(X[0]) && isfinite(X[1]) && isfinite(X[2]);     // TriangulationCheiralityException
+        if (i < vp.M && b.mask[vp.m0 + i]) {
+            const uint2 m = match[i];
+            const double2 m1 = kp1[m.x], m2 = kp2[m.y];
+            double x1, y1, x2, y2;
+            vm::calibrate(m1.x, m1.y, vp.cal1, &x1, &y1);
+            vm::calibrate(m2.x, m2.y, vp.cal2, &x2, &y2);
+            const double* R = s_pose.R;
+            const double* t = s_pose.t;
+            // rows of the DLT matrix: x P_3 - P_1, y P_3 - P_2 for P = [I | 0] and [R | t]
+            double A[16] = {-1, 0, x1, 0, 0, -1, y1, 0,
+                            x2 * R[6] - R[0], x2 * R[7] - R[1], x2 * R[8] - R[2], x2 * t[2] - t[0],
+                            y2 * R[6] - R[3], y2 * R[7] - R[4], y2 * R[8] - R[5], y2 * t[2] - t[1]};
+            double Q[4];
+            vm::dlt_null4(A, Q);
+            good = fabs(Q[3]) > 1e-300;
             if (good) {
-                good = ba_project(vp.cal1, X[0], X[1], X[2], &u, &v, nullptr) && hypot(u - m1.x, v - m1.y) < b.tri_thr;
-                good = good && ba_project(vp.cal2, rx, ry, rz, &u, &v, nullptr) && hypot(u - m2.x, v - m2.y) < b.tri_thr;
-            }
-            if (good && b.min_angle_deg > 0) {
-                // angle subtended at the landmark by the camera centres c1 = 0 and c2 = -R^T t (utils/tracks.py:82-102):
-                // X - c1 = X and X - c2 = R^T (R X + t)
-                const double ax = X[0], ay = X[1], az = X[2];
-                const double bx = R[0] * rx + R[3] * ry + R[6] * rz, by = R[1] * rx + R[4] * ry + R[7] * rz, bz = R[2] * rx + R[5] * ry + R[8] * rz;
-                const double cs = (ax * bx + ay * by + az * bz) / (sqrt(ax * ax + ay * ay + az * az) * sqrt(bx * bx + by * by + bz * bz));
-                good = acos(fmin(1.0, fmax(-1.0, cs))) * 57.29577951308232 >= b.min_angle_deg;
+                X[0] = Q[0] / Q[3]; X[1] = Q[1] / Q[3]; X[2] = Q[2] / Q[3];
+                for (int it = 0; it < 3; ++it) {
+                    BaLin L;
+                    ba_linearise(s_pose, vp.cal1, vp.cal2, X, m1, m2, 1e300, true, L);        // no robust weight in the triangulation
+                    double V[6] = {0, 0, 0, 0, 0, 0}, g[3] = {0, 0, 0};
+                    for (int r = 0; r < 2; ++r) {
+                        const double* a0 = L.A0 + 3 * r;
+                        const double* a1 = L.A1 + 3 * r;
+                        const double w0 = L.w0 > 0 ? 1.0 : 0.0, w1 = L.w1 > 0 ? 1.0 : 0.0;
+                        V[0] += w0 * a0[0] * a0[0] + w1 * a1[0] * a1[0]; V[1] += w0 * a0[0] * a0[1] + w1 * a1[0] * a1[1];
+                        V[2] += w0 * a0[0] * a0[2] + w1 * a1[0] * a1[2]; V[3] += w0 * a0[1] * a0[1] + w1 * a1[1] * a1[1];
+                        V[4] += w0 * a0[1] * a0[2] + w1 * a1[1] * a1[2]; V[5] += w0 * a0[2] * a0[2] + w1 * a1[2] * a1[2];
+                        for (int c = 0; c < 3; ++c) g[c] += w0 * a0[c] * L.e0[r] + w1 * a1[c] * L.e1[r];
+                    }
+                    double Vi[6];
+                    if (!inv_sym3(V, Vi)) break;
+                    X[0] -= Vi[0] * g[0] + Vi[1] * g[1] + Vi[2] * g[2];
+                    X[1] -= Vi[1] * g[0] + Vi[3] * g[1] + Vi[4] * g[2];
+                    X[2] -= Vi[2] * g[0] + Vi[4] * g[1] + Vi[5] * g[2];
+                }
+                double u, v;
+                const double rx = R[0] * X[0] + R[1] * X[1] + R[2] * X[2] + t[0], ry = R[3] * X[0] + R[4] * X[1] + R[5] * X[2] + t[1],
+                             rz = R[6] * X[0] + R[7] * X[1] + R[8] * X[2] + t[2];
+                good = X[2] > 0 && rz > 0 && isfinite(X[0]) && isfinite(X[1]) && isfinite(X[2]);     // TriangulationCheiralityException
+                if (good) {
+                    good = ba_project(vp.cal1, X[0], X[1], X[2], &u, &v, nullptr) && hypot(u - m1.x, v - m1.y) < b.tri_thr;
+                    good = good && ba_project(vp.cal2, rx, ry, rz, &u, &v, nullptr) && hypot(u - m2.x, v - m2.y) < b.tri_thr;
+                }
+                if (good && b.min_angle_deg > 0) {
+                    // angle subtended at the landmark by the camera centres c1 = 0 and c2 = -R^T t (utils/tracks.py:82-102):
+                    // X - c1 = X and X - c2 = R^T (R X + t)
+                    const double ax = X[0], ay = X[1], az = X[2];
+                    const double bx = R[0] * rx + R[3] * ry + R[6] * rz, by = R[1] * rx + R[4] * ry + R[7] * rz, bz = R[2] * rx + R[5] * ry + R[8] * rz;
+                    const double cs = (ax * bx + ay * by + az * bz) / (sqrt(ax * ax + ay * ay + az * az) * sqrt(bx * bx + by * by + bz * bz));
+                    good = acos(fmin(1.0, fmax(-1.0, cs))) * 57.29577951308232 >= b.min_angle_deg;
+                }
             }
         }
-        b.tri[vp.m0 + i] = good ? 1 : 0;
-        if (!good) b.ba_mask[vp.m0 + i] = 0;
-        double* Xo = b.X + 3 * (vp.m0 + i);
-        Xo[0] = X[0]; Xo[1] = X[1]; Xo[2] = X[2];
-        acc[0] += good ? 1.0 : 0.0;
+        if (i < vp.M) b.ba_mask[vp.m0 + i] = 0;          // rewritten by the filter at the end for the tracks that stay
+        const unsigned bal = __ballot_sync(0xffffffffu, good);
+        if (lane == 0) s_wcnt[warp] = __popc(bal);
+        __syncthreads();
+        int pos = n_tri + __popc(bal & ((1u << lane) - 1u));
+        for (int w = 0; w < warp; ++w) pos += s_wcnt[w];
+        if (good) {
+            didx[pos] = i;
+            Xcur[3 * pos] = X[0]; Xcur[3 * pos + 1] = X[1]; Xcur[3 * pos + 2] = X[2];
+        }
+        for (int w = 0; w < kBaThreads / 32; ++w) n_tri += s_wcnt[w];
+        __syncthreads();
     }
-    block_sum<1>(acc, s_red, s_out);
-    const int n_tri = static_cast<int>(s_out[0]);
-    __syncthreads();
+    __syncthreads();                                     // the dense list is read by other threads from here on
     if (n_tri == 0) {                                    // two_view_estimator.py:179-180: the initial pose, no correspondences
         if (tid == 0) { b.out_n[p] = 0; b.out_status[p] = 2; }
         return;
@@ -253,11 +268,10 @@ __global__ void __launch_bounds__(kBaThreads) two_view_ba_kernel(StoreView st, B
     // ---- robust cost at the start: 0.5 sum rho (gtsam's graph.error)
     auto cost_pass = [&](const BaPose& ps, const double* Xs) {
         double c[1] = {0.0};
-        for (int i = tid; i < vp.M; i += kBaThreads) {
-            if (!b.tri[vp.m0 + i]) continue;
-            const uint2 m = match[i];
+        for (int j = tid; j < n_tri; j += kBaThreads) {
+            const uint2 m = match[didx[j]];
             BaLin L;
-            ba_linearise(ps, vp.cal1, vp.cal2, Xs + 3 * (vp.m0 + i), kp1[m.x], kp2[m.y], b.huber_k, false, L);
+            ba_linearise(ps, vp.cal1, vp.cal2, Xs + 3 * j, kp1[m.x], kp2[m.y], b.huber_k, false, L);
             c[0] += huber_loss(L.e0[0] * L.e0[0] + L.e0[1] * L.e0[1], b.huber_k) + huber_loss(L.e1[0] * L.e1[0] + L.e1[1] * L.e1[1], b.huber_k);
         }
         block_sum<1>(c, s_red, s_out);
@@ -265,17 +279,16 @@ __global__ void __launch_bounds__(kBaThreads) two_view_ba_kernel(StoreView st, B
         __syncthreads();
         return r;
     };
-    double cost = cost_pass(s_pose, b.X);
+    double cost = cost_pass(s_pose, Xcur);
     double lambda = 1e-5;                                 // gtsam LevenbergMarquardtParams: lambdaInitial 1e-5, lambdaFactor 10,
     int iters = 0;                                        // lambdaUpperBound 1e5, relative / absolute error tolerance 1e-5
     for (int trial = 0; trial < 4 * b.max_iters && iters < b.max_iters; ++trial) {
         // pass 1: Schur complement of the points onto the pose: S = U - sum W (V + lambda I)^-1 W^T, rhs = -gc + sum W (V + lambda I)^-1 gp
         for (int k = 0; k < 21; ++k) acc[k] = 0.0;
-        for (int i = tid; i < vp.M; i += kBaThreads) {
-            if (!b.tri[vp.m0 + i]) continue;
-            const uint2 m = match[i];
+        for (int j = tid; j < n_tri; j += kBaThreads) {
+            const uint2 m = match[didx[j]];
             BaLin L;
-            ba_linearise(s_pose, vp.cal1, vp.cal2, b.X + 3 * (vp.m0 + i), kp1[m.x], kp2[m.y], b.huber_k, true, L);
+            ba_linearise(s_pose, vp.cal1, vp.cal2, Xcur + 3 * j, kp1[m.x], kp2[m.y], b.huber_k, true, L);
             double V[6] = {lambda, 0, 0, lambda, 0, lambda}, gp[3] = {0, 0, 0}, W[15], gc[5] = {0, 0, 0, 0, 0};
             for (int k = 0; k < 15; ++k) W[k] = 0.0;
             for (int r = 0; r < 2; ++r) {
@@ -347,11 +360,10 @@ __global__ void __launch_bounds__(kBaThreads) two_view_ba_kernel(StoreView st, B
         if (!s_ctrl) { lambda *= 10.0; if (lambda > 1e5) break; continue; }
         // pass 2: dX = -(V + lambda I)^-1 (gp + W^T dc) per point (same linearisation), trial points, robust cost at the trial state
         double c1[1] = {0.0};
-        for (int i = tid; i < vp.M; i += kBaThreads) {
-            if (!b.tri[vp.m0 + i]) continue;
-            const uint2 m = match[i];
+        for (int j = tid; j < n_tri; j += kBaThreads) {
+            const uint2 m = match[didx[j]];
             const double2 m1 = kp1[m.x], m2 = kp2[m.y];
-            const double* Xc = b.X + 3 * (vp.m0 + i);
+            const double* Xc = Xcur + 3 * j;
             BaLin L;
             ba_linearise(s_pose, vp.cal1, vp.cal2, Xc, m1, m2, b.huber_k, true, L);
             double V[6] = {lambda, 0, 0, lambda, 0, lambda}, g[3] = {0, 0, 0};
@@ -372,7 +384,7 @@ __global__ void __launch_bounds__(kBaThreads) two_view_ba_kernel(StoreView st, B
                 Xt[1] -= Vi[1] * g[0] + Vi[3] * g[1] + Vi[4] * g[2];
                 Xt[2] -= Vi[2] * g[0] + Vi[4] * g[1] + Vi[5] * g[2];
             }
-            double* Xo = b.Xn + 3 * (vp.m0 + i);
+            double* Xo = Xtry + 3 * j;
             Xo[0] = Xt[0]; Xo[1] = Xt[1]; Xo[2] = Xt[2];
             BaLin T;
             ba_linearise(s_trial, vp.cal1, vp.cal2, Xt, m1, m2, b.huber_k, false, T);
@@ -382,13 +394,8 @@ __global__ void __launch_bounds__(kBaThreads) two_view_ba_kernel(StoreView st, B
         const double new_cost = s_out[0];
         __syncthreads();
         if (new_cost < cost && isfinite(new_cost)) {
-            // accept: the trial state becomes current (every thread copies the points it owns: same stride as above)
-            for (int i = tid; i < vp.M; i += kBaThreads) {
-                if (!b.tri[vp.m0 + i]) continue;
-                const double* Xs = b.Xn + 3 * (vp.m0 + i);
-                double* Xd = b.X + 3 * (vp.m0 + i);
-                Xd[0] = Xs[0]; Xd[1] = Xs[1]; Xd[2] = Xs[2];
-            }
+            // accept: the trial state becomes current (the point buffers swap roles)
+            double* sw = Xcur; Xcur = Xtry; Xtry = sw;
             if (tid == 0) s_pose = s_trial;
             __syncthreads();
             const double dec = cost - new_cost;
@@ -405,11 +412,11 @@ __global__ void __launch_bounds__(kBaThreads) two_view_ba_kernel(StoreView st, B
 
     // ---- filter_landmarks(ba_reproj_error_thresholds[-1]): a track stays when both reprojection errors are below the threshold
     double nv[1] = {0.0};
-    for (int i = tid; i < vp.M; i += kBaThreads) {
-        if (!b.tri[vp.m0 + i]) continue;
+    for (int j = tid; j < n_tri; j += kBaThreads) {
+        const int i = didx[j];
         const uint2 m = match[i];
         const double2 m1 = kp1[m.x], m2 = kp2[m.y];
-        const double* X = b.X + 3 * (vp.m0 + i);
+        const double* X = Xcur + 3 * j;
         const double* R = s_pose.R;
         double u, v;
         bool good = ba_project(vp.cal1, X[0], X[1], X[2], &u, &v, nullptr) && hypot(u - m1.x, v - m1.y) < b.ba_thr;
@@ -433,7 +440,7 @@ __global__ void __launch_bounds__(kBaThreads) two_view_ba_kernel(StoreView st, B
 
 using namespace g2v;
 
-// v_bufs slots of this stage: 27 = points (current | trial), 28 = per-row flags (triangulated | valid after BA),
+// v_bufs slots of this stage: 27 = points (two buffers), 28 = dense track list (int) | valid-after-BA flags per row,
 // 29 = per-pair outputs (R 9, t 3 doubles; valid tracks, status, iterations as ints)
 extern "C" int gtsfm_two_view_ba_batch(gtsfm_ctx* c, int n_pairs, const gtsfm_two_view_ba_params* prm, double* i2Ri1, double* i2Ui1,
                                        uint8_t* valid_mask, int32_t* num_valid, int32_t* ba_status, int32_t* iterations)
@@ -448,13 +455,13 @@ extern "C" int gtsfm_two_view_ba_batch(gtsfm_ctx* c, int n_pairs, const gtsfm_tw
     DevBuf* vb = c->v_bufs;
     const size_t total = static_cast<size_t>(c->verify_total), P = static_cast<size_t>(n_pairs);
     G2V_CUDA(c, vb[27].reserve(48 * (total + 1), false, s));
-    G2V_CUDA(c, vb[28].reserve(2 * (total + 1), false, s));
+    G2V_CUDA(c, vb[28].reserve(5 * (total + 1), false, s));
     G2V_CUDA(c, vb[29].reserve(112 * P, false, s));
     BaBufs b{};
     b.pairs = vb[0].as<VPair>(); b.match = c->match_out.p; b.mask = vb[12].as<unsigned char>();
     b.R = vb[7].as<double>(); b.t = vb[8].as<double>(); b.ninl = vb[10].as<int>(); b.status = vb[11].as<int>();
     b.X = vb[27].as<double>(); b.Xn = b.X + 3 * (total + 1);
-    b.tri = vb[28].as<unsigned char>(); b.ba_mask = b.tri + (total + 1);
+    b.idx = vb[28].as<int>(); b.ba_mask = vb[28].as<unsigned char>() + 4 * (total + 1);
     b.out_R = vb[29].as<double>(); b.out_t = b.out_R + 9 * P;
     b.out_n = reinterpret_cast<int*>(b.out_t + 3 * P); b.out_status = b.out_n + P; b.out_iters = b.out_status + P;
     b.min_inliers = prm->min_num_inliers; b.max_iters = prm->max_iterations;
