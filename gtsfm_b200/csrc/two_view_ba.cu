@@ -147,7 +147,7 @@ __device__ __forceinline__ void ba_linearise(const BaPose& ps, const double* cal
 constexpr int kBaThreads = 128;
 static_assert(kBaThreads == kFinThreads, "block_sum is written for kFinThreads threads");
 
-__global__ void __launch_bounds__(kBaThreads) two_view_ba_kernel(StoreView st, BaBufs b, int n_pairs)
+__global__ void __launch_bounds__(kBaThreads, 3) two_view_ba_kernel(StoreView st, BaBufs b, int n_pairs)
 {
     __shared__ double s_red[kBaThreads / 32][24];
     __shared__ double s_out[24];
