@@ -240,58 +240,62 @@ __global__ void __launch_bounds__(256) score_kernel(VerifyBufs b, VerifyDims d, 
         }
         if (threadIdx.x == 0) s_next = 0;
         __syncthreads();
-        for (;;) {
-            // candidates are handed out dynamically: early exits make their cost very uneven
-            int ci = 0;
-            if (lane == 0) ci = atomicAdd(&s_next, 1);
-            ci = __shfl_sync(0xffffffffu, ci, 0);
-            if (ci >= n) break;
-            if (s_dead[ci]) continue;
+        // One candidate's state while a warp scores it over the staged tile
+        struct Cand { f32x2 p[9]; float e[9]; float before, acc0, acc1; int ci, done; bool dead; };
+        auto load_cand = [&](Cand& c, int ci) {
             const int code = s_cand[ci];
             const float* E = Ebase + ((code >> 4) * vm::kMaxCand + (code & 15)) * 9;
-            const float e0 = __ldg(E), e1 = __ldg(E + 1), e2 = __ldg(E + 2), e3 = __ldg(E + 3), e4 = __ldg(E + 4), e5 = __ldg(E + 5),
-                        e6 = __ldg(E + 6), e7 = __ldg(E + 7), e8 = __ldg(E + 8);
-            const f32x2 p0 = pk2(e0, e0), p1 = pk2(e1, e1), p2 = pk2(e2, e2), p3 = pk2(e3, e3), p4 = pk2(e4, e4), p5 = pk2(e5, e5),
-                        p6 = pk2(e6, e6), p7 = pk2(e7, e7), p8 = pk2(e8, e8);
-            const float before = s_cost[ci];           // cost over the previous tiles
-            float acc0 = 0.f, acc1 = 0.f;
-            bool dead = false;
-            int done = 0;
-            // Early exit (exact): the MSAC cost only grows, so a candidate whose partial cost already exceeds the lowest
-            // COMPLETE cost of the pair (by more than the fp32 accumulation noise) cannot be the minimum.
-            for (int c0 = 0; c0 < nq; c0 += kScoreCheck) {
+#pragma unroll
+            for (int k = 0; k < 9; ++k) { c.e[k] = __ldg(E + k); c.p[k] = pk2(c.e[k], c.e[k]); }
+            c.before = s_cost[ci];                     // cost over the previous tiles
+            c.acc0 = c.acc1 = 0.f; c.ci = ci; c.done = 0; c.dead = false;
+        };
+        // squared Sampson distances of the packed pair (A, B) under candidate c, clamped and added to its two accumulators
+        auto eval = [&](Cand& c, const ulonglong2& A, const ulonglong2& B) {
+            const f32x2 l0 = fma2(c.p[0], A.x, fma2(c.p[1], A.y, c.p[2])), l1 = fma2(c.p[3], A.x, fma2(c.p[4], A.y, c.p[5])),
+                        l2 = fma2(c.p[6], A.x, fma2(c.p[7], A.y, c.p[8]));
+            const f32x2 m0 = fma2(c.p[0], B.x, fma2(c.p[3], B.y, c.p[6])), m1 = fma2(c.p[1], B.x, fma2(c.p[4], B.y, c.p[7]));
+            const f32x2 num = fma2(B.x, l0, fma2(B.y, l1, l2));
+            const f32x2 den = fma2(l0, l0, fma2(l1, l1, fma2(m0, m0, mul2(m1, m1))));
+            float d0, d1;
+            upk2(den, d0, d1);
+            const f32x2 sq = mul2(mul2(num, num), pk2(rcp_fast(d0), rcp_fast(d1)));
+            float s0, s1;
+            upk2(sq, s0, s1);
+            c.acc0 += fminf(s0, thr2);                 // NaN -> thr2: counts as an outlier
+            c.acc1 += fminf(s1, thr2);
+        };
+        // Early exit (exact): the MSAC cost only grows, so a candidate whose partial cost already exceeds the lowest COMPLETE
+        // cost of the pair (by more than the fp32 accumulation noise) cannot be the minimum.  The warp total of the partial
+        // costs is taken in fixed point (one REDUX instead of a five-step shuffle tree): every lane's share is below thr2 * M,
+        // so 2^30 / (thr2 * M) per unit cannot overflow; the rounding (< 2^-25 of the full scale) is far inside the 1.001 margin.
+        auto check = [&](Cand& c, int c1, float bestv) {
+            c.done = c1;
+            const int part_q = __float2int_rn((c.acc0 + c.acc1) * q_scale);
+            const float part = static_cast<float>(__reduce_add_sync(0xffffffffu, part_q)) * q_inv;
+            if (c.before + part > bestv * 1.001f) c.dead = true;
+        };
+        auto run_single = [&](Cand& c, int from) {
+            for (int c0 = from; c0 < nq && !c.dead; c0 += kScoreCheck) {
                 const int c1 = min(nq, c0 + kScoreCheck);
-                const float bestv = *best;                 // issued here, consumed after the segment: latency hidden
+                const float bestv = *best;             // issued here, consumed after the segment: latency hidden
 #pragma unroll 2
                 for (int k = c0 + lane; k < c1; k += 32) {
                     const ulonglong2 A = *reinterpret_cast<const ulonglong2*>(sA + k);   // x1 pair, y1 pair
                     const ulonglong2 B = *reinterpret_cast<const ulonglong2*>(sB + k);   // x2 pair, y2 pair
-                    const f32x2 l0 = fma2(p0, A.x, fma2(p1, A.y, p2)), l1 = fma2(p3, A.x, fma2(p4, A.y, p5)), l2 = fma2(p6, A.x, fma2(p7, A.y, p8));
-                    const f32x2 m0 = fma2(p0, B.x, fma2(p3, B.y, p6)), m1 = fma2(p1, B.x, fma2(p4, B.y, p7));
-                    const f32x2 num = fma2(B.x, l0, fma2(B.y, l1, l2));
-                    const f32x2 den = fma2(l0, l0, fma2(l1, l1, fma2(m0, m0, mul2(m1, m1))));
-                    float d0, d1;
-                    upk2(den, d0, d1);
-                    const f32x2 sq = mul2(mul2(num, num), pk2(rcp_fast(d0), rcp_fast(d1)));
-                    float s0, s1;
-                    upk2(sq, s0, s1);
-                    acc0 += fminf(s0, thr2);               // NaN -> thr2: counts as an outlier
-                    acc1 += fminf(s1, thr2);
+                    eval(c, A, B);
                 }
-                done = c1;
-                // warp total of the partial costs in fixed point (one REDUX instead of a five-step shuffle tree): every
-                // lane's share is below thr2 * M, so 2^30 / (thr2 * M) per unit cannot overflow; the rounding (< 2^-25
-                // of the full scale) is far inside the 1.001 margin of the test
-                const int part_q = __float2int_rn((acc0 + acc1) * q_scale);
-                const float part = static_cast<float>(__reduce_add_sync(0xffffffffu, part_q)) * q_inv;
-                if (before + part > bestv * 1.001f) { dead = true; break; }
+                check(c, c1, bestv);
             }
-            float acc = acc0 + acc1;
-            if (!dead && (tn & 1) && lane == 0) {      // odd tail: first half of the last (duplicated) pair
+        };
+        auto finish = [&](Cand& c) {
+            float acc = c.acc0 + c.acc1;
+            if (!c.dead && (tn & 1) && lane == 0) {    // odd tail: first half of the last (duplicated) pair
                 const float4 a4 = sA[nq], b4 = sB[nq];
                 const float x1 = a4.x, y1 = a4.z, x2 = b4.x, y2 = b4.z;
-                const float l0 = fmaf(e0, x1, fmaf(e1, y1, e2)), l1 = fmaf(e3, x1, fmaf(e4, y1, e5)), l2 = fmaf(e6, x1, fmaf(e7, y1, e8));
-                const float m0 = fmaf(e0, x2, fmaf(e3, y2, e6)), m1 = fmaf(e1, x2, fmaf(e4, y2, e7));
+                const float* e = c.e;
+                const float l0 = fmaf(e[0], x1, fmaf(e[1], y1, e[2])), l1 = fmaf(e[3], x1, fmaf(e[4], y1, e[5])), l2 = fmaf(e[6], x1, fmaf(e[7], y1, e[8]));
+                const float m0 = fmaf(e[0], x2, fmaf(e[3], y2, e[6])), m1 = fmaf(e[1], x2, fmaf(e[4], y2, e[7]));
                 const float num = fmaf(x2, l0, fmaf(y2, l1, l2));
                 const float den = fmaf(l0, l0, fmaf(l1, l1, fmaf(m0, m0, m1 * m1)));
                 acc += fminf(num * num * rcp_fast(den), thr2);
@@ -299,12 +303,54 @@ __global__ void __launch_bounds__(256) score_kernel(VerifyBufs b, VerifyDims d, 
 #pragma unroll
             for (int off = 16; off > 0; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
             if (lane == 0) {
-                const float total = before + acc;
-                s_cost[ci] = total;
-                if (dead) s_dead[ci] = 1;
+                const float total = c.before + acc;
+                s_cost[c.ci] = total;
+                if (c.dead) s_dead[c.ci] = 1;
                 else if (last_tile) atomicMin(b.best_cost + p, __float_as_uint(total));
-                atomicAdd(&s_exec, static_cast<unsigned long long>(2 * done + (dead ? 0 : (tn & 1))));
+                atomicAdd(&s_exec, static_cast<unsigned long long>(2 * c.done + (c.dead ? 0 : (tn & 1))));
             }
+        };
+        for (;;) {
+            // candidates are handed out dynamically, two at a time: early exits make their cost very uneven.  A warp scores
+            // its two candidates in ONE pass over the tile -- every LDS.128 feeds both (the shared-memory pipe was the limiter
+            // with one candidate per pass) -- and each keeps its own accumulators, checks and exit, so a candidate's cost does
+            // not depend on its partner.
+            int ci = 0;
+            if (lane == 0) ci = atomicAdd(&s_next, 2);
+            ci = __shfl_sync(0xffffffffu, ci, 0);
+            if (ci >= n) break;
+            const bool liveA = !s_dead[ci], liveB = ci + 1 < n && !s_dead[ci + 1];
+            if (!liveA && !liveB) continue;
+            if (liveA != liveB) {
+                Cand c;
+                load_cand(c, liveA ? ci : ci + 1);
+                run_single(c, 0);
+                finish(c);
+                continue;
+            }
+            Cand ca, cb;
+            load_cand(ca, ci);
+            load_cand(cb, ci + 1);
+            for (int c0 = 0; c0 < nq; c0 += kScoreCheck) {
+                const int c1 = min(nq, c0 + kScoreCheck);
+                const float bestv = *best;
+#pragma unroll 2
+                for (int k = c0 + lane; k < c1; k += 32) {
+                    const ulonglong2 A = *reinterpret_cast<const ulonglong2*>(sA + k);
+                    const ulonglong2 B = *reinterpret_cast<const ulonglong2*>(sB + k);
+                    eval(ca, A, B);
+                    eval(cb, A, B);
+                }
+                check(ca, c1, bestv);
+                check(cb, c1, bestv);
+                if (ca.dead || cb.dead) {              // the survivor (if any) goes on alone
+                    if (!ca.dead) run_single(ca, c1);
+                    if (!cb.dead) run_single(cb, c1);
+                    break;
+                }
+            }
+            finish(ca);
+            finish(cb);
         }
     }
     __syncthreads();
