@@ -170,7 +170,13 @@ class TwoViewEstimator:
 def _apply_two_view_estimator_shard(two_view_estimator, keypoints: Dict[int, Keypoints], putative: Dict[Tuple[int, int], np.ndarray],
                                     intrinsics: Dict[int, Any], priors: Dict[Tuple[int, int], Any], gt_cameras: Dict[int, Any],
                                     gt_scene_mesh: Optional[Any], device: int) -> Dict[Tuple[int, int], TWO_VIEW_OUTPUT]:
-    return two_view_estimator.run_2view_batch(keypoints, putative, intrinsics, priors, gt_cameras, gt_scene_mesh, device=device)
+    if hasattr(two_view_estimator, "run_2view_batch"):
+        return two_view_estimator.run_2view_batch(keypoints, putative, intrinsics, priors, gt_cameras, gt_scene_mesh, device=device)
+    # a foreign estimator (only run_2view): the reference's per-pair loop (two_view_estimator.py:567-584) inside the shard
+    return {(int(i), int(j)): two_view_estimator.run_2view(
+        keypoints[i], keypoints[j], corr, intrinsics[i], intrinsics[j], priors.get((i, j)) if priors else None,
+        gt_cameras[i] if gt_cameras is not None else None, gt_cameras[j] if gt_cameras is not None else None, gt_scene_mesh)
+        for (i, j), corr in putative.items()}
 
 
 def run_two_view_estimator_as_futures(client: Any, two_view_estimator: TwoViewEstimator, keypoints_list: List[Keypoints],

@@ -77,6 +77,35 @@ class TwoViewEstimatorCacher:
         self.misses += len(missing)
         return hits, missing, paths
 
+    def run_2view_batch(self, keypoints, putative_corr_idxs_dict: Dict[Tuple[int, int], np.ndarray], camera_intrinsics,
+                        relative_pose_priors=None, gt_cameras=None, gt_scene_mesh: Optional[Any] = None,
+                        device: Optional[int] = None) -> Dict[Tuple[int, int], Any]:
+        """TwoViewEstimator.run_2view_batch behind the cache (what run_two_view_estimator_as_futures calls per GPU shard when
+        the configuration wraps the estimator, configs/sift_front_end.yaml:36-39): the pairs with an entry come from disk, the
+        misses go to the wrapped estimator as ONE batch (per pair when it has no batched path) and are written back.  Keys and
+        order of the input dictionary."""
+        putative = {(int(k[0]), int(k[1])): v for k, v in putative_corr_idxs_dict.items()}
+        keys = list(putative.keys())
+        if not keys:
+            return {}
+        hits, missing, paths = self.lookup_batch(keypoints, np.asarray(keys).reshape(-1, 2), [putative[k] for k in keys])
+        fresh: Dict[Tuple[int, int], Any] = {}
+        if missing:
+            miss_keys = [keys[p] for p in missing]
+            sub = {k: putative[k] for k in miss_keys}
+            priors = {k: relative_pose_priors.get(k) for k in miss_keys} if relative_pose_priors else None
+            if hasattr(self._two_view_estimator, "run_2view_batch"):
+                fresh = self._two_view_estimator.run_2view_batch(keypoints, sub, camera_intrinsics, priors, gt_cameras, gt_scene_mesh,
+                                                                 device=device)
+            else:
+                for (i, j) in miss_keys:
+                    fresh[(i, j)] = self._two_view_estimator.run_2view(
+                        keypoints[i], keypoints[j], sub[(i, j)], camera_intrinsics[i], camera_intrinsics[j],
+                        priors[(i, j)] if priors else None, gt_cameras[i] if gt_cameras is not None else None,
+                        gt_cameras[j] if gt_cameras is not None else None, gt_scene_mesh)
+            self.store_batch(paths, missing, [fresh[k] for k in miss_keys])
+        return {k: (hits[p] if p in hits else fresh[k]) for p, k in enumerate(keys)}
+
     @staticmethod
     def store_batch(paths: Sequence[Path], positions: Sequence[int], results: Sequence[Any]) -> None:
         for p, r in zip(positions, results):

@@ -158,3 +158,40 @@ def test_two_view_cacher_hit_miss_and_batch(gold, tmp_path):
     cacher.store_batch(paths, missing, [("R2", "U2", np.zeros((0, 2)), None, None, None)])
     hits, missing, _ = cacher.lookup_batch(kps, pairs, putative)
     assert sorted(hits) == [0, 1] and not missing and hits[1][0] == "R2"
+
+
+def test_two_view_cacher_run_2view_batch_sends_only_misses(gold, tmp_path):
+    """The default configuration wraps the estimator in the cacher (configs/sift_front_end.yaml:36-39), so the per-shard call of
+    run_two_view_estimator_as_futures lands here: hits from disk, the misses as ONE batch, everything in the input order."""
+    from gtsfm_b200.two_view_estimator import run_two_view_estimator_as_futures
+    kps = [Keypoints(coordinates=gold["t0_c1"]), Keypoints(coordinates=gold["t0_c2"]), Keypoints(coordinates=gold["t1_c1"]),
+           Keypoints(coordinates=gold["t1_c2"])]
+    putative = {(0, 1): gold["t0_idx"], (2, 3): gold["t1_idx"], (1, 0): np.ascontiguousarray(gold["t0_idx"][:5, ::-1])}
+
+    class Inner:
+        def __init__(self):
+            self.batches = []
+
+        def run_2view_batch(self, keypoints, corr, intrinsics, priors=None, gt_cameras=None, gt_scene_mesh=None, device=None):
+            self.batches.append(list(corr.keys()))
+            return {k: ("R%d%d" % k, "U", np.asarray(v)[:2], None, None, None) for k, v in corr.items()}
+
+    inner = Inner()
+    cacher = TwoViewEstimatorCacher(inner, cache_root=tmp_path)
+    cacher.store_batch([cacher._path(two_view_cache_key(kps[2], kps[3], putative[(2, 3)]))], [0], [("warm", "U", np.zeros((0, 2)), None, None, None)])
+    out = cacher.run_2view_batch(kps, putative, [None] * 4)
+    assert list(out.keys()) == [(0, 1), (2, 3), (1, 0)] and inner.batches == [[(0, 1), (1, 0)]]
+    assert out[(2, 3)][0] == "warm" and out[(0, 1)][0] == "R01" and out[(1, 0)][0] == "R10"
+    again = cacher.run_2view_batch(kps, putative, [None] * 4)                      # everything is warm now
+    assert inner.batches == [[(0, 1), (1, 0)]] and again[(1, 0)][0] == "R10" and cacher.hits == 1 + 3
+    # through the batched caller (one shard, no client), and with a per-pair-only estimator behind the cache
+    out2 = run_two_view_estimator_as_futures(None, cacher, kps, putative, [None] * 4, {}, None, None, num_shards=1)
+    assert list(out2.keys()) == list(putative.keys()) and out2[(0, 1)][0] == "R01"
+    per_pair = MagicMock(spec=["run_2view"])
+    per_pair.run_2view.return_value = ("P", "U", np.zeros((0, 2)), None, None, None)
+    cold = TwoViewEstimatorCacher(per_pair, cache_root=tmp_path / "cold")
+    out3 = run_two_view_estimator_as_futures(None, cold, kps, putative, [None] * 4, {}, None, None, num_shards=1)
+    assert per_pair.run_2view.call_count == 3 and out3[(2, 3)][0] == "P"
+    # a foreign estimator without the cacher: the reference's per-pair loop inside the shard
+    out4 = run_two_view_estimator_as_futures(None, per_pair, kps, putative, [None] * 4, {}, None, None, num_shards=1)
+    assert per_pair.run_2view.call_count == 6 and list(out4.keys()) == list(putative.keys())
