@@ -106,7 +106,7 @@ int gtsfm_match_batch(gtsfm_ctx* c, const int32_t* pairs, int n_pairs, double ra
         pd.q_maxn2 = qa.max_norm2; pd.t_maxn2 = tb.max_norm2;
         const long long rp = (pd.path == 0 || pd.path == 2) ? static_cast<long long>(pd.nq_pad) * (pd.nt_pad / kHalfT) : 0;
         const int n_tg = (pd.nq_pad / kTileQ + kFlushTiles - 1) / kFlushTiles;      // path 2: column minima per group of 4 query tiles
-        const long long cr = pd.path == 0 ? static_cast<long long>(pd.nt_pad) * kTileQ
+        const long long cr = pd.path == 0 ? static_cast<long long>(pd.nt_pad) * 4       // folded column minima: v1, v2, class (+ pad)
                                           : pd.path == 2 ? static_cast<long long>(pd.nt_pad) * n_tg * kTileQ : 0;
         const int items = pd.path == 0 && pd.nq > 0 ? pd.nt_pad / kBlockT : 0;
         const int fitems = pd.path == 2 && pd.nq > 0 ? pd.nt_pad / kBlockT : 0;

@@ -95,62 +95,31 @@ __global__ void __launch_bounds__(128) merge_rows_kernel(StoreView st, MatchWork
     w.row_key[pos] = static_cast<unsigned>((hb1 << 3) | g1) | (slot << 16);
 }
 
-// merge, columns: eight lanes per train column (four float4 loads each: a column's 512 bytes are read in 128-byte
-// pieces), kColsPerCta columns per CTA.  Every CTA lies inside one pair because column ranges start on multiples of 256,
-// so the pair lookup is done once per CTA.  col_d1 <- k1, col_d2 <- k2, col_key <- winning lane class | slot << 8.
-constexpr int kColsPerCta = 64;
+// merge, columns: the screening kernel already folded the 128 lane classes of every column (match_screen.cu), so this is a
+// 12-byte read per column: col_d1 <- k1, col_d2 <- k2, col_key <- winning lane class | slot << 8.  Every CTA lies inside one
+// pair because column ranges start on multiples of 256, so the pair lookup is done once per CTA.
+constexpr int kColsPerCta = 256;
 __global__ void __launch_bounds__(256) merge_cols_kernel(StoreView st, MatchWork w, long long total_cols)
 {
-    const int l8 = threadIdx.x & 7, sub = threadIdx.x >> 3;       // 32 columns per pass
     const long long pos0 = static_cast<long long>(blockIdx.x) * kColsPerCta;
-    if (pos0 >= total_cols) return;
+    const long long pos = pos0 + threadIdx.x;
+    if (pos >= total_cols) return;
     const int p = find_by_cb_base(w.pairs, w.n_pairs, pos0);
     const PairDesc pd = w.pairs[p];
     if (pd.path != 0) return;
-#pragma unroll
-    for (int u0 = 0; u0 < kColsPerCta; u0 += 32) {
-        const long long pos = pos0 + u0 + sub;
-        const int j = static_cast<int>(pos - pd.cb_base);
-        const bool live = j < pd.nt && st.valid[pd.t_row0 + j];
-        float k1 = kHuge * 8.0f, k2 = kHuge * 8.0f;
-        int c1 = 0;
-        if (live) {
-            const float4* src = reinterpret_cast<const float4*>(w.colraw + pd.cr_base + static_cast<long long>(j) * kTileQ) + l8;
-            float4 c4[4];
-#pragma unroll
-            for (int u = 0; u < 4; ++u) c4[u] = __ldg(src + 8 * u);
-#pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                const float cv[4] = {c4[u].x, c4[u].y, c4[u].z, c4[u].w};
-#pragma unroll
-                for (int v = 0; v < 4; ++v) {
-                    const bool lt = cv[v] < k1;                   // ascending class order: the lowest class wins ties
-                    k2 = lt ? k1 : fminf(k2, cv[v]);
-                    c1 = lt ? 32 * u + 4 * l8 + v : c1;
-                    k1 = fminf(k1, cv[v]);
-                }
-            }
-        }
-#pragma unroll
-        for (int off = 4; off > 0; off >>= 1) {
-            const float o1 = __shfl_xor_sync(0xffffffffu, k1, off), o2 = __shfl_xor_sync(0xffffffffu, k2, off);
-            const int oc = __shfl_xor_sync(0xffffffffu, c1, off);
-            const bool take = (o1 < k1) || (o1 == k1 && oc < c1);
-            const float lose = take ? k1 : o1;
-            k2 = fminf(fminf(k2, o2), lose);
-            if (take) { k1 = o1; c1 = oc; }
-        }
-        if (l8 == 0) {
-            if (live) {
-                w.col_d1[pos] = k1;
-                w.col_d2[pos] = k2;
-                const unsigned slot = static_cast<unsigned>(atomicAdd(w.col_cnt + static_cast<long long>(p) * (kTileQ + 1) + c1, 1));
-                w.col_key[pos] = static_cast<unsigned>(c1) | (slot << 8);
-            } else {
-                w.col_key[pos] = 0xffffffffu;
-                if (j < pd.nt) { w.col_best[pos] = -1; w.col_d1[pos] = FLT_MAX; w.col_d2[pos] = FLT_MAX; }
-            }
-        }
+    const int j = static_cast<int>(pos - pd.cb_base);
+    if (j >= pd.nt_pad) return;
+    const bool live = j < pd.nt && st.valid[pd.t_row0 + j];
+    if (live) {
+        const float* cf = w.colraw + pd.cr_base + j;
+        const int c1 = __float_as_int(__ldg(cf + 2 * static_cast<long long>(pd.nt_pad)));
+        w.col_d1[pos] = __ldg(cf);
+        w.col_d2[pos] = __ldg(cf + pd.nt_pad);
+        const unsigned slot = static_cast<unsigned>(atomicAdd(w.col_cnt + static_cast<long long>(p) * (kTileQ + 1) + c1, 1));
+        w.col_key[pos] = static_cast<unsigned>(c1) | (slot << 8);
+    } else {
+        w.col_key[pos] = 0xffffffffu;
+        if (j < pd.nt) { w.col_best[pos] = -1; w.col_d1[pos] = FLT_MAX; w.col_d2[pos] = FLT_MAX; }
     }
 }
 

@@ -14,7 +14,9 @@
 //   * query direction: minimum of every group of 16 consecutive train columns (FMNMX3 chains), then best / second-best
 //     group of the 8 groups -> row partial (v1, v2, g1) per (query row, 128-column half block);
 //   * train direction: running minimum per column over all query tiles (1 FMNMX per element), i.e. the minimum of
-//     each "lane class" {q : q mod 128 == lane}; written once per item as colraw[t][lane].
+//     each "lane class" {q : q mod 128 == lane}; at the end of the item the 128 classes of a column are folded on the SM
+//     (CREDUX.MIN.F32 + ballot per warp, shared memory across the four warps) into (smallest, second smallest, winning
+//     class) and written as colraw[{v1, v2, class}][t].
 // The exact best / second-best and their indices are recovered by the resolve kernels, which recompute only the
 // winning group / lane class exactly (match_resolve.cu).  Nothing here is approximate for the integer path.
 #include "ptx.cuh"
@@ -38,7 +40,9 @@ template <int KCH> struct ScreenSmem {
     static constexpr int kOffTAug = KCH * kChunkT;
     static constexpr int kOffQ = kTBytes;
     static constexpr int kOffBar = kTBytes + kStages * kQBytes;
-    static constexpr int kTotal = kOffBar + 256 + 1024;     // barriers + alignment slack
+    static constexpr int kOffFold = kOffBar + 256;          // column fold: [2 halves][4 warps][128 columns] (v1, v2) + class bytes
+    static constexpr int kFoldBytes = 2 * 4 * kHalfT * (8 + 1);
+    static constexpr int kTotal = kOffFold + kFoldBytes + 1024;   // + alignment slack
 };
 
 struct ScreenArgs {
@@ -221,9 +225,44 @@ match_screen_kernel(const __grid_constant__ CUtensorMap tm_desc, const __grid_co
                 args.rp_g[e] = static_cast<uint8_t>(g1);
                 e += kTileQ;
             }
-            float* cr = args.colraw + args.pairs[p].cr_base + (static_cast<long long>(blk) * kBlockT + half * kHalfT) * kTileQ + m_local;
+            // ---- fold the column minima over the 128 lane classes before they leave the SM: per column the smallest value,
+            // the second smallest and the lowest class that holds the smallest (ties as merge_cols resolved them: ascending
+            // class order, strict <).  Inside a warp two CREDUX.MIN.F32 and a ballot per column; the four warps of a half meet
+            // in shared memory and thread m_local finishes column m_local.  9 bytes per column instead of 512.
+            uint2* s_fold = reinterpret_cast<uint2*>(smem + L::kOffFold) + (half * 4) * kHalfT;
+            uint8_t* s_fcls = smem + L::kOffFold + 2 * 4 * kHalfT * 8 + (half * 4) * kHalfT;
+            const int wq = warp & 3;
 #pragma unroll
-            for (int i = 0; i < kHalfT; ++i) cr[static_cast<long long>(i) * kTileQ] = cmin[i];
+            for (int i = 0; i < kHalfT; ++i) {
+                const float v = cmin[i];
+                const float mn = ptx::redux_min_f32(v);
+                const int l1 = __ffs(__ballot_sync(0xffffffffu, v == mn)) - 1;
+                const float mn2 = ptx::redux_min_f32(lane == l1 ? __int_as_float(0x7f800000) : v);
+                if (lane == (i & 31)) {
+                    s_fold[wq * kHalfT + i] = make_uint2(__float_as_uint(mn), __float_as_uint(mn2));
+                    s_fcls[wq * kHalfT + i] = static_cast<uint8_t>(lane_base + l1);
+                }
+            }
+            ptx::named_bar_sync(1 + half, kHalfT);
+            {
+                float k1 = kHuge * 8.0f, k2 = kHuge * 8.0f;
+                int c1 = 0;
+#pragma unroll
+                for (int w4 = 0; w4 < 4; ++w4) {
+                    const uint2 e2 = s_fold[w4 * kHalfT + m_local];
+                    const float a = __uint_as_float(e2.x), b2 = __uint_as_float(e2.y);
+                    const bool lt = a < k1;                      // strict: the lowest class wins ties
+                    k2 = lt ? fminf(k1, b2) : fminf(k2, a);
+                    c1 = lt ? s_fcls[w4 * kHalfT + m_local] : c1;
+                    k1 = fminf(k1, a);
+                }
+                const int nt_pad = args.pairs[p].nt_pad;
+                float* cf = args.colraw + args.pairs[p].cr_base + blk * kBlockT + half * kHalfT + m_local;
+                cf[0] = k1;
+                cf[nt_pad] = k2;
+                cf[2 * static_cast<long long>(nt_pad)] = __int_as_float(c1);
+            }
+            ptx::named_bar_sync(1 + half, kHalfT);               // the fold buffer is rewritten at the end of the next item
         }
     }
 

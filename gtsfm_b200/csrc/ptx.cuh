@@ -183,4 +183,14 @@ __host__ __device__ constexpr uint32_t idesc_f16(int M, int N, bool negate_b)
     return (1u << 4) | ((negate_b ? 1u : 0u) << 14) | (static_cast<uint32_t>(N >> 3) << 17) | (static_cast<uint32_t>(M >> 4) << 24);
 }
 
+// warp-wide float minimum in one instruction (CREDUX.MIN.F32, sm_100a)
+__device__ __forceinline__ float redux_min_f32(float v)
+{
+    float r;
+    asm volatile("redux.sync.min.f32 %0, %1, 0xffffffff;" : "=f"(r) : "f"(v));
+    return r;
+}
+// named barrier over `count` threads (a multiple of 32); id 0 is __syncthreads'
+__device__ __forceinline__ void named_bar_sync(int id, int count) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory"); }
+
 }  // namespace ptx

@@ -32,7 +32,7 @@ struct PairDesc {
                              // 2 = float, fp16 tensor-core screening + exact recompute of the winning group (ratio test off)
                              // 3 = binary descriptors, HAMMING distance (match_hamming.cu)
     long long rp_base;       // entry offset into the row-partial arrays: [nt_pad / kHalfT][nq_pad]
-    long long cr_base;       // float offset into colraw: [nt_pad][kTileQ]; path 2: [nt_pad][ceil(nq_pad / 512)][kTileQ]
+    long long cr_base;       // float offset into colraw: path 0 [{v1, v2, class, pad}][nt_pad]; path 2: [nt_pad][ceil(nq_pad / 512)][kTileQ]
     long long out_base;      // offset of this pair's slot in the per-query-row arrays and the match slot (capacity nq_pad)
     long long cb_base;       // offset of this pair's slot in the per-train-column arrays (capacity nt_pad)
     int img_q, img_t;        // image slots (for keypoints / calibration)

@@ -152,3 +152,34 @@ def test_two_view_estimator_with_bundle_adjustment_builds_the_reference_tuples(c
     key = pairs[5]
     one = mk(True).run_2view(kps[key[0]], kps[key[1]], putative[key], cals[key[0]], cals[key[1]], None, cams[key[0]], cams[key[1]])
     assert one[0] is not None and one[4].num_inliers_est_model == len(one[4].v_corr_idxs)
+
+
+def test_ba_with_radial_distortion_and_different_calibrations():
+    """Cal3Bundler k1, k2 != 0 and K1 != K2 through triangulation (fixed-point undistortion), projection and its Jacobian."""
+    import gtsfm_b200
+    from oracle import two_view_ba as OB
+    from tests.test_two_view_ba_restatement import _scene
+    cal1, cal2, R, t, X, u1, u2 = _scene(seed=3, n=260, noise=0.3, outliers=12)
+    rng = np.random.default_rng(1)
+    perm1, perm2 = rng.permutation(len(u1)), rng.permutation(len(u2))          # keypoint order differs from match order
+    k1, k2 = np.empty_like(u1), np.empty_like(u2)
+    k1[perm1], k2[perm2] = u1, u2
+    matches = np.stack([perm1, perm2], 1).astype(np.uint32)
+    ctx = gtsfm_b200.Context(0)
+    ctx.upload_image(0, None, k1, cal1)
+    ctx.upload_image(1, None, k2, cal2)
+    prm = gtsfm_b200.VerifyParams()
+    prm.threshold_px, prm.n_hypotheses, prm.lo_iters, prm.seed = 4.0, 512, 20, 7
+    v = ctx.verify_batch(np.array([[0, 1]], np.int32), prm, matches, np.array([0, len(matches)], np.int64))
+    assert v["status"][0] == 0 and v["n_inliers"][0] >= 200
+    ba = ctx.two_view_ba_batch(1, len(matches), 15, 100, 100.0, 0.5, 1.345)
+    mask = v["mask"] == 1
+    ref = OB.bundle_adjust(cal1, cal2, v["R"][0], v["t"][0], u1[mask], u2[mask])
+    assert ba["status"][0] == ref["status"] == 0
+    assert _angle_deg(ba["R"][0], ref["R"]) < TOL_DEG and _dir_deg(ba["t"][0], ref["t"]) < TOL_DEG
+    assert ((ba["valid_mask"][mask] == 1) == ref["valid"]).mean() > 0.97
+    assert _angle_deg(ba["R"][0], R) < 0.1 and _dir_deg(ba["t"][0], t) < 0.5      # and it lands on the scene's pose
+    # a minimum triangulation angle above what the scene offers rejects every track (point3d_initializer.py:287-291)
+    far = ctx.two_view_ba_batch(1, len(matches), 15, 100, 100.0, 0.5, 1.345, min_triangulation_angle_deg=60.0)
+    assert far["status"][0] == 2 and far["num_valid"][0] == 0
+    ctx.close()
