@@ -58,17 +58,20 @@ def parse_args():
     return ap.parse_args()
 
 
-def load_traffic(args, cfg):
-    """dram__bytes_read.sum + dram__bytes_write.sum of one match_screen_kernel launch (one full workspace chunk), from the committed
-    `ncu --set full` capture of this same workload: profiles/r2_screen_ncu.json (C3, 512 pairs per launch) or
-    profiles/r1_screen_ncu.json (C2, 450 pairs); None for any other workload.  Returns (bytes, provenance)."""
-    name = {"C3": "r2_screen_ncu.json", "C2": "r1_screen_ncu.json"}.get(args.config)
-    if args.images or args.kps or name is None or not os.path.exists(os.path.join(ROOT, "profiles", name)):
+def load_traffic(args, cfg, pairs_per_launch):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one match_screen_kernel launch, from the committed `ncu --set full` capture
+    of a full workspace chunk of the C3 workload (profiles/r2_screen_ncu.json: 512 pairs of 8192 x 8192 x 128).  C3 and C2 have the
+    same pair shape, so the capture's bytes per pair are scaled to this run's average pairs per launch (the figure `achieved` is
+    quoted on); None for any other workload.  Returns (bytes, provenance)."""
+    name = "r2_screen_ncu.json"
+    if args.config not in ("C3", "C2") or args.images or args.kps or not os.path.exists(os.path.join(ROOT, "profiles", name)):
         return None, None
     with open(os.path.join(ROOT, "profiles", name)) as f:
         rec = json.load(f)
-    src = f"profiles/{name}: {rec.get('pairs_per_launch', 450)} pairs per launch, captured at commit {rec.get('commit', 'baca470 (round 1)')}"
-    return rec.get("dram_bytes_per_launch"), src
+    cap_pairs = rec.get("pairs_per_launch", 512)
+    src = (f"profiles/{name}: {rec.get('dram_bytes_per_launch', 0) / 1e9:.2f} GB for {cap_pairs} pairs per launch, captured at commit "
+           f"{rec.get('commit', '?')}; scaled to this run's {pairs_per_launch:.0f} pairs per launch")
+    return rec.get("dram_bytes_per_launch") * pairs_per_launch / cap_pairs, src
 
 
 def load_peaks():
@@ -498,7 +501,7 @@ def run_b200(args):
                                "executed_evaluations_per_step": n_evals_exec / args.steps,
                                "executed_tflops": 34.0 * n_evals_exec / (sc_ms * 1e-3) / 1e12 if sc_ms > 0 else 0.0, "candidates_per_hypothesis": n_cand / max(n_hyp_solved, 1),
                                "share_of_step": sc_ms / total_kernel_ms if total_kernel_ms else None}
-        roofline["traffic"], roofline["traffic_source"] = load_traffic(args, cfg)
+        roofline["traffic"], roofline["traffic_source"] = load_traffic(args, cfg, P * args.steps / max(scr_calls, 1))
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": step_ms, "higher_is_better": True, "scaling": "strong" if strong else "weak", "vs_baseline": None, "dtype": "bf16 GEMM / f32 scoring / f64 finalize",
                 "data": "reference fixture (Lund door SIFT features)" if args.config == "C1" else "synthetic",

@@ -20,7 +20,8 @@
 // One CTA per pair.  A Levenberg-Marquardt trial is two passes over the tracks: (1) linearise -- per track the two residuals,
 // their Jacobians, the 3 x 3 point block V, the 5 x 3 coupling W -- and reduce the Schur complement of the points onto the 5
 // pose parameters (block sum), (2) after thread 0 solved the 5 x 5 system, back-substitute every point, and evaluate the
-// robust cost at the trial state.  Points live in global scratch (current and trial copy).
+// robust cost at the trial state.  The triangulated tracks are compacted into a dense per-pair list first (row order), so the
+// passes run with full warps; their points live in two global scratch buffers that swap roles when a step is accepted.
 #include <cfloat>
 #include <cmath>
 
@@ -182,7 +183,7 @@ __global__ void __launch_bounds__(kBaThreads, 3) two_view_ba_kernel(StoreView st
     // triangulation_options.reproj_error_threshold (point3d_initializer.py:262-281)
     // The tracks that pass are appended to the pair's DENSE list in row order (ballot + prefix over the CTA, deterministic), so
     // the LM passes below run with full warps whatever the inlier ratio is.
-    double acc[21];
+    double acc[20];
     int n_tri = 0;                                       // same value in every thread
     int* didx = b.idx + vp.m0;
     double* Xcur = b.X + 3 * vp.m0;
@@ -284,7 +285,7 @@ __global__ void __launch_bounds__(kBaThreads, 3) two_view_ba_kernel(StoreView st
     int iters = 0;                                        // lambdaUpperBound 1e5, relative / absolute error tolerance 1e-5
     for (int trial = 0; trial < 4 * b.max_iters && iters < b.max_iters; ++trial) {
         // pass 1: Schur complement of the points onto the pose: S = U - sum W (V + lambda I)^-1 W^T, rhs = -gc + sum W (V + lambda I)^-1 gp
-        for (int k = 0; k < 21; ++k) acc[k] = 0.0;
+        for (int k = 0; k < 20; ++k) acc[k] = 0.0;
         for (int j = tid; j < n_tri; j += kBaThreads) {
             const uint2 m = match[didx[j]];
             BaLin L;
