@@ -313,8 +313,11 @@ def run_b200(args):
     # all-gather, copy to rank 0's pinned memory -- runs on torch's stream while the library's stream computes sub-batch k + 1
     # (the e2e leg always pipelines: sub-batch 0 starts as soon as ITS images are on the device, the rest of the upload runs
     # on the copy stream behind it)
-    n_sub = max(1, min(args.sub_batches or 4, P))
-    n_sub_e2e = max(1, min(args.sub_batches or (4 if world == 1 else 6), P))
+    # a sub-batch costs about a millisecond of fixed work (two host synchronisations, the exchange), so a rank with few pairs
+    # (C1: 66) runs them as one batch
+    small = P < 1024
+    n_sub = max(1, min(args.sub_batches or (1 if small else 4), P))
+    n_sub_e2e = max(1, min(args.sub_batches or (1 if small else 4 if world == 1 else 6), P))
 
     def sub_bounds(n):
         # equal sub-batches except a last one of half the size: its exchange is the only one nothing overlaps
