@@ -472,12 +472,18 @@ __device__ void lo_pass(const VerifyBufs& b, const VPair& vp, const double* s_R,
     const int lane = threadIdx.x & 31;
     double4* q = s_q[threadIdx.x >> 5];
     int qn = 0;                                             // warp-uniform: inliers waiting in the queue (< 32 between rounds)
+    // the next row's correspondence is requested before the current one is used: the rows of a pair are re-read from L2 on
+    // every pass (211 KB of double4 per C2 pair against four CTAs' worth of L1), and a dependent load per iteration left the
+    // warps waiting on it (long scoreboard was the first stall reason)
+    const double4* corr = static_cast<const double4*>(b.corr_d) + vp.m0;
+    double4 cn = make_double4(0, 0, 0, 0);
+    if (static_cast<int>(threadIdx.x) < vp.M) cn = corr[threadIdx.x];
     for (int i0 = threadIdx.x - lane; i0 < vp.M; i0 += kFinThreads) {
         const int i = i0 + lane;
         bool in = false;
-        double4 c = make_double4(0, 0, 0, 0);
+        const double4 c = cn;
+        if (i + kFinThreads < vp.M) cn = corr[i + kFinThreads];
         if (i < vp.M) {
-            c = static_cast<const double4*>(b.corr_d)[vp.m0 + i];
             in = vm::sampson_sq(E, c.x, c.y, c.z, c.w) < vp.thr2;
             if (!in) acc[0] += vp.thr2;
         }
@@ -614,8 +620,12 @@ __global__ void __launch_bounds__(kFinThreads, 4) finalize_kernel(VerifyBufs b, 
         double acc[kTopK];
 #pragma unroll
         for (int k = 0; k < kTopK; ++k) acc[k] = 0;
+        const double4* corr = static_cast<const double4*>(b.corr_d) + vp.m0;
+        double4 cn = make_double4(0, 0, 0, 0);
+        if (tid < vp.M) cn = corr[tid];
         for (int i = tid; i < vp.M; i += kFinThreads) {
-            const double4 c = static_cast<const double4*>(b.corr_d)[vp.m0 + i];
+            const double4 c = cn;                           // software prefetch, as in lo_pass
+            if (i + kFinThreads < vp.M) cn = corr[i + kFinThreads];
 #pragma unroll
             for (int k = 0; k < kTopK; ++k) {
                 if (k < n_top) {
