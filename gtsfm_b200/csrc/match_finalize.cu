@@ -24,13 +24,12 @@ __device__ __forceinline__ void bitonic_sort(KeyPtr keys, int n_pow2)
 {
     for (int k = 2; k <= n_pow2; k <<= 1) {
         for (int j = k >> 1; j > 0; j >>= 1) {
-            for (int t = threadIdx.x; t < n_pow2; t += blockDim.x) {
-                const int x = t ^ j;
-                if (x > t) {
-                    const unsigned long long a = keys[t], b = keys[x];
-                    const bool up = (t & k) == 0;
-                    if ((a > b) == up) { keys[t] = b; keys[x] = a; }
-                }
+            // one compare-exchange per thread and iteration: pair q couples t (bit j clear) with t | j
+            for (int q = threadIdx.x; q < (n_pow2 >> 1); q += blockDim.x) {
+                const int t = ((q & ~(j - 1)) << 1) | (q & (j - 1)), x = t | j;
+                const unsigned long long a = keys[t], b = keys[x];
+                const bool up = (t & k) == 0;
+                if ((a > b) == up) { keys[t] = b; keys[x] = a; }
             }
             __syncthreads();
         }
