@@ -224,8 +224,9 @@ __device__ __forceinline__ float dist_or_max(int d2) { return d2 == INT_MAX ? FL
 
 // bucket, rows: one CTA per (pair, half block of 128 train columns).  The members of the half block are sorted by group;
 // a warp takes 16 members of one group at a time and multiplies them with the group's 16 staged train rows.
+constexpr int kBucketRowThreads = 512;   // 8 warps: a half block has ~12 tiles of 16 members, i.e. two rounds of a gather-latency-bound chain
 template <int N16>
-__global__ void __launch_bounds__(128, 8) bucket_rows_kernel(StoreView st, MatchWork w)
+__global__ void __launch_bounds__(kBucketRowThreads, 2) bucket_rows_kernel(StoreView st, MatchWork w)
 {
     constexpr int kStride = Staged<N16>::kStride;
     __shared__ uint4 s_t[kHalfT * kStride];
@@ -279,16 +280,18 @@ __global__ void __launch_bounds__(128, 8) bucket_rows_kernel(StoreView st, Match
     const long long trow0 = static_cast<long long>(pd.t_row0) + hb * kHalfT;
     const uint4* tsrc = reinterpret_cast<const uint4*>(st.desc_u8) + trow0 * N16;
 #pragma unroll
-    for (int it = 0; it < kHalfT * N16 / 128; ++it) {                       // all loads of the block in flight at once
-        const int idx = tid + it * 128;
+    for (int it = 0; it < kHalfT * N16 / kBucketRowThreads; ++it) {         // all loads of the block in flight at once
+        const int idx = tid + it * kBucketRowThreads;
         const int r = idx / N16, k = idx % N16;
         s_t[r * kStride + k] = __ldg(tsrc + idx);
     }
-    s_norm[tid] = st.norm_i[trow0 + tid];
-    s_valid[tid] = (hb * kHalfT + tid < pd.nt) ? st.valid[trow0 + tid] : 0;
+    if (tid < kHalfT) {
+        s_norm[tid] = st.norm_i[trow0 + tid];
+        s_valid[tid] = (hb * kHalfT + tid < pd.nt) ? st.valid[trow0 + tid] : 0;
+    }
     __syncthreads();
 
-    for (int tile = warp; tile < tiles; tile += 4) {
+    for (int tile = warp; tile < tiles; tile += kBucketRowThreads / 32) {
         if (tile != warp) fetch(tile);
         Top2 tl{INT_MAX, INT_MAX, INT_MAX}, th{INT_MAX, INT_MAX, INT_MAX};
 #pragma unroll
@@ -348,6 +351,27 @@ __global__ void __launch_bounds__(128) bucket_cols_kernel(StoreView st, MatchWor
     uint4* s_q = s_dyn;
     int* s_norm = reinterpret_cast<int*>(s_dyn + n_cls8 * kStride);
     uint8_t* s_valid = reinterpret_cast<uint8_t*>(s_norm + n_cls8);
+    // registers of one tile of 16 member columns: everything that comes from global memory.  A warp's first tile is fetched
+    // BEFORE the class rows are staged, so the two dependent gathers (member list -> descriptor rows) hide behind the staging
+    // loads and the barrier, as in bucket_rows
+    const int* list = w.col_list + pd.cb_base + start;
+    bool act_lo = false, act_hi = false;
+    int j_lo = 0, j_hi = 0, n_lo = 0, n_hi = 0;
+    long long pos = 0;
+    float k1 = 0.f, k2 = 0.f;
+    uint4 L[N16 / 4], H[N16 / 4];
+    auto fetch = [&](int first) {
+        act_lo = first + gid < n; act_hi = first + gid + 8 < n;
+        j_lo = act_lo ? list[first + gid] : list[first]; j_hi = act_hi ? list[first + gid + 8] : j_lo;
+        const uint4* r_lo = reinterpret_cast<const uint4*>(st.desc_u8) + static_cast<long long>(pd.t_row0 + j_lo) * N16 + q;
+        const uint4* r_hi = reinterpret_cast<const uint4*>(st.desc_u8) + static_cast<long long>(pd.t_row0 + j_hi) * N16 + q;
+#pragma unroll
+        for (int k = 0; k < N16 / 4; ++k) { L[k] = __ldg(r_lo + 4 * k); H[k] = __ldg(r_hi + 4 * k); }
+        n_lo = st.norm_i[pd.t_row0 + j_lo]; n_hi = st.norm_i[pd.t_row0 + j_hi];
+        pos = pd.cb_base + ((q & 1) ? j_hi : j_lo);
+        k1 = w.col_d1[pos]; k2 = w.col_d2[pos];
+    };
+    if (16 * warp < n) fetch(16 * warp);
     const uint4* qsrc = reinterpret_cast<const uint4*>(st.desc_u8) + (static_cast<long long>(pd.q_row0) + c) * N16;
     for (int idx = tid; idx < n_cls8 * N16; idx += 128) {
         const int t = idx / N16, k = idx % N16;
@@ -361,18 +385,8 @@ __global__ void __launch_bounds__(128) bucket_cols_kernel(StoreView st, MatchWor
     }
     __syncthreads();
 
-    const int* list = w.col_list + pd.cb_base + start;
     for (int first = 16 * warp; first < n; first += 64) {
-        const bool act_lo = first + gid < n, act_hi = first + gid + 8 < n;
-        const int j_lo = act_lo ? list[first + gid] : list[first], j_hi = act_hi ? list[first + gid + 8] : j_lo;
-        const uint4* r_lo = reinterpret_cast<const uint4*>(st.desc_u8) + static_cast<long long>(pd.t_row0 + j_lo) * N16 + q;
-        const uint4* r_hi = reinterpret_cast<const uint4*>(st.desc_u8) + static_cast<long long>(pd.t_row0 + j_hi) * N16 + q;
-        uint4 L[N16 / 4], H[N16 / 4];
-#pragma unroll
-        for (int k = 0; k < N16 / 4; ++k) { L[k] = __ldg(r_lo + 4 * k); H[k] = __ldg(r_hi + 4 * k); }
-        const int n_lo = st.norm_i[pd.t_row0 + j_lo], n_hi = st.norm_i[pd.t_row0 + j_hi];
-        const long long pos = pd.cb_base + ((q & 1) ? j_hi : j_lo);
-        const float k1 = w.col_d1[pos], k2 = w.col_d2[pos];
+        if (first != 16 * warp) fetch(first);
         Top2 tl{INT_MAX, INT_MAX, INT_MAX}, th{INT_MAX, INT_MAX, INT_MAX};
 #pragma unroll 2
         for (int nt = 0; nt < n_cls8 / 8; ++nt) {
@@ -437,8 +451,8 @@ cudaError_t launch_resolve_int(const StoreView& st, const MatchWork& w, int whic
         prefix_counts_kernel<<<w.n_pairs, 128, 0, s>>>(w.row_cnt, stride);
         scatter_rows_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, s>>>(w, total);
         const unsigned grid = static_cast<unsigned>(w.n_pairs) * w.max_hb;
-        if (st.kpad == 64) bucket_rows_kernel<4><<<grid, 128, 0, s>>>(st, w);
-        else bucket_rows_kernel<8><<<grid, 128, 0, s>>>(st, w);
+        if (st.kpad == 64) bucket_rows_kernel<4><<<grid, kBucketRowThreads, 0, s>>>(st, w);
+        else bucket_rows_kernel<8><<<grid, kBucketRowThreads, 0, s>>>(st, w);
     } else {
         const int stride = kTileQ + 1;
         if ((e = cudaMemsetAsync(w.col_cnt, 0, sizeof(int) * static_cast<size_t>(w.n_pairs) * stride, s)) != cudaSuccess) return e;
